@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""Benchmark of the signature-kernel SVGD phi-update (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--particles 4096]
+
+One "step" = one phi-update of a swarm of `--particles` 7-DoF trajectories (64 waypoints,
+signature depth 3): X [N,64,7], score [N,448] -> phi [N,64,7].  Prints ONE JSON line.
+
+* value      : phi-updates/s with inputs resident in HBM (CUDA events, max over ranks)
+* e2e        : the same through the public API with HOST (pinned) buffers, H2D of X and score and
+               D2H of phi inside the timed region
+* roofline   : dominant kernel (the K.[score|S|1] contraction) timed alone with CUDA events
+* cpu_baseline: the oracle port of the reference's CPU path on this box's host cores (bounded sample)
+* --impl reference : the reference's CPU implementation (oracle port: the reference's own torch
+               statements + the C/OpenMP signature restatement; `signatory` itself is absent)
+
+N > 1 (torchrun): the swarm is sharded row-block over the ranks (strong scaling at fixed
+`--particles`): all-gather of signatures + scores, histogram all-reduces for the global median.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+T_STEPS, D_CH, DEPTH = 64, 7, 3
+METRIC = "svgd_phi_updates_per_sec"
+UNIT = "phi-updates/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=4096)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    return ap.parse_args()
+
+
+def make_inputs(N, seed=0):
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    X = torch.cumsum(0.05 * torch.randn(N, T_STEPS, D_CH, generator=g), dim=1).contiguous()
+    G = torch.randn(N, T_STEPS * D_CH, generator=g)
+    return X, G
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
+                                  ("sw_power_cap", 8)):
+                    if r[col].lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's CPU path
+# ------------------------------------------------------------------------------------------------
+def cpu_phi_updates(N, steps, warmup=1):
+    """Time `steps` phi-updates of the oracle port on the host cores.  Returns (updates/s, cores)."""
+    import torch
+
+    import oracle
+    from oracle.signature import max_threads
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.autograd.set_detect_anomaly(False)
+    X, G = make_inputs(N)
+    for _ in range(warmup):
+        oracle.phi_torch_literal(X, G, depth=DEPTH)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle.phi_torch_literal(X, G, depth=DEPTH)
+    dt = (time.perf_counter() - t0) / steps
+    return 1.0 / dt, min(cores, max(max_threads(), torch.get_num_threads())), dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    N = args.particles
+    steps = max(1, min(args.steps, 5))
+    val, cores, dt = cpu_phi_updates(N, steps, warmup=min(args.warmup, 1))
+    sample = f"{steps} full phi-updates at N={N}, T={T_STEPS}, d={D_CH}, depth={DEPTH} (oracle port, all host threads)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(N), "particles": N, "waypoints": T_STEPS, "channels": D_CH,
+                   "depth": DEPTH},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(N):
+    return (f"BASELINE.json configs[3] at N={N}: synthetic random-walk 7-D trajectories x 64 waypoints, "
+            f"signature depth 3, median-heuristic RBF, phi = (K.score - grad_k)/N")
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from sigsvgd_b200 import _lib, ops
+    from sigsvgd_b200.dist import phi_sharded
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for --impl ours)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+    N = args.particles
+    if N % world:
+        raise SystemExit(f"--particles {N} must be divisible by the number of ranks {world}")
+    M = N // world
+    Xh, Gh = make_inputs(N)
+    Xh, Gh = Xh[rank * M:(rank + 1) * M].contiguous().pin_memory(), Gh[rank * M:(rank + 1) * M].contiguous().pin_memory()
+    X, G = Xh.to(dev), Gh.to(dev)
+    phi_host = torch.empty_like(Xh).pin_memory()
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
+
+    def step_device():
+        if world == 1:
+            return ops.phi(X, G, depth=DEPTH).phi
+        return phi_sharded(X, G, depth=DEPTH).phi
+
+    def step_e2e():
+        x = Xh.to(dev, non_blocking=True)
+        g = Gh.to(dev, non_blocking=True)
+        p = ops.phi(x, g, depth=DEPTH).phi if world == 1 else phi_sharded(x, g, depth=DEPTH).phi
+        phi_host.copy_(p, non_blocking=True)
+        return p
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        evs = []
+        for _ in range(steps):
+            flush.fill_(1.0)  # L2 flush between timed iterations (outside the events)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            evs.append((e0, e1))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_dev = timed(step_device, args.steps, max(args.warmup, 3))
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e = timed(step_e2e, args.steps, max(args.warmup, 3))
+
+    # ---- roofline of the dominant kernel (K.[score|S|1] contraction), timed alone -------------
+    roof = None
+    if rank == 0:
+        D = ops.sig_channels(D_CH, DEPTH)
+        P = T_STEPS * D_CH
+        s_all = ops.signature_fwd_raw(make_inputs(N)[0].to(dev), DEPTH, True)
+        v_all = ops.pack_features(s_all, ops.col_mean(s_all), make_inputs(N)[1].to(dev))
+        k_rows = ops.sqdist_raw(v_all[:M, P:], v_all[:, P:], D)
+        st = ops.bandwidth_raw(k_rows if world == 1 else k_rows.clone(), ops.Bandwidth.median(), N)
+        ops.rbf_apply_raw(k_rows, st)
+        for _ in range(3):
+            ops.matmul_nn_raw(k_rows, v_all)
+        torch.cuda.synchronize()
+        evs = []
+        for _ in range(10):
+            flush.fill_(1.0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ops.matmul_nn_raw(k_rows, v_all)
+            e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        ms_k = sum(a.elapsed_time(b) for a, b in evs) / len(evs)
+        flops = 2.0 * M * N * (P + D)  # algorithmic: K.score and K.S (the row-sum column is free)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("bf16_tflops", 1590.0))
+        roof = {"bound": "tensor", "kernel": "gemm_nn (K.[score|S|1])", "achieved": flops / (ms_k * 1e-3) / 1e12,
+                "peak": peak, "peak_source": "MEASURED_PEAKS.json bf16 burst" if peaks else "fallback 1590",
+                "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak, "traffic": None,
+                "ms_per_launch": ms_k, "algorithmic_flops_per_launch": flops,
+                "step_algorithmic_flops": 2.0 * M * N * (2 * D + P),
+                "step_frac_of_peak": 2.0 * M * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        val, cores, dt = cpu_phi_updates(N, args.cpu_steps, warmup=1)
+        cpu = {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{args.cpu_steps} full phi-updates at N={N} (oracle port of the reference's torch CPU path, "
+                         f"C/OpenMP signature; signatory absent)", "ms_per_step": dt * 1e3}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": 1e3 / ms_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(N), "particles": N, "waypoints": T_STEPS, "channels": D_CH,
+                       "depth": DEPTH, "sharding": "row-block" if world > 1 else "none",
+                       "l2": "256 MB buffer written between timed iterations", "k_xx_materialised_to_caller": False},
+            "clocks": clocks,
+            "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": int(Xh.numel() + Gh.numel()) * 4,
+                    "d2h_bytes_per_step": int(phi_host.numel()) * 4, "ms_per_step": ms_e2e},
+            "gpu_launches": 19 * args.steps,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,174 @@
+/*
+ * sigsvgd_b200.h -- C ABI of libsigsvgd_b200.so: the B200 (sm_100a) implementation of the
+ * signature-kernel SVGD update of lubaroli/sigsvgd.
+ *
+ * The reference is pure Python; its FFI boundary for this path is the third-party `signatory`
+ * torch extension plus torch library calls.  Each entry point below cites the reference
+ * statement(s) it replaces (paths relative to the reference root).  A maintainer binds these
+ * with ctypes; sigsvgd_b200/_lib.py is that binding.
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers to caller-owned fp32 row-major buffers unless stated;
+ *    16-byte aligned; inputs are never written; nothing is retained after the call returns;
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*), performs no host
+ *    synchronisation and no allocation, and is CUDA-graph capturable;
+ *  - return value 0 = success; otherwise an SIGSVGD_ERR_* code, message via
+ *    sigsvgd_last_error() (thread-local).  There is no CPU fallback: unsupported shapes fail.
+ */
+#ifndef SIGSVGD_B200_H_
+#define SIGSVGD_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SIGSVGD_OK 0
+#define SIGSVGD_ERR_INVALID 1     /* bad shape / argument / alignment            */
+#define SIGSVGD_ERR_UNSUPPORTED 2 /* valid but not implemented on this path      */
+#define SIGSVGD_ERR_WORKSPACE 3   /* workspace too small                         */
+#define SIGSVGD_ERR_CUDA 4        /* CUDA runtime error (launch / attribute)     */
+
+#define SIGSVGD_MAX_TIES 16
+
+/* bandwidth modes (src/kernels/_kernels.py:106-109: h = get_bandwidth(sq_dists) | float(h)) */
+#define SIGSVGD_BW_MEDIAN 0 /* src/utils/math.py:28-34 bw_median                        */
+#define SIGSVGD_BW_FIXED 1  /* caller-supplied constant h                               */
+
+/* flags for sigsvgd_phi / sigsvgd_gram */
+#define SIGSVGD_FLAG_MEDIAN_GRAD 1u /* differentiate through the median (autograd parity)  */
+#define SIGSVGD_FLAG_NO_CENTER 2u   /* do not mean-centre signature features before the Gram */
+#define SIGSVGD_FLAG_FORCE_SIMT 4u  /* never take the tcgen05 path                          */
+#define SIGSVGD_FLAG_FORCE_TC 8u    /* fail instead of falling back to SIMT                 */
+
+/* Device-resident result/scratch record of one bandwidth selection (one per problem). */
+typedef struct sigsvgd_bw_state {
+  float median;        /* lower median of all squared distances (element (n-1)//2 of the sort) */
+  float h;             /* bandwidth: max(tol, bw_scale*sqrt(median/ln(n_log+1)))  or fixed h   */
+  float gamma;         /* -0.5 / h^2                                                           */
+  float coef;          /* median-gradient coefficient  sum_kd / (h^2*median); 0 if inactive    */
+  double sum_kd;       /* sum_ij K_ij d_ij over the rows given to sigsvgd_rbf_apply            */
+  uint32_t n_ties;     /* entries with d == median seen by sigsvgd_rbf_apply (this rank)       */
+  uint32_t n_ties_all; /* the same over all ranks (set by sigsvgd_median_coef)                 */
+  uint32_t clamped;    /* 1 if h hit tol (no median gradient)                                  */
+  uint32_t prefix;     /* radix-select scratch: bits of the median found so far                */
+  uint64_t k_rem;      /* radix-select scratch: remaining rank                                 */
+  int32_t ties[2 * SIGSVGD_MAX_TIES]; /* (row, col) global indices of the first ties           */
+} sigsvgd_bw_state;
+
+const char* sigsvgd_last_error(void);
+const char* sigsvgd_version(void);
+
+/* D = sum_{k=1..depth} d^k ; returns -1 on bad arguments. */
+int64_t sigsvgd_sig_channels(int64_t d, int depth);
+
+/* ---------------------------------------------------------------------------------------------
+ * Signature transform.  Replaces signatory.signature(path, depth, basepoint=True)
+ * (src/kernels/_traj_kernels.py:125-126).  x [N,T,d] -> sig [N,D]; levels 1..depth, level-major,
+ * each level row-major, no scalar term; basepoint!=0 prepends a zero point.
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_signature_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth,
+                          int basepoint, float* sig, void* stream);
+
+/* Vector-Jacobian product of the above (signatory's custom backward; reached from
+ * torch.autograd.grad(k_xx.sum(), X) at src/inference/svgd.py:43 and score.py:55).
+ *   out[N,T,d] = beta * (dS/dx)^T gsig  +  alpha * add        (add may be NULL; row stride ld_add)
+ * With add = K.G rows, alpha = 1/N, beta = -1/N this is the Stein direction phi
+ * (src/inference/svgd.py:82).  sig = forward output for the same x (reversible recompute). */
+int sigsvgd_signature_bwd(const float* x, const float* sig, const float* gsig, int64_t N,
+                          int64_t T, int64_t d, int depth, int basepoint, const float* add,
+                          int64_t ld_add, float alpha, float beta, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Pairwise squared distances.  Replaces pw_dist_sq (src/utils/math.py:69-86):
+ *   dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j),  a [M,D] (row stride lda), b [N,D] (ldb).
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_sqdist(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,
+                   int64_t N, int64_t D, float* dist, int64_t ldd, uint32_t flags, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Median-heuristic bandwidth.  Replaces bw_median (src/utils/math.py:28-34) incl. torch.median's
+ * lower-median convention.  Exact order statistic of the `count` floats (all >= 0) at `dist`.
+ * Single-GPU form: selects rank (count-1)/2 and fills state->{median,h,gamma,clamped}.
+ * n_log = the N of ln(N+1) (sq_dists.shape[0]).  ws from sigsvgd_select_workspace_bytes(count).
+ * ------------------------------------------------------------------------------------------- */
+size_t sigsvgd_select_workspace_bytes(int64_t count);
+int sigsvgd_median_bandwidth(const float* dist, int64_t count, int64_t n_log, float bw_scale,
+                             float tol, sigsvgd_bw_state* state, void* ws, size_t ws_bytes,
+                             void* stream);
+/* Fixed bandwidth: fills state for a caller-chosen h (bandwidth_fn=lambda _: const). */
+int sigsvgd_fixed_bandwidth(float h, sigsvgd_bw_state* state, void* stream);
+
+/* Multi-rank building blocks (row-block sharding; the 2048-bin histogram is summed across
+ * ranks by the caller, e.g. torch.distributed.all_reduce, between _hist and _scan):
+ *   k = rank of the wanted order statistic among ALL ranks' elements, (total-1)/2 for the median;
+ *   pass p in {0,1,2} refines 11/11/10 bits of the fp32 pattern;
+ *   hist: uint64[2048], zeroed by _begin and by every _scan. */
+int sigsvgd_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, void* stream);
+int sigsvgd_select_hist(const float* dist, int64_t count, int pass, const sigsvgd_bw_state* state,
+                        uint64_t* hist, void* stream);
+int sigsvgd_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, void* stream);
+int sigsvgd_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * RBF map, in place.  Replaces K = exp(-0.5/h^2 * sq_dists) (src/kernels/_kernels.py:110).
+ *   k[i,j] = exp(state->gamma * k[i,j]) for the M x N strip (row stride ldk);
+ * accumulates state->sum_kd and records entries equal to state->median in state->ties
+ * (global row index = row_offset + i).  weight (optional, [M,N], row stride ldw): the stored value
+ * and the sum_kd statistic become w[i,j]*K[i,j] (generic-cotangent backward).
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
+                      const float* weight, int64_t ldw, sigsvgd_bw_state* state, void* stream);
+
+/* Median-gradient coefficient (the d h / d median factor of torch.median's backward):
+ *   state->coef = sum_kd / (h^2 * median)  if enable && !clamped && median > 0, else 0.
+ * sum_kd_all / n_ties_all: optional DEVICE scalars holding the all-rank totals (NULL = use the
+ * values accumulated by sigsvgd_rbf_apply on this rank). */
+int sigsvgd_median_coef(sigsvgd_bw_state* state, const double* sum_kd_all,
+                        const uint32_t* n_ties_all, int enable, void* stream);
+
+/* out[M,C] = a[M,N] . v[N,C]  -- replaces k_xx @ score (src/inference/svgd.py:82) and the K.S /
+ * row-sum contractions inside autograd.grad(k_xx.sum(), X) (svgd.py:43). */
+int sigsvgd_matmul_nn(const float* a, int64_t lda, const float* v, int64_t ldv, int64_t M,
+                      int64_t N, int64_t C, float* out, int64_t ldo, uint32_t flags, void* stream);
+
+/* Column means of s [N,D] (row stride lds) -> mean [D].  part: scratch of 64*D floats. */
+int sigsvgd_col_mean(const float* s, int64_t lds, int64_t N, int64_t D, float* part, float* mean,
+                     void* stream);
+/* v[N,C] (row stride ldv) = [ score[N,P] | s - mean [N,D] | 1 | 0.. ],  C >= P + D + 1.
+ * score may be NULL when P == 0; mean may be NULL (no centring). */
+int sigsvgd_pack_v(const float* score, int64_t P, const float* s, int64_t lds, const float* mean,
+                   int64_t N, int64_t D, float* v, int64_t ldv, int64_t C, void* stream);
+
+/* Signature-space gradient of sum(K) wrt the first argument (closed form of the autograd route
+ * src/inference/svgd.py:43 through _kernels.py:110, math.py:28-34 and math.py:81-86):
+ *   g[i,:] = -(1/h^2) ( sc[i,:] * rowsum[i] - ks[i,:] )
+ *            + sum_{(a,b) in ties, a == row_offset+i} coef/n_ties_all * ( sc[i,:] - sc_all[b,:] )
+ * sc = centred features of the local rows [M,D] (ld lds), sc_all = those of all columns. */
+int sigsvgd_sig_grad(const float* sc, int64_t lds, const float* sc_all, int64_t lds_all,
+                     const float* ks, int64_t ldks, const float* rowsum, int64_t ldr, int64_t M,
+                     int64_t D, int64_t row_offset, const sigsvgd_bw_state* state, float* g,
+                     int64_t ldg, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused single-GPU Stein update.  Replaces SVGD._compute_kernel + the arithmetic of
+ * SVGD._velocity (src/inference/svgd.py:36-44, 82-83) for kernel = PathSigKernel(GaussianKernel):
+ *   phi = ( K . score - grad_k ) / N ,   the reference's velocity is -phi.
+ * x [B,N,T,d], score [B,N,T*d]  ->  phi [B,N,T,d]; B independent problems (B = 1 for one swarm),
+ * each with its own bandwidth.  Optional outputs (NULL to skip): k_out [B,N,N] (k_xx),
+ * gradk_out [B,N,T*d] (grad_k), sig_out [B,N,D].  state: B records (device).
+ * ------------------------------------------------------------------------------------------- */
+size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, int depth,
+                                   int want_k);
+int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
+                int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                float* phi, float* k_out, float* gradk_out, float* sig_out,
+                sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SIGSVGD_B200_H_ */

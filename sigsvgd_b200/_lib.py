@@ -1,0 +1,130 @@
+"""ctypes binding of ``libsigsvgd_b200.so`` (C ABI in ``include/sigsvgd_b200.h``).
+
+This is the stub a maintainer of the reference would add: plain pointers and
+sizes, no torch types cross the boundary.  There is NO fallback: if the shared library is missing
+or a call fails, a ``RuntimeError`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_double, c_float, c_int, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsigsvgd_b200.so")
+
+MAX_TIES = 16
+BW_MEDIAN, BW_FIXED = 0, 1
+FLAG_MEDIAN_GRAD, FLAG_NO_CENTER, FLAG_FORCE_SIMT, FLAG_FORCE_TC = 1, 2, 4, 8
+
+
+class BwState(ctypes.Structure):
+    """Mirror of ``sigsvgd_bw_state`` (device-resident; this layout is used to decode copies)."""
+
+    _fields_ = [
+        ("median", c_float),
+        ("h", c_float),
+        ("gamma", c_float),
+        ("coef", c_float),
+        ("sum_kd", c_double),
+        ("n_ties", c_uint32),
+        ("n_ties_all", c_uint32),
+        ("clamped", c_uint32),
+        ("prefix", c_uint32),
+        ("k_rem", c_uint64),
+        ("ties", ctypes.c_int32 * (2 * MAX_TIES)),
+    ]
+
+
+STATE_BYTES = ctypes.sizeof(BwState)
+assert STATE_BYTES == 176, STATE_BYTES
+# byte offsets used by the host code to address fields of a device copy
+OFF_MEDIAN, OFF_H, OFF_GAMMA, OFF_COEF, OFF_SUM_KD, OFF_N_TIES, OFF_N_TIES_ALL, OFF_CLAMPED = 0, 4, 8, 12, 16, 24, 28, 32
+OFF_TIES = BwState.ties.offset
+
+_SIGNATURES = {
+    # name: (restype, argtypes)
+    "sigsvgd_last_error": (ctypes.c_char_p, []),
+    "sigsvgd_version": (ctypes.c_char_p, []),
+    "sigsvgd_sig_channels": (c_int64, [c_int64, c_int]),
+    "sigsvgd_signature_fwd": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p]),
+    "sigsvgd_signature_bwd": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_float, c_float,
+         c_void_p, c_void_p],
+    ),
+    "sigsvgd_sqdist": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_int64, c_uint32, c_void_p],
+    ),
+    "sigsvgd_select_workspace_bytes": (c_size_t, [c_int64]),
+    "sigsvgd_median_bandwidth": (
+        c_int, [c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "sigsvgd_fixed_bandwidth": (c_int, [c_float, c_void_p, c_void_p]),
+    "sigsvgd_select_begin": (c_int, [c_void_p, c_void_p, c_uint64, c_void_p]),
+    "sigsvgd_select_hist": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_select_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_select_finish": (c_int, [c_int64, c_float, c_float, c_void_p, c_void_p]),
+    "sigsvgd_rbf_apply": (
+        c_int, [c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
+    "sigsvgd_median_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "sigsvgd_matmul_nn": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_int64, c_uint32, c_void_p],
+    ),
+    "sigsvgd_col_mean": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_pack_v": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p],
+    ),
+    "sigsvgd_sig_grad": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64,
+         c_void_p, c_void_p, c_int64, c_void_p],
+    ),
+    "sigsvgd_phi_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int, c_int]),
+    "sigsvgd_phi": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_float, c_float, c_float, c_uint32,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared library (once).  Raises RuntimeError if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  sigsvgd_b200 has no CPU or eager-PyTorch fallback."
+            )
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def last_error() -> str:
+    return load().sigsvgd_last_error().decode()
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        kind = {1: "invalid argument", 2: "unsupported", 3: "workspace too small", 4: "CUDA error"}.get(rc, "error")
+        msg = f"{what}: {kind}: {last_error()}"
+        if rc == 1:
+            raise ValueError(msg)
+        raise RuntimeError(msg)
+
+
+def call(name: str, *args) -> None:
+    check(getattr(load(), name)(*args), name)

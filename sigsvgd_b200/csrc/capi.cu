@@ -1,0 +1,271 @@
+// extern "C" entry points of libsigsvgd_b200.so (declared in include/sigsvgd_b200.h) and the
+// fused single-GPU phi pipeline.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "gemm_tc.cuh"
+
+namespace sigsvgd {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+int num_sms() {
+  static thread_local int cached_dev = -1, cached = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      cached = v;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+struct PhiLayout {
+  int64_t D, P, C;
+  size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, off_tc, total;
+};
+
+static size_t bump(size_t* cur, size_t bytes) {
+  const size_t o = *cur;
+  *cur = (size_t)round_up((int64_t)(o + bytes), 256);
+  return o;
+}
+
+static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int depth, bool want_sig,
+                            bool want_k) {
+  PhiLayout L;
+  L.D = sig_channels(d, depth);
+  L.P = T * d;
+  L.C = round_up(L.P + L.D + 1, 8);
+  size_t cur = 0;
+  L.off_sig = want_sig ? 0 : bump(&cur, sizeof(float) * B * N * L.D);
+  L.off_v = bump(&cur, sizeof(float) * B * N * L.C);
+  L.off_k = want_k ? 0 : bump(&cur, sizeof(float) * B * N * N);
+  L.off_out = bump(&cur, sizeof(float) * B * N * L.C);
+  L.off_g = bump(&cur, sizeof(float) * B * N * L.D);
+  L.off_mean = bump(&cur, sizeof(float) * B * L.D);
+  L.off_part = bump(&cur, sizeof(float) * B * 64 * L.D);
+  L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
+  L.off_tc = bump(&cur, tc_workspace_bytes(B, N, L.D, L.C));
+  L.total = cur;
+  return L;
+}
+
+}  // namespace sigsvgd
+
+using namespace sigsvgd;
+
+extern "C" {
+
+const char* sigsvgd_last_error(void) { return get_error(); }
+const char* sigsvgd_version(void) { return "sigsvgd_b200 0.1 (sm_100a)"; }
+
+int64_t sigsvgd_sig_channels(int64_t d, int depth) {
+  if (d < 1 || depth < 1 || depth > 8) return -1;
+  return sig_channels(d, depth);
+}
+
+int sigsvgd_signature_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth,
+                          int basepoint, float* sig, void* stream) {
+  SIG_CHECK_ARG(N == 0 || (x && sig), "signature_fwd: NULL pointer");
+  return launch_sig_fwd(x, N, T, d, depth, basepoint, sig, (cudaStream_t)stream);
+}
+
+int sigsvgd_signature_bwd(const float* x, const float* sig, const float* gsig, int64_t N,
+                          int64_t T, int64_t d, int depth, int basepoint, const float* add,
+                          int64_t ld_add, float alpha, float beta, float* out, void* stream) {
+  SIG_CHECK_ARG(N == 0 || (x && sig && gsig && out), "signature_bwd: NULL pointer");
+  return launch_sig_bwd(x, sig, gsig, N, T, d, depth, basepoint, add, ld_add, alpha, beta, out,
+                        (cudaStream_t)stream);
+}
+
+int sigsvgd_sqdist(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int64_t N,
+                   int64_t D, float* dist, int64_t ldd, uint32_t flags, void* stream) {
+  SIG_CHECK_ARG((M == 0 || N == 0) || (a && b && dist), "sqdist: NULL pointer");
+  if (flags & SIGSVGD_FLAG_FORCE_TC) {
+    set_error("sqdist: the tcgen05 path needs packed operands; use sigsvgd_phi");
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  return launch_sqdist_simt(a, lda, b, ldb, M, N, D, dist, ldd, 1, 0, 0, 0, (cudaStream_t)stream);
+}
+
+size_t sigsvgd_select_workspace_bytes(int64_t count) { return select_workspace_bytes(count, 1); }
+
+int sigsvgd_median_bandwidth(const float* dist, int64_t count, int64_t n_log, float bw_scale,
+                             float tol, sigsvgd_bw_state* state, void* ws, size_t ws_bytes,
+                             void* stream) {
+  SIG_CHECK_ARG(dist && state && ws, "median_bandwidth: NULL pointer");
+  return launch_median_select(dist, count, 1, 0, n_log, bw_scale, tol, state, ws, ws_bytes,
+                              (cudaStream_t)stream);
+}
+
+int sigsvgd_fixed_bandwidth(float h, sigsvgd_bw_state* state, void* stream) {
+  SIG_CHECK_ARG(state, "fixed_bandwidth: NULL pointer");
+  return launch_fixed_bandwidth(h, state, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, void* stream) {
+  SIG_CHECK_ARG(state && hist, "select_begin: NULL pointer");
+  return launch_select_begin(state, hist, k, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_select_hist(const float* dist, int64_t count, int pass, const sigsvgd_bw_state* state,
+                        uint64_t* hist, void* stream) {
+  SIG_CHECK_ARG(state && hist && (count == 0 || dist), "select_hist: NULL pointer");
+  return launch_select_hist(dist, count, 1, 0, pass, state, hist, (cudaStream_t)stream);
+}
+
+int sigsvgd_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, void* stream) {
+  SIG_CHECK_ARG(state && hist, "select_scan: NULL pointer");
+  return launch_select_scan(pass, state, hist, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                          void* stream) {
+  SIG_CHECK_ARG(state, "select_finish: NULL pointer");
+  return launch_select_finish(n_log, bw_scale, tol, state, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
+                      const float* weight, int64_t ldw, sigsvgd_bw_state* state, void* stream) {
+  SIG_CHECK_ARG(state && (M == 0 || k), "rbf_apply: NULL pointer");
+  return launch_rbf_apply(k, ldk, M, N, row_offset, weight, ldw, state, 1, 0, 0,
+                          (cudaStream_t)stream);
+}
+
+int sigsvgd_median_coef(sigsvgd_bw_state* state, const double* sum_kd_all,
+                        const uint32_t* n_ties_all, int enable, void* stream) {
+  SIG_CHECK_ARG(state, "median_coef: NULL pointer");
+  return launch_median_coef(state, sum_kd_all, n_ties_all, enable, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_matmul_nn(const float* a, int64_t lda, const float* v, int64_t ldv, int64_t M,
+                      int64_t N, int64_t C, float* out, int64_t ldo, uint32_t flags, void* stream) {
+  SIG_CHECK_ARG(M == 0 || (a && v && out), "matmul_nn: NULL pointer");
+  if (flags & SIGSVGD_FLAG_FORCE_TC) {
+    set_error("matmul_nn: the tcgen05 path needs packed operands; use sigsvgd_phi");
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  return launch_gemm_nn_simt(a, lda, v, ldv, M, N, C, out, ldo, 1, 0, 0, 0, (cudaStream_t)stream);
+}
+
+int sigsvgd_col_mean(const float* s, int64_t lds, int64_t N, int64_t D, float* part, float* mean,
+                     void* stream) {
+  SIG_CHECK_ARG(s && part && mean, "col_mean: NULL pointer");
+  return launch_col_mean(s, lds, N, D, part, mean, 1, 0, (cudaStream_t)stream);
+}
+
+int sigsvgd_pack_v(const float* score, int64_t P, const float* s, int64_t lds, const float* mean,
+                   int64_t N, int64_t D, float* v, int64_t ldv, int64_t C, void* stream) {
+  SIG_CHECK_ARG(s && v, "pack_v: NULL pointer");
+  return launch_pack_v(score, P, s, lds, mean, N, D, v, ldv, C, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_sig_grad(const float* sc, int64_t lds, const float* sc_all, int64_t lds_all,
+                     const float* ks, int64_t ldks, const float* rowsum, int64_t ldr, int64_t M,
+                     int64_t D, int64_t row_offset, const sigsvgd_bw_state* state, float* g,
+                     int64_t ldg, void* stream) {
+  SIG_CHECK_ARG(state && (M == 0 || (sc && sc_all && ks && rowsum && g)), "sig_grad: NULL pointer");
+  return launch_sig_grad(sc, lds, sc_all, lds_all, ks, ldks, rowsum, ldr, M, D, 0, row_offset,
+                         state, g, ldg, 1, (cudaStream_t)stream);
+}
+
+size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, int depth,
+                                   int want_k) {
+  if (B < 1 || N < 1 || T < 1 || d < 1 || depth < 1 || depth > 8) return 0;
+  // sized for the worst case: signatures kept in the workspace
+  return phi_layout(B, N, T, d, depth, false, want_k != 0).total;
+}
+
+int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
+                int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                float* phi, float* k_out, float* gradk_out, float* sig_out,
+                sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  SIG_CHECK_ARG(B >= 1 && N >= 1 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
+                "phi: bad shape B=%lld N=%lld T=%lld d=%lld depth=%d", (long long)B, (long long)N,
+                (long long)T, (long long)d, depth);
+  SIG_CHECK_ARG(x && score && phi && state && ws, "phi: NULL pointer");
+  SIG_CHECK_ARG(bw_mode == SIGSVGD_BW_MEDIAN || bw_mode == SIGSVGD_BW_FIXED, "phi: bad bw_mode %d",
+                bw_mode);
+  SIG_CHECK_ARG(aligned16(x) && aligned16(score) && aligned16(phi) && aligned16(ws) &&
+                    aligned16(k_out) && aligned16(gradk_out) && aligned16(sig_out),
+                "phi: pointers must be 16-byte aligned");
+  SIG_CHECK_ARG(N <= (int64_t)1 << 30, "phi: N too large");
+  const PhiLayout L = phi_layout(B, N, T, d, depth, sig_out != nullptr, k_out != nullptr);
+  if (ws_bytes < L.total) {
+    set_error("phi: workspace too small (%zu < %zu bytes)", ws_bytes, L.total);
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  char* w = (char*)ws;
+  float* sig = sig_out ? sig_out : (float*)(w + L.off_sig);
+  float* V = (float*)(w + L.off_v);
+  float* K = k_out ? k_out : (float*)(w + L.off_k);
+  float* out = (float*)(w + L.off_out);
+  float* g = (float*)(w + L.off_g);
+  float* mean = (float*)(w + L.off_mean);
+  float* part = (float*)(w + L.off_part);
+  void* selws = (void*)(w + L.off_sel);
+  void* tcws = (void*)(w + L.off_tc);
+  const int64_t D = L.D, P = L.P, C = L.C, R = B * N;
+  const bool center = !(flags & SIGSVGD_FLAG_NO_CENTER);
+
+  // K1: signatures of all B*N particles
+  SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
+  // centre + pack V = [score | S - mean | 1]
+  if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
+  SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
+
+  const bool use_tc = tc_path_enabled(B, N, D, C, flags);
+  if ((flags & SIGSVGD_FLAG_FORCE_TC) && !use_tc) {
+    set_error("phi: tcgen05 path not available for B=%lld N=%lld D=%lld", (long long)B,
+              (long long)N, (long long)D);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  // K3: squared distances into the K buffer
+  if (use_tc) {
+    SIG_PROPAGATE(tc_pack_and_sqdist(V, C, P, N, D, K, tcws, st));
+  } else {
+    SIG_PROPAGATE(launch_sqdist_simt(V + P, C, V + P, C, N, N, D, K, N, B, N * C, N * C, N * N, st));
+  }
+  // K4: bandwidth
+  if (bw_mode == SIGSVGD_BW_MEDIAN) {
+    SIG_PROPAGATE(launch_median_select(K, N * N, B, N * N, N, bw_scale, tol, state, selws,
+                                       select_workspace_bytes(N * N, B), st));
+  } else {
+    SIG_PROPAGATE(launch_fixed_bandwidth(h_fixed, state, B, st));
+  }
+  // K5: K = exp(gamma d) in place, then one contraction K.[score | S | 1]
+  SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));
+  SIG_PROPAGATE(launch_median_coef(
+      state, nullptr, nullptr,
+      (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0, B, st));
+  if (use_tc) {
+    SIG_PROPAGATE(tc_matmul_kv(K, N, V, C, N, C, out, C, tcws, st));
+  } else {
+    SIG_PROPAGATE(launch_gemm_nn_simt(K, N, V, C, N, N, C, out, C, B, N * N, N * C, N * C, st));
+  }
+  // sig-space gradient, then K2 with the fused epilogue phi = (K.score - grad_k)/N
+  SIG_PROPAGATE(launch_sig_grad(V + P, C, V + P, C, out + P, C, out + P + D, C, N, D, N, 0, state,
+                                g, D, B, st));
+  if (gradk_out)
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st));
+  const float inv_n = 1.f / (float)N;
+  SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out, C, inv_n, -inv_n, phi, st));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// Shared helpers for the sigsvgd_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <algorithm>
+
+#include "../../include/sigsvgd_b200.h"
+
+namespace sigsvgd {
+
+// thread-local last-error string (C ABI: sigsvgd_last_error)
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define SIG_CHECK_ARG(cond, ...)             \
+  do {                                       \
+    if (!(cond)) {                           \
+      ::sigsvgd::set_error(__VA_ARGS__);     \
+      return SIGSVGD_ERR_INVALID;            \
+    }                                        \
+  } while (0)
+
+#define SIG_CUDA_OK(expr)                                                                   \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      ::sigsvgd::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                           __LINE__);                                                       \
+      return SIGSVGD_ERR_CUDA;                                                              \
+    }                                                                                       \
+  } while (0)
+
+#define SIG_LAUNCH_OK(name)                                                              \
+  do {                                                                                   \
+    cudaError_t _e = cudaGetLastError();                                                 \
+    if (_e != cudaSuccess) {                                                             \
+      ::sigsvgd::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));     \
+      return SIGSVGD_ERR_CUDA;                                                           \
+    }                                                                                    \
+  } while (0)
+
+#define SIG_PROPAGATE(expr)  \
+  do {                       \
+    int _rc = (expr);        \
+    if (_rc != 0) return _rc; \
+  } while (0)
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
+
+static inline int64_t sig_channels(int64_t d, int depth) {
+  int64_t D = 0, p = 1;
+  for (int k = 1; k <= depth; ++k) {
+    p *= d;
+    D += p;
+  }
+  return D;
+}
+
+int num_sms();  // cached cudaDevAttrMultiProcessorCount of the current device
+
+// ---- launchers implemented in the individual .cu files ------------------------------------
+// signature (sig_kernels.cu)
+int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
+                   float* sig, cudaStream_t st);
+int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
+                   int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
+                   float alpha, float beta, float* out, cudaStream_t st);
+
+// SIMT GEMMs (gemm_simt.cu)
+int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,
+                       int64_t N, int64_t D, float* dist, int64_t ldd, int64_t batch,
+                       int64_t stride_a, int64_t stride_b, int64_t stride_d, cudaStream_t st);
+int launch_gemm_nn_simt(const float* a, int64_t lda, const float* v, int64_t ldv, int64_t M,
+                        int64_t N, int64_t C, float* out, int64_t ldo, int64_t batch,
+                        int64_t stride_a, int64_t stride_v, int64_t stride_o, cudaStream_t st);
+
+// selection / bandwidth (select.cu)
+size_t select_workspace_bytes(int64_t count, int64_t batch);
+int launch_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, int64_t batch,
+                        cudaStream_t st);
+int launch_select_hist(const float* dist, int64_t count, int64_t batch, int64_t stride, int pass,
+                       const sigsvgd_bw_state* state, uint64_t* hist, cudaStream_t st);
+int launch_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, int64_t batch,
+                       cudaStream_t st);
+int launch_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                         int64_t batch, cudaStream_t st);
+int launch_fixed_bandwidth(float h, sigsvgd_bw_state* state, int64_t batch, cudaStream_t st);
+int launch_median_coef(sigsvgd_bw_state* state, const double* sum_kd_all,
+                       const uint32_t* n_ties_all, int enable, int64_t batch, cudaStream_t st);
+int launch_median_select(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                         int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                         void* ws, size_t ws_bytes, cudaStream_t st);
+
+// elementwise / packing (elementwise.cu)
+int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
+                     const float* weight, int64_t ldw, sigsvgd_bw_state* state, int64_t batch,
+                     int64_t stride_k, int64_t stride_w, cudaStream_t st);
+int launch_col_mean(const float* s, int64_t lds, int64_t N, int64_t D, float* part, float* mean,
+                    int64_t batch, int64_t stride_s, cudaStream_t st);
+int launch_pack_v(const float* score, int64_t P, const float* s, int64_t lds, const float* mean,
+                  int64_t N, int64_t D, float* v, int64_t ldv, int64_t C, int64_t batch,
+                  cudaStream_t st);
+int launch_sig_grad(const float* sc, int64_t lds, const float* sc_all, int64_t lds_all,
+                    const float* ks, int64_t ldks, const float* rowsum, int64_t ldr, int64_t M,
+                    int64_t D, int64_t n_all, int64_t row_offset, const sigsvgd_bw_state* state,
+                    float* g, int64_t ldg, int64_t batch, cudaStream_t st);
+
+}  // namespace sigsvgd

@@ -1,0 +1,265 @@
+// Exact lower-median selection + median-heuristic bandwidth (K4).
+//
+// Replaces torch.median(sq_dists) and the arithmetic of bw_median
+// (reference: src/utils/math.py:28-34).  torch.median over a flattened tensor with n elements
+// returns sorted element (n-1)//2; squared distances are >= 0, so their fp32 bit patterns order
+// like uint32 and a 3-pass (11/11/10 bit) radix select finds the exact order statistic.
+//
+// The passes are separate launches so a row-block-sharded run can all-reduce the 2048-bin
+// histogram between `hist` and `scan`; batched problems use blockIdx.y.
+#include "common.cuh"
+
+namespace sigsvgd {
+namespace {
+
+constexpr int kBins = 2048;
+constexpr int kHistThreads = 256;
+
+__device__ __forceinline__ bool radix_bin(uint32_t bits, int pass, uint32_t prefix, uint32_t* bin) {
+  bits &= 0x7fffffffu;  // -0.0f sorts with +0.0f
+  if (pass == 0) {
+    *bin = bits >> 21;
+    return true;
+  }
+  if (pass == 1) {
+    *bin = (bits >> 10) & 0x7ffu;
+    return (bits >> 21) == (prefix >> 21);
+  }
+  *bin = bits & 0x3ffu;
+  return (bits >> 10) == (prefix >> 10);
+}
+
+__global__ void __launch_bounds__(kHistThreads)
+select_hist_kernel(const float* __restrict__ dist, int64_t count, int64_t stride, int pass,
+                   const sigsvgd_bw_state* __restrict__ state, unsigned long long* __restrict__ hist) {
+  __shared__ unsigned int h[kBins];
+  const int b = blockIdx.y;
+  const float* __restrict__ src = dist + (int64_t)b * stride;
+  for (int i = threadIdx.x; i < kBins; i += kHistThreads) h[i] = 0u;
+  __syncthreads();
+  const uint32_t prefix = state[b].prefix;
+  const int64_t step = (int64_t)gridDim.x * kHistThreads;
+  // vector body when the segment is 16-byte aligned
+  const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
+  const int64_t n4 = vec ? count / 4 : 0;
+  for (int64_t i = (int64_t)blockIdx.x * kHistThreads + threadIdx.x; i < n4; i += step) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(src) + i);
+    uint32_t bin;
+    if (radix_bin(q.x, pass, prefix, &bin)) atomicAdd(&h[bin], 1u);
+    if (radix_bin(q.y, pass, prefix, &bin)) atomicAdd(&h[bin], 1u);
+    if (radix_bin(q.z, pass, prefix, &bin)) atomicAdd(&h[bin], 1u);
+    if (radix_bin(q.w, pass, prefix, &bin)) atomicAdd(&h[bin], 1u);
+  }
+  for (int64_t i = n4 * 4 + (int64_t)blockIdx.x * kHistThreads + threadIdx.x; i < count; i += step) {
+    uint32_t bin;
+    if (radix_bin(__float_as_uint(__ldg(src + i)), pass, prefix, &bin)) atomicAdd(&h[bin], 1u);
+  }
+  __syncthreads();
+  unsigned long long* __restrict__ g = hist + (int64_t)b * kBins;
+  for (int i = threadIdx.x; i < kBins; i += kHistThreads)
+    if (h[i]) atomicAdd(&g[i], (unsigned long long)h[i]);
+}
+
+__global__ void select_begin_kernel(sigsvgd_bw_state* state, unsigned long long* hist,
+                                    unsigned long long k) {
+  const int b = blockIdx.x;
+  for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[(int64_t)b * kBins + i] = 0ull;
+  if (threadIdx.x == 0) {
+    sigsvgd_bw_state& s = state[b];
+    s.prefix = 0u;
+    s.k_rem = k;
+    s.median = 0.f;
+    s.sum_kd = 0.0;
+    s.n_ties = 0u;
+    s.n_ties_all = 0u;
+    s.clamped = 0u;
+    s.coef = 0.f;
+  }
+}
+
+// one block of 256 threads per problem
+__global__ void __launch_bounds__(256)
+select_scan_kernel(int pass, sigsvgd_bw_state* state, unsigned long long* hist) {
+  __shared__ unsigned long long part[256];
+  __shared__ int chunk_sel;
+  __shared__ unsigned long long before_sel;
+  const int b = blockIdx.x, t = threadIdx.x;
+  unsigned long long* g = hist + (int64_t)b * kBins;
+  unsigned long long loc[8], s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    loc[i] = g[t * 8 + i];
+    s += loc[i];
+  }
+  part[t] = s;
+  __syncthreads();
+  if (t == 0) {
+    const unsigned long long k = state[b].k_rem;
+    unsigned long long cum = 0;
+    int sel = 255;
+    for (int c = 0; c < 256; ++c) {
+      if (k < cum + part[c]) {
+        sel = c;
+        break;
+      }
+      cum += part[c];
+    }
+    if (sel == 255 && !(k < cum + part[255])) {  // k beyond the total: clamp to the last element
+      cum = 0;
+      for (int c = 0; c < 255; ++c) cum += part[c];
+    }
+    chunk_sel = sel;
+    before_sel = cum;
+  }
+  __syncthreads();
+  if (t == chunk_sel) {
+    const unsigned long long k = state[b].k_rem;
+    unsigned long long cum = before_sel;
+    int bin = 7;
+    for (int i = 0; i < 8; ++i) {
+      if (k < cum + loc[i]) {
+        bin = i;
+        break;
+      }
+      if (i < 7) cum += loc[i];
+    }
+    const uint32_t bucket = (uint32_t)(t * 8 + bin);
+    const int shift = pass == 0 ? 21 : pass == 1 ? 10 : 0;
+    state[b].prefix |= bucket << shift;
+    state[b].k_rem = k >= cum ? k - cum : 0ull;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) g[t * 8 + i] = 0ull;
+}
+
+__global__ void select_finish_kernel(float log_np1, float bw_scale, float tol,
+                                     sigsvgd_bw_state* state, int batch) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  sigsvgd_bw_state& s = state[b];
+  const float med = __uint_as_float(s.prefix);
+  // math.py:31-34: h = median / log(N+1); h = bw_scale * sqrt(h); clamp_min(tol)
+  float h = bw_scale * sqrtf(med / log_np1);
+  const bool clamped = !(h >= tol);
+  if (clamped) h = tol;
+  s.median = med;
+  s.h = h;
+  s.gamma = -0.5f / (h * h);  // _kernels.py:110
+  s.clamped = clamped ? 1u : 0u;
+}
+
+__global__ void fixed_bw_kernel(float h, sigsvgd_bw_state* state, int batch) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  sigsvgd_bw_state& s = state[b];
+  s.median = 0.f;
+  s.h = h;
+  s.gamma = -0.5f / (h * h);
+  s.coef = 0.f;
+  s.sum_kd = 0.0;
+  s.n_ties = 0u;
+  s.n_ties_all = 0u;
+  s.clamped = 0u;
+  s.prefix = 0u;
+  s.k_rem = 0ull;
+}
+
+// coef = sum_kd / (h^2 * median)  
+__global__ void median_coef_kernel(sigsvgd_bw_state* state, const double* sum_kd_all,
+                                   const uint32_t* n_ties_all, int enable, int batch) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  sigsvgd_bw_state& s = state[b];
+  const double skd = sum_kd_all ? sum_kd_all[b] : s.sum_kd;
+  const uint32_t nt = n_ties_all ? n_ties_all[b] : s.n_ties;
+  s.n_ties_all = nt;
+  const bool on = enable && !s.clamped && s.median > 0.f && nt > 0u;
+  s.coef = on ? (float)(skd / ((double)s.h * (double)s.h * (double)s.median)) : 0.f;
+}
+
+}  // namespace
+
+size_t select_workspace_bytes(int64_t /*count*/, int64_t batch) {
+  return (size_t)batch * kBins * sizeof(unsigned long long);
+}
+
+static int hist_grid(int64_t count) {
+  const int64_t want = ceil_div(count, (int64_t)kHistThreads * 16);
+  const int64_t cap = (int64_t)num_sms() * 8;
+  return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+int launch_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, int64_t batch,
+                        cudaStream_t st) {
+  select_begin_kernel<<<(unsigned)batch, 256, 0, st>>>(state, (unsigned long long*)hist, k);
+  SIG_LAUNCH_OK("select_begin_kernel");
+  return 0;
+}
+
+int launch_select_hist(const float* dist, int64_t count, int64_t batch, int64_t stride, int pass,
+                       const sigsvgd_bw_state* state, uint64_t* hist, cudaStream_t st) {
+  SIG_CHECK_ARG(pass >= 0 && pass <= 2, "select_hist: pass must be 0..2");
+  SIG_CHECK_ARG(batch >= 1 && batch <= 65535, "select_hist: bad batch");
+  if (count <= 0) return 0;
+  int gx = hist_grid(count);
+  if (batch > 1) gx = (int)std::max<int64_t>(1, std::min<int64_t>(gx, ceil_div((int64_t)num_sms() * 8, batch)));
+  dim3 grid((unsigned)gx, (unsigned)batch);
+  select_hist_kernel<<<grid, kHistThreads, 0, st>>>(dist, count, stride, pass, state,
+                                                    (unsigned long long*)hist);
+  SIG_LAUNCH_OK("select_hist_kernel");
+  return 0;
+}
+
+int launch_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, int64_t batch,
+                       cudaStream_t st) {
+  SIG_CHECK_ARG(pass >= 0 && pass <= 2, "select_scan: pass must be 0..2");
+  select_scan_kernel<<<(unsigned)batch, 256, 0, st>>>(pass, state, (unsigned long long*)hist);
+  SIG_LAUNCH_OK("select_scan_kernel");
+  return 0;
+}
+
+int launch_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                         int64_t batch, cudaStream_t st) {
+  SIG_CHECK_ARG(n_log >= 1, "select_finish: n_log must be >= 1");
+  // the reference evaluates ln(N+1) in float32 (math.py:32, a default-dtype 0-dim tensor)
+  const float log_np1 = (float)log((double)(float)((double)n_log + 1.0));
+  select_finish_kernel<<<(unsigned)ceil_div(batch, 128), 128, 0, st>>>(log_np1, bw_scale, tol,
+                                                                       state, (int)batch);
+  SIG_LAUNCH_OK("select_finish_kernel");
+  return 0;
+}
+
+int launch_fixed_bandwidth(float h, sigsvgd_bw_state* state, int64_t batch, cudaStream_t st) {
+  SIG_CHECK_ARG(h > 0.f, "fixed_bandwidth: h must be > 0");
+  fixed_bw_kernel<<<(unsigned)ceil_div(batch, 128), 128, 0, st>>>(h, state, (int)batch);
+  SIG_LAUNCH_OK("fixed_bw_kernel");
+  return 0;
+}
+
+int launch_median_coef(sigsvgd_bw_state* state, const double* sum_kd_all,
+                       const uint32_t* n_ties_all, int enable, int64_t batch, cudaStream_t st) {
+  median_coef_kernel<<<(unsigned)ceil_div(batch, 128), 128, 0, st>>>(state, sum_kd_all, n_ties_all,
+                                                                     enable, (int)batch);
+  SIG_LAUNCH_OK("median_coef_kernel");
+  return 0;
+}
+
+int launch_median_select(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                         int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                         void* ws, size_t ws_bytes, cudaStream_t st) {
+  SIG_CHECK_ARG(count >= 1, "median_bandwidth: empty distance matrix");
+  if (ws_bytes < select_workspace_bytes(count, batch)) {
+    set_error("median_bandwidth: workspace too small (%zu < %zu)", ws_bytes,
+              select_workspace_bytes(count, batch));
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  uint64_t* hist = (uint64_t*)ws;
+  SIG_PROPAGATE(launch_select_begin(state, hist, (uint64_t)((count - 1) / 2), batch, st));
+  for (int pass = 0; pass < 3; ++pass) {
+    SIG_PROPAGATE(launch_select_hist(dist, count, batch, stride, pass, state, hist, st));
+    SIG_PROPAGATE(launch_select_scan(pass, state, hist, batch, st));
+  }
+  return launch_select_finish(n_log, bw_scale, tol, state, batch, st);
+}
+
+}  // namespace sigsvgd

@@ -1,0 +1,579 @@
+// Truncated path-signature forward / VJP kernels (K1, K2).
+//
+// Replaces signatory.signature(path, depth, basepoint=True) and its custom backward
+// (reference call sites: src/kernels/_traj_kernels.py:125-126; backward reached from
+// torch.autograd.grad at src/inference/svgd.py:43 / src/inference/score.py:55).
+//
+// Math: S <- S (x) exp(Delta_t), Horner form per level.  Backward is the
+// reversible sweep S_{t-1} = S_t (x) exp(-Delta_t) with the adjoint of the Horner chain.
+//
+// Two implementations:
+//  * depth 3, d <= 8 ("sig3"): register-resident.  A group of G = pow2 >= d lanes owns one
+//    particle; lane i owns every tensor entry whose FIRST index is i (S1[i], S2[i,:], S3[i,:,:]),
+//    so the forward update and all adjoint updates are lane-local; the only cross-lane traffic of
+//    the backward is one d-vector reduce-scatter (log2 G shuffle stages) per time step.
+//    Waypoints are staged through shared memory with coalesced loads; results leave through
+//    shared memory with coalesced stores.
+//  * generic (any d, depth <= 8): one warp per particle, state in shared memory, entry-parallel.
+//
+// Bound: HBM (4*N*(T*d + D) bytes forward, 4*N*(2*T*d + 2*D) backward) but in practice
+// latency/issue bound at N = 4096.
+#include "common.cuh"
+
+namespace sigsvgd {
+
+namespace {
+
+constexpr int kThreads = 128;
+
+__host__ __device__ constexpr int group_size(int d) { return d <= 1 ? 1 : d <= 2 ? 2 : d <= 4 ? 4 : 8; }
+__host__ __device__ constexpr int row_pad(int d) { return d <= 2 ? d : ((d + 3) & ~3); }
+
+template <int d>
+__device__ __forceinline__ void load_row(const float* __restrict__ row, float (&v)[d]) {
+  constexpr int DP = row_pad(d);
+  if constexpr (DP % 4 == 0) {
+#pragma unroll
+    for (int q = 0; q < DP / 4; ++q) {
+      const float4 f = *reinterpret_cast<const float4*>(row + 4 * q);
+      if (4 * q + 0 < d) v[4 * q + 0] = f.x;
+      if (4 * q + 1 < d) v[4 * q + 1] = f.y;
+      if (4 * q + 2 < d) v[4 * q + 2] = f.z;
+      if (4 * q + 3 < d) v[4 * q + 3] = f.w;
+    }
+  } else if constexpr (DP == 2) {
+    const float2 f = *reinterpret_cast<const float2*>(row);
+    v[0] = f.x;
+    v[1] = f.y;
+  } else {
+    v[0] = row[0];
+  }
+}
+
+// Reduce-scatter of a d-vector over the G lanes of a group: lane l returns sum_lanes pd[l].
+template <int G, int d>
+__device__ __forceinline__ float group_reduce_scatter(const float (&pd)[d], int lane) {
+  float v[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) v[k] = k < d ? pd[k < d ? k : 0] : 0.f;
+#pragma unroll
+  for (int w = G / 2; w >= 1; w >>= 1) {
+    const bool up = (lane & w) != 0;
+#pragma unroll
+    for (int k = 0; k < w; ++k) {
+      const float send = up ? v[k] : v[k + w];
+      const float keep = up ? v[k + w] : v[k];
+      v[k] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return v[0];
+}
+
+// ------------------------------------------------------------------------------------------
+// depth-3 forward
+// ------------------------------------------------------------------------------------------
+template <int d>
+__global__ void __launch_bounds__(kThreads)
+sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, int TC,
+                float* __restrict__ sig) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
+  constexpr int D = d + d * d + d * d * d;
+  extern __shared__ __align__(16) float smem[];
+  const int tid = threadIdx.x, grp = tid / G, lane = tid % G;
+  const int il = lane < d ? lane : d - 1;
+  const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const int npart = (int)min((int64_t)PPC, N - p0);
+  const bool active = grp < npart && lane < d;
+  const int gq = grp < npart ? grp : 0;
+  const int pstride = TC * DP;
+
+  float S1 = 0.f, S2[d], S3[d][d], xprev[d], xprev_i = 0.f;
+#pragma unroll
+  for (int j = 0; j < d; ++j) {
+    S2[j] = 0.f;
+    xprev[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < d; ++c) S3[j][c] = 0.f;
+  }
+
+  for (int c0 = 0; c0 < T; c0 += TC) {
+    const int len = min(TC, T - c0);
+    __syncthreads();
+    for (int q = 0; q < npart; ++q) {
+      const float* __restrict__ src = x + ((p0 + q) * (int64_t)T + c0) * d;
+      float* dst = smem + q * pstride;
+#pragma unroll 4
+      for (int i = tid; i < len * d; i += kThreads) {
+        const int t = i / d, c = i - t * d;
+        dst[t * DP + c] = __ldg(src + i);
+      }
+    }
+    __syncthreads();
+    const float* rows = smem + gq * pstride;
+    for (int r = 0; r < len; ++r) {
+      float xt[d];
+      load_row<d>(rows + r * DP, xt);
+      const float xi = rows[r * DP + il];
+      float dl[d];
+#pragma unroll
+      for (int c = 0; c < d; ++c) {
+        dl[c] = xt[c] - xprev[c];
+        xprev[c] = xt[c];
+      }
+      const float di = xi - xprev_i;
+      xprev_i = xi;
+      if (!basepoint && c0 + r == 0) continue;  // first point only seeds xprev
+      const float u3 = S1 + di * (1.f / 3.f);
+#pragma unroll
+      for (int j = 0; j < d; ++j) {
+        const float b = S2[j] + u3 * dl[j] * 0.5f;
+#pragma unroll
+        for (int c = 0; c < d; ++c) S3[j][c] = fmaf(b, dl[c], S3[j][c]);
+      }
+      const float u2 = S1 + di * 0.5f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) S2[j] = fmaf(u2, dl[j], S2[j]);
+      S1 += di;
+    }
+  }
+  // stage the result through shared memory for coalesced stores
+  __syncthreads();
+  if (active) {
+    float* o = smem + grp * D;
+    o[lane] = S1;
+#pragma unroll
+    for (int j = 0; j < d; ++j) {
+      o[d + lane * d + j] = S2[j];
+#pragma unroll
+      for (int c = 0; c < d; ++c) o[d + d * d + (lane * d + j) * d + c] = S3[j][c];
+    }
+  }
+  __syncthreads();
+  float* __restrict__ dst = sig + p0 * D;
+  for (int i = tid; i < npart * D; i += kThreads) dst[i] = smem[i];
+}
+
+// ------------------------------------------------------------------------------------------
+// depth-3 backward (VJP) with fused  out = beta * gx + alpha * add
+// ------------------------------------------------------------------------------------------
+template <int d>
+__global__ void __launch_bounds__(kThreads)
+sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
+                const float* __restrict__ gsig, int64_t N, int T, int basepoint, int TC,
+                const float* __restrict__ add, int64_t ld_add, float alpha, float beta,
+                float* __restrict__ out) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
+  constexpr int D = d + d * d + d * d * d;
+  extern __shared__ __align__(16) float smem[];
+  __shared__ float carry[PPC * DP];
+  const int tid = threadIdx.x, grp = tid / G, lane = tid % G;
+  const int il = lane < d ? lane : d - 1;
+  const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const int npart = (int)min((int64_t)PPC, N - p0);
+  const bool active = grp < npart && lane < d;
+  const int gq = grp < npart ? grp : 0;
+  const int pstride = (TC + 1) * DP;
+
+  float S1 = 0.f, S2[d], S3[d][d], A1 = 0.f, A2[d], g3[d][d];
+  // ---- load S_T and dL/dS_T (coalesced through smem) ----
+  {
+    const float* __restrict__ src = sig + p0 * D;
+    for (int i = tid; i < npart * D; i += kThreads) smem[i] = __ldg(src + i);
+    __syncthreads();
+    const float* o = smem + gq * D;
+    S1 = active ? o[il] : 0.f;
+#pragma unroll
+    for (int j = 0; j < d; ++j) {
+      S2[j] = active ? o[d + il * d + j] : 0.f;
+#pragma unroll
+      for (int c = 0; c < d; ++c) S3[j][c] = active ? o[d + d * d + (il * d + j) * d + c] : 0.f;
+    }
+    __syncthreads();
+    src = gsig + p0 * D;
+    for (int i = tid; i < npart * D; i += kThreads) smem[i] = __ldg(src + i);
+    __syncthreads();
+    A1 = active ? o[il] : 0.f;
+#pragma unroll
+    for (int j = 0; j < d; ++j) {
+      A2[j] = active ? o[d + il * d + j] : 0.f;
+#pragma unroll
+      for (int c = 0; c < d; ++c) g3[j][c] = active ? o[d + d * d + (il * d + j) * d + c] : 0.f;
+    }
+  }
+  for (int i = tid; i < PPC * DP; i += kThreads) carry[i] = 0.f;
+
+  const int t_first = basepoint ? 0 : 1;
+  const int n_chunks = (T + TC - 1) / TC;
+  for (int ch = n_chunks - 1; ch >= 0; --ch) {
+    const int c0 = ch * TC;
+    const int len = min(TC, T - c0);
+    __syncthreads();
+    // rows r = 0..len  <->  time c0-1+r ; row 0 is zero when c0 == 0 (the basepoint)
+    for (int q = 0; q < npart; ++q) {
+      float* dst = smem + q * pstride;
+      const int lo = c0 > 0 ? -1 : 0;  // first time index to read relative to c0
+      const float* __restrict__ src = x + ((p0 + q) * (int64_t)T + c0 + lo) * d;
+      const int cnt = (len - lo) * d;
+#pragma unroll 4
+      for (int i = tid; i < cnt; i += kThreads) {
+        const int t = i / d, c = i - t * d;
+        dst[(t + 1 + lo) * DP + c] = __ldg(src + i);
+      }
+      if (c0 == 0 && tid < DP) dst[tid] = 0.f;
+    }
+    __syncthreads();
+    float* rows = smem + gq * pstride;
+    for (int t = c0 + len - 1; t >= c0; --t) {
+      const int r = t - c0 + 1;
+      if (t < t_first) {  // no increment ends at point 0 without a basepoint
+        __syncwarp();
+        if (active) rows[r * DP + lane] = 0.f;
+        continue;
+      }
+      float xt[d], xp[d], dl[d];
+      load_row<d>(rows + r * DP, xt);
+      load_row<d>(rows + (r - 1) * DP, xp);
+      const float di = rows[r * DP + il] - rows[(r - 1) * DP + il];
+#pragma unroll
+      for (int c = 0; c < d; ++c) dl[c] = xt[c] - xp[c];
+      // ---- S_{t-1} = S_t (x) exp(-dl) ----
+      {
+        const float u3 = S1 - di * (1.f / 3.f);
+#pragma unroll
+        for (int j = 0; j < d; ++j) {
+          const float b = S2[j] - u3 * dl[j] * 0.5f;
+#pragma unroll
+          for (int c = 0; c < d; ++c) S3[j][c] = fmaf(-b, dl[c], S3[j][c]);
+        }
+        const float u2 = S1 - di * 0.5f;
+#pragma unroll
+        for (int j = 0; j < d; ++j) S2[j] = fmaf(-u2, dl[j], S2[j]);
+        S1 -= di;
+      }
+      // ---- adjoint of S_t = S_{t-1} (x) exp(dl) ----
+      float pd[d];
+#pragma unroll
+      for (int c = 0; c < d; ++c) pd[c] = 0.f;
+      float dI = A1, a1inc = 0.f;
+      const float u3 = S1 + di * (1.f / 3.f), u2 = S1 + di * 0.5f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) {
+        float rr = 0.f;
+#pragma unroll
+        for (int c = 0; c < d; ++c) rr = fmaf(g3[j][c], dl[c], rr);
+        const float B2 = S2[j] + u3 * dl[j] * 0.5f;
+#pragma unroll
+        for (int c = 0; c < d; ++c) pd[c] = fmaf(g3[j][c], B2, pd[c]);
+        pd[j] += rr * u3 * 0.5f + A2[j] * u2;
+        const float ub = rr * dl[j] * 0.5f, vb = A2[j] * dl[j];
+        a1inc += ub + vb;
+        dI += ub * (1.f / 3.f) + vb * 0.5f;
+        A2[j] += rr;
+      }
+      A1 += a1inc;
+      const float tot = group_reduce_scatter<G, d>(pd, lane) + dI;
+      __syncwarp();  // every lane of the group has consumed row r before it is overwritten
+      if (active) rows[r * DP + lane] = tot;
+    }
+    __syncthreads();
+    // gx[t] = gDelta[t] - gDelta[t+1]; coalesced store with the fused epilogue
+    for (int q = 0; q < npart; ++q) {
+      const float* src = smem + q * pstride;
+      const int64_t n = p0 + q;
+      float* __restrict__ o = out + (n * (int64_t)T + c0) * d;
+      const float* __restrict__ a = add ? add + n * ld_add + (int64_t)c0 * d : nullptr;
+#pragma unroll 4
+      for (int i = tid; i < len * d; i += kThreads) {
+        const int t = i / d, c = i - t * d;
+        const float nxt = (t + 1 < len) ? src[(t + 2) * DP + c] : carry[q * DP + c];
+        float v = beta * (src[(t + 1) * DP + c] - nxt);
+        if (a) v = fmaf(alpha, __ldg(a + i), v);
+        o[i] = v;
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < npart * DP; i += kThreads) {
+      const int q = i / DP, c = i - q * DP;
+      carry[i] = smem[q * pstride + DP + c];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// generic kernels: one warp per particle, state in shared memory
+// ------------------------------------------------------------------------------------------
+struct LevelInfo {
+  int off[10];  // off[k] = offset of level k (1-based) in the D-vector
+  int pw[10];   // pw[k] = d^k
+};
+
+// S <- S (x) exp(sgn*dl); dl[] in shared memory; warp-synchronous.
+__device__ __forceinline__ void generic_mul_exp(float* S, const float* dl, float sgn, int d, int m,
+                                                const LevelInfo& L, int lane) {
+  for (int k = m; k >= 1; --k) {
+    float* Sk = S + L.off[k];
+    for (int e = lane; e < L.pw[k]; e += 32) {
+      float b = 1.f;
+      for (int j = 1; j <= k - 1; ++j) {
+        const int pre = e / L.pw[k - j];  // index of (u_1..u_j) inside level j
+        const int uj = pre % d;
+        b = S[L.off[j] + pre] + b * (sgn * dl[uj]) / (float)(k - j + 1);
+      }
+      Sk[e] += b * (sgn * dl[e % d]);
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(32)
+sig_generic_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int d, int m, int basepoint,
+                       LevelInfo L, int D, float* __restrict__ sig) {
+  extern __shared__ __align__(16) float smem[];
+  float* S = smem;       // D
+  float* dl = smem + D;  // d
+  const int lane = threadIdx.x;
+  const int64_t n = blockIdx.x;
+  const float* xn = x + n * (int64_t)T * d;
+  for (int i = lane; i < D; i += 32) S[i] = 0.f;
+  __syncwarp();
+  for (int t = basepoint ? 0 : 1; t < T; ++t) {
+    for (int c = lane; c < d; c += 32)
+      dl[c] = __ldg(xn + (int64_t)t * d + c) - (t > 0 ? __ldg(xn + (int64_t)(t - 1) * d + c) : 0.f);
+    __syncwarp();
+    generic_mul_exp(S, dl, 1.f, d, m, L, lane);
+  }
+  for (int i = lane; i < D; i += 32) sig[n * D + i] = S[i];
+}
+
+__global__ void __launch_bounds__(32)
+sig_generic_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
+                       const float* __restrict__ gsig, int64_t N, int T, int d, int m,
+                       int basepoint, LevelInfo L, int D, const float* __restrict__ add,
+                       int64_t ld_add, float alpha, float beta, float* __restrict__ out) {
+  extern __shared__ __align__(16) float smem[];
+  float* S = smem;            // D
+  float* A = S + D;           // D
+  float* dl = A + D;          // d
+  float* gprev = dl + d;      // d : gDelta of step t+1
+  float* acc = gprev + d;     // d * 33 per-lane partial gDelta
+  const int lane = threadIdx.x;
+  const int64_t n = blockIdx.x;
+  const float* xn = x + n * (int64_t)T * d;
+  for (int i = lane; i < D; i += 32) {
+    S[i] = __ldg(sig + n * D + i);
+    A[i] = __ldg(gsig + n * D + i);
+  }
+  for (int c = lane; c < d; c += 32) gprev[c] = 0.f;
+  __syncwarp();
+  const int t_first = basepoint ? 0 : 1;
+  for (int t = T - 1; t >= 0; --t) {
+    if (t < t_first) {  // point 0 without basepoint: gx[0] = -gDelta[1]
+      for (int c = lane; c < d; c += 32) {
+        float v = beta * (0.f - gprev[c]);
+        if (add) v = fmaf(alpha, __ldg(add + n * ld_add + (int64_t)t * d + c), v);
+        out[(n * (int64_t)T + t) * d + c] = v;
+      }
+      break;
+    }
+    for (int c = lane; c < d; c += 32)
+      dl[c] = __ldg(xn + (int64_t)t * d + c) - (t > 0 ? __ldg(xn + (int64_t)(t - 1) * d + c) : 0.f);
+    for (int i = lane; i < d * 33; i += 32) acc[i] = 0.f;
+    __syncwarp();
+    generic_mul_exp(S, dl, -1.f, d, m, L, lane);  // S = S_{t-1}
+    // (a) gDelta contributions, entry-parallel over dL/dS_t (A still holds the "new" adjoint)
+    for (int k = 1; k <= m; ++k) {
+      for (int e = lane; e < L.pw[k]; e += 32) {
+        const float a = A[L.off[k] + e];
+        // suffix products suf_p = prod_{q>p} dl[u_q]; walk p = k..1 keeping Lp via recomputation
+        // L_1 = 1/k! ; L_{p+1} = L_p*dl[u_p] + P^p[u_1..u_p]/(k-p)!
+        float fact_inv[9];
+        {
+          float f = 1.f;
+          fact_inv[0] = 1.f;
+          for (int q = 1; q <= k; ++q) {
+            f *= (float)q;
+            fact_inv[q] = 1.f / f;
+          }
+        }
+        float Lp = fact_inv[k];
+        // forward over p computing L_p and multiplying by suffix computed on the fly
+        for (int p = 1; p <= k; ++p) {
+          const int pre = e / L.pw[k - p];
+          const int up = pre % d;
+          float suf = 1.f;
+          for (int q = p + 1; q <= k; ++q) suf *= dl[(e / L.pw[k - q]) % d];
+          acc[up * 33 + lane] += a * Lp * suf;
+          if (p < k) Lp = Lp * dl[up] + S[L.off[p] + pre] * fact_inv[k - p];
+        }
+      }
+    }
+    __syncwarp();
+    // (b) adjoint update, ascending levels, in place:
+    //     A^i[u] += sum_{j>=1} sum_{|v|=j} A^{i+j}[u,v] prod dl[v] / j!
+    for (int i = 1; i <= m - 1; ++i) {
+      for (int e = lane; e < L.pw[i]; e += 32) {
+        float s = 0.f, fj = 1.f;
+        for (int j = 1; j <= m - i; ++j) {
+          fj *= (float)j;
+          const float* Ak = A + L.off[i + j] + (int64_t)e * L.pw[j];
+          float sj = 0.f;
+          for (int v = 0; v < L.pw[j]; ++v) {
+            float w = 1.f;
+            int vv = v;
+            for (int q = 0; q < j; ++q) {
+              w *= dl[vv % d];
+              vv /= d;
+            }
+            sj = fmaf(Ak[v], w, sj);
+          }
+          s += sj / fj;
+        }
+        A[L.off[i] + e] += s;
+      }
+      __syncwarp();
+    }
+    // (c) reduce per-lane partials, emit gx[t] = gDelta[t] - gDelta[t+1]
+    for (int c = lane; c < d; c += 32) {
+      float s = 0.f;
+      for (int l = 0; l < 32; ++l) s += acc[c * 33 + l];
+      float v = beta * (s - gprev[c]);
+      if (add) v = fmaf(alpha, __ldg(add + n * ld_add + (int64_t)t * d + c), v);
+      out[(n * (int64_t)T + t) * d + c] = v;
+      gprev[c] = s;
+    }
+    __syncwarp();
+  }
+}
+
+template <int d>
+int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* sig,
+                    cudaStream_t st) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
+  constexpr int D = d + d * d + d * d * d;
+  constexpr int kBudget = 40 * 1024;
+  static_assert(PPC * D * 4 <= kBudget, "output staging must fit");
+  int TC = (int)std::min<int64_t>(T, kBudget / 4 / (PPC * DP));
+  size_t smem = (size_t)std::max(PPC * TC * DP, PPC * D) * 4;
+  const int64_t grid = ceil_div(N, PPC);
+  sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig);
+  SIG_LAUNCH_OK("sig3_fwd_kernel");
+  return 0;
+}
+
+template <int d>
+int launch_sig3_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
+                    int basepoint, const float* add, int64_t ld_add, float alpha, float beta,
+                    float* out, cudaStream_t st) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
+  constexpr int D = d + d * d + d * d * d;
+  constexpr int kBudget = 40 * 1024;
+  static_assert(PPC * D * 4 <= kBudget, "state staging must fit");
+  int TC = (int)std::min<int64_t>(T, kBudget / 4 / (PPC * DP) - 1);
+  size_t smem = (size_t)std::max(PPC * (TC + 1) * DP, PPC * D) * 4;
+  const int64_t grid = ceil_div(N, PPC);
+  sig3_bwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, sig, gsig, N, (int)T, basepoint,
+                                                              TC, add, ld_add, alpha, beta, out);
+  SIG_LAUNCH_OK("sig3_bwd_kernel");
+  return 0;
+}
+
+int make_levels(int64_t d, int depth, LevelInfo* L, int64_t* D) {
+  int64_t off = 0, p = 1;
+  L->pw[0] = 1;
+  for (int k = 1; k <= depth; ++k) {
+    p *= d;
+    if (p > (1 << 24)) return 1;
+    L->off[k] = (int)off;
+    L->pw[k] = (int)p;
+    off += p;
+  }
+  *D = off;
+  return 0;
+}
+
+}  // namespace
+
+int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
+                   float* sig, cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
+                "signature_fwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,
+                (long long)T, (long long)d, depth);
+  SIG_CHECK_ARG(basepoint || T >= 2, "signature_fwd: need >= 2 points without a basepoint");
+  SIG_CHECK_ARG(T < (1 << 24), "signature_fwd: T too large");
+  if (N == 0) return 0;
+  if (depth == 3) {
+    switch (d) {
+      case 1: return launch_sig3_fwd<1>(x, N, T, basepoint, sig, st);
+      case 2: return launch_sig3_fwd<2>(x, N, T, basepoint, sig, st);
+      case 3: return launch_sig3_fwd<3>(x, N, T, basepoint, sig, st);
+      case 4: return launch_sig3_fwd<4>(x, N, T, basepoint, sig, st);
+      case 5: return launch_sig3_fwd<5>(x, N, T, basepoint, sig, st);
+      case 6: return launch_sig3_fwd<6>(x, N, T, basepoint, sig, st);
+      case 7: return launch_sig3_fwd<7>(x, N, T, basepoint, sig, st);
+      case 8: return launch_sig3_fwd<8>(x, N, T, basepoint, sig, st);
+      default: break;
+    }
+  }
+  LevelInfo L;
+  int64_t D;
+  if (make_levels(d, depth, &L, &D) != 0 || (D + d) * 4 > 200 * 1024) {
+    set_error("signature_fwd: d=%lld depth=%d (D=%lld) exceeds the shared-memory resident state",
+              (long long)d, depth, (long long)sig_channels(d, depth));
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  const size_t smem = (size_t)(D + d) * 4;
+  if (smem > 48 * 1024)
+    SIG_CUDA_OK(cudaFuncSetAttribute(sig_generic_fwd_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sig_generic_fwd_kernel<<<(unsigned)N, 32, smem, st>>>(x, N, (int)T, (int)d, depth, basepoint, L,
+                                                        (int)D, sig);
+  SIG_LAUNCH_OK("sig_generic_fwd_kernel");
+  return 0;
+}
+
+int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
+                   int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
+                   float alpha, float beta, float* out, cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
+                "signature_bwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,
+                (long long)T, (long long)d, depth);
+  SIG_CHECK_ARG(basepoint || T >= 2, "signature_bwd: need >= 2 points without a basepoint");
+  SIG_CHECK_ARG(T < (1 << 24), "signature_bwd: T too large");
+  SIG_CHECK_ARG(add == nullptr || ld_add >= T * d, "signature_bwd: ld_add < T*d");
+  if (N == 0) return 0;
+  if (depth == 3) {
+    switch (d) {
+#define SIG3_BWD_CASE(dd) \
+  case dd:                \
+    return launch_sig3_bwd<dd>(x, sig, gsig, N, T, basepoint, add, ld_add, alpha, beta, out, st);
+      SIG3_BWD_CASE(1)
+      SIG3_BWD_CASE(2)
+      SIG3_BWD_CASE(3)
+      SIG3_BWD_CASE(4)
+      SIG3_BWD_CASE(5)
+      SIG3_BWD_CASE(6)
+      SIG3_BWD_CASE(7)
+      SIG3_BWD_CASE(8)
+#undef SIG3_BWD_CASE
+      default: break;
+    }
+  }
+  LevelInfo L;
+  int64_t D;
+  if (make_levels(d, depth, &L, &D) != 0 || (2 * D + 2 * d + 33 * d) * 4 > 200 * 1024) {
+    set_error("signature_bwd: d=%lld depth=%d (D=%lld) exceeds the shared-memory resident state",
+              (long long)d, depth, (long long)sig_channels(d, depth));
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  const size_t smem = (size_t)(2 * D + 2 * d + 33 * d) * 4;
+  if (smem > 48 * 1024)
+    SIG_CUDA_OK(cudaFuncSetAttribute(sig_generic_bwd_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sig_generic_bwd_kernel<<<(unsigned)N, 32, smem, st>>>(x, sig, gsig, N, (int)T, (int)d, depth,
+                                                        basepoint, L, (int)D, add, ld_add, alpha,
+                                                        beta, out);
+  SIG_LAUNCH_OK("sig_generic_bwd_kernel");
+  return 0;
+}
+
+}  // namespace sigsvgd

@@ -1,0 +1,450 @@
+"""Torch-facing operators over the C ABI: device memory, streams and autograd plumbing only.
+
+* ``signature``      -- drop-in for ``signatory.signature(path, depth, basepoint=True)``
+                        (reference call sites src/kernels/_traj_kernels.py:125-126)
+* ``sig_rbf_gram``   -- K = GaussianKernel(signature(X), signature(Y)) as ONE autograd node whose
+                        backward is the closed form of ``autograd.grad(k_xx.sum(), X)``
+                        (src/inference/svgd.py:43, src/inference/score.py:55) incl. the gradient
+                        through ``torch.median`` (src/utils/math.py:31)
+* ``rbf_gram``       -- the static RBF kernel on plain features (src/kernels/_kernels.py:78-115)
+* ``phi``            -- fused Stein update (src/inference/svgd.py:36-44 + 82-83)
+
+Everything computes in fp32 on the current CUDA device; other float dtypes are cast in and the
+result is cast back.  No CPU path exists: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import call
+
+
+# ---------------------------------------------------------------------------------------------
+# helpers
+# ---------------------------------------------------------------------------------------------
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _prep(t: torch.Tensor, what: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{what}: expected a torch.Tensor, got {type(t)}")
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{what}: tensor is on {t.device}; sigsvgd_b200 runs on CUDA (sm_100a) only and has no CPU fallback"
+        )
+    if not t.is_floating_point():
+        raise TypeError(f"{what}: expected a floating-point tensor, got {t.dtype}")
+    return t.detach().to(torch.float32).contiguous()
+
+
+def sig_channels(d: int, depth: int) -> int:
+    return sum(d ** k for k in range(1, depth + 1))
+
+
+@dataclass
+class Bandwidth:
+    """How the RBF bandwidth is chosen (src/kernels/_kernels.py:106-109)."""
+
+    mode: int = _lib.BW_MEDIAN  # BW_MEDIAN: src/utils/math.py:28-34 ; BW_FIXED: float(h)
+    h: float = 1.0
+    bw_scale: float = 1.0
+    tol: float = 1.0e-8
+    median_grad: bool = True  # differentiate through the median like torch.autograd does
+
+    @staticmethod
+    def median(bw_scale: float = 1.0, tol: float = 1.0e-8, median_grad: bool = True) -> "Bandwidth":
+        return Bandwidth(_lib.BW_MEDIAN, 1.0, float(bw_scale), float(tol), bool(median_grad))
+
+    @staticmethod
+    def fixed(h: float) -> "Bandwidth":
+        h = float(h)
+        if not h > 0:
+            raise ValueError(f"bandwidth must be > 0, got {h}")
+        return Bandwidth(_lib.BW_FIXED, h, 1.0, 1.0e-8, False)
+
+
+def new_state(device, batch: int = 1) -> torch.Tensor:
+    """Device buffer holding ``batch`` sigsvgd_bw_state records (as int32 words)."""
+    return torch.zeros(batch, _lib.STATE_BYTES // 4, dtype=torch.int32, device=device)
+
+
+def state_field(state: torch.Tensor, name: str) -> torch.Tensor:
+    """View of one field of every record, still on the device (no sync)."""
+    if name in ("median", "h", "gamma", "coef"):
+        off = {"median": 0, "h": 1, "gamma": 2, "coef": 3}[name]
+        return state[:, off].view(torch.float32)
+    if name == "sum_kd":
+        return state[:, 4:6].contiguous().view(torch.float64).reshape(-1)
+    if name in ("n_ties", "n_ties_all", "clamped"):
+        return state[:, {"n_ties": 6, "n_ties_all": 7, "clamped": 8}[name]]
+    if name == "ties":
+        return state[:, _lib.OFF_TIES // 4:].reshape(state.shape[0], _lib.MAX_TIES, 2)
+    raise KeyError(name)
+
+
+def read_state(state: torch.Tensor, index: int = 0) -> dict:
+    """Synchronising host copy of one record (diagnostics / tests)."""
+    raw = bytes(state[index].cpu().numpy().tobytes())
+    s = _lib.BwState.from_buffer_copy(raw)
+    n = min(int(s.n_ties), _lib.MAX_TIES)
+    return dict(median=s.median, h=s.h, gamma=s.gamma, coef=s.coef, sum_kd=s.sum_kd, n_ties=int(s.n_ties),
+                n_ties_all=int(s.n_ties_all), clamped=int(s.clamped),
+                ties=[(s.ties[2 * i], s.ties[2 * i + 1]) for i in range(n)])
+
+
+# ---------------------------------------------------------------------------------------------
+# raw (non-autograd) wrappers, one per C entry point
+# ---------------------------------------------------------------------------------------------
+def signature_fwd_raw(x: torch.Tensor, depth: int, basepoint: bool = True) -> torch.Tensor:
+    N, T, d = x.shape
+    sig = torch.empty(N, sig_channels(d, depth), dtype=torch.float32, device=x.device)
+    call("sigsvgd_signature_fwd", _p(x), N, T, d, depth, int(basepoint), _p(sig), _stream())
+    return sig
+
+
+def signature_bwd_raw(x, sig, gsig, depth, basepoint=True, add=None, alpha=0.0, beta=1.0) -> torch.Tensor:
+    N, T, d = x.shape
+    out = torch.empty_like(x)
+    ld_add = 0 if add is None else add.stride(0)
+    call("sigsvgd_signature_bwd", _p(x), _p(sig), _p(gsig), N, T, d, depth, int(basepoint), _p(add), ld_add,
+         float(alpha), float(beta), _p(out), _stream())
+    return out
+
+
+def pack_features(s: torch.Tensor, mean: Optional[torch.Tensor], score: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """V = [score | s - mean | 1 | 0-pad]  (row stride a multiple of 8 floats)."""
+    N, D = s.shape
+    P = 0 if score is None else score.shape[1]
+    C = (P + D + 1 + 7) // 8 * 8
+    v = torch.empty(N, C, dtype=torch.float32, device=s.device)
+    call("sigsvgd_pack_v", _p(score), P, _p(s), s.stride(0), _p(mean), N, D, _p(v), C, C, _stream())
+    return v
+
+
+def col_mean(s: torch.Tensor) -> torch.Tensor:
+    N, D = s.shape
+    part = torch.empty(64, D, dtype=torch.float32, device=s.device)
+    mean = torch.empty(D, dtype=torch.float32, device=s.device)
+    call("sigsvgd_col_mean", _p(s), s.stride(0), N, D, _p(part), _p(mean), _stream())
+    return mean
+
+
+def sqdist_raw(a: torch.Tensor, b: torch.Tensor, D: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """a, b: 2-D fp32 views whose first D columns are the features (row stride = .stride(0))."""
+    M, N = a.shape[0], b.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    call("sigsvgd_sqdist", _p(a), a.stride(0), _p(b), b.stride(0), M, N, D, _p(out), out.stride(0), 0, _stream())
+    return out
+
+
+def bandwidth_raw(dist: torch.Tensor, bw: Bandwidth, n_log: int, state: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if state is None:
+        state = new_state(dist.device)
+    if bw.mode == _lib.BW_FIXED:
+        call("sigsvgd_fixed_bandwidth", bw.h, _p(state), _stream())
+    else:
+        if not dist.is_contiguous():
+            raise ValueError("median bandwidth needs a contiguous distance matrix")
+        nbytes = _lib.load().sigsvgd_select_workspace_bytes(dist.numel())
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dist.device)
+        call("sigsvgd_median_bandwidth", _p(dist), dist.numel(), n_log, bw.bw_scale, bw.tol, _p(state), _p(ws),
+             nbytes, _stream())
+    return state
+
+
+def rbf_apply_raw(k: torch.Tensor, state: torch.Tensor, row_offset: int = 0, weight: Optional[torch.Tensor] = None):
+    M, N = k.shape
+    call("sigsvgd_rbf_apply", _p(k), k.stride(0), M, N, row_offset, _p(weight),
+         0 if weight is None else weight.stride(0), _p(state), _stream())
+    return k
+
+
+def median_coef_raw(state, enable: bool, sum_kd_all=None, n_ties_all=None):
+    call("sigsvgd_median_coef", _p(state), _p(sum_kd_all), _p(n_ties_all), int(enable), _stream())
+
+
+def matmul_nn_raw(a: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    M, N = a.shape
+    C = v.shape[1]
+    out = torch.empty(M, C, dtype=torch.float32, device=a.device)
+    call("sigsvgd_matmul_nn", _p(a), a.stride(0), _p(v), v.stride(0), M, N, C, _p(out), C, 0, _stream())
+    return out
+
+
+def sig_grad_raw(sc, sc_all, ks, rowsum, state, row_offset: int = 0) -> torch.Tensor:
+    """sc/sc_all/ks: 2-D views (features in the first D columns of ks.shape[1]); rowsum: 1-D view."""
+    M, D = ks.shape
+    g = torch.empty(M, D, dtype=torch.float32, device=ks.device)
+    call("sigsvgd_sig_grad", _p(sc), sc.stride(0), _p(sc_all), sc_all.stride(0), _p(ks), ks.stride(0), _p(rowsum),
+         rowsum.stride(0), M, D, row_offset, _p(state), _p(g), D, _stream())
+    return g
+
+
+def _swap_ties(state: torch.Tensor) -> torch.Tensor:
+    """Record with (row, col) of every tie exchanged -- the second-argument view of the tie set."""
+    s2 = state.clone()
+    o = _lib.OFF_TIES // 4
+    s2[:, o:] = state[:, o:].reshape(-1, _lib.MAX_TIES, 2).flip(-1).reshape(state.shape[0], -1)
+    return s2
+
+
+def _same_data(a: torch.Tensor, b: torch.Tensor) -> bool:
+    return a.data_ptr() == b.data_ptr() and a.shape == b.shape and a.stride() == b.stride() and a.dtype == b.dtype
+
+
+def _is_uniform_cotangent(g: torch.Tensor) -> bool:
+    """True for the expanded scalar that ``k_xx.sum().backward()`` produces."""
+    return all(s == 0 for s in g.stride()) or g.numel() == 1
+
+
+# ---------------------------------------------------------------------------------------------
+# autograd nodes
+# ---------------------------------------------------------------------------------------------
+class _Signature(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, path, depth, basepoint):
+        x = _prep(path, "signature")
+        if x.dim() != 3:
+            raise ValueError(f"signature: expected [batch, length, channels], got {tuple(x.shape)}")
+        sig = signature_fwd_raw(x, depth, basepoint)
+        ctx.save_for_backward(x, sig)
+        ctx.depth, ctx.basepoint, ctx.in_dtype = depth, basepoint, path.dtype
+        return sig.to(path.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, sig = ctx.saved_tensors
+        gx = signature_bwd_raw(x, sig, _prep(g, "signature.backward"), ctx.depth, ctx.basepoint)
+        return gx.to(ctx.in_dtype), None, None
+
+
+def signature(path, depth, stream=False, basepoint=False, inverse=False, initial=None, scalar_term=False):
+    """``signatory.signature`` with the options the reference uses (path, depth, basepoint)."""
+    if stream or inverse or initial is not None or scalar_term:
+        raise NotImplementedError("sigsvgd_b200.signature supports (path, depth, basepoint) only")
+    if isinstance(basepoint, torch.Tensor):
+        bp = basepoint.to(path).reshape(-1, 1, path.shape[2]).expand(path.shape[0], 1, path.shape[2])
+        path = torch.cat([bp, path], dim=1)
+        basepoint = False
+    return _Signature.apply(path, int(depth), bool(basepoint))
+
+
+class _GramCore:
+    """Shared forward/backward of the two Gram nodes, operating on fp32 feature matrices."""
+
+    @staticmethod
+    def forward(sx, sy, same, bw: Bandwidth, center: bool):
+        N, D = sx.shape
+        mean = col_mean(sx) if center else None
+        vx = pack_features(sx, mean)
+        vy = vx if same else pack_features(sy, mean)
+        K = sqdist_raw(vx, vy, D)
+        state = bandwidth_raw(K, bw, N)
+        rbf_apply_raw(K, state)
+        median_coef_raw(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad)
+        return K, vx, vy, state
+
+    @staticmethod
+    def backward(gK, K, vx, vy, state, same, D, need_y, bw: Bandwidth):
+        """Returns (g_x [N,D], g_y [N,D] or None): gradients wrt the feature matrices."""
+        if _is_uniform_cotangent(gK):
+            scale = gK[(0,) * gK.dim()].reshape(1).to(torch.float32)  # device scalar, applied at the end
+            A, st = K, state
+        else:
+            # generic cotangent W: weighted kernel A = W o K with its own statistics
+            W = _prep(gK, "gram.backward")
+            scale = None
+            A = sqdist_raw(vx, vy, D)
+            st = state.clone()
+            st[:, 4:8] = 0  # sum_kd, n_ties, n_ties_all
+            rbf_apply_raw(A, st, weight=W)
+            median_coef_raw(st, bw.mode == _lib.BW_MEDIAN and bw.median_grad)
+        out = matmul_nn_raw(A, vy)
+        gx = sig_grad_raw(vx, vy, out[:, :D], out[:, D], st)
+        gy = None
+        if need_y:
+            if same and scale is not None:
+                gy = gx  # K and the tie set are bit-symmetric (see gemm_simt.cu), so g^Y == g^X
+            else:
+                At = A.t().contiguous()
+                out_t = matmul_nn_raw(At, vx)
+                gy = sig_grad_raw(vy, vx, out_t[:, :D], out_t[:, D], _swap_ties(st))
+        if scale is not None:
+            gx = gx * scale
+            gy = None if gy is None else (gx if gy is gx else gy * scale)
+        return gx, gy
+
+
+class _SigRBFGram(torch.autograd.Function):
+    """K[i,j] = exp(-|S(X_i) - S(Y_j)|^2 / (2 h^2)); PathSigKernel with a Gaussian static kernel."""
+
+    @staticmethod
+    def forward(ctx, X, Y, depth, bw, center):
+        same = _same_data(X, Y)
+        x = _prep(X, "PathSigKernel")
+        y = x if same else _prep(Y, "PathSigKernel")
+        sx = signature_fwd_raw(x, depth, True)
+        sy = sx if same else signature_fwd_raw(y, depth, True)
+        K, vx, vy, state = _GramCore.forward(sx, sy, same, bw, center)
+        ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state)
+        ctx.meta = (depth, bw, same, X.dtype)
+        ctx.set_materialize_grads(False)
+        ctx.bw_state = state
+        return K if X.dtype == torch.float32 else K.to(X.dtype)
+
+    @staticmethod
+    def backward(ctx, gK):
+        if gK is None:
+            return None, None, None, None, None
+        x, y, sx, sy, vx, vy, K, state = ctx.saved_tensors
+        depth, bw, same, in_dtype = ctx.meta
+        need_x, need_y = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        D = sx.shape[1]
+        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, need_y, bw)
+        gX = signature_bwd_raw(x, sx, gsx, depth, True).to(in_dtype) if need_x else None
+        gY = None
+        if need_y:
+            if gsy is gsx and gX is not None and same:
+                gY = gX
+            else:
+                gY = signature_bwd_raw(y, sy, gsy, depth, True).to(in_dtype)
+        return gX, gY, None, None, None
+
+
+class _RBFGram(torch.autograd.Function):
+    """Static Gaussian kernel on [N, dim] features (src/kernels/_kernels.py:78-115)."""
+
+    @staticmethod
+    def forward(ctx, X, Y, bw, center):
+        same = _same_data(X, Y)
+        sx = _prep(X, "GaussianKernel")
+        sy = sx if same else _prep(Y, "GaussianKernel")
+        K, vx, vy, state = _GramCore.forward(sx, sy, same, bw, center)
+        ctx.save_for_backward(vx, vy, K, state)
+        ctx.meta = (bw, same, X.dtype, sx.shape[1])
+        ctx.set_materialize_grads(False)
+        ctx.bw_state = state
+        return K if X.dtype == torch.float32 else K.to(X.dtype)
+
+    @staticmethod
+    def backward(ctx, gK):
+        if gK is None:
+            return None, None, None, None
+        vx, vy, K, state = ctx.saved_tensors
+        bw, same, in_dtype, D = ctx.meta
+        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, ctx.needs_input_grad[1], bw)
+        gX = gsx.to(in_dtype) if ctx.needs_input_grad[0] else None
+        gY = gsy.to(in_dtype) if (ctx.needs_input_grad[1] and gsy is not None) else None
+        return gX, gY, None, None
+
+
+def sig_rbf_gram(X, Y, depth: int = 3, bandwidth: Optional[Bandwidth] = None, center: bool = True) -> torch.Tensor:
+    if X.shape != Y.shape:
+        raise AssertionError("X and Y must have the same dimensions.")
+    return _SigRBFGram.apply(X, Y, int(depth), bandwidth or Bandwidth.median(), bool(center))
+
+
+def rbf_gram(X, Y, bandwidth: Optional[Bandwidth] = None, center: bool = True) -> torch.Tensor:
+    if X.shape != Y.shape:
+        raise AssertionError("X and Y must have the same dimensions.")
+    return _RBFGram.apply(X, Y, bandwidth or Bandwidth.median(), bool(center))
+
+
+def rbf_gram_with_grad(X, Y, bandwidth: Optional[Bandwidth] = None, center: bool = True):
+    """(K, sum_j dK_ij/dx_i) -- the analytic-gradient branch of GaussianKernel
+    (src/kernels/_kernels.py:111-113): d_K.sum(1) = -(1/h^2) sum_j K_ij (x_i - y_j), constant h."""
+    bw = bandwidth or Bandwidth.median()
+    same = _same_data(X, Y)
+    sx = _prep(X, "GaussianKernel")
+    sy = sx if same else _prep(Y, "GaussianKernel")
+    D = sx.shape[1]
+    bw_nograd = Bandwidth(bw.mode, bw.h, bw.bw_scale, bw.tol, False)
+    K, vx, vy, state = _GramCore.forward(sx, sy, same, bw_nograd, center)
+    out = matmul_nn_raw(K, vy)
+    dK = sig_grad_raw(vx, vy, out[:, :D], out[:, D], state)
+    return K.to(X.dtype), dK.to(X.dtype), state
+
+
+# ---------------------------------------------------------------------------------------------
+# fused Stein update
+# ---------------------------------------------------------------------------------------------
+_WS_CACHE: dict = {}
+
+
+def _workspace(device, nbytes: int) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS_CACHE.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = None
+        _WS_CACHE.pop(key, None)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _WS_CACHE[key] = ws
+    return ws
+
+
+@dataclass
+class PhiResult:
+    phi: torch.Tensor  # [.., N, T, d]  Stein direction (K.score - grad_k)/N ; reference velocity = -phi
+    state: torch.Tensor  # device record(s): median, h, ties ...
+    k_xx: Optional[torch.Tensor] = None
+    grad_k: Optional[torch.Tensor] = None
+    sig: Optional[torch.Tensor] = None
+
+    @property
+    def h(self) -> torch.Tensor:
+        return state_field(self.state, "h")
+
+
+def phi(X: torch.Tensor, score: torch.Tensor, depth: int = 3, bandwidth: Optional[Bandwidth] = None,
+        want_k: bool = False, want_grad_k: bool = False, want_sig: bool = False, center: bool = True,
+        flags: int = 0) -> PhiResult:
+    """Fused update for one swarm ``X [N,T,d]`` or a batch of independent swarms ``X [B,N,T,d]``.
+
+    ``score`` = grad_log_p (+ grad_log_prior), any shape that flattens to ``[.., N, T*d]``."""
+    bw = bandwidth or Bandwidth.median()
+    x = _prep(X, "phi")
+    batched = x.dim() == 4
+    if x.dim() not in (3, 4):
+        raise ValueError(f"phi: X must be [N,T,d] or [B,N,T,d], got {tuple(x.shape)}")
+    B = x.shape[0] if batched else 1
+    N, T, d = x.shape[-3:]
+    g = _prep(score, "phi").reshape(B, N, -1)
+    if g.shape[-1] != T * d:
+        raise ValueError(f"phi: score has {g.shape[-1]} columns per particle, expected T*d = {T * d}")
+    lib = _lib.load()
+    D = sig_channels(d, depth)
+    dev = x.device
+    out = torch.empty_like(x)
+    k_out = torch.empty(B, N, N, dtype=torch.float32, device=dev) if want_k else None
+    gk_out = torch.empty(B, N, T * d, dtype=torch.float32, device=dev) if want_grad_k else None
+    sig_out = torch.empty(B, N, D, dtype=torch.float32, device=dev) if want_sig else None
+    state = new_state(dev, B)
+    nbytes = lib.sigsvgd_phi_workspace_bytes(B, N, T, d, depth, int(want_k))
+    if nbytes == 0:
+        raise ValueError("phi: bad shape")
+    ws = _workspace(dev, nbytes)
+    fl = int(flags) | (_lib.FLAG_MEDIAN_GRAD if (bw.mode == _lib.BW_MEDIAN and bw.median_grad) else 0)
+    if not center:
+        fl |= _lib.FLAG_NO_CENTER
+    call("sigsvgd_phi", _p(x), _p(g), B, N, T, d, depth, bw.mode, bw.h, bw.bw_scale, bw.tol, fl, _p(out), _p(k_out),
+         _p(gk_out), _p(sig_out), _p(state), _p(ws), ws.numel(), _stream())
+    if not batched:
+        k_out = None if k_out is None else k_out[0]
+        gk_out = None if gk_out is None else gk_out[0]
+        sig_out = None if sig_out is None else sig_out[0]
+    return PhiResult(out.to(X.dtype), state, k_out, gk_out, sig_out)
+
+
+def log_np1(n: int) -> float:
+    return math.log(n + 1.0)

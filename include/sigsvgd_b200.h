@@ -154,6 +154,40 @@ int sigsvgd_sig_grad(const float* sc, int64_t lds, const float* sc_all, int64_t 
                      int64_t ldg, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Tensor-core building blocks (tcgen05 + TMA, split-fp16: every fp32 operand is two fp16 planes
+ * hi/lo of value*alpha, a product is hi.hi + hi.lo + lo.hi accumulated in fp32 TMEM).  They replace
+ * the same reference statements as sigsvgd_sqdist / sigsvgd_rbf_apply / sigsvgd_matmul_nn and are
+ * what sigsvgd_phi runs for large swarms; exported so a row-block-sharded caller can compose them.
+ *   scales : device buffer of 8 + Cp floats: {alpha_S, alpha_S^-2, alpha_G, 0, <4 words scratch>,
+ *            colscale[Cp]}, filled by sigsvgd_tc_scales
+ *   planes : fp16 row-major, row pitch (elements) a multiple of 8, 16-byte aligned
+ *   F      : [ (S - mean)*alpha_S | 1 | score*alpha_G | 0.. ]   Cp = round_up(D + 1 + P, 8) columns
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_tc_available(void);
+int sigsvgd_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, int64_t D,
+                      const float* score, int64_t ld_score, int64_t P, int64_t Cp, float* scales,
+                      void* stream);
+int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float* s, int64_t lds,
+                    const float* mean, int64_t N, int64_t D, const float* scales, void* f_hi,
+                    void* f_lo, int64_t ldp, int64_t Cp, float* norms, float* s_centred,
+                    int64_t ld_sc, void* stream);
+/* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
+ * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack. */
+int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
+                      const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
+                      int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,
+                      void* stream);
+/* K = exp(state->gamma * dist) (_kernels.py:110) written as planes of K*2^14 and, if k_out is not
+ * NULL, as fp32 (k_out may alias dist).  Accumulates sum_kd / ties like sigsvgd_rbf_apply. */
+int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
+                   sigsvgd_bw_state* state, void* k_hi, void* k_lo, int64_t ldp, float* k_out,
+                   int64_t ldk, void* stream);
+/* out[M,C] = K[M,N] . F[N,C] in unscaled units: [K.(S-mean) | rowsum(K) | K.score] (svgd.py:82, :43) */
+int sigsvgd_tc_matmul(const void* k_hi, const void* k_lo, int64_t ldk, const void* f_hi,
+                      const void* f_lo, int64_t ldf, int64_t M, int64_t N, int64_t C,
+                      const float* scales, float* out, int64_t ldo, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Fused single-GPU Stein update.  Replaces SVGD._compute_kernel + the arithmetic of
  * SVGD._velocity (src/inference/svgd.py:36-44, 82-83) for kernel = PathSigKernel(GaussianKernel):
  *   phi = ( K . score - grad_k ) / N ,   the reference's velocity is -phi.

@@ -82,6 +82,29 @@ _SIGNATURES = {
         [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64,
          c_void_p, c_void_p, c_int64, c_void_p],
     ),
+    "sigsvgd_tc_available": (c_int, []),
+    "sigsvgd_tc_scales": (
+        c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
+    "sigsvgd_tc_pack": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+         c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p],
+    ),
+    "sigsvgd_tc_sqdist": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
+         c_void_p, c_void_p, c_int64, c_void_p],
+    ),
+    "sigsvgd_tc_rbf": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
+         c_void_p],
+    ),
+    "sigsvgd_tc_matmul": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
+         c_int64, c_void_p],
+    ),
     "sigsvgd_phi_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int, c_int]),
     "sigsvgd_phi": (
         c_int,

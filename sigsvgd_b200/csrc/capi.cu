@@ -34,8 +34,10 @@ int num_sms() {
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 struct PhiLayout {
-  int64_t D, P, C;
-  size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, off_tc, total;
+  int64_t D, P, C, Np;
+  size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, total;
+  // tensor-core path (B == 1): fp16 planes of F [N x C] and K [N x Np], norms, scales
+  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales;
 };
 
 static size_t bump(size_t* cur, size_t bytes) {
@@ -49,7 +51,7 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   PhiLayout L;
   L.D = sig_channels(d, depth);
   L.P = T * d;
-  L.C = round_up(L.P + L.D + 1, 8);
+  L.C = round_up(L.P + L.D + 1, 8);  // columns of V / F (row pitch of the planes)
   size_t cur = 0;
   L.off_sig = want_sig ? 0 : bump(&cur, sizeof(float) * B * N * L.D);
   L.off_v = bump(&cur, sizeof(float) * B * N * L.C);
@@ -59,9 +61,27 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   L.off_mean = bump(&cur, sizeof(float) * B * L.D);
   L.off_part = bump(&cur, sizeof(float) * B * 64 * L.D);
   L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
-  L.off_tc = bump(&cur, tc_workspace_bytes(B, N, L.D, L.C));
+  L.Np = round_up(N, 8);
+  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = 0;
+  if (B == 1) {
+    L.off_fh = bump(&cur, sizeof(__half) * N * L.C);
+    L.off_fl = bump(&cur, sizeof(__half) * N * L.C);
+    L.off_kh = bump(&cur, sizeof(__half) * N * L.Np);
+    L.off_kl = bump(&cur, sizeof(__half) * N * L.Np);
+    L.off_norms = bump(&cur, sizeof(float) * N);
+    L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
+  }
   L.total = cur;
   return L;
+}
+
+// The tcgen05 path serves one swarm (B == 1) whose N^2 work dwarfs the fixed costs; small swarms
+// and batches of small scenes stay on the exact-fp32 SIMT kernels (launch-bound regime).
+static bool tc_path_enabled(int64_t B, int64_t N, uint32_t flags) {
+  if (flags & SIGSVGD_FLAG_FORCE_SIMT) return false;
+  if (B != 1 || !tc_available()) return false;
+  if (flags & SIGSVGD_FLAG_FORCE_TC) return true;
+  return N >= 1024;
 }
 
 }  // namespace sigsvgd
@@ -96,7 +116,7 @@ int sigsvgd_sqdist(const float* a, int64_t lda, const float* b, int64_t ldb, int
                    int64_t D, float* dist, int64_t ldd, uint32_t flags, void* stream) {
   SIG_CHECK_ARG((M == 0 || N == 0) || (a && b && dist), "sqdist: NULL pointer");
   if (flags & SIGSVGD_FLAG_FORCE_TC) {
-    set_error("sqdist: the tcgen05 path needs packed operands; use sigsvgd_phi");
+    set_error("sqdist: the tcgen05 path takes fp16 planes; use sigsvgd_tc_sqdist");
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   return launch_sqdist_simt(a, lda, b, ldb, M, N, D, dist, ldd, 1, 0, 0, 0, (cudaStream_t)stream);
@@ -156,7 +176,7 @@ int sigsvgd_matmul_nn(const float* a, int64_t lda, const float* v, int64_t ldv, 
                       int64_t N, int64_t C, float* out, int64_t ldo, uint32_t flags, void* stream) {
   SIG_CHECK_ARG(M == 0 || (a && v && out), "matmul_nn: NULL pointer");
   if (flags & SIGSVGD_FLAG_FORCE_TC) {
-    set_error("matmul_nn: the tcgen05 path needs packed operands; use sigsvgd_phi");
+    set_error("matmul_nn: the tcgen05 path takes fp16 planes; use sigsvgd_tc_matmul");
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   return launch_gemm_nn_simt(a, lda, v, ldv, M, N, C, out, ldo, 1, 0, 0, 0, (cudaStream_t)stream);
@@ -181,6 +201,53 @@ int sigsvgd_sig_grad(const float* sc, int64_t lds, const float* sc_all, int64_t 
   SIG_CHECK_ARG(state && (M == 0 || (sc && sc_all && ks && rowsum && g)), "sig_grad: NULL pointer");
   return launch_sig_grad(sc, lds, sc_all, lds_all, ks, ldks, rowsum, ldr, M, D, 0, row_offset,
                          state, g, ldg, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_available(void) { return tc_available() ? 1 : 0; }
+
+int sigsvgd_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, int64_t D,
+                      const float* score, int64_t ld_score, int64_t P, int64_t Cp, float* scales,
+                      void* stream) {
+  SIG_CHECK_ARG(s && scales, "tc_scales: NULL pointer");
+  return launch_tc_scales(s, lds, mean, N, D, score, ld_score, P, Cp, (unsigned int*)(scales + 4),
+                          scales, scales + 8, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float* s, int64_t lds,
+                    const float* mean, int64_t N, int64_t D, const float* scales, void* f_hi,
+                    void* f_lo, int64_t ldp, int64_t Cp, float* norms, float* s_centred,
+                    int64_t ld_sc, void* stream) {
+  SIG_CHECK_ARG(s && scales && f_hi && f_lo, "tc_pack: NULL pointer");
+  SIG_CHECK_ARG(aligned16(f_hi) && aligned16(f_lo), "tc_pack: planes must be 16-byte aligned");
+  return launch_tc_pack(score, ld_score, P, s, lds, mean, N, D, scales, (__half*)f_hi, (__half*)f_lo,
+                        ldp, Cp, norms, s_centred, ld_sc, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
+                      const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
+                      int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,
+                      void* stream) {
+  SIG_CHECK_ARG(a_hi && a_lo && b_hi && b_lo && na && nb && scales && dist, "tc_sqdist: NULL pointer");
+  return tc_sqdist(TcPlanes{(const __half*)a_hi, (const __half*)a_lo, lda},
+                   TcPlanes{(const __half*)b_hi, (const __half*)b_lo, ldb}, M, N, D, na, nb,
+                   scales + 1, dist, ldd, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
+                   sigsvgd_bw_state* state, void* k_hi, void* k_lo, int64_t ldp, float* k_out,
+                   int64_t ldk, void* stream) {
+  SIG_CHECK_ARG(state && (M == 0 || (dist && k_hi && k_lo)), "tc_rbf: NULL pointer");
+  return launch_tc_rbf(dist, ldd, M, N, row_offset, state, (__half*)k_hi, (__half*)k_lo, ldp, k_out,
+                       ldk, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_matmul(const void* k_hi, const void* k_lo, int64_t ldk, const void* f_hi,
+                      const void* f_lo, int64_t ldf, int64_t M, int64_t N, int64_t C,
+                      const float* scales, float* out, int64_t ldo, void* stream) {
+  SIG_CHECK_ARG(k_hi && k_lo && f_hi && f_lo && scales && out, "tc_matmul: NULL pointer");
+  return tc_matmul_nn(TcPlanes{(const __half*)k_hi, (const __half*)k_lo, ldk},
+                      TcPlanes{(const __half*)f_hi, (const __half*)f_lo, ldf}, M, N, C, scales + 8,
+                      out, ldo, (cudaStream_t)stream);
 }
 
 size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, int depth,
@@ -219,26 +286,42 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
   float* mean = (float*)(w + L.off_mean);
   float* part = (float*)(w + L.off_part);
   void* selws = (void*)(w + L.off_sel);
-  void* tcws = (void*)(w + L.off_tc);
   const int64_t D = L.D, P = L.P, C = L.C, R = B * N;
   const bool center = !(flags & SIGSVGD_FLAG_NO_CENTER);
+  const bool use_tc = tc_path_enabled(B, N, flags);
+  if ((flags & SIGSVGD_FLAG_FORCE_TC) && !use_tc) {
+    set_error("phi: tcgen05 path not available for B=%lld N=%lld", (long long)B, (long long)N);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  __half* Fh = (__half*)(w + L.off_fh);
+  __half* Fl = (__half*)(w + L.off_fl);
+  __half* Kh = (__half*)(w + L.off_kh);
+  __half* Kl = (__half*)(w + L.off_kl);
+  float* norms = (float*)(w + L.off_norms);
+  float* scales = (float*)(w + L.off_scales);
 
   // K1: signatures of all B*N particles
   SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
-  // centre + pack V = [score | S - mean | 1]
   if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
-  SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
-
-  const bool use_tc = tc_path_enabled(B, N, D, C, flags);
-  if ((flags & SIGSVGD_FLAG_FORCE_TC) && !use_tc) {
-    set_error("phi: tcgen05 path not available for B=%lld N=%lld D=%lld", (long long)B,
-              (long long)N, (long long)D);
-    return SIGSVGD_ERR_UNSUPPORTED;
-  }
-  // K3: squared distances into the K buffer
+  // feature block (centred), its row pitch, and the [K.S | rowsum | K.score] blocks of `out`
+  const float* feat;
+  int64_t ldf;
+  const float *out_ks, *out_rowsum, *out_kg;
   if (use_tc) {
-    SIG_PROPAGATE(tc_pack_and_sqdist(V, C, P, N, D, K, tcws, st));
+    // planes F = [S - mean | 1 | score] (fp16 hi/lo), centred fp32 features in the V buffer
+    SIG_PROPAGATE(launch_tc_scales(sig, D, center ? mean : nullptr, N, D, score, P, P, C,
+                                   (unsigned int*)(scales + 4), scales, scales + 8, 1, st));
+    SIG_PROPAGATE(launch_tc_pack(score, P, P, sig, D, center ? mean : nullptr, N, D, scales, Fh, Fl,
+                                 C, C, norms, V, D, 1, st));
+    feat = V, ldf = D;
+    out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
+    // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product)
+    SIG_PROPAGATE(tc_sqdist(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
+                            scales + 1, K, N, st));
   } else {
+    SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
+    feat = V + P, ldf = C;
+    out_kg = out, out_ks = out + P, out_rowsum = out + P + D;
     SIG_PROPAGATE(launch_sqdist_simt(V + P, C, V + P, C, N, N, D, K, N, B, N * C, N * C, N * N, st));
   }
   // K4: bandwidth
@@ -248,23 +331,26 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
   } else {
     SIG_PROPAGATE(launch_fixed_bandwidth(h_fixed, state, B, st));
   }
-  // K5: K = exp(gamma d) in place, then one contraction K.[score | S | 1]
-  SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));
-  SIG_PROPAGATE(launch_median_coef(
-      state, nullptr, nullptr,
-      (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0, B, st));
+  // K5: K = exp(gamma d), then one contraction K.[S | 1 | score]
+  const int median_grad =
+      (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0;
   if (use_tc) {
-    SIG_PROPAGATE(tc_matmul_kv(K, N, V, C, N, C, out, C, tcws, st));
+    SIG_PROPAGATE(launch_tc_rbf(K, N, N, N, 0, state, Kh, Kl, L.Np, k_out ? K : nullptr, N, st));
+    SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
+    SIG_PROPAGATE(tc_matmul_nn(TcPlanes{Kh, Kl, L.Np}, TcPlanes{Fh, Fl, C}, N, N, D + 1 + P,
+                               scales + 8, out, C, st));
   } else {
+    SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));
+    SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, B, st));
     SIG_PROPAGATE(launch_gemm_nn_simt(K, N, V, C, N, N, C, out, C, B, N * N, N * C, N * C, st));
   }
   // sig-space gradient, then K2 with the fused epilogue phi = (K.score - grad_k)/N
-  SIG_PROPAGATE(launch_sig_grad(V + P, C, V + P, C, out + P, C, out + P + D, C, N, D, N, 0, state,
+  SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,
                                 g, D, B, st));
   if (gradk_out)
     SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st));
   const float inv_n = 1.f / (float)N;
-  SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out, C, inv_n, -inv_n, phi, st));
+  SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st));
   return 0;
 }
 

@@ -1,18 +1,54 @@
 // tcgen05 / TMA tensor-core path for the two N^2 contractions (declared here, gemm_tc.cu).
+//
+// fp32-grade accuracy on the fp16 tensor pipe: every fp32 operand x is held as two fp16 "planes"
+//   x * alpha = hi + lo ,  hi = fp16(x*alpha), lo = fp16(x*alpha - hi)       (alpha = power of two)
+// and a product is accumulated as  hi.hi + hi.lo + lo.hi  in fp32 TMEM accumulators (3 MMAs of
+// kind::f16 per fp32 product; the dropped lo.lo term is 2^-22 relative).  See DESIGN.md.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace sigsvgd {
 
-// bytes of scratch the tensor-core path needs inside the phi workspace
-size_t tc_workspace_bytes(int64_t B, int64_t N, int64_t D, int64_t C);
-// true when the tcgen05 kernels handle this problem (else the SIMT fp32 kernels run)
-bool tc_path_enabled(int64_t B, int64_t N, int64_t D, int64_t C, uint32_t flags);
-// split V's feature block into fp16 hi/lo planes and write dist[N,N] = pairwise sq. distances
-int tc_pack_and_sqdist(const float* V, int64_t ldv, int64_t P, int64_t N, int64_t D, float* dist,
-                       void* tcws, cudaStream_t st);
-// out[N,C] = K[N,N] . V[N,C] with both operands split into fp16 hi/lo planes
-int tc_matmul_kv(const float* K, int64_t ldk, const float* V, int64_t ldv, int64_t N, int64_t C,
-                 float* out, int64_t ldo, void* tcws, cudaStream_t st);
+// fp16 hi/lo planes of a row-major matrix: element (r, c) at hi[r*ld + c], lo[r*ld + c].
+// ld (elements) must be a multiple of 8 and both pointers 16-byte aligned (TMA constraints).
+struct TcPlanes {
+  const __half* hi;
+  const __half* lo;
+  int64_t ld;
+};
+
+// dist[i,j] = max(0, (na[i] + nb[j] - 2 * sum_c A[i,c] B[j,c]) * scal[0])   i < M, j < N, c < D
+//   A, B: planes [M x >=D], [N x >=D] (features along the row: K-major for both operands)
+//   na, nb: squared row norms in plane units; scal: DEVICE pointer, scal[0] = alpha^-2
+int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
+              const float* nb, const float* scal, float* dist, int64_t ldd, cudaStream_t st);
+
+// out[i,c] = colscale[c] * sum_j A[i,j] V[j,c]      i < M, j < K, c < C
+//   A: planes [M x >=K] (K-major), V: planes [K x >=C] (the contraction index is the ROW of V:
+//   MN-major B operand), colscale: DEVICE vector [C] undoing the plane scalings
+int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
+                 float* out, int64_t ldo, cudaStream_t st);
+
+// true when this process can create TMA descriptors (driver entry point resolved)
+bool tc_available();
+
+// ---- operand preparation (planes.cu) ---------------------------------------------------------
+// per problem b: tcs[4b..] = {alpha_S, alpha_S^-2, alpha_G, 0}; colscale[b*Cp + c]; mx: 2 uints
+int launch_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, int64_t D,
+                     const float* score, int64_t lsc, int64_t P, int64_t Cp, unsigned int* mx,
+                     float* tcs, float* colscale, int64_t batch, cudaStream_t st);
+// F = [ (s - mean)*alpha_S | 1 | score*alpha_G | 0.. ] -> planes fh/fl [rows x ldp];
+// norms[row] = |F_S|^2 (plane units, may be NULL); sc (optional) = centred fp32 features
+int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, int64_t lds,
+                   const float* mean, int64_t N, int64_t D, const float* tcs, __half* fh, __half* fl,
+                   int64_t ldp, int64_t Cp, float* norms, float* sc, int64_t ldsc, int64_t batch,
+                   cudaStream_t st);
+// K = exp(gamma d) as planes of K*2^14 (+ optional fp32 K into kout, may alias d);
+// accumulates state->sum_kd, records median ties (global row = row_offset + i)
+int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
+                  sigsvgd_bw_state* state, __half* kh, __half* kl, int64_t ldp, float* kout,
+                  int64_t ldk, cudaStream_t st);
 
 }  // namespace sigsvgd

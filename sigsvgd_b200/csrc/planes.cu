@@ -1,0 +1,277 @@
+// Operand preparation for the split-fp16 tensor-core GEMMs (gemm_tc.cu): power-of-two scaling,
+// hi/lo fp16 planes, row norms, and the RBF map that writes K directly as planes.
+//
+//   tc_scales   : alpha_S, alpha_G (powers of two placing the largest |value| in [2^13, 2^14)),
+//                 alpha_S^-2 for the distance epilogue, colscale[] for the K.V epilogue
+//   tc_pack     : F = [ (S - mean)*alpha_S | 1 | score*alpha_G | 0.. ] as fp16 hi/lo planes,
+//                 |F_S|^2 row norms (plane units), and the centred fp32 features
+//   tc_rbf      : K = exp(gamma d) -> hi/lo planes of K*2^14 (+ optional fp32 K, sum K*d, ties)
+//                 reference: src/kernels/_kernels.py:110
+#include "gemm_tc.cuh"
+
+namespace sigsvgd {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr float kKScale = 16384.f;  // 2^14: K in [0,1] -> [0, 2^14]
+
+__device__ __forceinline__ void split_half(float x, __half& hi, __half& lo) {
+  hi = __float2half_rn(x);
+  lo = __float2half_rn(x - __half2float(hi));
+}
+
+// mx[b*2+0] = max |s - mean| over [N,D], mx[b*2+1] = max |score| over [N,P]   (float bits, >= 0)
+__global__ void __launch_bounds__(kThreads)
+absmax_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ mean, int64_t N,
+              int64_t D, const float* __restrict__ score, int64_t lsc, int64_t P,
+              unsigned int* __restrict__ mx) {
+  const int b = blockIdx.y;
+  const int64_t W = D + P;
+  const int64_t total = N * W;
+  float ms = 0.f, mg = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * kThreads) {
+    const int64_t r = i / W, c = i - r * W;
+    const int64_t row = (int64_t)b * N + r;
+    if (c < D) {
+      float v = __ldg(s + row * lds + c);
+      if (mean) v -= __ldg(mean + (int64_t)b * D + c);
+      ms = fmaxf(ms, fabsf(v));
+    } else {
+      mg = fmaxf(mg, fabsf(__ldg(score + row * lsc + (c - D))));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    ms = fmaxf(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+    mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    // NaN/inf inputs propagate through the GEMM anyway; the scale only needs finite maxima
+    if (ms > 0.f && ms < INFINITY) atomicMax(mx + 2 * b, __float_as_uint(ms));
+    if (mg > 0.f && mg < INFINITY) atomicMax(mx + 2 * b + 1, __float_as_uint(mg));
+  }
+}
+
+__device__ __forceinline__ float pow2_scale(float m) {
+  if (!(m > 0.f)) return 1.f;
+  int e = ilogbf(m);  // m in [2^e, 2^(e+1))
+  e = max(-100, min(100, e));
+  return ldexpf(1.f, 13 - e);
+}
+
+// tcs[b*4 + {0,1,2,3}] = alpha_S, alpha_S^-2, alpha_G, 0 ; colscale[b*Cp + c]
+__global__ void __launch_bounds__(kThreads)
+scales_kernel(const unsigned int* __restrict__ mx, int64_t D, int64_t P, int64_t Cp,
+              float* __restrict__ tcs, float* __restrict__ colscale) {
+  const int b = blockIdx.x;
+  const float as = pow2_scale(__uint_as_float(mx[2 * b]));
+  const float ag = pow2_scale(__uint_as_float(mx[2 * b + 1]));
+  if (threadIdx.x == 0) {
+    tcs[4 * b + 0] = as;
+    tcs[4 * b + 1] = (1.f / as) * (1.f / as);
+    tcs[4 * b + 2] = ag;
+    tcs[4 * b + 3] = 0.f;
+  }
+  for (int64_t c = threadIdx.x; c < Cp; c += kThreads) {
+    float v = 0.f;
+    if (c < D) v = 1.f / (kKScale * as);
+    else if (c == D) v = 1.f / kKScale;
+    else if (c < D + 1 + P) v = 1.f / (kKScale * ag);
+    colscale[(int64_t)b * Cp + c] = v;
+  }
+}
+
+// one warp per row
+__global__ void __launch_bounds__(kThreads)
+pack_planes_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
+                   const float* __restrict__ s, int64_t lds, const float* __restrict__ mean,
+                   int64_t N, int64_t D, const float* __restrict__ tcs, __half* __restrict__ fh,
+                   __half* __restrict__ fl, int64_t ldp, int64_t Cp, float* __restrict__ norms,
+                   float* __restrict__ sc, int64_t ldsc, int64_t rows_total) {
+  const int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows_total) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t b = row / N;
+  const float as = tcs[4 * b], ag = tcs[4 * b + 2];
+  const float* __restrict__ mrow = mean ? mean + b * D : nullptr;
+  float nrm = 0.f;
+  for (int64_t c0 = 2 * lane; c0 < Cp; c0 += 64) {
+    float x[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int64_t c = c0 + e;
+      float v = 0.f;
+      if (c < D) {
+        v = __ldg(s + row * lds + c);
+        if (mrow) v -= __ldg(mrow + c);
+        if (sc) sc[row * ldsc + c] = v;
+        v *= as;
+      } else if (c == D) {
+        v = 1.f;
+      } else if (c < D + 1 + P) {
+        v = __ldg(score + row * lsc + (c - D - 1)) * ag;
+      }
+      x[e] = v;
+    }
+    __half h0, l0, h1, l1;
+    split_half(x[0], h0, l0);
+    split_half(x[1], h1, l1);
+    if (c0 < D) {
+      const float r0 = __half2float(h0) + __half2float(l0);
+      nrm = fmaf(r0, r0, nrm);
+    }
+    if (c0 + 1 < D) {
+      const float r1 = __half2float(h1) + __half2float(l1);
+      nrm = fmaf(r1, r1, nrm);
+    }
+    *reinterpret_cast<__half2*>(fh + row * ldp + c0) = __halves2half2(h0, h1);
+    *reinterpret_cast<__half2*>(fl + row * ldp + c0) = __halves2half2(l0, l1);
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+  if (lane == 0 && norms) norms[row] = nrm;
+}
+
+__device__ __forceinline__ double block_sum_double(double v, double* sm) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[w] = v;
+  __syncthreads();
+  double s = 0.0;
+  if (threadIdx.x == 0)
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += sm[i];
+  return s;
+}
+
+// grid: (col blocks, row blocks); each thread handles 4 consecutive columns of `rows_per_block` rows
+__global__ void __launch_bounds__(kThreads)
+rbf_planes_kernel(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
+                  sigsvgd_bw_state* __restrict__ state, __half* __restrict__ kh,
+                  __half* __restrict__ kl, int64_t ldp, float* kout, int64_t ldk,
+                  int rows_per_block) {
+  __shared__ double red[kThreads / 32];
+  sigsvgd_bw_state& s = *state;
+  const float gamma = s.gamma;
+  const uint32_t med_bits = __float_as_uint(s.median);
+  const bool track_ties = s.median > 0.f;
+  const int64_t c0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  const bool vec_in = ((ldd & 3) == 0) && ((reinterpret_cast<uintptr_t>(d) & 15u) == 0) && (c0 + 3 < N);
+  const bool vec_out = kout && ((ldk & 3) == 0) && ((reinterpret_cast<uintptr_t>(kout) & 15u) == 0) && (c0 + 3 < N);
+  const int64_t r_begin = (int64_t)blockIdx.y * rows_per_block;
+  const int64_t r_end = min(M, r_begin + rows_per_block);
+  double acc = 0.0;
+  if (c0 < ldp) {  // planes are written up to their padded pitch (zeros beyond N)
+    for (int64_t r = r_begin; r < r_end; ++r) {
+      float dv[4], kv[4];
+      const float* row = d + r * ldd + c0;
+      const int nv = (int)max((int64_t)0, min((int64_t)4, N - c0));
+      if (vec_in) {
+        const float4 q = *reinterpret_cast<const float4*>(row);
+        dv[0] = q.x, dv[1] = q.y, dv[2] = q.z, dv[3] = q.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) dv[e] = e < nv ? row[e] : 0.f;
+      }
+      float part = 0.f;
+      __half h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        kv[e] = e < nv ? expf(gamma * dv[e]) : 0.f;
+        if (e < nv) {
+          part = fmaf(kv[e], dv[e], part);
+          if (track_ties && (__float_as_uint(dv[e]) & 0x7fffffffu) == med_bits) {
+            const uint32_t slot = atomicAdd(&s.n_ties, 1u);
+            if (slot < SIGSVGD_MAX_TIES) {
+              s.ties[2 * slot] = (int32_t)(row_offset + r);
+              s.ties[2 * slot + 1] = (int32_t)(c0 + e);
+            }
+          }
+        }
+        split_half(kv[e] * kKScale, h[e], l[e]);
+      }
+      acc += (double)part;
+      // ldp is a multiple of 8 and c0 a multiple of 4: 8-byte aligned plane stores
+      {
+        __half2 a = __halves2half2(h[0], h[1]), b2 = __halves2half2(h[2], h[3]);
+        __half2 c = __halves2half2(l[0], l[1]), e2 = __halves2half2(l[2], l[3]);
+        uint2 uh, ul;
+        uh.x = *reinterpret_cast<uint32_t*>(&a);
+        uh.y = *reinterpret_cast<uint32_t*>(&b2);
+        ul.x = *reinterpret_cast<uint32_t*>(&c);
+        ul.y = *reinterpret_cast<uint32_t*>(&e2);
+        *reinterpret_cast<uint2*>(kh + r * ldp + c0) = uh;
+        *reinterpret_cast<uint2*>(kl + r * ldp + c0) = ul;
+      }
+      if (kout) {
+        float* orow = kout + r * ldk + c0;
+        if (vec_out) {
+          *reinterpret_cast<float4*>(orow) = make_float4(kv[0], kv[1], kv[2], kv[3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e < nv) orow[e] = kv[e];
+        }
+      }
+    }
+  }
+  const double tot = block_sum_double(acc, red);
+  if (threadIdx.x == 0 && tot != 0.0) atomicAdd(&s.sum_kd, tot);
+}
+
+}  // namespace
+
+int launch_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, int64_t D,
+                     const float* score, int64_t lsc, int64_t P, int64_t Cp, unsigned int* mx,
+                     float* tcs, float* colscale, int64_t batch, cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && (P == 0 || (score && lsc >= P)) &&
+                    Cp >= D + 1 + P && batch >= 1 && batch <= 65535,
+                "tc_scales: bad shape N=%lld D=%lld P=%lld Cp=%lld", (long long)N, (long long)D,
+                (long long)P, (long long)Cp);
+  SIG_CUDA_OK(cudaMemsetAsync(mx, 0, sizeof(unsigned int) * 2 * batch, st));
+  const int64_t want = ceil_div(N * (D + P), (int64_t)kThreads * 8);
+  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)num_sms() * 8));
+  absmax_kernel<<<dim3((unsigned)gx, (unsigned)batch), kThreads, 0, st>>>(s, lds, mean, N, D, score,
+                                                                        lsc, P, mx);
+  SIG_LAUNCH_OK("absmax_kernel");
+  scales_kernel<<<(unsigned)batch, kThreads, 0, st>>>(mx, D, P, Cp, tcs, colscale);
+  SIG_LAUNCH_OK("scales_kernel");
+  return 0;
+}
+
+int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, int64_t lds,
+                   const float* mean, int64_t N, int64_t D, const float* tcs, __half* fh, __half* fl,
+                   int64_t ldp, int64_t Cp, float* norms, float* sc, int64_t ldsc, int64_t batch,
+                   cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && Cp >= D + 1 + P && ldp >= Cp &&
+                    (Cp & 7) == 0 && (ldp & 7) == 0 && (sc == nullptr || ldsc >= D),
+                "tc_pack: bad shape N=%lld D=%lld P=%lld Cp=%lld ldp=%lld", (long long)N,
+                (long long)D, (long long)P, (long long)Cp, (long long)ldp);
+  SIG_CHECK_ARG(P == 0 || (score != nullptr && lsc >= P), "tc_pack: score is NULL but P > 0");
+  const int64_t rows = batch * N;
+  pack_planes_kernel<<<(unsigned)ceil_div(rows, kThreads / 32), kThreads, 0, st>>>(
+      score, lsc, P, s, lds, mean, N, D, tcs, fh, fl, ldp, Cp, norms, sc, ldsc, rows);
+  SIG_LAUNCH_OK("pack_planes_kernel");
+  return 0;
+}
+
+int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
+                  sigsvgd_bw_state* state, __half* kh, __half* kl, int64_t ldp, float* kout,
+                  int64_t ldk, cudaStream_t st) {
+  SIG_CHECK_ARG(M >= 0 && N >= 1 && ldd >= N && ldp >= N && (ldp & 7) == 0 && (kout == nullptr || ldk >= N),
+                "tc_rbf: bad shape M=%lld N=%lld ldd=%lld ldp=%lld", (long long)M, (long long)N,
+                (long long)ldd, (long long)ldp);
+  if (M == 0) return 0;
+  const int64_t gx = ceil_div(ldp, (int64_t)kThreads * 4);
+  int64_t gy = std::min<int64_t>(65535, std::max<int64_t>(1, ceil_div((int64_t)num_sms() * 16, gx)));
+  gy = std::min(gy, M);
+  const int rows_per_block = (int)ceil_div(M, gy);
+  gy = ceil_div(M, rows_per_block);
+  rbf_planes_kernel<<<dim3((unsigned)gx, (unsigned)gy), kThreads, 0, st>>>(
+      d, ldd, M, N, row_offset, state, kh, kl, ldp, kout, ldk, rows_per_block);
+  SIG_LAUNCH_OK("rbf_planes_kernel");
+  return 0;
+}
+
+}  // namespace sigsvgd

@@ -182,6 +182,71 @@ def matmul_nn_raw(a: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
     return out
 
 
+# ---- tensor-core building blocks (tcgen05 split-fp16 path) ----------------------------------
+@dataclass
+class Planes:
+    """fp16 hi/lo planes of a scaled fp32 matrix (see include/sigsvgd_b200.h)."""
+
+    hi: torch.Tensor
+    lo: torch.Tensor
+
+    @property
+    def ld(self) -> int:
+        return self.hi.stride(0)
+
+
+def tc_available() -> bool:
+    return bool(_lib.load().sigsvgd_tc_available())
+
+
+def tc_pack_raw(s: torch.Tensor, mean: Optional[torch.Tensor], score: Optional[torch.Tensor] = None):
+    """-> (F planes [N, Cp], norms [N], scales [8 + Cp], centred fp32 features [N, D])."""
+    N, D = s.shape
+    P = 0 if score is None else score.shape[1]
+    Cp = (D + 1 + P + 7) // 8 * 8
+    dev = s.device
+    scales = torch.empty(8 + Cp, dtype=torch.float32, device=dev)
+    call("sigsvgd_tc_scales", _p(s), s.stride(0), _p(mean), N, D, _p(score), 0 if score is None else score.stride(0), P,
+         Cp, _p(scales), _stream())
+    fh = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+    fl = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+    norms = torch.empty(N, dtype=torch.float32, device=dev)
+    sc = torch.empty(N, D, dtype=torch.float32, device=dev)
+    call("sigsvgd_tc_pack", _p(score), 0 if score is None else score.stride(0), P, _p(s), s.stride(0), _p(mean), N, D,
+         _p(scales), _p(fh), _p(fl), Cp, Cp, _p(norms), _p(sc), D, _stream())
+    return Planes(fh, fl), norms, scales, sc
+
+
+def tc_sqdist_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int, scales: torch.Tensor,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    M, N = a.hi.shape[0], b.hi.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=a.hi.device)
+    call("sigsvgd_tc_sqdist", _p(a.hi), _p(a.lo), a.ld, _p(na), _p(b.hi), _p(b.lo), b.ld, _p(nb), M, N, D, _p(scales),
+         _p(out), out.stride(0), _stream())
+    return out
+
+
+def tc_rbf_raw(dist: torch.Tensor, state: torch.Tensor, row_offset: int = 0, want_k: bool = False):
+    """-> (K planes [M, Np]); if want_k, ``dist`` is overwritten with the fp32 kernel values."""
+    M, N = dist.shape
+    Np = (N + 7) // 8 * 8
+    kh = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
+    kl = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
+    call("sigsvgd_tc_rbf", _p(dist), dist.stride(0), M, N, row_offset, _p(state), _p(kh), _p(kl), Np,
+         _p(dist) if want_k else None, dist.stride(0), _stream())
+    return Planes(kh, kl)
+
+
+def tc_matmul_raw(k: Planes, f: Planes, N: int, C: int, scales: torch.Tensor) -> torch.Tensor:
+    """out [M, Cp] = K[M, N] . F[N, :C] (columns >= C are not written)."""
+    M = k.hi.shape[0]
+    out = torch.zeros(M, f.hi.shape[1], dtype=torch.float32, device=k.hi.device)
+    call("sigsvgd_tc_matmul", _p(k.hi), _p(k.lo), k.ld, _p(f.hi), _p(f.lo), f.ld, M, N, C, _p(scales), _p(out),
+         out.stride(0), _stream())
+    return out
+
+
 def sig_grad_raw(sc, sc_all, ks, rowsum, state, row_offset: int = 0) -> torch.Tensor:
     """sc/sc_all/ks: 2-D views (features in the first D columns of ks.shape[1]); rowsum: 1-D view."""
     M, D = ks.shape

@@ -1,0 +1,97 @@
+"""GPU tests of the tcgen05 split-fp16 path (gemm_tc.cu / planes.cu) through the C ABI: each
+building block against float64 numpy, and the fused update forced onto the tensor-core path
+against the CPU oracle.  Tolerances as in tests/util.py (fp32-grade: the path must be as accurate
+as the fp32 SIMT kernels it replaces)."""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import TOL_H, TOL_K, TOL_PHI, closed_form_with_ties, make_paths, rel_max
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    from sigsvgd_b200 import _lib, ops
+
+DEV = "cuda:0"
+
+
+def cu(a):
+    return torch.as_tensor(np.ascontiguousarray(a), device=DEV)
+
+
+def test_tc_available():
+    assert ops.tc_available()
+
+
+@pytest.mark.parametrize("M,N,D,scale", [(128, 256, 64, 1.0), (130, 70, 17, 1.0), (300, 517, 399, 1e-3),
+                                         (1024, 1024, 399, 50.0), (257, 255, 65, 1.0), (64, 64, 14, 1.0)])
+def test_tc_sqdist_vs_float64(M, N, D, scale):
+    rng = np.random.default_rng(M + N + D)
+    # columns with very different magnitudes, like signature levels 1..3
+    colmag = np.exp(rng.uniform(-6, 0, size=D))
+    a = (rng.standard_normal((M, D)) * colmag * scale).astype(np.float32)
+    b = (rng.standard_normal((N, D)) * colmag * scale).astype(np.float32)
+    allrows = cu(np.concatenate([a, b]))
+    planes, norms, scales, sc = ops.tc_pack_raw(allrows, None)
+    assert torch.equal(sc, allrows)
+    pa = ops.Planes(planes.hi[:M], planes.lo[:M])
+    pb = ops.Planes(planes.hi[M:], planes.lo[M:])
+    got = ops.tc_sqdist_raw(pa, norms[:M], pb, norms[M:], D, scales).cpu().numpy()
+    a64, b64 = a.astype(np.float64), b.astype(np.float64)
+    ref = np.maximum((a64 ** 2).sum(1)[:, None] + (b64 ** 2).sum(1)[None] - 2 * a64 @ b64.T, 0)
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= 2e-6 * ref.max()
+    assert (got >= 0).all()
+
+
+@pytest.mark.parametrize("M,N,D,P", [(128, 128, 14, 20), (130, 200, 39, 27), (512, 512, 399, 448), (300, 1000, 399, 448), (128, 4100, 399, 448)])
+def test_tc_rbf_and_matmul_vs_float64(M, N, D, P):
+    rng = np.random.default_rng(M * 3 + N)
+    s = (rng.standard_normal((N, D)) * np.exp(rng.uniform(-5, 0, size=D))).astype(np.float32)
+    g = (rng.standard_normal((N, P)) * 30).astype(np.float32)
+    dist = (rng.random((M, N)) * 6).astype(np.float32)
+    dist[0, :3] = 0
+    mean = cu(s.mean(0).astype(np.float32))
+    planes, norms, scales, sc = ops.tc_pack_raw(cu(s), mean, cu(g))
+    state = ops.new_state(torch.device(DEV))
+    _lib.call("sigsvgd_fixed_bandwidth", 1.3, state.data_ptr(), ops._stream())
+    d_dev = cu(dist)
+    kpl = ops.tc_rbf_raw(d_dev, state, want_k=True)
+    K64 = np.exp(-0.5 / np.float64(np.float32(1.3)) ** 2 * dist.astype(np.float64))
+    assert np.abs(d_dev.cpu().numpy() - K64).max() <= 1e-6
+    rec = ops.read_state(state)
+    assert abs(rec["sum_kd"] - (K64 * dist).sum()) <= 1e-5 * (K64 * dist).sum()
+    C = D + 1 + P
+    out = ops.tc_matmul_raw(kpl, planes, N, C, scales).cpu().numpy()
+    sc64 = s.astype(np.float64) - mean.cpu().numpy().astype(np.float64)
+    ref = np.concatenate([K64 @ sc64, K64.sum(1, keepdims=True), K64 @ g.astype(np.float64)], axis=1)
+    for lo, hi in ((0, D), (D, D + 1), (D + 1, C)):
+        blk = ref[:, lo:hi]
+        # TMEM accumulation truncates (round toward zero): the bias grows with the chain length,
+        # which tc_matmul bounds at 192 MMAs per partial sum
+        assert np.abs(out[:, lo:hi] - blk).max() <= 1e-5 * np.abs(blk).max(), (lo, hi)
+
+
+@pytest.mark.parametrize("kind,N,T,d,depth", [("walk", 256, 64, 7, 3), ("panda", 256, 64, 7, 3), ("walk", 1000, 20, 7, 3),
+                                              ("field", 100, 10, 2, 3), ("walk", 1024, 64, 7, 3)])
+def test_phi_forced_tc_vs_oracle(kind, N, T, d, depth):
+    X = make_paths(kind, N, T, d, seed=3)
+    G = np.random.default_rng(4).standard_normal((N, T * d)).astype(np.float32)
+    res = ops.phi(cu(X), cu(G), depth=depth, want_k=True, want_grad_k=True, flags=_lib.FLAG_FORCE_TC)
+    rec = ops.read_state(res.state)
+    cf = closed_form_with_ties(X.astype(np.float64), G.astype(np.float64), depth, rec["ties"])
+    assert abs(rec["h"] - cf["h"]) <= TOL_H * cf["h"]
+    assert np.abs(res.k_xx.cpu().numpy() - cf["K"]).max() <= TOL_K
+    assert rel_max(res.grad_k.cpu().numpy(), cf["grad_k"]) <= TOL_PHI
+    assert rel_max(res.phi.cpu().numpy(), cf["phi"]) <= TOL_PHI
+    # the exact-fp32 SIMT path and the tensor-core path agree far inside the tolerance
+    simt = ops.phi(cu(X), cu(G), depth=depth, want_k=True, flags=_lib.FLAG_FORCE_SIMT,
+                   bandwidth=ops.Bandwidth.median(median_grad=False))
+    tc = ops.phi(cu(X), cu(G), depth=depth, want_k=True, flags=_lib.FLAG_FORCE_TC,
+                 bandwidth=ops.Bandwidth.median(median_grad=False))
+    assert float((simt.k_xx - tc.k_xx).abs().max()) <= 2e-5
+    assert rel_max(tc.phi.cpu().numpy(), simt.phi.cpu().numpy()) <= 2e-5
+    # K not requested: same phi
+    res2 = ops.phi(cu(X), cu(G), depth=depth, flags=_lib.FLAG_FORCE_TC)
+    assert rel_max(res2.phi.cpu().numpy(), res.phi.cpu().numpy()) <= 1e-6

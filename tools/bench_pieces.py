@@ -1,0 +1,61 @@
+"""Per-kernel CUDA-event timings of the phi-update pieces (development aid; run under gpurun)."""
+import sys, os, json
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from sigsvgd_b200 import _lib, ops
+
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+T, d, depth = 64, 7, 3
+dev = torch.device("cuda:0")
+g = torch.Generator().manual_seed(0)
+X = torch.cumsum(0.05 * torch.randn(N, T, d, generator=g), dim=1).to(dev)
+G = torch.randn(N, T * d, generator=g).to(dev)
+flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+
+
+def timeit(fn, n=20, warm=3, do_flush=True):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(n):
+        if do_flush:
+            flush.fill_(1.0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e3)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+D = ops.sig_channels(d, depth)
+P = T * d
+res = {}
+sig = ops.signature_fwd_raw(X, depth, True)
+res["sig_fwd"] = timeit(lambda: ops.signature_fwd_raw(X, depth, True))
+mean = ops.col_mean(sig)
+res["col_mean"] = timeit(lambda: ops.col_mean(sig))
+planes, norms, scales, sc = ops.tc_pack_raw(sig, mean, G)
+res["tc_pack(+scales)"] = timeit(lambda: ops.tc_pack_raw(sig, mean, G))
+dist = torch.empty(N, N, device=dev)
+res["tc_sqdist"] = timeit(lambda: ops.tc_sqdist_raw(planes, norms, planes, norms, D, scales, out=dist))
+res["tc_sqdist_noflush"] = timeit(lambda: ops.tc_sqdist_raw(planes, norms, planes, norms, D, scales, out=dist), do_flush=False)
+state = ops.bandwidth_raw(dist, ops.Bandwidth.median(), N)
+res["median_select"] = timeit(lambda: ops.bandwidth_raw(dist, ops.Bandwidth.median(), N, state))
+d2 = dist.clone()
+kpl = ops.tc_rbf_raw(d2, state)
+res["tc_rbf"] = timeit(lambda: ops.tc_rbf_raw(d2, state))
+out = ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)
+res["tc_matmul"] = timeit(lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales))
+res["tc_matmul_noflush"] = timeit(lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales), do_flush=False)
+gs = ops.sig_grad_raw(sc, sc, out[:, :D], out[:, D], state)
+res["sig_grad"] = timeit(lambda: ops.sig_grad_raw(sc, sc, out[:, :D], out[:, D], state))
+res["sig_bwd"] = timeit(lambda: ops.signature_bwd_raw(X, sig, gs, depth, True, add=out[:, D + 1:], alpha=1.0 / N, beta=-1.0 / N))
+res["phi_total"] = timeit(lambda: ops.phi(X, G, depth=depth))
+res["phi_total_noflush"] = timeit(lambda: ops.phi(X, G, depth=depth), do_flush=False)
+res["phi_simt"] = timeit(lambda: ops.phi(X, G, depth=depth, flags=_lib.FLAG_FORCE_SIMT), n=5)
+fl_gram, fl_kv = 2.0 * N * N * D, 2.0 * N * N * (D + P)
+res["TFLOPs_alg_sqdist"] = fl_gram / res["tc_sqdist"] / 1e6
+res["TFLOPs_alg_matmul"] = fl_kv / res["tc_matmul"] / 1e6
+print(json.dumps({"N": N, "us": res}, indent=1))

@@ -95,6 +95,16 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
          c_void_p, c_void_p, c_int64, c_void_p],
     ),
+    "sigsvgd_tc_gram": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
+         c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p],
+    ),
+    "sigsvgd_tc_median_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "sigsvgd_tc_median_prepare": (
+        c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "sigsvgd_tc_median_select": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p]),
     "sigsvgd_tc_rbf": (
         c_int,
         [c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,

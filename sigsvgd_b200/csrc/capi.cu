@@ -37,7 +37,7 @@ struct PhiLayout {
   int64_t D, P, C, Np;
   size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, total;
   // tensor-core path (B == 1): fp16 planes of F [N x C] and K [N x Np], norms, scales
-  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales;
+  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales, off_win;
 };
 
 static size_t bump(size_t* cur, size_t bytes) {
@@ -51,7 +51,9 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   PhiLayout L;
   L.D = sig_channels(d, depth);
   L.P = T * d;
-  L.C = round_up(L.P + L.D + 1, 8);  // columns of V / F (row pitch of the planes)
+  // columns of V / F = row pitch of the planes: 64 fp16 = 128 bytes, so every 128-byte TMA row
+  // segment is one aligned L2 line (misaligned rows double the L2 sector traffic)
+  L.C = round_up(L.P + L.D + 1, 64);
   size_t cur = 0;
   L.off_sig = want_sig ? 0 : bump(&cur, sizeof(float) * B * N * L.D);
   L.off_v = bump(&cur, sizeof(float) * B * N * L.C);
@@ -61,8 +63,8 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   L.off_mean = bump(&cur, sizeof(float) * B * L.D);
   L.off_part = bump(&cur, sizeof(float) * B * 64 * L.D);
   L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
-  L.Np = round_up(N, 8);
-  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = 0;
+  L.Np = round_up(N, 64);
+  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = L.off_win = 0;
   if (B == 1) {
     L.off_fh = bump(&cur, sizeof(__half) * N * L.C);
     L.off_fl = bump(&cur, sizeof(__half) * N * L.C);
@@ -70,6 +72,7 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
     L.off_kl = bump(&cur, sizeof(__half) * N * L.Np);
     L.off_norms = bump(&cur, sizeof(float) * N);
     L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
+    L.off_win = bump(&cur, window_workspace_bytes(N, N, nullptr));
   }
   L.total = cur;
   return L;
@@ -233,6 +236,46 @@ int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const flo
                    scales + 1, dist, ldd, (cudaStream_t)stream);
 }
 
+int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
+                    const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
+                    int64_t N, int64_t D, const float* scales, int symmetric, void* median_ws,
+                    float* dist, int64_t ldd, void* stream) {
+  SIG_CHECK_ARG(a_hi && a_lo && b_hi && b_lo && na && nb && scales && dist, "tc_gram: NULL pointer");
+  SelWindow* win = nullptr;
+  float* cand = nullptr;
+  if (median_ws) window_pointers(median_ws, &win, &cand);
+  return tc_gram(TcPlanes{(const __half*)a_hi, (const __half*)a_lo, lda},
+                 TcPlanes{(const __half*)b_hi, (const __half*)b_lo, ldb}, M, N, D, na, nb, scales + 1,
+                 symmetric, win, cand, dist, ldd, (cudaStream_t)stream);
+}
+
+size_t sigsvgd_tc_median_workspace_bytes(int64_t M, int64_t N) {
+  if (M < 1 || N < 1) return 0;
+  return window_workspace_bytes(M, N, nullptr);
+}
+
+int sigsvgd_tc_median_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,
+                              int64_t N, int64_t D, void* median_ws, size_t ws_bytes,
+                              sigsvgd_bw_state* state, void* stream) {
+  SIG_CHECK_ARG(a && b && median_ws && state, "tc_median_prepare: NULL pointer");
+  if (ws_bytes < window_workspace_bytes(M, N, nullptr)) {
+    set_error("tc_median_prepare: workspace too small");
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  SelWindow* win;
+  float* cand;
+  return launch_window_prepare(a, lda, M, b, ldb, N, D, median_ws, state, &win, &cand,
+                               (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
+                             int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                             void* stream) {
+  SIG_CHECK_ARG(median_ws && dist && state, "tc_median_select: NULL pointer");
+  return launch_window_select(median_ws, dist, M, N, ldd, n_log, bw_scale, tol, state,
+                              (cudaStream_t)stream);
+}
+
 int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
                    sigsvgd_bw_state* state, void* k_hi, void* k_lo, int64_t ldp, float* k_out,
                    int64_t ldk, void* stream) {
@@ -315,9 +358,15 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
                                  C, C, norms, V, D, 1, st));
     feat = V, ldf = D;
     out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
-    // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product)
-    SIG_PROPAGATE(tc_sqdist(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
-                            scales + 1, K, N, st));
+    // K4a: candidate window for the median from a sample of the matrix
+    SelWindow* win = nullptr;
+    float* cand = nullptr;
+    if (bw_mode == SIGSVGD_BW_MEDIAN)
+      SIG_PROPAGATE(launch_window_prepare(V, D, N, V, D, N, D, w + L.off_win, state, &win, &cand, st));
+    // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product; upper triangle
+    // mirrored), counting / collecting the median candidates on the way out
+    SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
+                          scales + 1, 1, win, cand, K, N, st));
   } else {
     SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
     feat = V + P, ldf = C;
@@ -325,7 +374,9 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
     SIG_PROPAGATE(launch_sqdist_simt(V + P, C, V + P, C, N, N, D, K, N, B, N * C, N * C, N * N, st));
   }
   // K4: bandwidth
-  if (bw_mode == SIGSVGD_BW_MEDIAN) {
+  if (bw_mode == SIGSVGD_BW_MEDIAN && use_tc) {
+    SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, N, N, bw_scale, tol, state, st));
+  } else if (bw_mode == SIGSVGD_BW_MEDIAN) {
     SIG_PROPAGATE(launch_median_select(K, N * N, B, N * N, N, bw_scale, tol, state, selws,
                                        select_workspace_bytes(N * N, B), st));
   } else {

@@ -24,7 +24,9 @@ constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
 constexpr uint32_t kBBytes = BN * BK * 2;   // 32 KB per plane
 constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // hi+lo of A and B: 96 KB
 constexpr uint32_t kBarBytes = 256;
-constexpr uint32_t kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+constexpr int kXposePitch = 33;                               // 32 x 32 transpose tile per epilogue warp
+constexpr uint32_t kXposeBytes = 4 * 32 * kXposePitch * 4;
+constexpr uint32_t kSmemBytes = kStages * kStageBytes + kBarBytes + kXposeBytes + 1024;  // + alignment slack
 constexpr uint32_t kTmemCols = 512;
 constexpr int kMaxChainKb = 16;
 
@@ -197,53 +199,45 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
       const uint32_t aph = (tcount >> 1) & 1u;
       ptx::mbar_wait(tfull_bar(a), aph);
       ptx::tc_fence_after();
-      const int64_t row = (int64_t)tm * BM + q * 32 + lane;
+      const int64_t row0 = (int64_t)tm * BM + q * 32;
+      const int64_t row = row0 + lane;
       const bool row_ok = row < p.M;
       float rv = 0.f;
       if constexpr (kEpi == EPI_SQDIST) rv = row_ok ? __ldg(p.row_vec + row) : 0.f;
-      float* __restrict__ orow = p.out + (row_ok ? row : 0) * p.ldo;
-      const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15u) == 0);
+      float* xp = reinterpret_cast<float*>(smem + kStages * kStageBytes + kBarBytes) + q * (32 * kXposePitch);
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int64_t col0 = (int64_t)tn * BN + c * 32;
         if (c * 32 >= wk.ncols || col0 >= p.N) break;  // warp-uniform
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * BN + c * 32, v);
+        const bool col_ok = col0 + lane < p.N;
+        const float cvl = col_ok ? __ldg(p.col_vec + col0 + lane) : 0.f;
         ptx::tmem_ld_wait();
-        float o[32];
+        // a thread owns one row in TMEM; transpose 32 x 32 through shared memory so that each
+        // store / red instruction covers 32 consecutive columns of one row (one 128-byte line)
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          const int64_t col = col0 + e;
-          const float cv = col < p.N ? __ldg(p.col_vec + col) : 0.f;
           const float acc = __uint_as_float(v[e]);
           if constexpr (kEpi == EPI_SQDIST) {
-            o[e] = fmaxf(fmaf(-2.f, acc, rv + cv) * scal0, 0.f);
+            const float cv = __shfl_sync(0xffffffffu, cvl, e);
+            xp[lane * kXposePitch + e] = fmaxf(fmaf(-2.f, acc, rv + cv) * scal0, 0.f);
           } else {
-            o[e] = acc * cv;
+            xp[lane * kXposePitch + e] = acc;
           }
         }
-        if (row_ok) {
-          if (accumulate_out) {
-            if (vec_ok && col0 + 32 <= p.N) {
-#pragma unroll
-              for (int e = 0; e < 32; e += 4)
-                atomicAdd(reinterpret_cast<float4*>(orow + col0 + e),
-                          make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]));
-            } else {
-#pragma unroll
-              for (int e = 0; e < 32; ++e)
-                if (col0 + e < p.N) atomicAdd(orow + col0 + e, o[e]);
-            }
-          } else if (vec_ok && col0 + 32 <= p.N) {
-#pragma unroll
-            for (int e = 0; e < 32; e += 4)
-              *reinterpret_cast<float4*>(orow + col0 + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
-          } else {
-#pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (col0 + e < p.N) orow[col0 + e] = o[e];
+        __syncwarp();
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+          if (row0 + r < p.M && col_ok) {
+            float val = xp[r * kXposePitch + lane];
+            if constexpr (kEpi == EPI_COLSCALE) val *= cvl;
+            float* dst = p.out + (row0 + r) * p.ldo + col0 + lane;
+            if (accumulate_out) atomicAdd(dst, val);
+            else *dst = val;
           }
         }
+        __syncwarp();
       }
       // all TMEM reads of this accumulator stage have completed (wait::ld above)
       ptx::tc_fence_before();
@@ -279,9 +273,11 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
+}  // namespace
+
 // fp16 matrix [outer x inner] with row pitch ld (elements); box = [box_outer x box_inner]
-int make_tmap(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer, int64_t ld,
-              uint32_t box_inner, uint32_t box_outer) {
+int make_tmap_f16(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer, int64_t ld,
+                  uint32_t box_inner, uint32_t box_outer) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -304,6 +300,13 @@ int make_tmap(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer,
     return SIGSVGD_ERR_CUDA;
   }
   return 0;
+}
+
+namespace {
+
+int make_tmap(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer, int64_t ld,
+              uint32_t box_inner, uint32_t box_outer) {
+  return make_tmap_f16(tm, base, inner, outer, ld, box_inner, box_outer);
 }
 
 template <bool kBMN, int kEpi>

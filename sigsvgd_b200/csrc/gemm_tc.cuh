@@ -19,11 +19,31 @@ struct TcPlanes {
   int64_t ld;
 };
 
+// Candidate window of the single-pass exact median (median_window.cu): while the distance matrix
+// is being written, entries below `lo` are counted and entries inside [lo, hi] are appended to a
+// candidate list; the order statistic is then selected among the candidates only.
+struct SelWindow {
+  float lo, hi;              // window bounds (sample quantiles bracketing the median)
+  unsigned int n_cand;       // candidates appended so far (may run past cap: overflow)
+  unsigned int cap;          // capacity of the candidate buffer
+  unsigned long long below;  // matrix entries < lo
+  unsigned int active;       // 0: no window (fixed bandwidth) -> epilogue skips the bookkeeping
+  unsigned int fallback;     // set by the select kernel when the window missed the median
+};
+
 // dist[i,j] = max(0, (na[i] + nb[j] - 2 * sum_c A[i,c] B[j,c]) * scal[0])   i < M, j < N, c < D
 //   A, B: planes [M x >=D], [N x >=D] (features along the row: K-major for both operands)
 //   na, nb: squared row norms in plane units; scal: DEVICE pointer, scal[0] = alpha^-2
 int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
               const float* nb, const float* scal, float* dist, int64_t ldd, cudaStream_t st);
+
+// Same distances with 128 x 128 tiles, separate TMEM accumulators for the hi.hi and the
+// correction products, and the median bookkeeping fused into the epilogue (win/cand may be NULL).
+// symmetric != 0: A and B are the same planes (M == N); only tiles on or above the diagonal are
+// computed, each is stored together with its transpose, and the diagonal is exactly 0.
+int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
+            const float* nb, const float* scal, int symmetric, SelWindow* win, float* cand,
+            float* dist, int64_t ldd, cudaStream_t st);
 
 // out[i,c] = colscale[c] * sum_j A[i,j] V[j,c]      i < M, j < K, c < C
 //   A: planes [M x >=K] (K-major), V: planes [K x >=C] (the contraction index is the ROW of V:
@@ -33,6 +53,20 @@ int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const 
 
 // true when this process can create TMA descriptors (driver entry point resolved)
 bool tc_available();
+
+// ---- single-pass exact median (median_window.cu) ---------------------------------------------
+// ws: window_workspace_bytes(M, N) bytes = [SelWindow | sample | histograms | candidates]
+size_t window_workspace_bytes(int64_t M, int64_t N, unsigned int* cap_out);
+void window_pointers(void* ws, SelWindow** win, float** cand);
+// sample the matrix (a, b: centred fp32 features of its rows / columns), set the window, reset
+// the counters and the selection fields of `state`
+int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,
+                          int64_t N, int64_t D, void* ws, sigsvgd_bw_state* state, SelWindow** win_out,
+                          float** cand_out, cudaStream_t st);
+// after tc_gram has filled dist + candidates: exact lower median -> state->{median,h,gamma,clamped}
+int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
+                         int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                         cudaStream_t st);
 
 // ---- operand preparation (planes.cu) ---------------------------------------------------------
 // per problem b: tcs[4b..] = {alpha_S, alpha_S^-2, alpha_G, 0}; colscale[b*Cp + c]; mx: 2 uints

@@ -203,7 +203,7 @@ def tc_pack_raw(s: torch.Tensor, mean: Optional[torch.Tensor], score: Optional[t
     """-> (F planes [N, Cp], norms [N], scales [8 + Cp], centred fp32 features [N, D])."""
     N, D = s.shape
     P = 0 if score is None else score.shape[1]
-    Cp = (D + 1 + P + 7) // 8 * 8
+    Cp = (D + 1 + P + 63) // 64 * 64  # 128-byte rows: aligned TMA segments
     dev = s.device
     scales = torch.empty(8 + Cp, dtype=torch.float32, device=dev)
     call("sigsvgd_tc_scales", _p(s), s.stride(0), _p(mean), N, D, _p(score), 0 if score is None else score.stride(0), P,
@@ -227,10 +227,38 @@ def tc_sqdist_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: i
     return out
 
 
+def tc_median_workspace(M: int, N: int, device) -> torch.Tensor:
+    nbytes = _lib.load().sigsvgd_tc_median_workspace_bytes(M, N)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def tc_median_prepare_raw(a_c: torch.Tensor, b_c: torch.Tensor, ws: torch.Tensor, state: torch.Tensor) -> None:
+    """a_c / b_c: centred fp32 features of the rows / columns of the distance matrix."""
+    call("sigsvgd_tc_median_prepare", _p(a_c), a_c.stride(0), a_c.shape[0], _p(b_c), b_c.stride(0), b_c.shape[0],
+         a_c.shape[1], _p(ws), ws.numel(), _p(state), _stream())
+
+
+def tc_gram_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int, scales: torch.Tensor,
+                symmetric: bool = False, median_ws: Optional[torch.Tensor] = None,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    M, N = a.hi.shape[0], b.hi.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=a.hi.device)
+    call("sigsvgd_tc_gram", _p(a.hi), _p(a.lo), a.ld, _p(na), _p(b.hi), _p(b.lo), b.ld, _p(nb), M, N, D, _p(scales),
+         int(symmetric), _p(median_ws), _p(out), out.stride(0), _stream())
+    return out
+
+
+def tc_median_select_raw(ws: torch.Tensor, dist: torch.Tensor, n_log: int, bw: "Bandwidth", state: torch.Tensor) -> None:
+    M, N = dist.shape
+    call("sigsvgd_tc_median_select", _p(ws), _p(dist), M, N, dist.stride(0), n_log, bw.bw_scale, bw.tol, _p(state),
+         _stream())
+
+
 def tc_rbf_raw(dist: torch.Tensor, state: torch.Tensor, row_offset: int = 0, want_k: bool = False):
     """-> (K planes [M, Np]); if want_k, ``dist`` is overwritten with the fp32 kernel values."""
     M, N = dist.shape
-    Np = (N + 7) // 8 * 8
+    Np = (N + 63) // 64 * 64
     kh = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
     kl = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
     call("sigsvgd_tc_rbf", _p(dist), dist.stride(0), M, N, row_offset, _p(state), _p(kh), _p(kl), Np,

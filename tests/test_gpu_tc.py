@@ -45,6 +45,63 @@ def test_tc_sqdist_vs_float64(M, N, D, scale):
     assert (got >= 0).all()
 
 
+@pytest.mark.parametrize("N,D,scale", [(64, 14, 1.0), (300, 39, 1.0), (1000, 399, 1e-2), (2048, 399, 30.0), (4099, 65, 1.0)])
+def test_tc_gram_symmetric_and_single_pass_median(N, D, scale):
+    rng = np.random.default_rng(N + D)
+    colmag = np.exp(rng.uniform(-6, 0, size=D))
+    s = (rng.standard_normal((N, D)) * colmag * scale).astype(np.float32)
+    s[3] = s[7]  # duplicate point -> an exact zero distance off the diagonal
+    mean = cu(s.mean(0).astype(np.float32))
+    planes, norms, scales, sc = ops.tc_pack_raw(cu(s), mean)
+    state = ops.new_state(torch.device(DEV))
+    ws = ops.tc_median_workspace(N, N, DEV)
+    ops.tc_median_prepare_raw(sc, sc, ws, state)
+    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True, median_ws=ws)
+    ops.tc_median_select_raw(ws, d, N, ops.Bandwidth.median(), state)
+    got = d.cpu().numpy()
+    s64 = s.astype(np.float64)
+    ref = np.maximum((s64 ** 2).sum(1)[:, None] + (s64 ** 2).sum(1)[None] - 2 * s64 @ s64.T, 0)
+    assert np.abs(got - ref).max() <= 1e-6 * ref.max()
+    assert np.array_equal(got, got.T)  # bit-symmetric
+    assert (np.diag(got) == 0).all()
+    rec = ops.read_state(state)
+    want = np.sort(got.reshape(-1))[(N * N - 1) // 2]  # exact lower median of OUR matrix
+    assert np.float32(rec["median"]) == want
+    win = np.frombuffer(ws[:32].cpu().numpy().tobytes(), dtype=np.uint32)
+    assert win[7] == 0, "window missed the median (fallback taken)"
+    lo, hi = np.frombuffer(ws[:8].cpu().numpy().tobytes(), dtype=np.float32)
+    assert lo <= want <= hi
+    assert int(win[2]) == int(((got >= lo) & (got <= hi)).sum())  # candidates collected exactly once each
+    # the non-symmetric kernel (strip of rows) gives the same numbers and the same median machinery
+    M = min(N, 200)
+    pa = ops.Planes(planes.hi[:M], planes.lo[:M])
+    ws2 = ops.tc_median_workspace(M, N, DEV)
+    state2 = ops.new_state(torch.device(DEV))
+    ops.tc_median_prepare_raw(sc[:M], sc, ws2, state2)
+    d2 = ops.tc_gram_raw(pa, norms[:M], planes, norms, D, scales, symmetric=False, median_ws=ws2)
+    ops.tc_median_select_raw(ws2, d2, N, ops.Bandwidth.median(), state2)
+    g2 = d2.cpu().numpy()
+    off = ~np.eye(N, dtype=bool)[:M]
+    # (mirrored entries of the symmetric kernel sum the two correction products in the other order)
+    assert np.abs(g2[off] - got[:M][off]).max() <= 1e-6 * ref.max()
+    assert np.float32(ops.read_state(state2)["median"]) == np.sort(g2.reshape(-1))[(M * N - 1) // 2]
+
+
+def test_single_pass_median_falls_back_when_window_misses():
+    # half of the entries are exactly equal: the candidate list overflows -> full-matrix fallback
+    N, D = 512, 8
+    s = np.zeros((N, D), np.float32)
+    s[: N // 4, 0] = np.random.default_rng(0).standard_normal(N // 4)
+    planes, norms, scales, sc = ops.tc_pack_raw(cu(s), None)
+    state = ops.new_state(torch.device(DEV))
+    ws = ops.tc_median_workspace(N, N, DEV)
+    ops.tc_median_prepare_raw(sc, sc, ws, state)
+    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True, median_ws=ws)
+    ops.tc_median_select_raw(ws, d, N, ops.Bandwidth.median(), state)
+    got = d.cpu().numpy()
+    assert np.float32(ops.read_state(state)["median"]) == np.sort(got.reshape(-1))[(N * N - 1) // 2]
+
+
 @pytest.mark.parametrize("M,N,D,P", [(128, 128, 14, 20), (130, 200, 39, 27), (512, 512, 399, 448), (300, 1000, 399, 448), (128, 4100, 399, 448)])
 def test_tc_rbf_and_matmul_vs_float64(M, N, D, P):
     rng = np.random.default_rng(M * 3 + N)

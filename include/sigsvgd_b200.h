@@ -178,22 +178,25 @@ int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const flo
                       int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,
                       void* stream);
 /* Same distances, 128x128 tiles with separate TMEM accumulators for the hi.hi and correction
- * products; symmetric != 0 (same planes on both sides, M == N) computes the upper triangle and
- * mirrors it, diagonal exactly 0.  median_ws (may be NULL) = workspace prepared by
- * sigsvgd_tc_median_prepare: entries below the window are counted and entries inside it are
- * collected while the matrix is written (single-pass exact median, math.py:28-34). */
+ * products and a TMA-store epilogue (needs dist 16-byte aligned and ldd % 4 == 0, else a slow
+ * per-element epilogue runs); symmetric != 0 (same planes on both sides, M == N) computes the
+ * upper triangle and mirrors it: the result is bit-symmetric with an exactly zero diagonal. */
 int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
                     const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
-                    int64_t N, int64_t D, const float* scales, int symmetric, void* median_ws,
-                    float* dist, int64_t ldd, void* stream);
+                    int64_t N, int64_t D, const float* scales, int symmetric, float* dist,
+                    int64_t ldd, void* stream);
 size_t sigsvgd_tc_median_workspace_bytes(int64_t M, int64_t N);
-/* a/b: centred fp32 features of the rows / columns (s_centred of sigsvgd_tc_pack); samples the
- * matrix, sets the candidate window, resets the selection fields of *state. */
+/* Single-pass exact median (math.py:28-34).  prepare: a/b = centred fp32 features of the rows /
+ * columns (s_centred of sigsvgd_tc_pack); samples 16384 entries of the matrix, sets a candidate
+ * window [lo, hi] around the sample median, resets the selection fields of *state.  It does not
+ * need the matrix and may run before or after the Gram kernel. */
 int sigsvgd_tc_median_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,
                               int64_t N, int64_t D, void* median_ws, size_t ws_bytes,
                               sigsvgd_bw_state* state, void* stream);
-/* after sigsvgd_tc_gram: exact lower median of the M*N distances and the bandwidth
- * (state->{median,h,gamma,clamped}); falls back to the full matrix if the window missed. */
+/* select (after the matrix is written): one pass over dist counts the entries below the window
+ * and collects those inside it, then the exact lower median of the M*N distances is selected
+ * among the candidates -> state->{median,h,gamma,clamped}.  Falls back to radix passes over the
+ * full matrix if the window missed, so the result is always exact. */
 int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
                              int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                              void* stream);

@@ -98,7 +98,7 @@ _SIGNATURES = {
     "sigsvgd_tc_gram": (
         c_int,
         [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
-         c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p],
+         c_void_p, c_int, c_void_p, c_int64, c_void_p],
     ),
     "sigsvgd_tc_median_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "sigsvgd_tc_median_prepare": (

@@ -238,15 +238,12 @@ int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const flo
 
 int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
                     const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
-                    int64_t N, int64_t D, const float* scales, int symmetric, void* median_ws,
-                    float* dist, int64_t ldd, void* stream) {
+                    int64_t N, int64_t D, const float* scales, int symmetric, float* dist,
+                    int64_t ldd, void* stream) {
   SIG_CHECK_ARG(a_hi && a_lo && b_hi && b_lo && na && nb && scales && dist, "tc_gram: NULL pointer");
-  SelWindow* win = nullptr;
-  float* cand = nullptr;
-  if (median_ws) window_pointers(median_ws, &win, &cand);
   return tc_gram(TcPlanes{(const __half*)a_hi, (const __half*)a_lo, lda},
                  TcPlanes{(const __half*)b_hi, (const __half*)b_lo, ldb}, M, N, D, na, nb, scales + 1,
-                 symmetric, win, cand, dist, ldd, (cudaStream_t)stream);
+                 symmetric, dist, ldd, (cudaStream_t)stream);
 }
 
 size_t sigsvgd_tc_median_workspace_bytes(int64_t M, int64_t N) {
@@ -359,14 +356,15 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
     feat = V, ldf = D;
     out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
     // K4a: candidate window for the median from a sample of the matrix
-    SelWindow* win = nullptr;
-    float* cand = nullptr;
-    if (bw_mode == SIGSVGD_BW_MEDIAN)
+    if (bw_mode == SIGSVGD_BW_MEDIAN) {
+      SelWindow* win = nullptr;
+      float* cand = nullptr;
       SIG_PROPAGATE(launch_window_prepare(V, D, N, V, D, N, D, w + L.off_win, state, &win, &cand, st));
+    }
     // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product; upper triangle
-    // mirrored), counting / collecting the median candidates on the way out
+    // mirrored)
     SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
-                          scales + 1, 1, win, cand, K, N, st));
+                          scales + 1, 1, K, N, st));
   } else {
     SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
     feat = V + P, ldf = C;

@@ -19,17 +19,22 @@ struct TcPlanes {
   int64_t ld;
 };
 
-// Candidate window of the single-pass exact median (median_window.cu): while the distance matrix
-// is being written, entries below `lo` are counted and entries inside [lo, hi] are appended to a
-// candidate list; the order statistic is then selected among the candidates only.
+// Candidate window of the single-pass exact median (median_window.cu): in ONE pass over the
+// freshly written distance matrix, entries below `lo` are counted and entries inside [lo, hi] are
+// compacted into candidate pools; the order statistic is then selected among the candidates only.
 struct SelWindow {
   float lo, hi;              // window bounds (sample quantiles bracketing the median)
-  unsigned int n_cand;       // candidates appended so far (may run past cap: overflow)
-  unsigned int cap;          // capacity of the candidate buffer
+  unsigned int n_cand;       // total candidates (filled in by the select kernel)
+  unsigned int cap;          // capacity of the candidate buffer (all pools)
   unsigned long long below;  // matrix entries < lo
   unsigned int active;       // 0: no window (fixed bandwidth) -> epilogue skips the bookkeeping
   unsigned int fallback;     // set by the select kernel when the window missed the median
+  // The candidate buffer is cut into `npool` pools of `poolcap` entries; block b of the select
+  // kernel appends to pool b through a shared-memory counter (no global atomics) and leaves its
+  // fill count in pool_cnt[b] (a count above poolcap = overflow -> fallback).
+  unsigned int npool, poolcap;
 };
+constexpr int kMaxPools = 1024;
 
 // dist[i,j] = max(0, (na[i] + nb[j] - 2 * sum_c A[i,c] B[j,c]) * scal[0])   i < M, j < N, c < D
 //   A, B: planes [M x >=D], [N x >=D] (features along the row: K-major for both operands)
@@ -38,12 +43,12 @@ int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const flo
               const float* nb, const float* scal, float* dist, int64_t ldd, cudaStream_t st);
 
 // Same distances with 128 x 128 tiles, separate TMEM accumulators for the hi.hi and the
-// correction products, and the median bookkeeping fused into the epilogue (win/cand may be NULL).
+// correction products, TMA-store epilogue.
 // symmetric != 0: A and B are the same planes (M == N); only tiles on or above the diagonal are
 // computed, each is stored together with its transpose, and the diagonal is exactly 0.
 int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
-            const float* nb, const float* scal, int symmetric, SelWindow* win, float* cand,
-            float* dist, int64_t ldd, cudaStream_t st);
+            const float* nb, const float* scal, int symmetric, float* dist, int64_t ldd,
+            cudaStream_t st);
 
 // out[i,c] = colscale[c] * sum_j A[i,j] V[j,c]      i < M, j < K, c < C
 //   A: planes [M x >=K] (K-major), V: planes [K x >=C] (the contraction index is the ROW of V:
@@ -57,7 +62,7 @@ bool tc_available();
 // ---- single-pass exact median (median_window.cu) ---------------------------------------------
 // ws: window_workspace_bytes(M, N) bytes = [SelWindow | sample | histograms | candidates]
 size_t window_workspace_bytes(int64_t M, int64_t N, unsigned int* cap_out);
-void window_pointers(void* ws, SelWindow** win, float** cand);
+void window_pointers(void* ws, SelWindow** win, float** cand, unsigned int** pool_cnt);
 // sample the matrix (a, b: centred fp32 features of its rows / columns), set the window, reset
 // the counters and the selection fields of `state`
 int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,

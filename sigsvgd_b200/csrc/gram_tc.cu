@@ -1,5 +1,5 @@
-// Pairwise squared distances of signature features on the tensor cores (K3), with the median
-// bookkeeping fused into the epilogue.  Reference: pw_dist_sq, src/utils/math.py:69-86.
+// Pairwise squared distances of signature features on the tensor cores (K3).
+// Reference: pw_dist_sq, src/utils/math.py:69-86.
 //
 // Output tile 128 x 128.  Per accumulator stage two TMEM buffers: `main` takes the hi.hi products,
 // `corr` the hi.lo + lo.hi products (2^-11 smaller), and the epilogue adds them in fp32 RN.  The
@@ -20,11 +20,11 @@ constexpr int kThreads = 256;
 constexpr uint32_t kPlaneBytes = GM * GK * 2;            // 16 KB: one plane of one operand tile
 constexpr uint32_t kStageBytes = 4 * kPlaneBytes;        // A hi/lo + B hi/lo = 64 KB
 constexpr uint32_t kBarBytes = 256;
-constexpr int kXposePitch = 33;                          // floats per row of a 32 x 32 transpose tile
-constexpr uint32_t kXposeBytes = 4 * 32 * kXposePitch * 4;  // one tile per epilogue warp
-constexpr int kCandStage = 1024;                         // staged median candidates per epilogue warp
-constexpr uint32_t kCandBytes = 4 * kCandStage * 4;
-constexpr uint32_t kSmemBytes = kStages * kStageBytes + kBarBytes + kXposeBytes + kCandBytes + 1024;
+constexpr uint32_t kOutTileBytes = 32 * 32 * 4;          // one 32 x 32 fp32 staging tile (TMA store box)
+constexpr uint32_t kColNormBytes = 4 * 32 * 4;           // scaled column norms of one chunk, per epilogue warp
+// [operand stages | 4 block tiles | 4 mirror tiles | barriers | column norms] + alignment slack
+constexpr uint32_t kSmemBytes = kStages * kStageBytes + 8 * kOutTileBytes + kBarBytes + kColNormBytes + 1024;
+static_assert(kSmemBytes <= 232448, "exceeds the 227 KB shared-memory limit of sm_100");
 constexpr uint32_t kTmemCols = 512;                      // 2 stages x (main 128 + corr 128)
 
 struct GramParams {
@@ -37,8 +37,6 @@ struct GramParams {
   const float* na;
   const float* nb;
   const float* scal;
-  SelWindow* win;
-  float* cand;
 };
 
 __device__ __forceinline__ void decode_sym(int t, int T, int& tm, int& tn) {
@@ -53,22 +51,22 @@ __device__ __forceinline__ void decode_sym(int t, int T, int& tm, int& tn) {
   tn = m + (t - start(m));
 }
 
-template <bool kSym>
+template <bool kSym, bool kTma>
 __global__ void __launch_bounds__(kThreads, 1)
 gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
             const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
-            const GramParams p) {
+            const __grid_constant__ CUtensorMap tmOut, const GramParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (sbase - raw);
-  const uint32_t bar0 = sbase + kStages * kStageBytes;
+  const uint32_t bar0 = sbase + kStages * kStageBytes + 8 * kOutTileBytes;
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (kStages + s); };
   auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * kStages + a); };
   auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * kStages + 2 + a); };
   volatile uint32_t* tmem_slot =
-      reinterpret_cast<volatile uint32_t*>(smem + kStages * kStageBytes + 8 * (2 * kStages + 4));
+      reinterpret_cast<volatile uint32_t*>(smem + kStages * kStageBytes + 8 * kOutTileBytes + 8 * (2 * kStages + 4));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
@@ -76,6 +74,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
     ptx::tma_prefetch_desc(&tmAl);
     ptx::tma_prefetch_desc(&tmBh);
     ptx::tma_prefetch_desc(&tmBl);
+    if (kTma) ptx::tma_prefetch_desc(&tmOut);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -160,166 +159,196 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue
+    // A thread owns one row (TMEM lane) of the tile and walks it in 4 chunks of 32 columns.
+    //  fast path (16-byte aligned output): the chunk is staged in shared memory in the
+    //    128-byte-swizzled box layout (two staging tiles per warp, alternating) and leaves through
+    //    a TMA store; in symmetric mode its transpose is stored straight from the registers (lanes
+    //    hold consecutive rows = consecutive addresses of the mirrored block);
+    //  slow path (unaligned output): per-element guarded stores.
     const int q = warp & 3;
     uint32_t tcount = 0;
-    const float scal0 = __ldg(p.scal);
-    const bool use_win = p.win != nullptr && p.win->active != 0;
-    float wlo = 0.f, whi = 0.f;
-    unsigned int cap = 0;
-    if (use_win) wlo = p.win->lo, whi = p.win->hi, cap = p.win->cap;
-    float* xp = reinterpret_cast<float*>(smem + kStages * kStageBytes + kBarBytes) + q * (32 * kXposePitch);
-    float* cstage = reinterpret_cast<float*>(smem + kStages * kStageBytes + kBarBytes + kXposeBytes) + q * kCandStage;
-    int cfill = 0;                     // staged candidates of this warp (warp-uniform)
-    unsigned long long below = 0ull;   // per-thread count of entries < lo (x multiplicity)
-    // flush the warp's staged candidates: one global atomic, coalesced copy
-    auto flush_cands = [&]() {
-      if (cfill == 0) return;
-      unsigned int base = 0;
-      if (lane == 0) base = atomicAdd(&p.win->n_cand, (unsigned int)cfill);
-      base = __shfl_sync(0xffffffffu, base, 0);
-      for (int i = lane; i < cfill; i += 32)
-        if (base + i < cap) p.cand[base + i] = cstage[i];
-      __syncwarp();
-      cfill = 0;
-    };
+    const float scal0 = __ldg(p.scal);  // alpha^-2, a power of two: scaling commutes with rounding
+    const float m2s = -2.f * scal0;
+    uint8_t* const stg0 = smem + kStages * kStageBytes + q * (2 * kOutTileBytes);
+    const uint32_t stg0_u = sbase + kStages * kStageBytes + q * (2 * kOutTileBytes);
+    float* xp = reinterpret_cast<float*>(stg0);  // slow path: 32 x 32 transpose tile, XOR-swizzled
+    float* cn = reinterpret_cast<float*>(smem + kStages * kStageBytes + 8 * kOutTileBytes + kBarBytes) + q * 32;
+    uint32_t nstore = 0;  // TMA stores committed by lane 0 (staging tile = nstore & 1)
+
     for (int w = blockIdx.x; w < p.num_work; w += gridDim.x, ++tcount) {
       int tm, tn;
       decode(w, tm, tn);
       const int a = tcount & 1;
       const uint32_t aph = (tcount >> 1) & 1u;
-      ptx::mbar_wait(tfull_bar(a), aph);
-      ptx::tc_fence_after();
       const int64_t row0 = (int64_t)tm * GM + q * 32;  // first row of this warp
       const int64_t row = row0 + lane;
       const bool row_ok = row < p.M;
-      const float rv = row_ok ? __ldg(p.na + row) : 0.f;
-      // symmetric mode: an entry above the diagonal stands for two matrix entries (it is stored
-      // twice and counted twice), the diagonal for one, and entries below the diagonal (they only
-      // occur inside diagonal tiles) are dropped in favour of their mirror image
       const bool diag = kSym && tm == tn;
-      unsigned int below1 = 0, below2 = 0;
+      // norms of this thread's row and of the tile's columns (lane-strided), fetched while the
+      // accumulator is still being produced
+      const float rvs = row_ok ? __ldg(p.na + row) * scal0 : 0.f;
+      float cnv[GN / 32];
+#pragma unroll
+      for (int k = 0; k < GN / 32; ++k) {
+        const int64_t col = (int64_t)tn * GN + k * 32 + lane;
+        cnv[k] = col < p.N ? __ldg(p.nb + col) * scal0 : 0.f;
+      }
+      ptx::mbar_wait(tfull_bar(a), aph);
+      ptx::tc_fence_after();
+      if (kTma) {
+        // ------------------------------------------------------------ fast path
+#pragma unroll
+        for (int c = 0; c < GN / 32; ++c) {
+          const int col0 = tn * GN + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          // 32 x 32 blocks of a diagonal tile: above the diagonal -> like any other block (stored
+          // with its mirror image); on the diagonal -> symmetrised inside the warp; below -> skipped
+          // (it is the mirror image of a block another warp stores)
+          const int blk = !diag ? 0 : (c > q ? 0 : (c == q ? 1 : 2));
+          if (blk == 2) continue;
+          uint32_t v[32], u[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * 256 + c * 32;
+          ptx::tmem_ld_32x32(taddr, v);
+          ptx::tmem_ld_32x32(taddr + 128, u);
+          __syncwarp();
+          cn[lane] = cnv[c];
+          __syncwarp();
+          float cnr[32];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float4 f = *reinterpret_cast<const float4*>(cn + 4 * k);
+            cnr[4 * k] = f.x, cnr[4 * k + 1] = f.y, cnr[4 * k + 2] = f.z, cnr[4 * k + 3] = f.w;
+          }
+          const int ncol = (int)min((int64_t)32, p.N - col0);
+          ptx::tmem_ld_wait();
+          float o[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float acc = __uint_as_float(v[e]) + __uint_as_float(u[e]);
+            o[e] = fmaxf(fmaf(m2s, acc, rvs + cnr[e]), 0.f);
+          }
+          // staging tile of this chunk; the TMA store issued two chunks ago read the same tile
+          uint8_t* const stg = stg0 + (nstore & 1u) * kOutTileBytes;
+          const uint32_t stg_u = stg0_u + (nstore & 1u) * kOutTileBytes;
+          if (nstore >= 2) {
+            if (lane == 0) ptx::bulk_wait_read1();
+            __syncwarp();
+          }
+          if (kSym && blk == 1) {
+            // diagonal block: (r, c) and (c, r) were accumulated in different orders; keep the upper
+            // triangle, take the lower one from the transposed tile, exact zeros on the diagonal
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              *reinterpret_cast<float*>(stg + e * 128 + ((((lane >> 2) ^ (e & 7)) << 4) | ((lane & 3) << 2))) = o[e];
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float4 f = *reinterpret_cast<const float4*>(stg + lane * 128 + ((k ^ (lane & 7)) << 4));
+              if (4 * k + 0 < lane) o[4 * k + 0] = f.x;
+              if (4 * k + 1 < lane) o[4 * k + 1] = f.y;
+              if (4 * k + 2 < lane) o[4 * k + 2] = f.z;
+              if (4 * k + 3 < lane) o[4 * k + 3] = f.w;
+            }
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (e == lane) o[e] = 0.f;
+            __syncwarp();
+          }
+          // block: row `lane`, 16-byte chunk k at (k ^ (lane & 7)) -- the SWIZZLE_128B box layout
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            *reinterpret_cast<float4*>(stg + lane * 128 + ((k ^ (lane & 7)) << 4)) =
+                make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tmOut, stg_u, col0, (int)row0);  // clipped at the matrix edges
+            ptx::bulk_commit();
+          }
+          ++nstore;
+          if (kSym && blk == 0) {
+            // mirrored block: entry (row, col0 + e) -> out[col0 + e][row]; one coalesced line per e
+            float* mp = p.out + (int64_t)col0 * p.ldo + row;
+            if (ncol == 32 && row0 + 32 <= p.M) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) mp[(int64_t)e * p.ldo] = o[e];
+            } else if (row_ok) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (e < ncol) mp[(int64_t)e * p.ldo] = o[e];
+            }
+          }
+        }
+      } else {
+        // ------------------------------------------------------------ slow path
+        // symmetric mode: an entry above the diagonal stands for two matrix entries (it is stored
+        // twice and counted twice), the diagonal for one, and entries below the diagonal (they only
+        // occur inside diagonal tiles) are dropped in favour of their mirror image
 #pragma unroll 1
-      for (int c = 0; c < GN / 32; ++c) {
-        const int64_t col0 = (int64_t)tn * GN + c * 32;
-        if (col0 >= p.N) break;  // warp-uniform
-        uint32_t v[32], u[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * 256 + c * 32;
-        ptx::tmem_ld_32x32(taddr, v);
-        ptx::tmem_ld_32x32(taddr + 128, u);
-        // column norms of this chunk: one coalesced load, broadcast by shuffle
-        const float cvl = (col0 + lane < p.N) ? __ldg(p.nb + col0 + lane) : 0.f;
-        // bit e set: column col0+e is inside the matrix and (symmetric) strictly above the diagonal
-        const int64_t ncol = min((int64_t)32, p.N - col0);
-        const uint32_t inmask = ncol >= 32 ? 0xffffffffu : ((1u << ncol) - 1u);
-        uint32_t upmask = 0u, dgmask = 0u;  // mirrored entries / plain entries of this thread
-        if (row_ok) {
-          if (!kSym) {
-            dgmask = inmask;
-          } else if (!diag) {
-            upmask = inmask;
-          } else {
-            const int64_t rel = row - col0;  // column index of the diagonal inside this chunk
-            if (rel < 0) upmask = inmask;
-            else if (rel < 32) {
-              upmask = inmask & ~((2u << rel) - 1u);  // 2u << 31 == 0 -> all lower: mask 0 ok
-              if (rel == 31) upmask = 0u;
-              dgmask = inmask & (1u << rel);
-            }
-          }
-        }
-        ptx::tmem_ld_wait();
-        float o[32];
-        uint32_t hitmask = 0;
-#pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const float cv = __shfl_sync(0xffffffffu, cvl, e);
-          const float acc = __uint_as_float(v[e]) + __uint_as_float(u[e]);
-          float dv = fmaxf(fmaf(-2.f, acc, rv + cv) * scal0, 0.f);
-          if (kSym && ((dgmask >> e) & 1u)) dv = 0.f;
-          o[e] = dv;
-          if (use_win) {
-            if (dv < wlo) below2 += (upmask >> e) & 1u, below1 += (dgmask >> e) & 1u;
-            if (dv >= wlo && dv <= whi) hitmask |= 1u << e;
-          }
-        }
-        if (use_win) {
-          const uint32_t hit2 = hitmask & upmask, hit1 = hitmask & dgmask;
-          const int hits = 2 * __popc(hit2) + __popc(hit1);
-          int incl = hits;
-#pragma unroll
-          for (int sft = 1; sft < 32; sft <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, sft);
-            if (lane >= sft) incl += t;
-          }
-          const int total = __shfl_sync(0xffffffffu, incl, 31);
-          if (total > 0) {  // warp-uniform
-            if (cfill + total > kCandStage) flush_cands();
-            if (total <= kCandStage) {
-              int off = cfill + incl - hits;
-#pragma unroll
-              for (int e = 0; e < 32; ++e) {
-                if ((hit2 >> e) & 1u) {
-                  cstage[off] = o[e];
-                  cstage[off + 1] = o[e];
-                  off += 2;
-                } else if ((hit1 >> e) & 1u) {
-                  cstage[off++] = o[e];
-                }
-              }
-              cfill += total;
-              __syncwarp();
+        for (int c = 0; c < GN / 32; ++c) {
+          const int64_t col0 = (int64_t)tn * GN + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint32_t v[32], u[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * 256 + c * 32;
+          ptx::tmem_ld_32x32(taddr, v);
+          ptx::tmem_ld_32x32(taddr + 128, u);
+          const float cvl = c == 0 ? cnv[0] : c == 1 ? cnv[1] : c == 2 ? cnv[2] : cnv[3];
+          // bit e set: column col0+e is inside the matrix and (symmetric) strictly above the diagonal
+          const int64_t ncol = min((int64_t)32, p.N - col0);
+          const uint32_t inmask = ncol >= 32 ? 0xffffffffu : ((1u << ncol) - 1u);
+          uint32_t upmask = 0u, dgmask = 0u;  // mirrored entries / plain entries of this thread
+          if (row_ok) {
+            if (!kSym) {
+              dgmask = inmask;
+            } else if (!diag) {
+              upmask = inmask;
             } else {
-              // dense window (more hits than the stage holds): straight to global
-              unsigned int base = 0;
-              if (lane == 31) base = atomicAdd(&p.win->n_cand, (unsigned int)total);
-              base = __shfl_sync(0xffffffffu, base, 31);
-              unsigned int off = base + (unsigned int)(incl - hits);
-#pragma unroll
-              for (int e = 0; e < 32; ++e) {
-                if ((hit2 >> e) & 1u) {
-                  if (off < cap) p.cand[off] = o[e];
-                  if (off + 1 < cap) p.cand[off + 1] = o[e];
-                  off += 2;
-                } else if ((hit1 >> e) & 1u) {
-                  if (off < cap) p.cand[off] = o[e];
-                  off += 1;
-                }
+              const int64_t rel = row - col0;  // column index of the diagonal inside this chunk
+              if (rel < 0) upmask = inmask;
+              else if (rel < 32) {
+                upmask = inmask & ~((2u << rel) - 1u);  // 2u << 31 == 0 -> all lower: mask 0 ok
+                if (rel == 31) upmask = 0u;
+                dgmask = inmask & (1u << rel);
               }
             }
           }
-        }
-        // transposed block straight from registers: lanes hold consecutive rows, so every store
-        // instruction writes one coalesced line of the mirrored block
-        if (kSym && upmask) {
+          ptx::tmem_ld_wait();
+          float o[32];
 #pragma unroll
-          for (int e = 0; e < 32; ++e)
-            if ((upmask >> e) & 1u) p.out[(col0 + e) * p.ldo + row] = o[e];
-        }
-        // direct block through a 32 x 32 shared-memory transpose so that each store instruction
-        // writes 32 consecutive columns of one row (a thread owns a row in TMEM)
+          for (int e = 0; e < 32; ++e) {
+            const float cv = __shfl_sync(0xffffffffu, cvl, e);
+            const float acc = __uint_as_float(v[e]) + __uint_as_float(u[e]);
+            float dv = fmaxf(fmaf(m2s, acc, rvs + cv), 0.f);
+            if (kSym && ((dgmask >> e) & 1u)) dv = 0.f;
+            o[e] = dv;
+          }
+          // transposed block straight from registers: lanes hold consecutive rows, so every store
+          // instruction writes one coalesced line of the mirrored block
+          if (kSym && upmask) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) xp[lane * kXposePitch + e] = o[e];
-        __syncwarp();
-        const int64_t col = col0 + lane;
-        const bool col_ok = col < p.N;
+            for (int e = 0; e < 32; ++e)
+              if ((upmask >> e) & 1u) p.out[(col0 + e) * p.ldo + row] = o[e];
+          }
+          // direct block through a 32 x 32 shared-memory transpose so that each store instruction
+          // writes 32 consecutive columns of one row (a thread owns a row in TMEM)
+#pragma unroll
+          for (int e = 0; e < 32; ++e) xp[lane * 32 + (e ^ lane)] = o[e];
+          __syncwarp();
+          const int64_t col = col0 + lane;
+          const bool col_ok = col < p.N;
 #pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-          const int64_t rr = row0 + r;
-          if (rr < p.M && col_ok && (!diag || col >= rr)) p.out[rr * p.ldo + col] = xp[r * kXposePitch + lane];
+          for (int r = 0; r < 32; ++r) {
+            const int64_t rr = row0 + r;
+            if (rr < p.M && col_ok && (!diag || col >= rr)) p.out[rr * p.ldo + col] = xp[r * 32 + (lane ^ r)];
+          }
+          __syncwarp();
         }
-        __syncwarp();
       }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(a));
-      below += (unsigned long long)below1 + 2ull * (unsigned long long)below2;
     }
-    if (use_win) {
-      flush_cands();
-#pragma unroll
-      for (int sft = 16; sft >= 1; sft >>= 1) below += __shfl_xor_sync(0xffffffffu, below, sft);
-      if (lane == 0 && below) atomicAdd(&p.win->below, below);
-    }
+    if (nstore && lane == 0) ptx::bulk_wait0();
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -333,16 +362,17 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
 
 int make_tmap_f16(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer, int64_t ld,
                   uint32_t box_inner, uint32_t box_outer);  // gemm_tc.cu
+int make_tmap_f32(CUtensorMap* tm, const float* base, int64_t inner, int64_t outer, int64_t ld,
+                  uint32_t box_inner, uint32_t box_outer);  // gemm_tc.cu
 
 int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
-            const float* nb, const float* scal, int symmetric, SelWindow* win, float* cand,
-            float* dist, int64_t ldd, cudaStream_t st) {
+            const float* nb, const float* scal, int symmetric, float* dist, int64_t ldd,
+            cudaStream_t st) {
   SIG_CHECK_ARG(M >= 1 && N >= 1 && D >= 1 && A.ld >= D && B.ld >= D && ldd >= N,
                 "tc_gram: bad shape M=%lld N=%lld D=%lld", (long long)M, (long long)N, (long long)D);
   SIG_CHECK_ARG(M < (1ll << 30) && N < (1ll << 30), "tc_gram: too many rows");
   SIG_CHECK_ARG(!symmetric || (M == N && A.hi == B.hi && A.lo == B.lo && na == nb),
                 "tc_gram: symmetric mode needs identical operands");
-  SIG_CHECK_ARG((win == nullptr) == (cand == nullptr), "tc_gram: win and cand go together");
   CUtensorMap ah, al, bh, bl;
   SIG_PROPAGATE(make_tmap_f16(&ah, A.hi, D, M, A.ld, GK, GM));
   SIG_PROPAGATE(make_tmap_f16(&al, A.lo, D, M, A.ld, GK, GM));
@@ -357,22 +387,29 @@ int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float
   p.num_work = (int)work;
   p.out = dist, p.ldo = ldd;
   p.na = na, p.nb = nb, p.scal = scal;
-  p.win = win, p.cand = cand;
+  // TMA-store epilogue needs a 16-byte aligned output with a 16-byte row pitch
+  const bool tma_out = (reinterpret_cast<uintptr_t>(dist) & 15u) == 0 && (ldd & 3) == 0;
+  CUtensorMap to = ah;  // placeholder when unused
+  if (tma_out) SIG_PROPAGATE(make_tmap_f32(&to, dist, N, M, ldd, 32, 32));
   static thread_local int configured_dev = -1;
   int dev = 0;
   SIG_CUDA_OK(cudaGetDevice(&dev));
   if (configured_dev != dev) {
-    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)kSmemBytes));
-    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)kSmemBytes));
+    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    SIG_CUDA_OK(cudaFuncSetAttribute(gram_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     configured_dev = dev;
   }
   const int grid = (int)std::min<int64_t>(work, num_sms());
-  if (symmetric)
-    gram_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, p);
+  if (symmetric && tma_out)
+    gram_kernel<true, true><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, to, p);
+  else if (symmetric)
+    gram_kernel<true, false><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, to, p);
+  else if (tma_out)
+    gram_kernel<false, true><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, to, p);
   else
-    gram_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, p);
+    gram_kernel<false, false><<<grid, kThreads, kSmemBytes, st>>>(ah, al, bh, bl, to, p);
   SIG_LAUNCH_OK("gram_kernel");
   return 0;
 }

@@ -7,12 +7,13 @@
 //                      not depend on them;
 //   2. window_bounds : one block selects two sample order statistics m/2 -+ 6 sigma -> [lo, hi],
 //                      which brackets the true median except with probability ~1e-9;
-//   3. tc_gram's epilogue counts the entries < lo and appends the entries in [lo, hi]
-//                      (about 5 % of the matrix) to a candidate list while it writes the matrix;
-//   4. window_select : one cooperative kernel radix-selects rank k - below among the candidates
-//                      (3 passes over the short list).  If the window missed (or the list
-//                      overflowed) the same kernel falls back to the full matrix, so the result
-//                      is always the exact order statistic.
+//   3. window_select : one cooperative kernel.  Phase A reads the matrix once (right after the
+//                      Gram kernel wrote it: L2 hits), counts the entries < lo and compacts the
+//                      entries in [lo, hi] (about 5 %) into per-block pools (ballot compaction,
+//                      shared-memory fill counters: no global atomics).  Then three radix passes
+//                      over the short candidate list select rank k - below.  If the window missed
+//                      (or a pool overflowed) the same kernel falls back to radix passes over the
+//                      full matrix, so the result is always the exact order statistic.
 #include <cooperative_groups.h>
 
 #include "gemm_tc.cuh"
@@ -152,7 +153,8 @@ __device__ float block_select_smem(const float* vals, int n, unsigned long long 
 // histograms used by window_select, and of the bandwidth record
 __global__ void __launch_bounds__(1024)
 window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned int cap,
-                     unsigned long long* ghist /*[3*kBins]*/, sigsvgd_bw_state* state) {
+                     unsigned int npool, unsigned long long* ghist /*[3*kBins]*/,
+                     unsigned int* pool_cnt /*[kMaxPools]*/, sigsvgd_bw_state* state) {
   extern __shared__ float sv[];  // kSample floats
   __shared__ unsigned int hist[kBins];
   __shared__ unsigned long long scratch[1024];
@@ -160,6 +162,7 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
   __shared__ unsigned long long sh_k;
   for (int i = threadIdx.x; i < kSample; i += blockDim.x) sv[i] = sample[i];
   for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
+  for (int i = threadIdx.x; i < 2 * kMaxPools; i += blockDim.x) pool_cnt[i] = 0u;
   __syncthreads();
   const float lo = block_select_smem(sv, kSample, kSample / 2 - kSampleHalfWin, hist, scratch,
                                      &sh_bucket, &sh_k);
@@ -173,6 +176,8 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
     win->below = 0ull;
     win->active = 1u;
     win->fallback = 0u;
+    win->npool = npool;
+    win->poolcap = cap / npool;
     sigsvgd_bw_state& s = *state;
     s.prefix = 0u;
     s.k_rem = 0ull;
@@ -185,59 +190,200 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
   }
 }
 
-// cooperative: exact order statistic k among the candidates (or the whole matrix on fallback)
+// cooperative: exact order statistic k_total of the M x N matrix `dist`
+//   phase A  one pass over the matrix: count entries < lo, compact entries in [lo, hi] into this
+//            block's pool, and histogram them on the top 11 bits of (bits - lo_bits)
+//   phase B/C  one or two more 11-bit passes over the (short) pools
+//   fallback  (window missed / pool overflow): three radix passes over the full matrix
 __global__ void __launch_bounds__(1024)
-window_select_kernel(SelWindow* win, const float* __restrict__ cand, const float* __restrict__ dist,
-                     int64_t M, int64_t N, int64_t ldd, unsigned long long k_total,
-                     unsigned long long* ghist, float log_np1, float bw_scale, float tol,
-                     sigsvgd_bw_state* state) {
+window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
+                     const float* __restrict__ dist, int64_t M, int64_t N, int64_t ldd,
+                     unsigned long long k_total, unsigned long long* ghist, float log_np1,
+                     float bw_scale, float tol, sigsvgd_bw_state* state) {
   cg::grid_group grid = cg::this_grid();
   __shared__ unsigned int hist[kBins];
   __shared__ unsigned long long scratch[1024];
   __shared__ uint32_t sh_bucket;
   __shared__ unsigned long long sh_k;
-  const unsigned int n_cand = win->n_cand;
-  const unsigned long long below = win->below;
-  const bool ok = n_cand <= win->cap && k_total >= below && k_total < below + n_cand;
-  unsigned long long k = ok ? k_total - below : k_total;
-  const int64_t count = ok ? (int64_t)n_cand : M * N;
-  uint32_t prefix = 0;
-  for (int pass = 0; pass < 3; ++pass) {
-    for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
-    __syncthreads();
-    const int64_t step = (int64_t)gridDim.x * blockDim.x;
-    // whole warps iterate together (hist_add is warp-collective): loop on the warp's first index
-    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < count; i0 += step) {
-      const int64_t i = i0 + (threadIdx.x & 31);
-      float v = 0.f;
-      const bool inb = i < count;
-      if (inb) {
-        if (ok) {
-          v = __ldg(cand + i);
+  __shared__ unsigned int sh_ncand, sh_over, sh_fill, sh_blt;
+  __shared__ unsigned long long sh_below;
+  const unsigned int npool = win->npool, poolcap = win->poolcap;
+  const int lane = threadIdx.x & 31;
+  const uint32_t lo_bits = __float_as_uint(win->lo), span_bits = __float_as_uint(win->hi) - lo_bits;
+  // radix digits of (bits - lo_bits): s1 = shift of the top digit (11 bits), then s2, then 0
+  const int nbits = 32 - __clz(span_bits | 1u);
+  const int s1 = max(0, nbits - 11), s2 = max(0, s1 - 11);
+  float* __restrict__ pool = cand + (size_t)blockIdx.x * poolcap;
+
+  // ---------------------------------------------------------------- phase A
+  if (threadIdx.x == 0) sh_fill = 0u, sh_blt = 0u, sh_ncand = 0u, sh_over = 0u, sh_below = 0ull;
+  for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
+  if (blockIdx.x == 0)  // the global histograms are only added to after a grid barrier
+    for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
+  __syncthreads();
+  {
+    const bool vec = (N & 3) == 0 && (ldd & 3) == 0 && (reinterpret_cast<uintptr_t>(dist) & 15u) == 0;
+    const int64_t nq = vec ? N / 4 : N;  // items per row
+    unsigned int nlt = 0;
+    // a thread classifies its batch of values locally; the warp then reserves pool space with ONE
+    // shared-memory atomic per batch (exclusive scan of the per-thread hit counts)
+    auto flush = [&](const float* v, uint32_t hitmask, int nval) {  // warp-collective
+      const int hits = __popc(hitmask);
+      int incl = hits;
+#pragma unroll
+      for (int sft = 1; sft < 32; sft <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, sft);
+        if (lane >= sft) incl += t;
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      if (total == 0) return;  // warp-uniform
+      unsigned int base = 0;
+      if (lane == 31) base = atomicAdd(&sh_fill, (unsigned int)total);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      unsigned int off = base + (unsigned int)(incl - hits);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        if (e < nval && ((hitmask >> e) & 1u)) {
+          if (off < poolcap) pool[off] = v[e];
+          ++off;
+        }
+      }
+    };
+    constexpr int kRows = 4;  // rows in flight per block (independent loads)
+    for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows) {
+      for (int64_t c0 = threadIdx.x & ~31; c0 < nq; c0 += blockDim.x) {
+        const int64_t c = c0 + lane;
+        const bool cin = c < nq;
+        float v[16];
+        uint32_t validmask = 0;
+        if (vec) {
+#pragma unroll
+          for (int j = 0; j < kRows; ++j) {
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (cin && r0 + j < M) {
+              f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
+              validmask |= 0xfu << (4 * j);
+            }
+            v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
+          }
         } else {
+#pragma unroll
+          for (int j = 0; j < kRows; ++j) {
+            v[j] = 0.f;
+            if (cin && r0 + j < M) v[j] = __ldg(dist + (r0 + j) * ldd + c), validmask |= 1u << j;
+          }
+        }
+        uint32_t hitmask = 0;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          if (!vec && e >= kRows) break;
+          const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
+          const bool ok_e = (validmask >> e) & 1u;
+          nlt += (ok_e && bits < lo_bits) ? 1u : 0u;
+          if (ok_e && bits - lo_bits <= span_bits) hitmask |= 1u << e;
+        }
+        flush(v, hitmask, vec ? 16 : kRows);
+      }
+    }
+    unsigned int tot = nlt;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (lane == 0 && tot) atomicAdd(&sh_blt, tot);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      // plain stores of per-block results: the kernel is idempotent (no counters to reset)
+      pool_cnt[blockIdx.x] = sh_fill;
+      pool_cnt[kMaxPools + blockIdx.x] = sh_blt;  // < 2^32: rows are dealt evenly
+    }
+  }
+  __threadfence();
+  grid.sync();
+  for (unsigned int i = threadIdx.x; i < npool; i += blockDim.x) {
+    const unsigned int c = pool_cnt[i];
+    atomicAdd(&sh_ncand, min(c, poolcap));
+    atomicAdd(&sh_below, (unsigned long long)pool_cnt[kMaxPools + i]);
+    if (c > poolcap) sh_over = 1u;
+  }
+  __syncthreads();
+  const unsigned int n_cand = sh_ncand;
+  const unsigned long long below = sh_below;
+  const bool ok = sh_over == 0u && k_total >= below && k_total < below + n_cand;
+  uint32_t result_bits = 0;
+  if (ok) {
+    // ---------------------------------------------------------------- window hit: digits of rel
+    unsigned long long k = k_total - below;
+    uint32_t rel_prefix = 0;
+    const int shifts[3] = {s1, s2, 0};
+    const int prev[3] = {32, s1, s2};
+    for (int pass = 0; pass < 3; ++pass) {
+      const int sp = prev[pass];  // digits above sp are fixed
+      if (sp == 0) break;         // nothing left to refine (grid-uniform)
+      const int sh = shifts[pass];
+      for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
+      __syncthreads();
+      for (unsigned int pl = blockIdx.x; pl < npool; pl += gridDim.x) {
+        const unsigned int cnt = min(pool_cnt[pl], poolcap);
+        const float* src = cand + (size_t)pl * poolcap;
+        for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
+          const unsigned int i = i0 + (unsigned int)lane;
+          const bool inb = i < cnt;
+          const uint32_t rel = inb ? (__float_as_uint(src[i]) & 0x7fffffffu) - lo_bits : 0u;
+          const bool in = inb && (sp >= 32 || (rel >> sp) == (rel_prefix >> sp));
+          hist_add(hist, sp >= 32 ? (rel >> sh) : ((rel >> sh) & ((1u << (sp - sh)) - 1u)), in);
+        }
+      }
+      __syncthreads();
+      unsigned long long* g = ghist + pass * kBins;
+      for (int i = threadIdx.x; i < kBins; i += blockDim.x)
+        if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
+      grid.sync();
+      block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
+      rel_prefix |= sh_bucket << sh;
+      k = sh_k;
+      __syncthreads();
+    }
+    result_bits = lo_bits + rel_prefix;
+  } else {
+    // ---------------------------------------------------------------- fallback: full matrix
+    unsigned long long k = k_total;
+    uint32_t prefix = 0;
+    grid.sync();  // everybody has read ghist[0..kBins) of the window attempt
+    if (blockIdx.x == 0)
+      for (int i = threadIdx.x; i < kBins; i += blockDim.x) ghist[i] = 0ull;
+    grid.sync();
+    const int64_t count = M * N;
+    const int64_t step = (int64_t)gridDim.x * blockDim.x;
+    for (int pass = 0; pass < 3; ++pass) {
+      for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
+      __syncthreads();
+      for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < count; i0 += step) {
+        const int64_t i = i0 + lane;
+        float v = 0.f;
+        const bool inb = i < count;
+        if (inb) {
           const int64_t r = i / N;
           v = __ldg(dist + r * ldd + (i - r * N));
         }
+        uint32_t bin;
+        const bool in = radix_bin(__float_as_uint(v), pass, prefix, &bin) && inb;
+        hist_add(hist, bin, in);
       }
-      uint32_t bin;
-      const bool in = radix_bin(__float_as_uint(v), pass, prefix, &bin) && inb;
-      hist_add(hist, bin, in);
+      __syncthreads();
+      unsigned long long* g = ghist + pass * kBins;
+      for (int i = threadIdx.x; i < kBins; i += blockDim.x)
+        if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
+      grid.sync();
+      block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
+      const int shift = pass == 0 ? 21 : pass == 1 ? 10 : 0;
+      prefix |= sh_bucket << shift;
+      k = sh_k;
+      __syncthreads();
     }
-    __syncthreads();
-    unsigned long long* g = ghist + pass * kBins;
-    for (int i = threadIdx.x; i < kBins; i += blockDim.x)
-      if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
-    grid.sync();
-    // every block picks the bucket redundantly from the global histogram (no second barrier)
-    block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
-    const int shift = pass == 0 ? 21 : pass == 1 ? 10 : 0;
-    prefix |= sh_bucket << shift;
-    k = sh_k;
-    __syncthreads();
+    result_bits = prefix;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     sigsvgd_bw_state& s = *state;
-    const float med = __uint_as_float(prefix);
+    const float med = __uint_as_float(result_bits);
     float h = bw_scale * sqrtf(med / log_np1);  // math.py:31-34
     const bool clamped = !(h >= tol);
     if (clamped) h = tol;
@@ -245,7 +391,9 @@ window_select_kernel(SelWindow* win, const float* __restrict__ cand, const float
     s.h = h;
     s.gamma = -0.5f / (h * h);  // _kernels.py:110
     s.clamped = clamped ? 1u : 0u;
-    s.prefix = prefix;
+    s.prefix = result_bits;
+    win->n_cand = n_cand;
+    win->below = below;
     win->fallback = ok ? 0u : 1u;
   }
 }
@@ -258,12 +406,13 @@ size_t window_workspace_bytes(int64_t M, int64_t N, unsigned int* cap_out) {
   const unsigned int cap = (unsigned int)std::min<double>(want, 4.0e9);
   if (cap_out) *cap_out = cap;
   return (size_t)round_up((int64_t)sizeof(SelWindow), 256) + (size_t)round_up(sizeof(float) * kSample, 256) +
-         (size_t)round_up(sizeof(unsigned long long) * 3 * kBins, 256) + sizeof(float) * (size_t)cap;
+         (size_t)round_up(sizeof(unsigned long long) * 3 * kBins, 256) + sizeof(unsigned int) * 2 * kMaxPools +
+         sizeof(float) * (size_t)cap;
 }
 
-// ws layout: [SelWindow | sample | ghist | cand]
+// ws layout: [SelWindow | sample | ghist | pool_cnt[kMaxPools] + below_cnt[kMaxPools] | cand]
 static void window_carve(void* ws, SelWindow** win, float** sample, unsigned long long** ghist,
-                         float** cand) {
+                         unsigned int** pool_cnt, float** cand) {
   char* w = (char*)ws;
   *win = (SelWindow*)w;
   w += round_up((int64_t)sizeof(SelWindow), 256);
@@ -271,13 +420,15 @@ static void window_carve(void* ws, SelWindow** win, float** sample, unsigned lon
   w += round_up(sizeof(float) * kSample, 256);
   *ghist = (unsigned long long*)w;
   w += round_up(sizeof(unsigned long long) * 3 * kBins, 256);
+  *pool_cnt = (unsigned int*)w;
+  w += sizeof(unsigned int) * 2 * kMaxPools;
   *cand = (float*)w;
 }
 
-void window_pointers(void* ws, SelWindow** win, float** cand) {
+void window_pointers(void* ws, SelWindow** win, float** cand, unsigned int** pool_cnt) {
   float* sample;
   unsigned long long* ghist;
-  window_carve(ws, win, &sample, &ghist, cand);
+  window_carve(ws, win, &sample, &ghist, pool_cnt, cand);
 }
 
 int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,
@@ -287,7 +438,8 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
   SelWindow* win;
   float *sample, *cand;
   unsigned long long* ghist;
-  window_carve(ws, &win, &sample, &ghist, &cand);
+  unsigned int* pool_cnt;
+  window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand);
   unsigned int cap = 0;
   window_workspace_bytes(M, N, &cap);
   window_sample_kernel<<<kSample / 8, 256, 0, st>>>(a, lda, M, b, ldb, N, D, sample);
@@ -300,7 +452,9 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
                                      (int)(sizeof(float) * kSample)));
     configured_dev = dev;
   }
-  window_bounds_kernel<<<1, 1024, sizeof(float) * kSample, st>>>(sample, win, cap, ghist, state);
+  const unsigned int npool = (unsigned int)std::min(num_sms(), kMaxPools);
+  window_bounds_kernel<<<1, 1024, sizeof(float) * kSample, st>>>(sample, win, cap, npool, ghist, pool_cnt,
+                                                                 state);
   SIG_LAUNCH_OK("window_bounds_kernel");
   *win_out = win;
   *cand_out = cand;
@@ -314,11 +468,11 @@ int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int6
   SelWindow* win;
   float *sample, *cand;
   unsigned long long* ghist;
-  window_carve(ws, &win, &sample, &ghist, &cand);
+  unsigned int* pool_cnt;
+  window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand);
   const float log_np1 = (float)log((double)(float)((double)n_log + 1.0));
   unsigned long long k_total = (unsigned long long)((M * N - 1) / 2);
-  const float* cand_c = cand;
-  void* args[] = {(void*)&win,   (void*)&cand_c,   (void*)&dist, (void*)&M,   (void*)&N,    (void*)&ldd,
+  void* args[] = {(void*)&win,   (void*)&cand, (void*)&pool_cnt,  (void*)&dist, (void*)&M,   (void*)&N,    (void*)&ldd,
                   (void*)&k_total, (void*)&ghist, (void*)&log_np1, (void*)&bw_scale, (void*)&tol, (void*)&state};
   // one block per SM: co-resident by construction (cooperative launch checks it)
   SIG_CUDA_OK(cudaLaunchCooperativeKernel((const void*)window_select_kernel, dim3((unsigned)num_sms()),

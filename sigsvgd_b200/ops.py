@@ -239,13 +239,12 @@ def tc_median_prepare_raw(a_c: torch.Tensor, b_c: torch.Tensor, ws: torch.Tensor
 
 
 def tc_gram_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int, scales: torch.Tensor,
-                symmetric: bool = False, median_ws: Optional[torch.Tensor] = None,
-                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                symmetric: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     M, N = a.hi.shape[0], b.hi.shape[0]
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=a.hi.device)
     call("sigsvgd_tc_gram", _p(a.hi), _p(a.lo), a.ld, _p(na), _p(b.hi), _p(b.lo), b.ld, _p(nb), M, N, D, _p(scales),
-         int(symmetric), _p(median_ws), _p(out), out.stride(0), _stream())
+         int(symmetric), _p(out), out.stride(0), _stream())
     return out
 
 

@@ -56,7 +56,7 @@ def test_tc_gram_symmetric_and_single_pass_median(N, D, scale):
     state = ops.new_state(torch.device(DEV))
     ws = ops.tc_median_workspace(N, N, DEV)
     ops.tc_median_prepare_raw(sc, sc, ws, state)
-    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True, median_ws=ws)
+    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True)
     ops.tc_median_select_raw(ws, d, N, ops.Bandwidth.median(), state)
     got = d.cpu().numpy()
     s64 = s.astype(np.float64)
@@ -78,7 +78,7 @@ def test_tc_gram_symmetric_and_single_pass_median(N, D, scale):
     ws2 = ops.tc_median_workspace(M, N, DEV)
     state2 = ops.new_state(torch.device(DEV))
     ops.tc_median_prepare_raw(sc[:M], sc, ws2, state2)
-    d2 = ops.tc_gram_raw(pa, norms[:M], planes, norms, D, scales, symmetric=False, median_ws=ws2)
+    d2 = ops.tc_gram_raw(pa, norms[:M], planes, norms, D, scales, symmetric=False)
     ops.tc_median_select_raw(ws2, d2, N, ops.Bandwidth.median(), state2)
     g2 = d2.cpu().numpy()
     off = ~np.eye(N, dtype=bool)[:M]
@@ -96,7 +96,7 @@ def test_single_pass_median_falls_back_when_window_misses():
     state = ops.new_state(torch.device(DEV))
     ws = ops.tc_median_workspace(N, N, DEV)
     ops.tc_median_prepare_raw(sc, sc, ws, state)
-    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True, median_ws=ws)
+    d = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, symmetric=True)
     ops.tc_median_select_raw(ws, d, N, ops.Bandwidth.median(), state)
     got = d.cpu().numpy()
     assert np.float32(ops.read_state(state)["median"]) == np.sort(got.reshape(-1))[(N * N - 1) // 2]

@@ -45,11 +45,11 @@ state = ops.new_state(dev)
 ws = ops.tc_median_workspace(N, N, dev)
 ops.tc_median_prepare_raw(sc, sc, ws, state)
 res["median_prepare"] = timeit(lambda: ops.tc_median_prepare_raw(sc, sc, ws, state))
-res["tc_gram_sym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, None, dist))
-res["tc_gram_nonsym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, False, None, dist))
+res["tc_gram_sym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist))
+res["tc_gram_nonsym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, False, dist))
 def _gram_win():
     ops.tc_median_prepare_raw(sc, sc, ws, state)
-    ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, ws, dist)
+    ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist)
 res["prepare+tc_gram_sym_win"] = timeit(_gram_win)
 res["median_window_select"] = timeit(lambda: ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state))
 state = ops.bandwidth_raw(dist, ops.Bandwidth.median(), N)

@@ -33,6 +33,7 @@ struct SelWindow {
   // kernel appends to pool b through a shared-memory counter (no global atomics) and leaves its
   // fill count in pool_cnt[b] (a count above poolcap = overflow -> fallback).
   unsigned int npool, poolcap;
+  unsigned int epoch;        // parity selects the histogram / counter buffers of the next select
 };
 constexpr int kMaxPools = 1024;
 

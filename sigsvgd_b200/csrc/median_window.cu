@@ -161,8 +161,8 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
   __shared__ uint32_t sh_bucket;
   __shared__ unsigned long long sh_k;
   for (int i = threadIdx.x; i < kSample; i += blockDim.x) sv[i] = sample[i];
-  for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
-  for (int i = threadIdx.x; i < 2 * kMaxPools; i += blockDim.x) pool_cnt[i] = 0u;
+  for (int i = threadIdx.x; i < 2 * 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
+  for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += blockDim.x) pool_cnt[i] = 0u;
   __syncthreads();
   const float lo = block_select_smem(sv, kSample, kSample / 2 - kSampleHalfWin, hist, scratch,
                                      &sh_bucket, &sh_k);
@@ -177,6 +177,7 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
     win->active = 1u;
     win->fallback = 0u;
     win->npool = npool;
+    win->epoch = 0u;
     win->poolcap = cap / npool;
     sigsvgd_bw_state& s = *state;
     s.prefix = 0u;
@@ -190,27 +191,37 @@ window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned 
   }
 }
 
+constexpr int kShort = 4096;  // capacity of the short list finished by a single block
+
 // cooperative: exact order statistic k_total of the M x N matrix `dist`
 //   phase A  one pass over the matrix: count entries < lo, compact entries in [lo, hi] into this
-//            block's pool, and histogram them on the top 11 bits of (bits - lo_bits)
-//   phase B/C  one or two more 11-bit passes over the (short) pools
-//   fallback  (window missed / pool overflow): three radix passes over the full matrix
+//            block's pool and histogram them on the top 11 bits of rel = bits - lo_bits
+//   phase B  entries of the chosen bucket (a few hundred) are gathered into a short list which one
+//            block finishes in shared memory; buckets too big for that (massive ties) take up to
+//            two more 11-bit radix passes over the pools
+//   fallback (window missed / pool overflow): three radix passes over the full matrix
+// Histograms / counters are double-buffered on win->epoch so the kernel leaves them clean for the
+// next call without a trailing grid barrier.
 __global__ void __launch_bounds__(1024)
-window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
+window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float* shortlist,
                      const float* __restrict__ dist, int64_t M, int64_t N, int64_t ldd,
-                     unsigned long long k_total, unsigned long long* ghist, float log_np1,
+                     unsigned long long k_total, unsigned long long* ghist2, float log_np1,
                      float bw_scale, float tol, sigsvgd_bw_state* state) {
   cg::grid_group grid = cg::this_grid();
   __shared__ unsigned int hist[kBins];
   __shared__ unsigned long long scratch[1024];
+  __shared__ float sl[kShort];
   __shared__ uint32_t sh_bucket;
   __shared__ unsigned long long sh_k;
   __shared__ unsigned int sh_ncand, sh_over, sh_fill, sh_blt;
   __shared__ unsigned long long sh_below;
   const unsigned int npool = win->npool, poolcap = win->poolcap;
+  const unsigned int epoch = win->epoch & 1u;
+  unsigned long long* ghist = ghist2 + (size_t)epoch * 3 * kBins;
+  unsigned int* short_cnt = pool_cnt + 2 * kMaxPools + epoch;
   const int lane = threadIdx.x & 31;
   const uint32_t lo_bits = __float_as_uint(win->lo), span_bits = __float_as_uint(win->hi) - lo_bits;
-  // radix digits of (bits - lo_bits): s1 = shift of the top digit (11 bits), then s2, then 0
+  // radix digits of rel: s1 = shift of the top digit (<= 11 bits), then s2, then 0
   const int nbits = 32 - __clz(span_bits | 1u);
   const int s1 = max(0, nbits - 11), s2 = max(0, s1 - 11);
   float* __restrict__ pool = cand + (size_t)blockIdx.x * poolcap;
@@ -218,8 +229,11 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
   // ---------------------------------------------------------------- phase A
   if (threadIdx.x == 0) sh_fill = 0u, sh_blt = 0u, sh_ncand = 0u, sh_over = 0u, sh_below = 0ull;
   for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
-  if (blockIdx.x == 0)  // the global histograms are only added to after a grid barrier
-    for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
+  if (blockIdx.x == 0) {  // clean the OTHER buffer for the next call
+    unsigned long long* other = ghist2 + (size_t)(epoch ^ 1u) * 3 * kBins;
+    for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) other[i] = 0ull;
+    if (threadIdx.x == 0) pool_cnt[2 * kMaxPools + (epoch ^ 1u)] = 0u;
+  }
   __syncthreads();
   {
     const bool vec = (N & 3) == 0 && (ldd & 3) == 0 && (reinterpret_cast<uintptr_t>(dist) & 15u) == 0;
@@ -245,6 +259,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
       for (int e = 0; e < 16; ++e) {
         if (e < nval && ((hitmask >> e) & 1u)) {
           if (off < poolcap) pool[off] = v[e];
+          atomicAdd(&hist[((__float_as_uint(v[e]) & 0x7fffffffu) - lo_bits) >> s1], 1u);
           ++off;
         }
       }
@@ -253,8 +268,24 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
     for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows) {
       for (int64_t c0 = threadIdx.x & ~31; c0 < nq; c0 += blockDim.x) {
         const int64_t c = c0 + lane;
-        const bool cin = c < nq;
         float v[16];
+        uint32_t hitmask = 0;
+        if (vec && r0 + kRows <= M && c0 + 32 <= nq) {  // interior: no validity bookkeeping
+#pragma unroll
+          for (int j = 0; j < kRows; ++j) {
+            const float4 f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
+            v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
+          }
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
+            nlt += bits < lo_bits ? 1u : 0u;
+            if (bits - lo_bits <= span_bits) hitmask |= 1u << e;
+          }
+          flush(v, hitmask, 16);
+          continue;
+        }
+        const bool cin = c < nq;
         uint32_t validmask = 0;
         if (vec) {
 #pragma unroll
@@ -273,7 +304,6 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
             if (cin && r0 + j < M) v[j] = __ldg(dist + (r0 + j) * ldd + c), validmask |= 1u << j;
           }
         }
-        uint32_t hitmask = 0;
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           if (!vec && e >= kRows) break;
@@ -291,10 +321,12 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
     if (lane == 0 && tot) atomicAdd(&sh_blt, tot);
     __syncthreads();
     if (threadIdx.x == 0) {
-      // plain stores of per-block results: the kernel is idempotent (no counters to reset)
+      // plain stores of per-block results (nothing to reset between calls)
       pool_cnt[blockIdx.x] = sh_fill;
       pool_cnt[kMaxPools + blockIdx.x] = sh_blt;  // < 2^32: rows are dealt evenly
     }
+    for (int i = threadIdx.x; i < kBins; i += blockDim.x)
+      if (hist[i]) atomicAdd(&ghist[i], (unsigned long long)hist[i]);
   }
   __threadfence();
   grid.sync();
@@ -310,46 +342,83 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
   const bool ok = sh_over == 0u && k_total >= below && k_total < below + n_cand;
   uint32_t result_bits = 0;
   if (ok) {
-    // ---------------------------------------------------------------- window hit: digits of rel
+    // ---------------------------------------------------------------- window hit
     unsigned long long k = k_total - below;
-    uint32_t rel_prefix = 0;
-    const int shifts[3] = {s1, s2, 0};
-    const int prev[3] = {32, s1, s2};
-    for (int pass = 0; pass < 3; ++pass) {
-      const int sp = prev[pass];  // digits above sp are fixed
-      if (sp == 0) break;         // nothing left to refine (grid-uniform)
-      const int sh = shifts[pass];
-      for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
-      __syncthreads();
-      for (unsigned int pl = blockIdx.x; pl < npool; pl += gridDim.x) {
-        const unsigned int cnt = min(pool_cnt[pl], poolcap);
-        const float* src = cand + (size_t)pl * poolcap;
-        for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
-          const unsigned int i = i0 + (unsigned int)lane;
-          const bool inb = i < cnt;
-          const uint32_t rel = inb ? (__float_as_uint(src[i]) & 0x7fffffffu) - lo_bits : 0u;
-          const bool in = inb && (sp >= 32 || (rel >> sp) == (rel_prefix >> sp));
-          hist_add(hist, sp >= 32 ? (rel >> sh) : ((rel >> sh) & ((1u << (sp - sh)) - 1u)), in);
+    block_pick_bucket(ghist, k, &sh_bucket, &sh_k, scratch);
+    uint32_t rel_prefix = sh_bucket << s1;
+    k = sh_k;
+    const unsigned long long bucket_n = ghist[sh_bucket];
+    __syncthreads();
+    if (s1 == 0) {
+      result_bits = lo_bits + rel_prefix;
+    } else if (bucket_n <= (unsigned long long)kShort) {
+      // phase B: gather the bucket into the short list, one block finishes
+      const unsigned int cnt = min(pool_cnt[blockIdx.x], poolcap);
+      for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
+        const unsigned int i = i0 + (unsigned int)lane;
+        const float v = i < cnt ? pool[i] : 0.f;
+        const uint32_t rel = (__float_as_uint(v) & 0x7fffffffu) - lo_bits;
+        const bool in = i < cnt && (rel >> s1) == (rel_prefix >> s1);
+        const unsigned m = __ballot_sync(0xffffffffu, in);
+        if (m) {
+          unsigned int base = 0;
+          if (lane == 0) base = atomicAdd(short_cnt, (unsigned int)__popc(m));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (in) shortlist[base + __popc(m & ((1u << lane) - 1u))] = v;
         }
       }
-      __syncthreads();
-      unsigned long long* g = ghist + pass * kBins;
-      for (int i = threadIdx.x; i < kBins; i += blockDim.x)
-        if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
+      __threadfence();
       grid.sync();
-      block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
-      rel_prefix |= sh_bucket << sh;
-      k = sh_k;
-      __syncthreads();
+      if (blockIdx.x == 0) {
+        const int n = (int)bucket_n;
+        const int npad = (n + 1023) & ~1023;
+        for (int i = threadIdx.x; i < npad; i += blockDim.x) sl[i] = i < n ? shortlist[i] : __uint_as_float(0x7f800000u);
+        __syncthreads();
+        const float med = block_select_smem(sl, npad, k, hist, scratch, &sh_bucket, &sh_k);
+        result_bits = __float_as_uint(med) & 0x7fffffffu;
+      }
+    } else {
+      // massive ties: keep refining the digits of rel over the pools
+      const int shifts[2] = {s2, 0};
+      const int prev[2] = {s1, s2};
+      for (int pass = 1; pass <= 2; ++pass) {
+        const int sp = prev[pass - 1];  // digits above sp are fixed
+        if (sp == 0) break;             // nothing left to refine (grid-uniform)
+        const int sh = shifts[pass - 1];
+        for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0u;
+        __syncthreads();
+        for (unsigned int pl = blockIdx.x; pl < npool; pl += gridDim.x) {
+          const unsigned int cnt = min(pool_cnt[pl], poolcap);
+          const float* src = cand + (size_t)pl * poolcap;
+          for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
+            const unsigned int i = i0 + (unsigned int)lane;
+            const bool inb = i < cnt;
+            const uint32_t rel = inb ? (__float_as_uint(src[i]) & 0x7fffffffu) - lo_bits : 0u;
+            const bool in = inb && (rel >> sp) == (rel_prefix >> sp);
+            hist_add(hist, (rel >> sh) & ((1u << (sp - sh)) - 1u), in);
+          }
+        }
+        __syncthreads();
+        unsigned long long* g = ghist + pass * kBins;
+        for (int i = threadIdx.x; i < kBins; i += blockDim.x)
+          if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
+        __threadfence();
+        grid.sync();
+        block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
+        rel_prefix |= sh_bucket << sh;
+        k = sh_k;
+        __syncthreads();
+      }
+      result_bits = lo_bits + rel_prefix;
     }
-    result_bits = lo_bits + rel_prefix;
   } else {
     // ---------------------------------------------------------------- fallback: full matrix
     unsigned long long k = k_total;
     uint32_t prefix = 0;
-    grid.sync();  // everybody has read ghist[0..kBins) of the window attempt
+    grid.sync();  // every block has consumed the window attempt's histogram
     if (blockIdx.x == 0)
       for (int i = threadIdx.x; i < kBins; i += blockDim.x) ghist[i] = 0ull;
+    __threadfence();
     grid.sync();
     const int64_t count = M * N;
     const int64_t step = (int64_t)gridDim.x * blockDim.x;
@@ -372,6 +441,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
       unsigned long long* g = ghist + pass * kBins;
       for (int i = threadIdx.x; i < kBins; i += blockDim.x)
         if (hist[i]) atomicAdd(&g[i], (unsigned long long)hist[i]);
+      __threadfence();
       grid.sync();
       block_pick_bucket(g, k, &sh_bucket, &sh_k, scratch);
       const int shift = pass == 0 ? 21 : pass == 1 ? 10 : 0;
@@ -395,6 +465,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt,
     win->n_cand = n_cand;
     win->below = below;
     win->fallback = ok ? 0u : 1u;
+    win->epoch = win->epoch + 1u;  // the next call uses the buffers cleaned above
   }
 }
 
@@ -406,22 +477,25 @@ size_t window_workspace_bytes(int64_t M, int64_t N, unsigned int* cap_out) {
   const unsigned int cap = (unsigned int)std::min<double>(want, 4.0e9);
   if (cap_out) *cap_out = cap;
   return (size_t)round_up((int64_t)sizeof(SelWindow), 256) + (size_t)round_up(sizeof(float) * kSample, 256) +
-         (size_t)round_up(sizeof(unsigned long long) * 3 * kBins, 256) + sizeof(unsigned int) * 2 * kMaxPools +
-         sizeof(float) * (size_t)cap;
+         (size_t)round_up(sizeof(unsigned long long) * 2 * 3 * kBins, 256) +
+         sizeof(unsigned int) * (2 * kMaxPools + 64) + sizeof(float) * 4096 + sizeof(float) * (size_t)cap;
 }
 
-// ws layout: [SelWindow | sample | ghist | pool_cnt[kMaxPools] + below_cnt[kMaxPools] | cand]
+// ws layout: [SelWindow | sample | ghist x2 | pool_cnt[kMaxPools] + below_cnt[kMaxPools] + misc[64] |
+//             shortlist[4096] | cand]
 static void window_carve(void* ws, SelWindow** win, float** sample, unsigned long long** ghist,
-                         unsigned int** pool_cnt, float** cand) {
+                         unsigned int** pool_cnt, float** cand, float** shortlist = nullptr) {
   char* w = (char*)ws;
   *win = (SelWindow*)w;
   w += round_up((int64_t)sizeof(SelWindow), 256);
   *sample = (float*)w;
   w += round_up(sizeof(float) * kSample, 256);
   *ghist = (unsigned long long*)w;
-  w += round_up(sizeof(unsigned long long) * 3 * kBins, 256);
+  w += round_up(sizeof(unsigned long long) * 2 * 3 * kBins, 256);
   *pool_cnt = (unsigned int*)w;
-  w += sizeof(unsigned int) * 2 * kMaxPools;
+  w += sizeof(unsigned int) * (2 * kMaxPools + 64);
+  if (shortlist) *shortlist = (float*)w;
+  w += sizeof(float) * 4096;
   *cand = (float*)w;
 }
 
@@ -469,10 +543,11 @@ int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int6
   float *sample, *cand;
   unsigned long long* ghist;
   unsigned int* pool_cnt;
-  window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand);
+  float* shortlist;
+  window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand, &shortlist);
   const float log_np1 = (float)log((double)(float)((double)n_log + 1.0));
   unsigned long long k_total = (unsigned long long)((M * N - 1) / 2);
-  void* args[] = {(void*)&win,   (void*)&cand, (void*)&pool_cnt,  (void*)&dist, (void*)&M,   (void*)&N,    (void*)&ldd,
+  void* args[] = {(void*)&win,   (void*)&cand, (void*)&pool_cnt, (void*)&shortlist, (void*)&dist, (void*)&M,   (void*)&N,    (void*)&ldd,
                   (void*)&k_total, (void*)&ghist, (void*)&log_np1, (void*)&bw_scale, (void*)&tol, (void*)&state};
   // one block per SM: co-resident by construction (cooperative launch checks it)
   SIG_CUDA_OK(cudaLaunchCooperativeKernel((const void*)window_select_kernel, dim3((unsigned)num_sms()),

@@ -3,6 +3,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "gemm_tc.cuh"
 
@@ -31,13 +33,40 @@ int num_sms() {
   return cached;
 }
 
+// Per-device side stream + fork/join events: independent pieces of the fused update (the median
+// window preparation) run beside the main pipeline.  Event record / wait are asynchronous and
+// CUDA-graph capturable (the side stream joins a capture through the fork event).
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static int side_stream(SideStream** out) {
+  static SideStream table[64];
+  static std::mutex mu;
+  int dev = 0;
+  SIG_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("device index %d out of range", dev);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  SideStream& s = table[dev];
+  if (!s.stream) {
+    SIG_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    SIG_CUDA_OK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+    SIG_CUDA_OK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  }
+  *out = &s;
+  return 0;
+}
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 struct PhiLayout {
   int64_t D, P, C, Np;
   size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, total;
   // tensor-core path (B == 1): fp16 planes of F [N x C] and K [N x Np], norms, scales
-  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales, off_win;
+  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales, off_win, off_stats;
 };
 
 static size_t bump(size_t* cur, size_t bytes) {
@@ -64,7 +93,7 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   L.off_part = bump(&cur, sizeof(float) * B * 64 * L.D);
   L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
   L.Np = round_up(N, 64);
-  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = L.off_win = 0;
+  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = L.off_win = L.off_stats = 0;
   if (B == 1) {
     L.off_fh = bump(&cur, sizeof(__half) * N * L.C);
     L.off_fl = bump(&cur, sizeof(__half) * N * L.C);
@@ -73,6 +102,7 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
     L.off_norms = bump(&cur, sizeof(float) * N);
     L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
     L.off_win = bump(&cur, window_workspace_bytes(N, N, nullptr));
+    L.off_stats = bump(&cur, sizeof(float) * (L.D + 2));
   }
   L.total = cur;
   return L;
@@ -342,30 +372,40 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
 
   // K1: signatures of all B*N particles
   SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
-  if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
   // feature block (centred), its row pitch, and the [K.S | rowsum | K.score] blocks of `out`
   const float* feat;
   int64_t ldf;
   const float *out_ks, *out_rowsum, *out_kg;
+  SideStream* side = nullptr;
+  const bool median_tc = use_tc && bw_mode == SIGSVGD_BW_MEDIAN;
   if (use_tc) {
-    // planes F = [S - mean | 1 | score] (fp16 hi/lo), centred fp32 features in the V buffer
-    SIG_PROPAGATE(launch_tc_scales(sig, D, center ? mean : nullptr, N, D, score, P, P, C,
-                                   (unsigned int*)(scales + 4), scales, scales + 8, 1, st));
-    SIG_PROPAGATE(launch_tc_pack(score, P, P, sig, D, center ? mean : nullptr, N, D, scales, Fh, Fl,
-                                 C, C, norms, V, D, 1, st));
-    feat = V, ldf = D;
-    out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
-    // K4a: candidate window for the median from a sample of the matrix
-    if (bw_mode == SIGSVGD_BW_MEDIAN) {
+    if (median_tc) {
+      // K4a on the side stream: sample the distance matrix straight from the raw signatures
+      // (distances are translation invariant) and set the candidate window of the median
+      SIG_PROPAGATE(side_stream(&side));
+      SIG_CUDA_OK(cudaEventRecord(side->fork, st));
+      SIG_CUDA_OK(cudaStreamWaitEvent(side->stream, side->fork, 0));
       SelWindow* win = nullptr;
       float* cand = nullptr;
-      SIG_PROPAGATE(launch_window_prepare(V, D, N, V, D, N, D, w + L.off_win, state, &win, &cand, st));
+      SIG_PROPAGATE(launch_window_prepare(sig, D, N, sig, D, N, D, w + L.off_win, state, &win, &cand,
+                                          side->stream));
+      SIG_CUDA_OK(cudaEventRecord(side->join, side->stream));
     }
+    // statistics pass (column sums, maxima), then planes F = [S - mean | 1 | score] (fp16 hi/lo)
+    // with the centred fp32 features going to the V buffer
+    float* stats = (float*)(w + L.off_stats);
+    SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 1, st));
+    SIG_PROPAGATE(launch_tc_pack_stats(score, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales, scales + 8,
+                                       Fh, Fl, C, C, norms, V, D, mean, st));
+    feat = V, ldf = D;
+    out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
     // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product; upper triangle
     // mirrored)
     SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
                           scales + 1, 1, K, N, st));
+    if (median_tc) SIG_CUDA_OK(cudaStreamWaitEvent(st, side->join, 0));
   } else {
+    if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
     SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
     feat = V + P, ldf = C;
     out_kg = out, out_ks = out + P, out_rowsum = out + P + D;

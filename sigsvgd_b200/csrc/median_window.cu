@@ -36,28 +36,6 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
   return x;
 }
 
-// one warp per sample: d = |a_i - b_j|^2 over D columns (fp32, difference form)
-__global__ void __launch_bounds__(256)
-window_sample_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
-                     const float* __restrict__ b, int64_t ldb, int64_t N, int64_t D,
-                     float* __restrict__ sample) {
-  const int s = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (s >= kSample) return;
-  const int lane = threadIdx.x & 31;
-  const int64_t i = (int64_t)(((uint64_t)hash32(2u * s + 1u) * (uint64_t)M) >> 32);
-  const int64_t j = (int64_t)(((uint64_t)hash32(2u * s + 0x9e3779b9u) * (uint64_t)N) >> 32);
-  const float* __restrict__ ai = a + i * lda;
-  const float* __restrict__ bj = b + j * ldb;
-  float acc = 0.f;
-  for (int64_t c = lane; c < D; c += 32) {
-    const float t = __ldg(ai + c) - __ldg(bj + c);
-    acc = fmaf(t, t, acc);
-  }
-#pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (lane == 0) sample[s] = acc;
-}
-
 __device__ __forceinline__ bool radix_bin(uint32_t bits, int pass, uint32_t prefix, uint32_t* bin) {
   bits &= 0x7fffffffu;
   if (pass == 0) {
@@ -149,36 +127,120 @@ __device__ float block_select_smem(const float* vals, int n, unsigned long long 
   return __uint_as_float(prefix);
 }
 
-// one block: window bounds from the sample, reset of the window counters, the three global
-// histograms used by window_select, and of the bandwidth record
-__global__ void __launch_bounds__(1024)
-window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned int cap,
-                     unsigned int npool, unsigned long long* ghist /*[3*kBins]*/,
-                     unsigned int* pool_cnt /*[kMaxPools]*/, sigsvgd_bw_state* state) {
-  extern __shared__ float sv[];  // kSample floats
+// Fused window preparation.  Every block evaluates 128 sample entries d = |a_i - b_j|^2 (one warp
+// per sample, fp32 difference form; the features need not be centred).  The last block to finish
+// (ticket counter) sorts the 16384 samples in shared memory (bitonic) and sets the window to the
+// sample order statistics m/2 -+ 6 sigma; it also resets the window / histogram / bandwidth
+// records.
+constexpr int kPrepThreads = 1024;
+constexpr int kSamplesPerBlock = 64;
+
+__global__ void __launch_bounds__(kPrepThreads)
+window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
+                      const float* __restrict__ b, int64_t ldb, int64_t N, int64_t D,
+                      float* __restrict__ sample, unsigned int* ticket, SelWindow* win,
+                      unsigned int cap, unsigned int npool, unsigned long long* ghist /*[2*3*kBins]*/,
+                      unsigned int* pool_cnt /*[2*kMaxPools + 64]*/, sigsvgd_bw_state* state) {
+  extern __shared__ float sv[];  // kSample floats (last block only)
+  __shared__ bool sh_last;
   __shared__ unsigned int hist[kBins];
   __shared__ unsigned long long scratch[1024];
+  __shared__ float sh_red[64];
   __shared__ uint32_t sh_bucket;
   __shared__ unsigned long long sh_k;
-  for (int i = threadIdx.x; i < kSample; i += blockDim.x) sv[i] = sample[i];
-  for (int i = threadIdx.x; i < 2 * 3 * kBins; i += blockDim.x) ghist[i] = 0ull;
-  for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += blockDim.x) pool_cnt[i] = 0u;
+  uint32_t bin0 = 0;
+  float inv_w0 = 0.f;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll 1
+  for (int q = 0; q < kSamplesPerBlock / (kPrepThreads / 32); ++q) {
+    const int sidx = blockIdx.x * kSamplesPerBlock + q * (kPrepThreads / 32) + wid;
+    const int64_t i = (int64_t)(((uint64_t)hash32(2u * sidx + 1u) * (uint64_t)M) >> 32);
+    const int64_t j = (int64_t)(((uint64_t)hash32(2u * sidx + 0x9e3779b9u) * (uint64_t)N) >> 32);
+    const float* __restrict__ ai = a + i * lda;
+    const float* __restrict__ bj = b + j * ldb;
+    float acc = 0.f;
+#pragma unroll 4
+    for (int64_t c = lane; c < D; c += 32) {
+      const float t = __ldg(ai + c) - __ldg(bj + c);
+      acc = fmaf(t, t, acc);
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) sample[sidx] = acc;
+  }
+  __threadfence();
   __syncthreads();
-  const float lo = block_select_smem(sv, kSample, kSample / 2 - kSampleHalfWin, hist, scratch,
-                                     &sh_bucket, &sh_k);
-  const float hi = block_select_smem(sv, kSample, kSample / 2 + kSampleHalfWin, hist, scratch,
-                                     &sh_bucket, &sh_k);
+  if (threadIdx.x == 0) sh_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!sh_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < kSample; i += kPrepThreads) sv[i] = __ldcg(sample + i);
+  for (int i = threadIdx.x; i < 2 * 3 * kBins; i += kPrepThreads) ghist[i] = 0ull;
+  for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += kPrepThreads) pool_cnt[i] = 0u;  // incl. the ticket
+  __syncthreads();
+  // Window bounds = sample order statistics m/2 -+ 6 sigma, located by two levels of 2048 linear
+  // bins (whole range, then the selected bin) and rounded OUTWARD by one fine bin: the bounds only
+  // steer the search, so a slightly wider window is harmless.
+  float mn = INFINITY, mx = 0.f;
+  for (int i = threadIdx.x; i < kSample; i += kPrepThreads) {
+    const float v = sv[i];
+    mn = fminf(mn, v), mx = fmaxf(mx, v);
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  if (lane == 0) sh_red[wid] = mn, sh_red[32 + wid] = mx;
+  __syncthreads();
+  mn = sh_red[lane], mx = sh_red[32 + lane];
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  float bound[2];
+  const int ranks[2] = {kSample / 2 - kSampleHalfWin, kSample / 2 + kSampleHalfWin};
+  for (int which = 0; which < 2; ++which) {
+    float base = mn, width = fmaxf((mx - mn) * (1.f / kBins), 0.f);
+    unsigned long long k = (unsigned long long)ranks[which];
+    for (int level = 0; level < 2; ++level) {
+      const float inv_w = width > 0.f ? 1.f / width : 0.f;
+      for (int i = threadIdx.x; i < kBins; i += kPrepThreads) hist[i] = 0u;
+      __syncthreads();
+      for (int i = threadIdx.x; i < kSample; i += kPrepThreads) {
+        const float v = sv[i];
+        // level 1 keeps only the values that level 0 put into the selected bin
+        bool in = true;
+        if (level == 1) in = min(kBins - 1, (int)((v - mn) * inv_w0)) == (int)bin0;
+        if (in) atomicAdd(&hist[max(0, min(kBins - 1, (int)((v - base) * inv_w)))], 1u);
+      }
+      __syncthreads();
+      block_pick_bucket(hist, k, &sh_bucket, &sh_k, scratch);
+      k = sh_k;
+      if (level == 0) {
+        bin0 = sh_bucket;
+        inv_w0 = inv_w;
+        base = mn + (float)sh_bucket * width;
+        width *= (1.f / kBins);
+      } else {
+        const float edge = base + ((float)sh_bucket + (which == 0 ? -1.f : 2.f)) * width;
+        bound[which] = which == 0 ? fmaxf(edge, 0.f) : edge;
+      }
+      __syncthreads();
+    }
+  }
   if (threadIdx.x == 0) {
-    win->lo = lo;
-    win->hi = hi;
+    win->lo = fminf(bound[0], bound[1]);
+    win->hi = fmaxf(bound[0], bound[1]);
     win->n_cand = 0u;
     win->cap = cap;
     win->below = 0ull;
     win->active = 1u;
     win->fallback = 0u;
     win->npool = npool;
-    win->epoch = 0u;
     win->poolcap = cap / npool;
+    win->epoch = 0u;
     sigsvgd_bw_state& s = *state;
     s.prefix = 0u;
     s.k_rem = 0ull;
@@ -516,20 +578,20 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
   window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand);
   unsigned int cap = 0;
   window_workspace_bytes(M, N, &cap);
-  window_sample_kernel<<<kSample / 8, 256, 0, st>>>(a, lda, M, b, ldb, N, D, sample);
-  SIG_LAUNCH_OK("window_sample_kernel");
+  unsigned int* ticket = pool_cnt + 2 * kMaxPools + 2;
+  SIG_CUDA_OK(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
   static thread_local int configured_dev = -1;
   int dev = 0;
   SIG_CUDA_OK(cudaGetDevice(&dev));
   if (configured_dev != dev) {
-    SIG_CUDA_OK(cudaFuncSetAttribute(window_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SIG_CUDA_OK(cudaFuncSetAttribute(window_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(sizeof(float) * kSample)));
     configured_dev = dev;
   }
   const unsigned int npool = (unsigned int)std::min(num_sms(), kMaxPools);
-  window_bounds_kernel<<<1, 1024, sizeof(float) * kSample, st>>>(sample, win, cap, npool, ghist, pool_cnt,
-                                                                 state);
-  SIG_LAUNCH_OK("window_bounds_kernel");
+  window_prepare_kernel<<<kSample / kSamplesPerBlock, kPrepThreads, sizeof(float) * kSample, st>>>(
+      a, lda, M, b, ldb, N, D, sample, ticket, win, cap, npool, ghist, pool_cnt, state);
+  SIG_LAUNCH_OK("window_prepare_kernel");
   *win_out = win;
   *cand_out = cand;
   return 0;

@@ -133,6 +133,139 @@ pack_planes_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
   if (lane == 0 && norms) norms[row] = nrm;
 }
 
+// ---------------------------------------------------------------------------------------------
+// fused front end of the tensor-core path: one statistics pass + one packing pass
+//   stats[0..D)  = column sums of s (float atomics)      stats[D] = max |s| bits
+//   stats[D+1]   = max |score| bits                       (zeroed by the launcher)
+// The pack kernel derives the mean and the scales itself: alpha_S from the bound
+// max|s - mean| <= max|s| + max|mean| (the planes keep >= 22 significant bits as long as the
+// centred features are not 2^17 times smaller than that bound).
+// ---------------------------------------------------------------------------------------------
+constexpr int kStatThreads = 512;
+
+__global__ void __launch_bounds__(kStatThreads)
+stats_kernel(const float* __restrict__ s, int64_t lds, int64_t N, int64_t D,
+             const float* __restrict__ score, int64_t lsc, int64_t P, int rows_per_block,
+             float* __restrict__ stats) {
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = min(N, r0 + rows_per_block);
+  float ms = 0.f, mg = 0.f;
+  for (int64_t c = threadIdx.x; c < D; c += kStatThreads) {
+    float sum = 0.f;
+    int64_t r = r0;
+    for (; r + 4 <= r1; r += 4) {  // four independent loads in flight
+      const float v0 = __ldg(s + r * lds + c), v1 = __ldg(s + (r + 1) * lds + c);
+      const float v2 = __ldg(s + (r + 2) * lds + c), v3 = __ldg(s + (r + 3) * lds + c);
+      sum += (v0 + v1) + (v2 + v3);
+      ms = fmaxf(fmaxf(ms, fmaxf(fabsf(v0), fabsf(v1))), fmaxf(fabsf(v2), fabsf(v3)));
+    }
+    for (; r < r1; ++r) {
+      const float v = __ldg(s + r * lds + c);
+      sum += v;
+      ms = fmaxf(ms, fabsf(v));
+    }
+    atomicAdd(stats + c, sum);
+  }
+  for (int64_t c = threadIdx.x; c < P; c += kStatThreads) {
+    int64_t r = r0;
+    for (; r + 4 <= r1; r += 4) {
+      const float v0 = __ldg(score + r * lsc + c), v1 = __ldg(score + (r + 1) * lsc + c);
+      const float v2 = __ldg(score + (r + 2) * lsc + c), v3 = __ldg(score + (r + 3) * lsc + c);
+      mg = fmaxf(fmaxf(mg, fmaxf(fabsf(v0), fabsf(v1))), fmaxf(fabsf(v2), fabsf(v3)));
+    }
+    for (; r < r1; ++r) mg = fmaxf(mg, fabsf(__ldg(score + r * lsc + c)));
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    ms = fmaxf(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+    mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    unsigned int* mx = reinterpret_cast<unsigned int*>(stats + D);
+    if (ms > 0.f && ms < INFINITY) atomicMax(mx, __float_as_uint(ms));
+    if (mg > 0.f && mg < INFINITY) atomicMax(mx + 1, __float_as_uint(mg));
+  }
+}
+
+// one warp per row; every block derives mean / scales from `stats` (n_total rows contributed)
+__global__ void __launch_bounds__(kThreads)
+pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
+                  const float* __restrict__ s, int64_t lds, const float* __restrict__ stats,
+                  int64_t n_total, int center, int64_t N, int64_t D, float* __restrict__ tcs,
+                  float* __restrict__ colscale, __half* __restrict__ fh, __half* __restrict__ fl,
+                  int64_t ldp, int64_t Cp, float* __restrict__ norms, float* __restrict__ sc,
+                  int64_t ldsc, float* __restrict__ mean_out) {
+  __shared__ float sh_mm[kThreads / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const float inv_n = center ? 1.f / (float)n_total : 0.f;
+  float mm = 0.f;  // max |mean|
+  for (int64_t c = threadIdx.x; c < D; c += kThreads) mm = fmaxf(mm, fabsf(stats[c] * inv_n));
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) mm = fmaxf(mm, __shfl_xor_sync(0xffffffffu, mm, o));
+  if (lane == 0) sh_mm[wid] = mm;
+  __syncthreads();
+  mm = 0.f;
+#pragma unroll
+  for (int i = 0; i < kThreads / 32; ++i) mm = fmaxf(mm, sh_mm[i]);
+  const unsigned int* mx = reinterpret_cast<const unsigned int*>(stats + D);
+  const float as = pow2_scale(__uint_as_float(mx[0]) + mm);
+  const float ag = pow2_scale(__uint_as_float(mx[1]));
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) {
+      tcs[0] = as;
+      tcs[1] = (1.f / as) * (1.f / as);
+      tcs[2] = ag;
+      tcs[3] = 0.f;
+    }
+    for (int64_t c = threadIdx.x; c < Cp; c += kThreads) {
+      float v = 0.f;
+      if (c < D) v = 1.f / (kKScale * as);
+      else if (c == D) v = 1.f / kKScale;
+      else if (c < D + 1 + P) v = 1.f / (kKScale * ag);
+      colscale[c] = v;
+    }
+    if (mean_out)
+      for (int64_t c = threadIdx.x; c < D; c += kThreads) mean_out[c] = stats[c] * inv_n;
+  }
+  const int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + wid;
+  if (row >= N) return;
+  float nrm = 0.f;
+  for (int64_t c0 = 2 * lane; c0 < Cp; c0 += 64) {
+    float x[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int64_t c = c0 + e;
+      float v = 0.f;
+      if (c < D) {
+        v = __ldg(s + row * lds + c) - stats[c] * inv_n;
+        if (sc) sc[row * ldsc + c] = v;
+        v *= as;
+      } else if (c == D) {
+        v = 1.f;
+      } else if (c < D + 1 + P) {
+        v = __ldg(score + row * lsc + (c - D - 1)) * ag;
+      }
+      x[e] = v;
+    }
+    __half h0, l0, h1, l1;
+    split_half(x[0], h0, l0);
+    split_half(x[1], h1, l1);
+    if (c0 < D) {
+      const float r0 = __half2float(h0) + __half2float(l0);
+      nrm = fmaf(r0, r0, nrm);
+    }
+    if (c0 + 1 < D) {
+      const float r1 = __half2float(h1) + __half2float(l1);
+      nrm = fmaf(r1, r1, nrm);
+    }
+    *reinterpret_cast<__half2*>(fh + row * ldp + c0) = __halves2half2(h0, h1);
+    *reinterpret_cast<__half2*>(fl + row * ldp + c0) = __halves2half2(l0, l1);
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+  if (lane == 0 && norms) norms[row] = nrm;
+}
+
 __device__ __forceinline__ double block_sum_double(double v, double* sm) {
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -253,6 +386,35 @@ int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, i
   pack_planes_kernel<<<(unsigned)ceil_div(rows, kThreads / 32), kThreads, 0, st>>>(
       score, lsc, P, s, lds, mean, N, D, tcs, fh, fl, ldp, Cp, norms, sc, ldsc, rows);
   SIG_LAUNCH_OK("pack_planes_kernel");
+  return 0;
+}
+
+int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
+                    int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && (P == 0 || (score && lsc >= P)),
+                "tc_stats: bad shape N=%lld D=%lld P=%lld", (long long)N, (long long)D, (long long)P);
+  if (zero_first) SIG_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * (D + 2), st));
+  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)num_sms() * 2, ceil_div(N, 8)));
+  const int rows_per_block = (int)ceil_div(N, blocks);
+  stats_kernel<<<(unsigned)ceil_div(N, rows_per_block), kStatThreads, 0, st>>>(s, lds, N, D, score, lsc, P,
+                                                                            rows_per_block, stats);
+  SIG_LAUNCH_OK("stats_kernel");
+  return 0;
+}
+
+int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float* s, int64_t lds,
+                         const float* stats, int64_t n_total, int center, int64_t N, int64_t D,
+                         float* tcs, float* colscale, __half* fh, __half* fl, int64_t ldp, int64_t Cp,
+                         float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st) {
+  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && Cp >= D + 1 + P && ldp >= Cp && (Cp & 7) == 0 &&
+                    (ldp & 7) == 0 && (sc == nullptr || ldsc >= D) && n_total >= 1,
+                "tc_pack_stats: bad shape N=%lld D=%lld P=%lld Cp=%lld ldp=%lld", (long long)N, (long long)D,
+                (long long)P, (long long)Cp, (long long)ldp);
+  SIG_CHECK_ARG(P == 0 || (score != nullptr && lsc >= P), "tc_pack_stats: score is NULL but P > 0");
+  pack_stats_kernel<<<(unsigned)ceil_div(N, kThreads / 32), kThreads, 0, st>>>(
+      score, lsc, P, s, lds, stats, n_total, center, N, D, tcs, colscale, fh, fl, ldp, Cp, norms, sc, ldsc,
+      mean_out);
+  SIG_LAUNCH_OK("pack_stats_kernel");
   return 0;
 }
 

@@ -14,8 +14,15 @@ signature depth 3): X [N,64,7], score [N,448] -> phi [N,64,7].  Prints ONE JSON 
 * --impl reference : the reference's CPU implementation (oracle port: the reference's own torch
                statements + the C/OpenMP signature restatement; `signatory` itself is absent)
 
-N > 1 (torchrun): the swarm is sharded row-block over the ranks (strong scaling at fixed
-`--particles`): all-gather of signatures + scores, histogram all-reduces for the global median.
+N > 1 (torchrun), two things are measured and both are in the line:
+* headline `value` ("scaling": "weak"): every rank updates its OWN independent swarm of
+  `--particles` particles -- no communication (BASELINE.json north_star: "batches of independent
+  planning problems shard with no communication"; also the reference's only multi-GPU mode,
+  examples/script_planning_robot.py:619-631); value = ranks x updates / max-over-ranks time.
+* `sharded_swarm`: ONE swarm sharded row-block over the ranks (all-gather of signatures + scores
+  over NCCL, histogram all-reduces for the exact global median), at `--particles` and at
+  `--large-particles` (default 65536, the north star's 1 -> 8 GPU scaling point; the same keys are
+  printed at N = 1 from the single-GPU path so the speed-up can be read across runs).
 """
 from __future__ import annotations
 
@@ -33,6 +40,10 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 T_STEPS, D_CH, DEPTH = 64, 7, 3
+# kernels of libsigsvgd_b200.so launched by one sigsvgd_phi call on the tcgen05 path (sig fwd, window
+# prepare, stats, pack, Gram, window select, rbf planes, median coef, K.F, sig grad, sig bwd); the
+# two memset nodes are not counted
+LAUNCHES_PER_UPDATE = 11
 METRIC = "svgd_phi_updates_per_sec"
 UNIT = "phi-updates/s"
 
@@ -44,6 +55,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=4096)
+    ap.add_argument("--large-particles", type=int, default=65536,
+                    help="swarm size of the extra row-block-sharded measurement (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-steps", type=int, default=3)
     return ap.parse_args()
@@ -140,10 +153,10 @@ def run_reference(args):
     sample = f"{steps} full phi-updates at N={N}, T={T_STEPS}, d={D_CH}, depth={DEPTH} (oracle port, all host threads)"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(N), "particles": N, "waypoints": T_STEPS, "channels": D_CH,
-                   "depth": DEPTH},
+                   "depth": DEPTH, "note": "host CPU arm: one swarm at a time on all host threads, whatever --gpus is"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -177,24 +190,21 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
     N = args.particles
-    if N % world:
-        raise SystemExit(f"--particles {N} must be divisible by the number of ranks {world}")
-    M = N // world
-    Xh, Gh = make_inputs(N)
-    Xh, Gh = Xh[rank * M:(rank + 1) * M].contiguous().pin_memory(), Gh[rank * M:(rank + 1) * M].contiguous().pin_memory()
+    # headline: one independent swarm of N particles per rank (rank r's swarm has seed r)
+    Xh, Gh = make_inputs(N, seed=rank)
+    Xh, Gh = Xh.pin_memory(), Gh.pin_memory()
     X, G = Xh.to(dev), Gh.to(dev)
     phi_host = torch.empty_like(Xh).pin_memory()
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
+    M = N
 
     def step_device():
-        if world == 1:
-            return ops.phi(X, G, depth=DEPTH).phi
-        return phi_sharded(X, G, depth=DEPTH).phi
+        return ops.phi(X, G, depth=DEPTH).phi
 
     def step_e2e():
         x = Xh.to(dev, non_blocking=True)
         g = Gh.to(dev, non_blocking=True)
-        p = ops.phi(x, g, depth=DEPTH).phi if world == 1 else phi_sharded(x, g, depth=DEPTH).phi
+        p = ops.phi(x, g, depth=DEPTH).phi
         phi_host.copy_(p, non_blocking=True)
         return p
 
@@ -222,6 +232,36 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()) / steps
 
+    def sharded_swarm(Ns, steps, warmup):
+        """ONE swarm of Ns particles, row-block over the ranks (single-GPU fused path at world 1)."""
+        try:
+            if Ns % world:
+                return {"particles": Ns, "error": f"not divisible by {world} ranks"}
+            Ms = Ns // world
+            # only this rank's rows are generated (rows are i.i.d. random walks)
+            g = torch.Generator().manual_seed(1234 + rank)
+            xs = torch.cumsum(0.05 * torch.randn(Ms, T_STEPS, D_CH, generator=g), dim=1).to(dev)
+            gs = torch.randn(Ms, T_STEPS * D_CH, generator=g).to(dev)
+            if world == 1:
+                fn = lambda: ops.phi(xs, gs, depth=DEPTH).phi  # noqa: E731
+            else:
+                fn = lambda: phi_sharded(xs, gs, depth=DEPTH).phi  # noqa: E731
+            ms = timed(fn, steps, warmup)
+            out = fn()
+            ok = bool(torch.isfinite(out).all().item())
+            del xs, gs, out
+            ops._WS_CACHE.clear()
+            torch.cuda.empty_cache()
+            D = ops.sig_channels(D_CH, DEPTH)
+            flops = 2.0 * Ns * Ns * (2 * D + T_STEPS * D_CH)
+            return {"particles": Ns, "ms_per_step": ms, "value": 1e3 / ms, "unit": UNIT, "steps": steps,
+                    "warmup": warmup, "finite": ok, "algorithmic_tflops": flops / (ms * 1e-3) / 1e12,
+                    "exchange": ("none (one GPU)" if world == 1 else
+                                 "NCCL all-gather of [S|score] rows + 3 histogram all-reduces + 1 stats all-reduce")}
+        except Exception as e:  # the headline must survive a failure of the extra measurement
+            torch.cuda.empty_cache()
+            return {"particles": Ns, "error": f"{type(e).__name__}: {e}"[:300]}
+
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -236,19 +276,18 @@ def run_ours(args):
         P = T_STEPS * D_CH
         Xa, Ga = make_inputs(N)
         s_all = ops.signature_fwd_raw(Xa.to(dev), DEPTH, True)
-        use_tc = world == 1 and ops.tc_available() and N >= 1024  # what the timed step actually ran
+        use_tc = ops.tc_available() and N >= 1024  # what the timed step actually ran
         if use_tc:
             # the tcgen05 contraction K.[S - mean | 1 | score] exactly as sigsvgd_phi launches it
             planes, norms, scales, sc = ops.tc_pack_raw(s_all, ops.col_mean(s_all), Ga.to(dev))
-            rows = ops.Planes(planes.hi[rank * M:(rank + 1) * M], planes.lo[rank * M:(rank + 1) * M])
-            d_rows = ops.tc_gram_raw(rows, norms[rank * M:(rank + 1) * M], planes, norms, D, scales, world == 1)
+            d_rows = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True)
             st = ops.bandwidth_raw(d_rows.clone(), ops.Bandwidth.median(), N)
             kpl = ops.tc_rbf_raw(d_rows, st)
             dominant = lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)  # noqa: E731
             kname = "tc_matmul_kernel (tcgen05 split-fp16, K.[S|1|score])"
         else:
             v_all = ops.pack_features(s_all, ops.col_mean(s_all), Ga.to(dev))
-            k_rows = ops.sqdist_raw(v_all[rank * M:(rank + 1) * M, P:], v_all[:, P:], D)
+            k_rows = ops.sqdist_raw(v_all[:, P:], v_all[:, P:], D)
             st = ops.bandwidth_raw(k_rows.clone(), ops.Bandwidth.median(), N)
             ops.rbf_apply_raw(k_rows, st)
             dominant = lambda: ops.matmul_nn_raw(k_rows, v_all)  # noqa: E731
@@ -282,6 +321,13 @@ def run_ours(args):
                 "step_algorithmic_flops": 2.0 * M * N * (2 * D + P),
                 "step_frac_of_peak": 2.0 * M * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak}
 
+    # ---- one swarm sharded row-block over the ranks (the path's NCCL exchange) ------------------
+    sharded = []
+    if world > 1:
+        sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
+    if args.large_particles > 0:
+        sharded.append(sharded_swarm(args.large_particles, 3, 3))
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         val, cores, dt = cpu_phi_updates(N, args.cpu_steps, warmup=1)
@@ -291,16 +337,23 @@ def run_ours(args):
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": 1e3 / ms_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
+            "metric": METRIC, "value": world * 1e3 / ms_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(N), "particles": N, "waypoints": T_STEPS, "channels": D_CH,
-                       "depth": DEPTH, "sharding": "row-block" if world > 1 else "none",
+                       "depth": DEPTH,
+                       "sharding": ("none" if world == 1 else
+                                    f"replicas: {world} independent swarms of {N} particles, one per GPU, no communication "
+                                    "(north_star: independent planning problems; reference: "
+                                    "examples/script_planning_robot.py:619-631); see sharded_swarm for ONE swarm "
+                                    "sharded row-block over NCCL"),
                        "l2": "256 MB buffer written between timed iterations", "k_xx_materialised_to_caller": False},
             "clocks": clocks,
-            "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": int(Xh.numel() + Gh.numel()) * 4,
-                    "d2h_bytes_per_step": int(phi_host.numel()) * 4, "ms_per_step": ms_e2e},
-            "gpu_launches": 19 * args.steps,
+            "e2e": {"value": world * 1e3 / ms_e2e, "unit": UNIT,
+                    "h2d_bytes_per_step": world * int(Xh.numel() + Gh.numel()) * 4,
+                    "d2h_bytes_per_step": world * int(phi_host.numel()) * 4, "ms_per_step": ms_e2e},
+            "gpu_launches": world * LAUNCHES_PER_UPDATE * args.steps,
+            "sharded_swarm": sharded,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

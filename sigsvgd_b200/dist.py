@@ -37,23 +37,76 @@ def shard_scenes(n_scenes: int, rank: int, world: int) -> range:
     return range(lo, hi)
 
 
+@dataclass
+class Features:
+    """Operands of the two contractions, as one backend prepared them (opaque to the orchestration).
+
+    ``sc_all``/``sc_loc``: 2-D fp32 views whose first D columns are the centred features of all
+    particles / of this rank's rows; ``data``: whatever the backend's Gram and K.F kernels read."""
+
+    sc_all: torch.Tensor
+    sc_loc: torch.Tensor
+    data: object
+
+
 class CudaBackend:
-    """Thin adapter over ``ops``' raw wrappers (each one C-ABI call)."""
+    """Thin adapter over ``ops``' raw wrappers (each one C-ABI call).
+
+    ``tc=None`` picks the tcgen05 split-fp16 kernels when the swarm is large enough for them to
+    pay (N >= 1024, like ``sigsvgd_phi``), else the exact-fp32 SIMT kernels."""
 
     name = "cuda"
+
+    def __init__(self, tc: Optional[bool] = None):
+        self.tc = tc
+
+    def _use_tc(self, N: int) -> bool:
+        if self.tc is None:
+            return N >= 1024 and ops.tc_available()
+        if self.tc and not ops.tc_available():
+            raise RuntimeError("tcgen05 path requested but cuTensorMapEncodeTiled is unavailable")
+        return bool(self.tc)
 
     def sig_fwd(self, x, depth):
         return ops.signature_fwd_raw(x, depth, True)
 
-    def col_mean(self, s):
-        return ops.col_mean(s)
+    # ---- operand preparation / Gram / RBF / contraction ---------------------------------------
+    def pack(self, s_all, g_all, center, r0, M) -> Features:
+        N, D = s_all.shape
+        P = g_all.shape[1]
+        mean = ops.col_mean(s_all) if center else None
+        if self._use_tc(N):
+            planes, norms, scales, sc = ops.tc_pack_raw(s_all, mean, g_all)
+            return Features(sc, sc[r0:r0 + M], ("tc", planes, norms, scales, D, P, r0, M))
+        v = ops.pack_features(s_all, mean, g_all.contiguous())  # [N, C] = [score | S - mean | 1 | 0]
+        return Features(v[:, P:], v[r0:r0 + M, P:], ("simt", v, D, P, r0, M))
 
-    def pack_v(self, score, s, mean):
-        return ops.pack_features(s, mean, score)
+    def gram(self, f: Features) -> torch.Tensor:
+        if f.data[0] == "tc":
+            _, planes, norms, scales, D, P, r0, M = f.data
+            rows = ops.Planes(planes.hi[r0:r0 + M], planes.lo[r0:r0 + M])
+            return ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False)
+        _, v, D, P, r0, M = f.data
+        return ops.sqdist_raw(v[r0:r0 + M, P:], v[:, P:], D)
 
-    def sqdist(self, a, b, D):
-        return ops.sqdist_raw(a, b, D)
+    def rbf(self, k_rows, state, row_offset, f: Features, want_k: bool):
+        """exp in place (SIMT) or into fp16 planes (tcgen05).  Adds this strip's sum K*d / ties to
+        ``state``.  Returns the contraction operand."""
+        if f.data[0] == "tc":
+            return ops.tc_rbf_raw(k_rows, state, row_offset, want_k)
+        return ops.rbf_apply_raw(k_rows, state, row_offset)
 
+    def contract(self, kmat, f: Features):
+        """-> (K.Sc [M,D], rowsum [M], K.score [M,P]) views of one [M, C] result."""
+        if f.data[0] == "tc":
+            _, planes, norms, scales, D, P, r0, M = f.data
+            out = ops.tc_matmul_raw(kmat, planes, planes.hi.shape[0], D + 1 + P, scales)
+            return out[:, :D], out[:, D], out[:, D + 1:D + 1 + P]
+        _, v, D, P, r0, M = f.data
+        out = ops.matmul_nn_raw(kmat, v)
+        return out[:, P:P + D], out[:, P + D], out[:, :P]
+
+    # ---- bandwidth ------------------------------------------------------------------------------
     def new_state(self, device):
         return ops.new_state(device)
 
@@ -76,18 +129,12 @@ class CudaBackend:
     def select_finish(self, n_log, bw_scale, tol, state):
         _lib.call("sigsvgd_select_finish", n_log, float(bw_scale), float(tol), state.data_ptr(), ops._stream())
 
-    def rbf_apply(self, k, state, row_offset):
-        return ops.rbf_apply_raw(k, state, row_offset)
-
     def local_stats(self, state):
-        """(sum_kd [1] float64, n_ties [1] int64) device tensors for the all-reduce."""
-        return ops.state_field(state, "sum_kd").clone(), ops.state_field(state, "n_ties").to(torch.int64).clone()
+        """[sum_kd, n_ties] as one float64 device tensor for the all-reduce."""
+        return torch.cat([ops.state_field(state, "sum_kd"), ops.state_field(state, "n_ties").to(torch.float64)])
 
-    def median_coef(self, state, enable, sum_kd_all, n_ties_all):
-        ops.median_coef_raw(state, enable, sum_kd_all, n_ties_all.to(torch.int32))
-
-    def matmul_nn(self, a, v):
-        return ops.matmul_nn_raw(a, v)
+    def median_coef(self, state, enable, stats):
+        ops.median_coef_raw(state, enable, stats[:1].contiguous(), stats[1:].to(torch.int32))
 
     def sig_grad(self, sc, sc_all, ks, rowsum, state, row_offset):
         return ops.sig_grad_raw(sc, sc_all, ks, rowsum, state, row_offset)
@@ -136,16 +183,15 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
         s_all, g_all = allp[:, :D], allp[:, D:]
     else:
         s_all, g_all = s_local, g_local
-    mean = be.col_mean(s_all) if center else None
-    v_all = be.pack_v(g_all.contiguous(), s_all, mean)  # [N, C] = [score | S - mean | 1 | 0]
-    f_all = v_all[:, P:]
-    f_loc = v_all[r0:r0 + M, P:]
-    k_rows = be.sqdist(f_loc, f_all, D)  # [M, N]
+    feat = be.pack(s_all, g_all, center, r0, M)
+    k_rows = be.gram(feat)  # [M, N] squared distances of this rank's rows
 
     state = be.new_state(x_local.device)
     if bw.mode == _lib.BW_FIXED:
         be.fixed_bandwidth(bw.h, state)
     else:
+        # exact GLOBAL lower median: radix select (11/11/10 bits of the fp32 patterns), one 16 KiB
+        # histogram all-reduce per pass; every rank ends with the same median and h
         hist = be.new_hist(x_local.device)
         be.select_begin(state, hist, (N * N - 1) // 2)
         for p in range(3):
@@ -154,16 +200,15 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
             be.select_scan(p, state, hist)
         be.select_finish(N, bw.bw_scale, bw.tol, state)
-    be.rbf_apply(k_rows, state, r0)
-    sum_kd, n_ties = be.local_stats(state)
+    kmat = be.rbf(k_rows, state, r0, feat, want_k)
+    stats = be.local_stats(state)
     if world > 1:
-        dist.all_reduce(sum_kd, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(n_ties, op=dist.ReduceOp.SUM, group=group)
-    be.median_coef(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad, sum_kd, n_ties)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
+    be.median_coef(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad, stats)
 
-    out = be.matmul_nn(k_rows, v_all)  # [M, C] = [K.score | K.S | rowsum | 0]
-    g = be.sig_grad(f_loc, f_all, out[:, P:P + D], out[:, P + D], state, r0)
-    phi = be.sig_bwd(x_local, s_local, g, depth, out, 1.0 / N, -1.0 / N)
+    ks, rowsum, kg = be.contract(kmat, feat)  # K.Sc [M,D], row sums [M], K.score [M,P]
+    g = be.sig_grad(feat.sc_loc, feat.sc_all, ks, rowsum, state, r0)
+    phi = be.sig_bwd(x_local, s_local, g, depth, kg, 1.0 / N, -1.0 / N)
     return ShardedPhi(phi, state, k_rows if want_k else None, (r0, r0 + M))
 
 

@@ -268,7 +268,7 @@ def tc_rbf_raw(dist: torch.Tensor, state: torch.Tensor, row_offset: int = 0, wan
 def tc_matmul_raw(k: Planes, f: Planes, N: int, C: int, scales: torch.Tensor) -> torch.Tensor:
     """out [M, Cp] = K[M, N] . F[N, :C] (columns >= C are not written)."""
     M = k.hi.shape[0]
-    out = torch.zeros(M, f.hi.shape[1], dtype=torch.float32, device=k.hi.device)
+    out = torch.empty(M, f.hi.shape[1], dtype=torch.float32, device=k.hi.device)
     call("sigsvgd_tc_matmul", _p(k.hi), _p(k.lo), k.ld, _p(f.hi), _p(f.lo), f.ld, M, N, C, _p(scales), _p(out),
          out.stride(0), _stream())
     return out

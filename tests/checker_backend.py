@@ -28,21 +28,21 @@ class CheckerBackend:
     def sig_fwd(self, x, depth):
         return torch.from_numpy(oracle.signature_np(x.numpy().astype(np.float32), depth, True))
 
-    def col_mean(self, s):
-        return s.mean(0)
+    def pack(self, s_all, g_all, center, r0, M):
+        from sigsvgd_b200.dist import Features
 
-    def pack_v(self, score, s, mean):
-        N, D = s.shape
-        P = score.shape[1]
+        N, D = s_all.shape
+        P = g_all.shape[1]
         C = (P + D + 1 + 7) // 8 * 8
         v = torch.zeros(N, C, dtype=torch.float32)
-        v[:, :P] = score
-        v[:, P:P + D] = s - (mean if mean is not None else 0.0)
+        v[:, :P] = g_all
+        v[:, P:P + D] = s_all - (s_all.mean(0) if center else 0.0)
         v[:, P + D] = 1.0
-        return v
+        return Features(v[:, P:], v[r0:r0 + M, P:], (v, D, P, r0, M))
 
-    def sqdist(self, a, b, D):
-        a, b = a[:, :D].double(), b[:, :D].double()
+    def gram(self, f):
+        v, D, P, r0, M = f.data
+        a, b = v[r0:r0 + M, P:P + D].double(), v[:, P:P + D].double()
         d = (a * a).sum(1)[:, None] + (b * b).sum(1)[None, :] - 2.0 * a @ b.T
         return d.clamp_(min=0).float().contiguous()
 
@@ -83,7 +83,7 @@ class CheckerBackend:
         h = max(h, tol)
         state.update(h=h, gamma=-0.5 / (h * h))
 
-    def rbf_apply(self, k, state, row_offset):
+    def rbf(self, k, state, row_offset, f, want_k):
         med = np.float32(state["median"])
         d = k.clone()
         k.copy_(torch.exp(np.float32(state["gamma"]) * d))
@@ -94,16 +94,17 @@ class CheckerBackend:
         return k
 
     def local_stats(self, state):
-        return (torch.tensor([state["sum_kd"]], dtype=torch.float64),
-                torch.tensor([state["n_ties"]], dtype=torch.int64))
+        return torch.tensor([state["sum_kd"], float(state["n_ties"])], dtype=torch.float64)
 
-    def median_coef(self, state, enable, sum_kd_all, n_ties_all):
-        state["n_ties_all"] = int(n_ties_all)
+    def median_coef(self, state, enable, stats):
+        state["n_ties_all"] = int(stats[1])
         ok = enable and not state["clamped"] and state["median"] > 0
-        state["coef"] = float(sum_kd_all) / (state["h"] ** 2 * state["median"]) if ok else 0.0
+        state["coef"] = float(stats[0]) / (state["h"] ** 2 * state["median"]) if ok else 0.0
 
-    def matmul_nn(self, a, v):
-        return (a.double() @ v.double()).float()
+    def contract(self, kmat, f):
+        v, D, P, r0, M = f.data
+        out = (kmat.double() @ v.double()).float()
+        return out[:, P:P + D], out[:, P + D], out[:, :P]
 
     def sig_grad(self, sc, sc_all, ks, rowsum, state, row_offset):
         D = ks.shape[1]  # sc / sc_all are views whose first D columns are the centred features

@@ -24,7 +24,30 @@ namespace sigsvgd {
 
 namespace {
 
-constexpr int kThreads = 128;
+// One warp per CTA: 32 / G particles.  N = 4096 particles of d = 7 give 1024 CTAs, ~7 per SM, so
+// the per-SM load is balanced to 1 % (128-thread CTAs left 40 of the 148 SMs with half the work)
+// and every phase of a CTA overlaps with the other resident CTAs' phases.
+constexpr int kThreads = 32;
+constexpr int kGroupPad = 8;  // floats between the particles' shared-memory blocks: bank spread
+
+// Contiguous global -> shared copy, 16-byte vectors, up to 8 loads in flight per thread.
+__device__ __forceinline__ void copy_in_f4(float* dst, const float* __restrict__ src, int n4, int tid) {
+  const float4* __restrict__ s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  int i = tid;
+  for (; i + 7 * kThreads < n4; i += 8 * kThreads) {
+    float4 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __ldg(s4 + i + k * kThreads);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) d4[i + k * kThreads] = v[k];
+  }
+  for (; i < n4; i += kThreads) d4[i] = __ldg(s4 + i);
+}
+
+__device__ __forceinline__ bool is_aligned16(const void* p) {
+  return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
 
 __host__ __device__ constexpr int group_size(int d) { return d <= 1 ? 1 : d <= 2 ? 2 : d <= 4 ? 4 : 8; }
 __host__ __device__ constexpr int row_pad(int d) { return d <= 2 ? d : ((d + 3) & ~3); }
@@ -85,7 +108,9 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   const int npart = (int)min((int64_t)PPC, N - p0);
   const bool active = grp < npart && lane < d;
   const int gq = grp < npart ? grp : 0;
-  const int pstride = TC * DP;
+  const int pstride = TC * DP + kGroupPad;
+  // whole paths resident and 16-byte aligned: the CTA's waypoints are ONE contiguous block
+  const bool vec = TC >= T && ((T * d) & 3) == 0 && is_aligned16(x);
 
   float S1 = 0.f, S2[d], S3[d][d], xprev[d], xprev_i = 0.f;
 #pragma unroll
@@ -99,13 +124,40 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   for (int c0 = 0; c0 < T; c0 += TC) {
     const int len = min(TC, T - c0);
     __syncthreads();
-    for (int q = 0; q < npart; ++q) {
-      const float* __restrict__ src = x + ((p0 + q) * (int64_t)T + c0) * d;
-      float* dst = smem + q * pstride;
+    if (vec) {
+      // all loads of the block in flight at once (batches of 8 x 16 B per thread), then the
+      // scatter into the padded rows
+      const float4* __restrict__ s4 = reinterpret_cast<const float4*>(x + p0 * (int64_t)T * d);
+      const int per4 = (T * d) >> 2, n4 = npart * per4;
+      for (int i0 = tid; i0 < n4; i0 += 8 * kThreads) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (i0 + k * kThreads < n4) v[k] = __ldg(s4 + i0 + k * kThreads);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i4 = i0 + k * kThreads;
+          if (i4 < n4) {
+            const int q = i4 / per4, e = (i4 - q * per4) * 4;
+            float* dst = smem + q * pstride;
+            const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (e + u) / d, c = (e + u) - t * d;
+              dst[t * DP + c] = f[u];
+            }
+          }
+        }
+      }
+    } else {
+      for (int q = 0; q < npart; ++q) {
+        const float* __restrict__ src = x + ((p0 + q) * (int64_t)T + c0) * d;
+        float* dst = smem + q * pstride;
 #pragma unroll 4
-      for (int i = tid; i < len * d; i += kThreads) {
-        const int t = i / d, c = i - t * d;
-        dst[t * DP + c] = __ldg(src + i);
+        for (int i = tid; i < len * d; i += kThreads) {
+          const int t = i / d, c = i - t * d;
+          dst[t * DP + c] = __ldg(src + i);
+        }
       }
     }
     __syncthreads();
@@ -150,7 +202,14 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   }
   __syncthreads();
   float* __restrict__ dst = sig + p0 * D;
-  for (int i = tid; i < npart * D; i += kThreads) dst[i] = smem[i];
+  const int nout = npart * D;
+  if ((nout & 3) == 0 && is_aligned16(dst)) {
+    float4* __restrict__ d4 = reinterpret_cast<float4*>(dst);
+    const float4* s4 = reinterpret_cast<const float4*>(smem);
+    for (int i = tid; i < (nout >> 2); i += kThreads) d4[i] = s4[i];
+  } else {
+    for (int i = tid; i < nout; i += kThreads) dst[i] = smem[i];
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -172,13 +231,44 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
   const int npart = (int)min((int64_t)PPC, N - p0);
   const bool active = grp < npart && lane < d;
   const int gq = grp < npart ? grp : 0;
-  const int pstride = (TC + 1) * DP;
+  const int pstride = (TC + 1) * DP + kGroupPad;
+  const bool vec = TC >= T && ((T * d) & 3) == 0 && is_aligned16(x) && is_aligned16(out) &&
+                   (add == nullptr || (is_aligned16(add) && (ld_add & 3) == 0));
 
   float S1 = 0.f, S2[d], S3[d][d], A1 = 0.f, A2[d], g3[d][d];
-  // ---- load S_T and dL/dS_T (coalesced through smem) ----
+  // ---- load S_T and dL/dS_T (coalesced through smem; both blocks in flight together) ----
   {
     const float* __restrict__ src = sig + p0 * D;
-    for (int i = tid; i < npart * D; i += kThreads) smem[i] = __ldg(src + i);
+    const float* __restrict__ gsrc = gsig + p0 * D;
+    float* gstage = smem + PPC * D;
+    const int nst = npart * D;
+    if ((nst & 3) == 0 && is_aligned16(src) && is_aligned16(gsrc)) {
+      const float4* __restrict__ a4 = reinterpret_cast<const float4*>(src);
+      const float4* __restrict__ b4 = reinterpret_cast<const float4*>(gsrc);
+      float4* da = reinterpret_cast<float4*>(smem);
+      float4* db = reinterpret_cast<float4*>(gstage);
+      const int n4 = nst >> 2;
+      for (int i0 = tid; i0 < n4; i0 += 4 * kThreads) {
+        float4 va[4], vb[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (i0 + k * kThreads < n4) {
+            va[k] = __ldg(a4 + i0 + k * kThreads);
+            vb[k] = __ldg(b4 + i0 + k * kThreads);
+          }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (i0 + k * kThreads < n4) {
+            da[i0 + k * kThreads] = va[k];
+            db[i0 + k * kThreads] = vb[k];
+          }
+      }
+    } else {
+      for (int i = tid; i < nst; i += kThreads) {
+        smem[i] = __ldg(src + i);
+        gstage[i] = __ldg(gsrc + i);
+      }
+    }
     __syncthreads();
     const float* o = smem + gq * D;
     S1 = active ? o[il] : 0.f;
@@ -188,16 +278,13 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
 #pragma unroll
       for (int c = 0; c < d; ++c) S3[j][c] = active ? o[d + d * d + (il * d + j) * d + c] : 0.f;
     }
-    __syncthreads();
-    src = gsig + p0 * D;
-    for (int i = tid; i < npart * D; i += kThreads) smem[i] = __ldg(src + i);
-    __syncthreads();
-    A1 = active ? o[il] : 0.f;
+    const float* og = gstage + gq * D;
+    A1 = active ? og[il] : 0.f;
 #pragma unroll
     for (int j = 0; j < d; ++j) {
-      A2[j] = active ? o[d + il * d + j] : 0.f;
+      A2[j] = active ? og[d + il * d + j] : 0.f;
 #pragma unroll
-      for (int c = 0; c < d; ++c) g3[j][c] = active ? o[d + d * d + (il * d + j) * d + c] : 0.f;
+      for (int c = 0; c < d; ++c) g3[j][c] = active ? og[d + d * d + (il * d + j) * d + c] : 0.f;
     }
   }
   for (int i = tid; i < PPC * DP; i += kThreads) carry[i] = 0.f;
@@ -209,6 +296,31 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
     const int len = min(TC, T - c0);
     __syncthreads();
     // rows r = 0..len  <->  time c0-1+r ; row 0 is zero when c0 == 0 (the basepoint)
+    if (vec) {
+      const float4* __restrict__ s4 = reinterpret_cast<const float4*>(x + p0 * (int64_t)T * d);
+      const int per4 = (T * d) >> 2, n4 = npart * per4;
+      for (int i0 = tid; i0 < n4; i0 += 8 * kThreads) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (i0 + k * kThreads < n4) v[k] = __ldg(s4 + i0 + k * kThreads);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i4 = i0 + k * kThreads;
+          if (i4 < n4) {
+            const int q = i4 / per4, e = (i4 - q * per4) * 4;
+            float* dst = smem + q * pstride + DP;
+            const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (e + u) / d, c = (e + u) - t * d;
+              dst[t * DP + c] = f[u];
+            }
+          }
+        }
+      }
+      for (int i = tid; i < npart * DP; i += kThreads) smem[(i / DP) * pstride + (i % DP)] = 0.f;
+    } else
     for (int q = 0; q < npart; ++q) {
       float* dst = smem + q * pstride;
       const int lo = c0 > 0 ? -1 : 0;  // first time index to read relative to c0
@@ -277,6 +389,47 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
     }
     __syncthreads();
     // gx[t] = gDelta[t] - gDelta[t+1]; coalesced store with the fused epilogue
+    if (vec) {
+      // whole paths resident: one contiguous block of the output, 16-byte stores; the loads of
+      // `add` (K.score rows) are issued 4 at a time before they are consumed
+      const int per4 = (T * d) >> 2, n4 = npart * per4;
+      float4* __restrict__ o4 = reinterpret_cast<float4*>(out + p0 * (int64_t)T * d);
+      for (int i0 = tid; i0 < n4; i0 += 4 * kThreads) {
+        float4 av[4];
+        if (add) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int i4 = i0 + k * kThreads;
+            if (i4 < n4) {
+              const int q = i4 / per4, e = (i4 - q * per4) * 4;
+              av[k] = __ldg(reinterpret_cast<const float4*>(add + (p0 + q) * ld_add + e));
+            }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i4 = i0 + k * kThreads;
+          if (i4 < n4) {
+            const int q = i4 / per4, e = (i4 - q * per4) * 4;
+            const float* src = smem + q * pstride;
+            float f[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (e + u) / d, c = (e + u) - t * d;
+              const float nxt = (t + 1 < T) ? src[(t + 2) * DP + c] : 0.f;
+              f[u] = beta * (src[(t + 1) * DP + c] - nxt);
+            }
+            if (add) {
+              f[0] = fmaf(alpha, av[k].x, f[0]);
+              f[1] = fmaf(alpha, av[k].y, f[1]);
+              f[2] = fmaf(alpha, av[k].z, f[2]);
+              f[3] = fmaf(alpha, av[k].w, f[3]);
+            }
+            o4[i4] = make_float4(f[0], f[1], f[2], f[3]);
+          }
+        }
+      }
+    } else
     for (int q = 0; q < npart; ++q) {
       const float* src = smem + q * pstride;
       const int64_t n = p0 + q;
@@ -452,8 +605,8 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
   static_assert(PPC * D * 4 <= kBudget, "output staging must fit");
-  int TC = (int)std::min<int64_t>(T, kBudget / 4 / (PPC * DP));
-  size_t smem = (size_t)std::max(PPC * TC * DP, PPC * D) * 4;
+  int TC = (int)std::min<int64_t>(T, (kBudget / 4 / PPC - kGroupPad) / DP);
+  size_t smem = (size_t)std::max(PPC * (TC * DP + kGroupPad), PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
   sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig);
   SIG_LAUNCH_OK("sig3_fwd_kernel");
@@ -467,9 +620,9 @@ int launch_sig3_bwd(const float* x, const float* sig, const float* gsig, int64_t
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
-  static_assert(PPC * D * 4 <= kBudget, "state staging must fit");
-  int TC = (int)std::min<int64_t>(T, kBudget / 4 / (PPC * DP) - 1);
-  size_t smem = (size_t)std::max(PPC * (TC + 1) * DP, PPC * D) * 4;
+  static_assert(2 * PPC * D * 4 <= kBudget, "state staging must fit");
+  int TC = (int)std::min<int64_t>(T, (kBudget / 4 / PPC - kGroupPad) / DP - 1);
+  size_t smem = (size_t)std::max(PPC * ((TC + 1) * DP + kGroupPad), 2 * PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
   sig3_bwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, sig, gsig, N, (int)T, basepoint,
                                                               TC, add, ld_add, alpha, beta, out);

@@ -202,11 +202,8 @@ def run_ours(args):
         return ops.phi(X, G, depth=DEPTH).phi
 
     def step_e2e():
-        x = Xh.to(dev, non_blocking=True)
-        g = Gh.to(dev, non_blocking=True)
-        p = ops.phi(x, g, depth=DEPTH).phi
-        phi_host.copy_(p, non_blocking=True)
-        return p
+        # the public host-input call: pinned X, score -> pinned phi (H2D and D2H inside the call)
+        return ops.phi_host(Xh, Gh, depth=DEPTH, out=phi_host, device=dev)
 
     def barrier():
         if world > 1:

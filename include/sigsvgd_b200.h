@@ -225,6 +225,23 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
                 float* phi, float* k_out, float* gradk_out, float* sig_out,
                 sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * The same update for HOST-resident particles and scores (one swarm).  The reference keeps its
+ * per-step tensors on the CPU side of the loop (src/inference/svgd.py:85-90 copies k_xx, grad_k and
+ * every tensor kwarg to the host each step; grad_log_p arrives from CPU cost functions in
+ * examples/script_planning_obstacle_field.py); this entry takes x_host [N,T,d], score_host
+ * [N,T*d] (pinned host memory for asynchronous copies) and writes phi_host [N,T,d].  X is copied
+ * first; the score's H2D copy runs on an internal stream beside the front half of the update
+ * (signatures, Gram, median, RBF need only X); phi is produced in row chunks whose D2H copies
+ * overlap the remaining signature backward.  phi_host is complete when `stream` reaches the end of
+ * the call.  state: one device record.  The workspace also holds the device copies.
+ * ------------------------------------------------------------------------------------------- */
+size_t sigsvgd_phi_host_workspace_bytes(int64_t N, int64_t T, int64_t d, int depth);
+int sigsvgd_phi_host(const float* x_host, const float* score_host, int64_t N, int64_t T, int64_t d,
+                     int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                     float* phi_host, sigsvgd_bw_state* state, void* ws, size_t ws_bytes,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

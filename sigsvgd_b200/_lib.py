@@ -121,6 +121,12 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_float, c_float, c_float, c_uint32,
          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "sigsvgd_phi_host_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int]),
+    "sigsvgd_phi_host": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_float, c_float, c_float, c_uint32,
+         c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

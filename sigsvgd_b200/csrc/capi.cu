@@ -60,6 +60,40 @@ static int side_stream(SideStream** out) {
   return 0;
 }
 
+// Host-input pipeline (sigsvgd_phi_host): the score's H2D copy runs on its own stream beside the
+// front half of the update (which needs only X), and phi leaves in row chunks whose D2H copies
+// overlap the signature backward of the next chunk.
+constexpr int kHostChunks = 4;
+struct HostPipe {
+  cudaStream_t h2d = nullptr, d2h = nullptr;
+  cudaEvent_t start = nullptr, score_ready = nullptr, done = nullptr;
+  cudaEvent_t chunk[kHostChunks] = {};
+  float* phi_host = nullptr;  // per call
+};
+static int host_pipe(HostPipe** out) {
+  static HostPipe table[64];
+  static std::mutex mu;
+  int dev = 0;
+  SIG_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("device index %d out of range", dev);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  HostPipe& h = table[dev];
+  if (!h.h2d) {
+    SIG_CUDA_OK(cudaStreamCreateWithFlags(&h.h2d, cudaStreamNonBlocking));
+    SIG_CUDA_OK(cudaStreamCreateWithFlags(&h.d2h, cudaStreamNonBlocking));
+    SIG_CUDA_OK(cudaEventCreateWithFlags(&h.start, cudaEventDisableTiming));
+    SIG_CUDA_OK(cudaEventCreateWithFlags(&h.score_ready, cudaEventDisableTiming));
+    SIG_CUDA_OK(cudaEventCreateWithFlags(&h.done, cudaEventDisableTiming));
+    for (int i = 0; i < kHostChunks; ++i)
+      SIG_CUDA_OK(cudaEventCreateWithFlags(&h.chunk[i], cudaEventDisableTiming));
+  }
+  *out = &h;
+  return 0;
+}
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 struct PhiLayout {
@@ -327,10 +361,16 @@ size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, i
   return phi_layout(B, N, T, d, depth, false, want_k != 0).total;
 }
 
-int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
-                int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
-                float* phi, float* k_out, float* gradk_out, float* sig_out,
-                sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream) {
+}  // extern "C"
+
+// The fused update.  hp == nullptr: everything is device resident (sigsvgd_phi).  hp != nullptr:
+// `score` is still in flight on hp->h2d (event hp->score_ready) and phi is also copied to
+// hp->phi_host chunk by chunk (sigsvgd_phi_host).
+static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
+                        int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                        float* phi, float* k_out, float* gradk_out, float* sig_out,
+                        sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream,
+                        HostPipe* hp) {
   cudaStream_t st = (cudaStream_t)stream;
   SIG_CHECK_ARG(B >= 1 && N >= 1 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
                 "phi: bad shape B=%lld N=%lld T=%lld d=%lld depth=%d", (long long)B, (long long)N,
@@ -394,9 +434,17 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
     // statistics pass (column sums, maxima), then planes F = [S - mean | 1 | score] (fp16 hi/lo)
     // with the centred fp32 features going to the V buffer
     float* stats = (float*)(w + L.off_stats);
-    SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 1, st));
-    SIG_PROPAGATE(launch_tc_pack_stats(score, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales, scales + 8,
-                                       Fh, Fl, C, C, norms, V, D, mean, st));
+    if (!hp) {
+      SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 1, st));
+      SIG_PROPAGATE(launch_tc_pack_stats(score, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales,
+                                         scales + 8, Fh, Fl, C, C, norms, V, D, mean, st));
+    } else {
+      // feature columns only; the score columns follow once its copy has landed
+      SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, nullptr, P, P, stats, 1, st));
+      SIG_PROPAGATE(launch_tc_pack_stats(nullptr, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales,
+                                         scales + 8, Fh, Fl, C, C, norms, V, D, mean, st, 0,
+                                         round_up(D + 1, 2)));
+    }
     feat = V, ldf = D;
     out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
     // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product; upper triangle
@@ -405,6 +453,7 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
                           scales + 1, 1, K, N, st));
     if (median_tc) SIG_CUDA_OK(cudaStreamWaitEvent(st, side->join, 0));
   } else {
+    if (hp) SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->score_ready, 0));
     if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
     SIG_PROPAGATE(launch_pack_v(score, P, sig, D, center ? mean : nullptr, N, D, V, C, C, B, st));
     feat = V + P, ldf = C;
@@ -426,6 +475,14 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
   if (use_tc) {
     SIG_PROPAGATE(launch_tc_rbf(K, N, N, N, 0, state, Kh, Kl, L.Np, k_out ? K : nullptr, N, st));
     SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
+    if (hp) {
+      float* stats = (float*)(w + L.off_stats);
+      SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->score_ready, 0));
+      SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 0, st, 0));
+      SIG_PROPAGATE(launch_tc_pack_stats(score, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales,
+                                         scales + 8, Fh, Fl, C, C, nullptr, nullptr, D, nullptr, st,
+                                         (D + 1) & ~(int64_t)1, C));
+    }
     SIG_PROPAGATE(tc_matmul_nn(TcPlanes{Kh, Kl, L.Np}, TcPlanes{Fh, Fl, C}, N, N, D + 1 + P,
                                scales + 8, out, C, st));
   } else {
@@ -439,8 +496,78 @@ int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_
   if (gradk_out)
     SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st));
   const float inv_n = 1.f / (float)N;
-  SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st));
+  if (!hp) {
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st));
+    return 0;
+  }
+  // K2 in row chunks; each chunk's D2H copy overlaps the next chunk's backward sweep
+  const int64_t per = round_up(ceil_div(R, kHostChunks), 32);
+  int n = 0;
+  for (int64_t r0 = 0; r0 < R; r0 += per, ++n) {
+    const int64_t rows = std::min(per, R - r0);
+    SIG_PROPAGATE(launch_sig_bwd(x + r0 * T * d, sig + r0 * D, g + r0 * D, rows, T, d, depth, 1,
+                                 out_kg + r0 * C, C, inv_n, -inv_n, phi + r0 * T * d, st));
+    SIG_CUDA_OK(cudaEventRecord(hp->chunk[n], st));
+    SIG_CUDA_OK(cudaStreamWaitEvent(hp->d2h, hp->chunk[n], 0));
+    SIG_CUDA_OK(cudaMemcpyAsync(hp->phi_host + r0 * T * d, phi + r0 * T * d,
+                                sizeof(float) * rows * T * d, cudaMemcpyDeviceToHost, hp->d2h));
+  }
+  SIG_CUDA_OK(cudaEventRecord(hp->done, hp->d2h));
+  SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->done, 0));
   return 0;
+}
+
+extern "C" {
+
+int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
+                int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                float* phi, float* k_out, float* gradk_out, float* sig_out,
+                sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream) {
+  return phi_pipeline(x, score, B, N, T, d, depth, bw_mode, h_fixed, bw_scale, tol, flags, phi, k_out,
+                      gradk_out, sig_out, state, ws, ws_bytes, stream, nullptr);
+}
+
+size_t sigsvgd_phi_host_workspace_bytes(int64_t N, int64_t T, int64_t d, int depth) {
+  if (N < 1 || T < 1 || d < 1 || depth < 1 || depth > 8) return 0;
+  const size_t io = (size_t)round_up((int64_t)sizeof(float) * N * T * d, 256);
+  return 3 * io + phi_layout(1, N, T, d, depth, false, false).total;
+}
+
+int sigsvgd_phi_host(const float* x_host, const float* score_host, int64_t N, int64_t T, int64_t d,
+                     int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
+                     float* phi_host, sigsvgd_bw_state* state, void* ws, size_t ws_bytes,
+                     void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  SIG_CHECK_ARG(N >= 1 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
+                "phi_host: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N, (long long)T,
+                (long long)d, depth);
+  SIG_CHECK_ARG(x_host && score_host && phi_host && state && ws, "phi_host: NULL pointer");
+  SIG_CHECK_ARG(aligned16(ws), "phi_host: workspace must be 16-byte aligned");
+  if (ws_bytes < sigsvgd_phi_host_workspace_bytes(N, T, d, depth)) {
+    set_error("phi_host: workspace too small (%zu < %zu bytes)", ws_bytes,
+              sigsvgd_phi_host_workspace_bytes(N, T, d, depth));
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  HostPipe* hp = nullptr;
+  SIG_PROPAGATE(host_pipe(&hp));
+  const size_t bytes = sizeof(float) * (size_t)(N * T * d);
+  const size_t io = (size_t)round_up((int64_t)bytes, 256);
+  char* w = (char*)ws;
+  float* x_dev = (float*)w;
+  float* score_dev = (float*)(w + io);
+  float* phi_dev = (float*)(w + 2 * io);
+  hp->phi_host = phi_host;
+  // the copy streams join the caller's stream here (earlier work on it may still use the buffers)
+  // X first (the front half needs nothing else); the score's copy queues behind it on its own stream
+  SIG_CUDA_OK(cudaMemcpyAsync(x_dev, x_host, bytes, cudaMemcpyHostToDevice, st));
+  SIG_CUDA_OK(cudaEventRecord(hp->start, st));
+  SIG_CUDA_OK(cudaStreamWaitEvent(hp->h2d, hp->start, 0));
+  SIG_CUDA_OK(cudaStreamWaitEvent(hp->d2h, hp->start, 0));
+  SIG_CUDA_OK(cudaMemcpyAsync(score_dev, score_host, bytes, cudaMemcpyHostToDevice, hp->h2d));
+  SIG_CUDA_OK(cudaEventRecord(hp->score_ready, hp->h2d));
+  return phi_pipeline(x_dev, score_dev, 1, N, T, d, depth, bw_mode, h_fixed, bw_scale, tol, flags,
+                      phi_dev, nullptr, nullptr, nullptr, state, w + 3 * io, ws_bytes - 3 * io, stream,
+                      hp);
 }
 
 }  // extern "C"

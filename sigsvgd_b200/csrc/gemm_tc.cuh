@@ -87,13 +87,15 @@ int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, i
                    cudaStream_t st);
 // fused front end: statistics pass (column sums, max |s|, max |score| -> stats[D + 2]) ...
 int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
-                    int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st);
+                    int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st,
+                    int do_s = 1);  // do_s = 0: only max |score| (score == NULL: only the s part)
 // ... and packing pass deriving mean (= colsum / n_total, 0 if !center) and scales from `stats`;
 // tcs[4], colscale[Cp], planes, norms, centred features (sc) and the mean (mean_out) are outputs
 int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float* s, int64_t lds,
                          const float* stats, int64_t n_total, int center, int64_t N, int64_t D,
                          float* tcs, float* colscale, __half* fh, __half* fl, int64_t ldp, int64_t Cp,
-                         float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st);
+                         float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st,
+                         int64_t c_lo = 0, int64_t c_hi = -1);  // plane columns [c_lo, c_hi) only
 // K = exp(gamma d) as planes of K*2^14 (+ optional fp32 K into kout, may alias d);
 // accumulates state->sum_kd, records median ties (global row = row_offset + i)
 int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,

@@ -146,11 +146,11 @@ constexpr int kStatThreads = 512;
 __global__ void __launch_bounds__(kStatThreads)
 stats_kernel(const float* __restrict__ s, int64_t lds, int64_t N, int64_t D,
              const float* __restrict__ score, int64_t lsc, int64_t P, int rows_per_block,
-             float* __restrict__ stats) {
+             int do_s, float* __restrict__ stats) {
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   const int64_t r1 = min(N, r0 + rows_per_block);
   float ms = 0.f, mg = 0.f;
-  for (int64_t c = threadIdx.x; c < D; c += kStatThreads) {
+  for (int64_t c = threadIdx.x; do_s && c < D; c += kStatThreads) {
     float sum = 0.f;
     int64_t r = r0;
     for (; r + 4 <= r1; r += 4) {  // four independent loads in flight
@@ -166,7 +166,7 @@ stats_kernel(const float* __restrict__ s, int64_t lds, int64_t N, int64_t D,
     }
     atomicAdd(stats + c, sum);
   }
-  for (int64_t c = threadIdx.x; c < P; c += kStatThreads) {
+  for (int64_t c = threadIdx.x; score && c < P; c += kStatThreads) {
     int64_t r = r0;
     for (; r + 4 <= r1; r += 4) {
       const float v0 = __ldg(score + r * lsc + c), v1 = __ldg(score + (r + 1) * lsc + c);
@@ -194,7 +194,9 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
                   int64_t n_total, int center, int64_t N, int64_t D, float* __restrict__ tcs,
                   float* __restrict__ colscale, __half* __restrict__ fh, __half* __restrict__ fl,
                   int64_t ldp, int64_t Cp, float* __restrict__ norms, float* __restrict__ sc,
-                  int64_t ldsc, float* __restrict__ mean_out) {
+                  int64_t ldsc, float* __restrict__ mean_out, int64_t c_lo, int64_t c_hi) {
+  // columns [c_lo, c_hi) (both even) of the planes are written; a NULL score leaves zeros in its
+  // columns (the host-input pipeline packs the feature and the score columns in two launches)
   __shared__ float sh_mm[kThreads / 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const float inv_n = center ? 1.f / (float)n_total : 0.f;
@@ -230,7 +232,7 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
   const int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + wid;
   if (row >= N) return;
   float nrm = 0.f;
-  for (int64_t c0 = 2 * lane; c0 < Cp; c0 += 64) {
+  for (int64_t c0 = c_lo + 2 * lane; c0 < c_hi; c0 += 64) {
     float x[2];
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
@@ -242,7 +244,7 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
         v *= as;
       } else if (c == D) {
         v = 1.f;
-      } else if (c < D + 1 + P) {
+      } else if (c < D + 1 + P && score) {
         v = __ldg(score + row * lsc + (c - D - 1)) * ag;
       }
       x[e] = v;
@@ -390,14 +392,14 @@ int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, i
 }
 
 int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
-                    int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st) {
-  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && (P == 0 || (score && lsc >= P)),
+                    int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st, int do_s) {
+  SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && (P == 0 || score == nullptr || lsc >= P),
                 "tc_stats: bad shape N=%lld D=%lld P=%lld", (long long)N, (long long)D, (long long)P);
   if (zero_first) SIG_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * (D + 2), st));
   const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)num_sms() * 2, ceil_div(N, 8)));
   const int rows_per_block = (int)ceil_div(N, blocks);
   stats_kernel<<<(unsigned)ceil_div(N, rows_per_block), kStatThreads, 0, st>>>(s, lds, N, D, score, lsc, P,
-                                                                            rows_per_block, stats);
+                                                                            rows_per_block, do_s, stats);
   SIG_LAUNCH_OK("stats_kernel");
   return 0;
 }
@@ -405,15 +407,18 @@ int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const flo
 int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float* s, int64_t lds,
                          const float* stats, int64_t n_total, int center, int64_t N, int64_t D,
                          float* tcs, float* colscale, __half* fh, __half* fl, int64_t ldp, int64_t Cp,
-                         float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st) {
+                         float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st,
+                         int64_t c_lo, int64_t c_hi) {
+  if (c_hi < 0) c_hi = Cp;
+  SIG_CHECK_ARG(c_lo >= 0 && c_hi <= Cp && (c_lo & 1) == 0 && (c_hi & 1) == 0, "tc_pack_stats: bad column range");
   SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && Cp >= D + 1 + P && ldp >= Cp && (Cp & 7) == 0 &&
                     (ldp & 7) == 0 && (sc == nullptr || ldsc >= D) && n_total >= 1,
                 "tc_pack_stats: bad shape N=%lld D=%lld P=%lld Cp=%lld ldp=%lld", (long long)N, (long long)D,
                 (long long)P, (long long)Cp, (long long)ldp);
-  SIG_CHECK_ARG(P == 0 || (score != nullptr && lsc >= P), "tc_pack_stats: score is NULL but P > 0");
+  SIG_CHECK_ARG(P == 0 || score == nullptr || lsc >= P, "tc_pack_stats: score pitch < P");
   pack_stats_kernel<<<(unsigned)ceil_div(N, kThreads / 32), kThreads, 0, st>>>(
       score, lsc, P, s, lds, stats, n_total, center, N, D, tcs, colscale, fh, fl, ldp, Cp, norms, sc, ldsc,
-      mean_out);
+      mean_out, c_lo, c_hi);
   SIG_LAUNCH_OK("pack_stats_kernel");
   return 0;
 }

@@ -538,5 +538,45 @@ def phi(X: torch.Tensor, score: torch.Tensor, depth: int = 3, bandwidth: Optiona
     return PhiResult(out.to(X.dtype), state, k_out, gk_out, sig_out)
 
 
+def phi_host(X: torch.Tensor, score: torch.Tensor, depth: int = 3, bandwidth: Optional[Bandwidth] = None,
+             out: Optional[torch.Tensor] = None, center: bool = True, flags: int = 0,
+             device: Optional[torch.device] = None) -> PhiResult:
+    """Fused update for HOST-resident inputs: ``X [N,T,d]``, ``score [N,T*d]`` fp32 CPU tensors
+    (pinned memory makes the copies asynchronous), result in ``out`` (CPU, pinned if given that
+    way).  One ``sigsvgd_phi_host`` call: H2D of X, the score's H2D beside the front half of the
+    update, chunked D2H of phi beside the signature backward.  The result is complete once the
+    current stream of ``device`` has finished (``torch.cuda.current_stream().synchronize()``)."""
+    bw = bandwidth or Bandwidth.median()
+    if X.is_cuda or score.is_cuda:
+        raise RuntimeError("phi_host takes CPU tensors; use ops.phi for device-resident inputs")
+    if X.dim() != 3:
+        raise ValueError(f"phi_host: X must be [N,T,d], got {tuple(X.shape)}")
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    x = X.detach().to(torch.float32).contiguous()
+    N, T, d = x.shape
+    g = score.detach().to(torch.float32).reshape(N, -1).contiguous()
+    if g.shape[1] != T * d:
+        raise ValueError(f"phi_host: score has {g.shape[1]} columns per particle, expected T*d = {T * d}")
+    if out is None:
+        out = torch.empty(N, T, d, dtype=torch.float32).pin_memory()
+    if out.is_cuda or out.dtype != torch.float32 or not out.is_contiguous() or out.shape != x.shape:
+        raise ValueError("phi_host: out must be a contiguous fp32 CPU tensor shaped like X")
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        state = new_state(dev, 1)
+        nbytes = lib.sigsvgd_phi_host_workspace_bytes(N, T, d, depth)
+        if nbytes == 0:
+            raise ValueError("phi_host: bad shape")
+        ws = _workspace(dev, nbytes)
+        fl = int(flags) | (_lib.FLAG_MEDIAN_GRAD if (bw.mode == _lib.BW_MEDIAN and bw.median_grad) else 0)
+        if not center:
+            fl |= _lib.FLAG_NO_CENTER
+        call("sigsvgd_phi_host", _p(x), _p(g), N, T, d, depth, bw.mode, bw.h, bw.bw_scale, bw.tol, fl, _p(out),
+             _p(state), _p(ws), ws.numel(), _stream())
+    res = PhiResult(out, state)
+    res._keep = (x, g)  # the asynchronous copies read these host buffers until the stream drains
+    return res
+
+
 def log_np1(n: int) -> float:
     return math.log(n + 1.0)

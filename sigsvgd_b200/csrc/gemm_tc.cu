@@ -10,6 +10,7 @@
 // x columns), two accumulator stages (all 512 TMEM columns) so the epilogue of tile t overlaps
 // the MMAs of tile t+1; K is consumed 64 elements per smem stage (one 128-byte swizzle atom).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "gemm_tc.cuh"
 #include "tc_ptx.cuh"
@@ -17,18 +18,31 @@
 namespace sigsvgd {
 namespace {
 
-constexpr int BM = 128, BN = 256, BK = 64;
-constexpr int kStages = 2;
+constexpr int BM = 128, BN = 256;
 constexpr int kGemmThreads = 256;
-constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
-constexpr uint32_t kBBytes = BN * BK * 2;   // 32 KB per plane
-constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // hi+lo of A and B: 96 KB
+// Pipeline shape per operand layout.  K-major B (tc_sqdist): 64-wide K blocks (one 128-byte
+// swizzle atom), 2 stages of 96 KB.  MN-major B (tc_matmul_nn, the dominant kernel): 32-wide K
+// blocks, 4 stages of 48 KB -- the same 192 KB, but a stage's TMA round trip now has three MMA
+// stage times to complete in instead of one (with 2 x 96 KB the tensor pipe idled ~45 % waiting
+// for the refill; profiles/r01e).  A (K-major) then has 64-byte rows: SWIZZLE_64B.
+template <bool kBMN>
+struct Pipe {
+  static constexpr int BK = kBMN ? 32 : 64;
+  static constexpr int kStages = kBMN ? 4 : 2;
+  static constexpr uint32_t kABytes = BM * BK * 2;  // per plane
+  static constexpr uint32_t kBBytes = BN * BK * 2;  // per plane
+  static constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // hi+lo of A and B
+  static constexpr int kK16 = BK / 16;               // UMMA K steps per stage
+  static constexpr int kMaxChainKb = 1024 / BK;      // K blocks per accumulation chain
+};
+constexpr uint32_t kPipeBytes = 192 * 1024;
+static_assert(Pipe<true>::kStages * Pipe<true>::kStageBytes == kPipeBytes, "");
+static_assert(Pipe<false>::kStages * Pipe<false>::kStageBytes == kPipeBytes, "");
 constexpr uint32_t kBarBytes = 256;
 constexpr int kXposePitch = 33;                               // 32 x 32 transpose tile per epilogue warp
 constexpr uint32_t kXposeBytes = 4 * 32 * kXposePitch * 4;
-constexpr uint32_t kSmemBytes = kStages * kStageBytes + kBarBytes + kXposeBytes + 1024;  // + alignment slack
+constexpr uint32_t kSmemBytes = kPipeBytes + kBarBytes + kXposeBytes + 1024;  // + alignment slack
 constexpr uint32_t kTmemCols = 512;
-constexpr int kMaxChainKb = 16;
 
 enum { EPI_SQDIST = 0, EPI_COLSCALE = 1 };
 
@@ -36,7 +50,9 @@ struct GemmParams {
   int64_t M, N;        // output rows / columns
   int num_k16;         // ceil(Kdim / 16): number of UMMA K steps
   int tiles_m, tiles_n;
-  int nsplit;          // K is cut into nsplit chunks of kb_per_split 64-wide blocks; chunks of one
+  int nsplit;          // K is cut into nsplit chunks of kb_per_split BK-wide blocks; chunks of one
+  int dbg;             // experiments: 1 = scalar red, 2 = no epilogue stores
+  int streamk;         // 1: equal-time spans of the (tile, K block) sequence (see the kernel)
   int kb_per_split;    // tile are separate work items whose results are summed with red.add
                        // (bounds the length of the truncating TMEM accumulation chain)
   float* out;
@@ -51,6 +67,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
               const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
               const GemmParams p) {
+  using P = Pipe<kBMN>;
+  constexpr int BK = P::BK, kStages = P::kStages, kK16 = P::kK16;
+  constexpr uint32_t kABytes = P::kABytes, kBBytes = P::kBBytes, kStageBytes = P::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
@@ -87,32 +106,87 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // work item w -> (column tile, row tile, K chunk); the column tile is the slowest index so the
-  // (possibly narrow) last column tile is scheduled last
+  // Work decomposition.  Static (p.streamk == 0): item w -> (column tile, row tile, K chunk), dealt
+  // round-robin.  Stream-K (p.streamk == 1, the K.F contraction): the (tile, K block) sequence --
+  // column tile slowest, each K block weighted by the tile's MMA width -- is cut into gridDim.x
+  // spans of equal tensor time; a CTA walks its span as chains of <= p.kb_per_split K blocks that
+  // never cross a tile.  With 512 static items of unequal width the busiest CTAs carried 3.3
+  // chains against a mean of 2.8 (profiles/r01e: 55 % tensor-pipe activity).
   const int num_work = p.tiles_m * p.tiles_n * p.nsplit;
-  const int num_kb_total = (p.num_k16 + 3) / 4;
+  const int num_kb_total = (p.num_k16 + kK16 - 1) / kK16;
   struct Work {
     int tm, tn, kb0, kb1, ncols;
   };
-  auto decode = [&](int w) {
-    Work k;
-    k.tn = w / (p.tiles_m * p.nsplit);
-    const int rem = w - k.tn * (p.tiles_m * p.nsplit);
-    k.tm = rem / p.nsplit;
-    const int sp = rem - k.tm * p.nsplit;
-    k.kb0 = sp * p.kb_per_split;
-    k.kb1 = min(num_kb_total, k.kb0 + p.kb_per_split);
+  struct WorkIter {
+    int w;                     // static: next item
+    int t, kb, t_end, kb_end;  // stream-K: position and end of the span (tile, K block)
+  };
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int w_last = (int)((min((int64_t)BN, p.N - (int64_t)(p.tiles_n - 1) * BN) + 15) / 16);
+  const long long u_full_tile = (long long)num_kb_total * (BN / 16);
+  const long long u_last_tile = (long long)num_kb_total * w_last;
+  const long long u_full = (long long)p.tiles_m * (p.tiles_n - 1) * u_full_tile;
+  auto locate = [&](long long u, int& t, int& kb) {
+    if (u < u_full) {
+      t = (int)(u / u_full_tile);
+      kb = (int)((u - (long long)t * u_full_tile) / (BN / 16));
+    } else {
+      const long long v = u - u_full;
+      const int tl = (int)(v / u_last_tile);
+      t = p.tiles_m * (p.tiles_n - 1) + tl;
+      kb = (int)((v - (long long)tl * u_last_tile) / w_last);
+    }
+  };
+  auto iter_init = [&]() {
+    WorkIter it;
+    it.w = blockIdx.x;
+    it.t = it.kb = it.t_end = it.kb_end = 0;
+    if (p.streamk) {
+      const long long U = u_full + (long long)p.tiles_m * u_last_tile;
+      locate(U * blockIdx.x / gridDim.x, it.t, it.kb);
+      if (blockIdx.x + 1 == gridDim.x) it.t_end = num_tiles, it.kb_end = 0;
+      else locate(U * (blockIdx.x + 1) / gridDim.x, it.t_end, it.kb_end);
+    }
+    return it;
+  };
+  auto iter_next = [&](WorkIter& it, Work& k) {
+    if (!p.streamk) {
+      // Items are dealt round-robin in (column tile, row tile, K chunk) order.  CTAs that run
+      // side by side then walk the SAME K blocks of the same column tile in phase, so their
+      // requests for the shared B lines coincide and L2 serves them once.  Two schedules with
+      // better-balanced tensor time -- stream-K spans (157 us) and dealing the narrow last
+      // column tile to the lighter CTAs (105 us) -- both lost to this one (93 us at N = 4096)
+      // because they break that phase alignment.
+      if (it.w >= num_work) return false;
+      const int w = it.w;
+      it.w += gridDim.x;
+      k.tn = w / (p.tiles_m * p.nsplit);
+      const int rem = w - k.tn * (p.tiles_m * p.nsplit);
+      k.tm = rem / p.nsplit;
+      const int sp = rem - k.tm * p.nsplit;
+      k.kb0 = sp * p.kb_per_split;
+      k.kb1 = min(num_kb_total, k.kb0 + p.kb_per_split);
+    } else {
+      if (it.t > it.t_end || (it.t == it.t_end && it.kb >= it.kb_end)) return false;
+      k.tn = it.t / p.tiles_m;
+      k.tm = it.t - k.tn * p.tiles_m;
+      k.kb0 = it.kb;
+      k.kb1 = min(num_kb_total, it.kb + p.kb_per_split);
+      if (it.t == it.t_end) k.kb1 = min(k.kb1, it.kb_end);
+      it.kb = k.kb1;
+      if (it.kb >= num_kb_total) it.t += 1, it.kb = 0;
+    }
     // MMA N of this tile: multiple of 16, at most BN
     k.ncols = (int)min((int64_t)BN, ((p.N - (int64_t)k.tn * BN) + 15) / 16 * 16);
-    return k;
+    return true;
   };
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       uint32_t it = 0;
-      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
-        const Work wk = decode(w);
+      Work wk;
+      for (WorkIter wi = iter_init(); iter_next(wi, wk);) {
         const int tm = wk.tm, tn = wk.tn;
         const int nbox = (wk.ncols + 63) / 64;  // MN-major B: 64-column boxes actually needed
         for (int kb = wk.kb0; kb < wk.kb1; ++kb, ++it) {
@@ -144,8 +218,8 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       uint32_t it = 0, tcount = 0;
-      for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++tcount) {
-        const Work wk = decode(w);
+      Work wk;
+      for (WorkIter wi = iter_init(); iter_next(wi, wk); ++tcount) {
         const uint32_t idesc = ptx::make_idesc_f16(BM, wk.ncols, false, kBMN);
         const int a = tcount & 1;
         const uint32_t aph = (tcount >> 1) & 1u;
@@ -159,11 +233,14 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
           ptx::mbar_wait(full_bar(s), ph);
           ptx::tc_fence_after();
           const uint32_t st = sbase + s * kStageBytes;
-          const int steps = min(4, p.num_k16 - kb * 4);
+          const int steps = min(kK16, p.num_k16 - kb * kK16);
           for (int k = 0; k < steps; ++k) {
-            // K-major SWIZZLE_128B: 8-row groups 1024 B apart, 16 K-elements = 32 bytes
-            const uint64_t ah = ptx::make_smem_desc(st + k * 32, 16, 1024, ptx::kLayoutSw128);
-            const uint64_t al = ptx::make_smem_desc(st + kABytes + k * 32, 16, 1024, ptx::kLayoutSw128);
+            // K-major A, rows of BK fp16 = one swizzle span (128 B or 64 B): 8-row groups
+            // 8 * span bytes apart, 16 K-elements = 32 bytes
+            constexpr uint32_t kASbo = 8 * BK * 2;
+            constexpr uint32_t kALayout = BK == 64 ? ptx::kLayoutSw128 : ptx::kLayoutSw64;
+            const uint64_t ah = ptx::make_smem_desc(st + k * 32, 16, kASbo, kALayout);
+            const uint64_t al = ptx::make_smem_desc(st + kABytes + k * 32, 16, kASbo, kALayout);
             uint64_t bh, bl;
             if constexpr (!kBMN) {
               bh = ptx::make_smem_desc(st + 2 * kABytes + k * 32, 16, 1024, ptx::kLayoutSw128);
@@ -191,9 +268,12 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
     uint32_t tcount = 0;
     float scal0 = 1.f;
     if constexpr (kEpi == EPI_SQDIST) scal0 = __ldg(p.scal);
-    const bool accumulate_out = p.nsplit > 1;
-    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++tcount) {
-      const Work wk = decode(w);
+    const bool accumulate_out = p.nsplit > 1 || p.streamk;
+    // 16-byte reductions (red.global.add.v4.f32): a quarter of the L2 atomic operations
+    const bool vec_red = accumulate_out && !(p.dbg & 1) && (p.ldo & 3) == 0 && (p.N & 3) == 0 &&
+                         (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+    Work wk;
+    for (WorkIter wi = iter_init(); iter_next(wi, wk); ++tcount) {
       const int tm = wk.tm, tn = wk.tn;
       const int a = tcount & 1;
       const uint32_t aph = (tcount >> 1) & 1u;
@@ -227,6 +307,24 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ 
           }
         }
         __syncwarp();
+        if (p.dbg & 2) {
+        } else if (vec_red) {
+          // lane -> (row r0 + lane / 8, columns 4 * (lane % 8) ..+3): 4 rows x 128 bytes per instruction
+          const int cg = (lane & 7) * 4;
+          const float s0 = __shfl_sync(0xffffffffu, cvl, cg), s1 = __shfl_sync(0xffffffffu, cvl, cg + 1);
+          const float s2 = __shfl_sync(0xffffffffu, cvl, cg + 2), s3 = __shfl_sync(0xffffffffu, cvl, cg + 3);
+          if (col0 + cg < p.N) {
+#pragma unroll
+            for (int rr = 0; rr < 32; rr += 4) {
+              const int r = rr + (lane >> 3);
+              if (row0 + r < p.M) {
+                const float* src = xp + r * kXposePitch + cg;
+                ptx::red_add_v4(p.out + (row0 + r) * p.ldo + col0 + cg, src[0] * s0, src[1] * s1,
+                                src[2] * s2, src[3] * s3);
+              }
+            }
+          }
+        } else
 #pragma unroll 8
         for (int r = 0; r < 32; ++r) {
           if (row0 + r < p.M && col_ok) {
@@ -279,6 +377,9 @@ EncodeTiledFn encode_fn() {
 // (elements); box = [box_outer x box_inner], 128-byte swizzle (box_inner * elem_bytes == 128)
 static int make_tmap_any(CUtensorMap* tm, const void* base, int elem_bytes, int64_t inner,
                          int64_t outer, int64_t ld, uint32_t box_inner, uint32_t box_outer) {
+  // swizzle span = bytes of one box row (128 or 64)
+  const CUtensorMapSwizzle swz =
+      box_inner * elem_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -294,7 +395,7 @@ static int make_tmap_any(CUtensorMap* tm, const void* base, int elem_bytes, int6
   cuuint32_t estr[2] = {1, 1};
   CUresult rc = fn(tm, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
                    2, const_cast<void*>(base), dims, strides,
-                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (rc != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld", (int)rc,
@@ -331,7 +432,7 @@ int launch_gemm3x(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMa
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     configured_dev = dev;
   }
-  const int grid = std::min(p.tiles_m * p.tiles_n * p.nsplit, num_sms());
+  const int grid = (int)std::min<int64_t>((int64_t)p.tiles_m * p.tiles_n * p.nsplit, num_sms());
   gemm3x_kernel<kBMN, kEpi><<<grid, kGemmThreads, kSmemBytes, st>>>(ah, al, bh, bl, p);
   SIG_LAUNCH_OK("gemm3x_kernel");
   return 0;
@@ -346,6 +447,7 @@ int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const flo
   SIG_CHECK_ARG(M >= 1 && N >= 1 && D >= 1 && A.ld >= D && B.ld >= D && ldd >= N,
                 "tc_sqdist: bad shape M=%lld N=%lld D=%lld", (long long)M, (long long)N, (long long)D);
   SIG_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31), "tc_sqdist: too many rows");
+  constexpr int BK = Pipe<false>::BK;
   CUtensorMap ah, al, bh, bl;
   SIG_PROPAGATE(make_tmap(&ah, A.hi, D, M, A.ld, BK, BM));
   SIG_PROPAGATE(make_tmap(&al, A.lo, D, M, A.ld, BK, BM));
@@ -355,7 +457,8 @@ int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const flo
   p.M = M, p.N = N;
   p.num_k16 = (int)ceil_div(D, 16);
   p.tiles_m = (int)ceil_div(M, BM), p.tiles_n = (int)ceil_div(N, BN);
-  p.nsplit = 1, p.kb_per_split = (p.num_k16 + 3) / 4;
+  p.dbg = 0;
+  p.nsplit = 1, p.streamk = 0, p.kb_per_split = (p.num_k16 + Pipe<false>::kK16 - 1) / Pipe<false>::kK16;
   p.out = dist, p.ldo = ldd;
   p.row_vec = na, p.col_vec = nb, p.scal = scal;
   return launch_gemm3x<false, EPI_SQDIST>(ah, al, bh, bl, p, st);
@@ -366,8 +469,10 @@ int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const 
   SIG_CHECK_ARG(M >= 1 && K >= 1 && C >= 1 && A.ld >= K && V.ld >= C && ldo >= C,
                 "tc_matmul_nn: bad shape M=%lld K=%lld C=%lld", (long long)M, (long long)K, (long long)C);
   SIG_CHECK_ARG(M < (1ll << 31) && K < (1ll << 31), "tc_matmul_nn: too many rows");
+  using P = Pipe<true>;
+  constexpr int BK = P::BK;
   CUtensorMap ah, al, bh, bl;
-  SIG_PROPAGATE(make_tmap(&ah, A.hi, K, M, A.ld, BK, BM));
+  SIG_PROPAGATE(make_tmap(&ah, A.hi, K, M, A.ld, BK, BM));  // 64-byte rows: SWIZZLE_64B
   SIG_PROPAGATE(make_tmap(&al, A.lo, K, M, A.ld, BK, BM));
   SIG_PROPAGATE(make_tmap(&bh, V.hi, C, K, V.ld, 64, BK));
   SIG_PROPAGATE(make_tmap(&bl, V.lo, C, K, V.ld, 64, BK));
@@ -375,15 +480,21 @@ int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const 
   p.M = M, p.N = C;
   p.num_k16 = (int)ceil_div(K, 16);
   p.tiles_m = (int)ceil_div(M, BM), p.tiles_n = (int)ceil_div(C, BN);
-  // K chunks of at most 16 blocks (1024 contraction indices = 192 chained MMAs): the TMEM
-  // accumulator adds with truncation, so the chain length bounds the rounding bias
-  const int num_kb = (p.num_k16 + 3) / 4;
-  p.kb_per_split = std::min(num_kb, kMaxChainKb);
+  // K chunks of at most 1024 contraction indices (192 chained MMAs): the TMEM accumulator adds
+  // with truncation, so the chain length bounds the rounding bias
+  const int num_kb = (p.num_k16 + P::kK16 - 1) / P::kK16;
+  p.kb_per_split = std::min(num_kb, P::kMaxChainKb);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
   p.kb_per_split = (int)ceil_div(num_kb, p.nsplit);  // balance the chunks
+  // stream-K measured 1.7x SLOWER than the static deal (157 vs 93 us at N = 4096): CTAs that walk
+  // the K range out of phase never request the same operand lines at the same time, and the
+  // L2 -> SM path then has to deliver every byte separately.  Kept as an experiment switch.
+  p.streamk = getenv("SIGSVGD_KF_STREAMK") ? 1 : 0;
+  p.dbg = getenv("SIGSVGD_KF_DBG") ? atoi(getenv("SIGSVGD_KF_DBG")) : 0;
+  if (p.streamk) p.kb_per_split = P::kMaxChainKb;
   p.out = out, p.ldo = ldo;
   p.row_vec = nullptr, p.col_vec = colscale, p.scal = nullptr;
-  if (p.nsplit > 1)
+  if (p.nsplit > 1 || p.streamk)
     SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, M, st));
   return launch_gemm3x<true, EPI_COLSCALE>(ah, al, bh, bl, p, st);
 }

@@ -154,6 +154,13 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// 16-byte vector reduction to global memory (sm_90+): one L2 atomic operation for four floats
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
 // ---- descriptors ---------------------------------------------------------------------------
 // UMMA shared-memory matrix descriptor (sm_100): start address, leading/stride byte offsets
 // (all >> 4), version = 1, layout type in bits [61,64) (2 = SWIZZLE_128B).
@@ -168,6 +175,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   return d;
 }
 constexpr uint32_t kLayoutSw128 = 2;
+constexpr uint32_t kLayoutSw64 = 4;
 
 // kind::f16 instruction descriptor: fp16 x fp16 -> fp32, shape M x N, operand majors
 __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, bool a_mn_major,

@@ -491,13 +491,18 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     SIG_PROPAGATE(launch_gemm_nn_simt(K, N, V, C, N, N, C, out, C, B, N * N, N * C, N * C, st));
   }
   // sig-space gradient, then K2 with the fused epilogue phi = (K.score - grad_k)/N
-  SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,
-                                g, D, B, st));
+  // (one swarm, depth 3: the backward kernel forms the cotangent itself while staging)
+  const bool fuse_grad = B == 1 && sig_bwd_fuses_grad(d, depth);
+  SigGradSpec gs{feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, 0, state};
+  const SigGradSpec* spec = fuse_grad ? &gs : nullptr;
+  if (!fuse_grad)
+    SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,
+                                  g, D, B, st));
   if (gradk_out)
-    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st));
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st, spec));
   const float inv_n = 1.f / (float)N;
   if (!hp) {
-    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st));
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st, spec));
     return 0;
   }
   // K2 in row chunks; each chunk's D2H copy overlaps the next chunk's backward sweep
@@ -505,8 +510,11 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   int n = 0;
   for (int64_t r0 = 0; r0 < R; r0 += per, ++n) {
     const int64_t rows = std::min(per, R - r0);
+    SigGradSpec gc = gs;
+    gc.sc += r0 * ldf, gc.ks += r0 * C, gc.rowsum += r0 * C, gc.row_offset = r0;
     SIG_PROPAGATE(launch_sig_bwd(x + r0 * T * d, sig + r0 * D, g + r0 * D, rows, T, d, depth, 1,
-                                 out_kg + r0 * C, C, inv_n, -inv_n, phi + r0 * T * d, st));
+                                 out_kg + r0 * C, C, inv_n, -inv_n, phi + r0 * T * d, st,
+                                 fuse_grad ? &gc : nullptr));
     SIG_CUDA_OK(cudaEventRecord(hp->chunk[n], st));
     SIG_CUDA_OK(cudaStreamWaitEvent(hp->d2h, hp->chunk[n], 0));
     SIG_CUDA_OK(cudaMemcpyAsync(hp->phi_host + r0 * T * d, phi + r0 * T * d,

@@ -65,9 +65,27 @@ int num_sms();  // cached cudaDevAttrMultiProcessorCount of the current device
 // signature (sig_kernels.cu)
 int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
                    float* sig, cudaStream_t st);
+// Optional producer of the cotangent: instead of reading gsig, the depth-3 backward kernel forms
+//   g_i = -(1/h^2) (sc_i * rowsum_i - ks_i) + median-gradient term on the tie rows
+// (the closed form of autograd.grad(k_xx.sum(), X) in signature space) while it
+// stages its operands -- what sig_grad_kernel computes, without the [N,D] round trip through HBM.
+struct SigGradSpec {
+  const float* sc;       // centred features of these rows, pitch lds
+  int64_t lds;
+  const float* sc_all;   // centred features of ALL particles (tie partners), pitch lds_all
+  int64_t lds_all;
+  const float* ks;       // K . Sc rows, pitch ldks
+  int64_t ldks;
+  const float* rowsum;   // K row sums, element pitch ldr
+  int64_t ldr;
+  int64_t row_offset;    // global index of row 0 (ties hold global indices)
+  const sigsvgd_bw_state* state;  // one record
+};
+bool sig_bwd_fuses_grad(int64_t d, int depth);
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
-                   float alpha, float beta, float* out, cudaStream_t st);
+                   float alpha, float beta, float* out, cudaStream_t st,
+                   const SigGradSpec* spec = nullptr);
 
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,

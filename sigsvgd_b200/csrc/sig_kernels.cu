@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(kThreads)
 sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
                 const float* __restrict__ gsig, int64_t N, int T, int basepoint, int TC,
                 const float* __restrict__ add, int64_t ld_add, float alpha, float beta,
-                float* __restrict__ out) {
+                float* __restrict__ out, const SigGradSpec gs) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   extern __shared__ __align__(16) float smem[];
@@ -242,7 +242,48 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
     const float* __restrict__ gsrc = gsig + p0 * D;
     float* gstage = smem + PPC * D;
     const int nst = npart * D;
-    if ((nst & 3) == 0 && is_aligned16(src) && is_aligned16(gsrc)) {
+    if (gs.sc != nullptr) {
+      // S_T by 16-byte loads where possible, the cotangent computed in place (see SigGradSpec)
+      if ((nst & 3) == 0 && is_aligned16(src)) copy_in_f4(smem, src, nst >> 2, tid);
+      else
+        for (int i = tid; i < nst; i += kThreads) smem[i] = __ldg(src + i);
+      const float gam2 = 2.f * gs.state->gamma;  // -(1/h^2) = 2*gamma
+      for (int i0 = tid; i0 < nst; i0 += 8 * kThreads) {
+        float a[8], b[8], r[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = i0 + k * kThreads;
+          if (i < nst) {
+            const int q = i / D, c = i - q * D;
+            const int64_t row = p0 + q;
+            a[k] = __ldg(gs.sc + row * gs.lds + c);
+            b[k] = __ldg(gs.ks + row * gs.ldks + c);
+            r[k] = __ldg(gs.rowsum + row * gs.ldr);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = i0 + k * kThreads;
+          if (i < nst) gstage[i] = gam2 * (a[k] * r[k] - b[k]);
+        }
+      }
+      const float coef = gs.state->coef;
+      if (coef != 0.f) {
+        __syncthreads();
+        const uint32_t nl = min(gs.state->n_ties, (uint32_t)SIGSVGD_MAX_TIES);
+        const float wt = coef / (float)gs.state->n_ties_all;
+        for (uint32_t t = 0; t < nl; ++t) {
+          const int64_t a_loc = (int64_t)gs.state->ties[2 * t] - gs.row_offset - p0;
+          if (a_loc < 0 || a_loc >= npart) continue;  // block-uniform
+          const int64_t jb = gs.state->ties[2 * t + 1];
+          for (int c = tid; c < D; c += kThreads)
+            gstage[a_loc * D + c] = fmaf(wt, __ldg(gs.sc + (p0 + a_loc) * gs.lds + c) -
+                                                 __ldg(gs.sc_all + jb * gs.lds_all + c),
+                                         gstage[a_loc * D + c]);
+          __syncthreads();
+        }
+      }
+    } else if ((nst & 3) == 0 && is_aligned16(src) && is_aligned16(gsrc)) {
       const float4* __restrict__ a4 = reinterpret_cast<const float4*>(src);
       const float4* __restrict__ b4 = reinterpret_cast<const float4*>(gsrc);
       float4* da = reinterpret_cast<float4*>(smem);
@@ -616,7 +657,7 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
 template <int d>
 int launch_sig3_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                     int basepoint, const float* add, int64_t ld_add, float alpha, float beta,
-                    float* out, cudaStream_t st) {
+                    float* out, cudaStream_t st, const SigGradSpec& gs) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
@@ -625,7 +666,7 @@ int launch_sig3_bwd(const float* x, const float* sig, const float* gsig, int64_t
   size_t smem = (size_t)std::max(PPC * ((TC + 1) * DP + kGroupPad), 2 * PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
   sig3_bwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, sig, gsig, N, (int)T, basepoint,
-                                                              TC, add, ld_add, alpha, beta, out);
+                                                              TC, add, ld_add, alpha, beta, out, gs);
   SIG_LAUNCH_OK("sig3_bwd_kernel");
   return 0;
 }
@@ -684,9 +725,17 @@ int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, i
   return 0;
 }
 
+bool sig_bwd_fuses_grad(int64_t d, int depth) { return depth == 3 && d >= 1 && d <= 8; }
+
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
-                   float alpha, float beta, float* out, cudaStream_t st) {
+                   float alpha, float beta, float* out, cudaStream_t st, const SigGradSpec* spec) {
+  SigGradSpec gs{};
+  if (spec) {
+    gs = *spec;
+    SIG_CHECK_ARG(sig_bwd_fuses_grad(d, depth) && gs.sc && gs.sc_all && gs.ks && gs.rowsum && gs.state,
+                  "signature_bwd: fused gradient needs depth 3, d <= 8 and a complete spec");
+  }
   SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
                 "signature_bwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,
                 (long long)T, (long long)d, depth);
@@ -698,7 +747,7 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
     switch (d) {
 #define SIG3_BWD_CASE(dd) \
   case dd:                \
-    return launch_sig3_bwd<dd>(x, sig, gsig, N, T, basepoint, add, ld_add, alpha, beta, out, st);
+    return launch_sig3_bwd<dd>(x, sig, gsig, N, T, basepoint, add, ld_add, alpha, beta, out, st, gs);
       SIG3_BWD_CASE(1)
       SIG3_BWD_CASE(2)
       SIG3_BWD_CASE(3)

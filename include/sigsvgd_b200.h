@@ -110,6 +110,20 @@ int sigsvgd_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, vo
 int sigsvgd_select_hist(const float* dist, int64_t count, int pass, const sigsvgd_bw_state* state,
                         uint64_t* hist, void* stream);
 int sigsvgd_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, void* stream);
+/* Windowed first pass for the sharded median: `sigsvgd_select_window` draws a fixed pseudo-random
+ * sample of pair distances from the centred features of ALL particles (identical input on every
+ * rank -> identical result) and writes bounds[0..1] = [lo, hi] bracketing the median at the start
+ * of `ws`; `sigsvgd_select_collect` reads one strip once, counts the entries below lo and compacts
+ * the entries inside [lo, hi] into `cand` (cand_cap floats; unused slots are padded with a value
+ * above every candidate).  totals[3] (device, zeroed by the call) += {#below, #kept, #overflowed
+ * pools}.  After summing totals over the ranks the caller runs select_begin/hist/scan/finish on
+ * `cand` with k - #below, or falls back to the strip if the window missed or a pool overflowed. */
+size_t sigsvgd_select_window_workspace_bytes(void);
+int sigsvgd_select_window(const float* feat, int64_t ld, int64_t N, int64_t D, void* ws,
+                          size_t ws_bytes, sigsvgd_bw_state* state, void* stream);
+int64_t sigsvgd_select_collect_min_capacity(void);
+int sigsvgd_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
+                           int64_t cand_cap, uint64_t* totals, void* stream);
 int sigsvgd_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                           void* stream);
 
@@ -173,6 +187,13 @@ int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float
                     int64_t ld_sc, void* stream);
 /* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
  * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack. */
+/* tc_scales + tc_pack (and the column means) in two passes over the data instead of four: one
+ * statistics pass (column sums, max |s|, max |score| into stats[D + 2]) and one packing pass that
+ * derives the mean (center != 0) and the scales itself.  mean_out [D] / s_centred / norms may be NULL. */
+int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const float* s, int64_t lds,
+                          int64_t N, int64_t D, int center, float* scales, void* f_hi, void* f_lo,
+                          int64_t ldp, int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
+                          float* mean_out, float* stats, void* stream);
 int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
                       const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
                       int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,

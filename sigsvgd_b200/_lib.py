@@ -121,6 +121,15 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_float, c_float, c_float, c_uint32,
          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "sigsvgd_tc_pack_fused": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
+         c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
+    ),
+    "sigsvgd_select_window_workspace_bytes": (c_size_t, []),
+    "sigsvgd_select_window": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "sigsvgd_select_collect_min_capacity": (c_int64, []),
+    "sigsvgd_select_collect": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "sigsvgd_phi_host_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int]),
     "sigsvgd_phi_host": (
         c_int,

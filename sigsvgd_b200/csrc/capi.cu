@@ -226,6 +226,31 @@ int sigsvgd_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_s
   return launch_select_finish(n_log, bw_scale, tol, state, 1, (cudaStream_t)stream);
 }
 
+size_t sigsvgd_select_window_workspace_bytes(void) { return window_workspace_bytes(1, 1, nullptr); }
+
+int sigsvgd_select_window(const float* feat, int64_t ld, int64_t N, int64_t D, void* ws,
+                          size_t ws_bytes, sigsvgd_bw_state* state, void* stream) {
+  SIG_CHECK_ARG(feat && ws && state && N >= 1 && D >= 1 && ld >= D, "select_window: bad argument");
+  if (ws_bytes < window_workspace_bytes(1, 1, nullptr)) {
+    set_error("select_window: workspace too small");
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  // only the header of the window workspace is touched (bounds at its start; no candidate pool)
+  SelWindow* win;
+  float* cand;
+  return launch_window_prepare(feat, ld, N, feat, ld, N, D, ws, state, &win, &cand,
+                               (cudaStream_t)stream);
+}
+
+int64_t sigsvgd_select_collect_min_capacity(void) { return select_collect_blocks(); }
+
+int sigsvgd_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
+                           int64_t cand_cap, uint64_t* totals, void* stream) {
+  SIG_CHECK_ARG(bounds && cand && totals && (count == 0 || dist), "select_collect: NULL pointer");
+  return launch_select_collect(dist, count, bounds, cand, cand_cap, (unsigned long long*)totals,
+                               (cudaStream_t)stream);
+}
+
 int sigsvgd_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
                       const float* weight, int64_t ldw, sigsvgd_bw_state* state, void* stream) {
   SIG_CHECK_ARG(state && (M == 0 || k), "rbf_apply: NULL pointer");
@@ -288,6 +313,19 @@ int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float
   SIG_CHECK_ARG(aligned16(f_hi) && aligned16(f_lo), "tc_pack: planes must be 16-byte aligned");
   return launch_tc_pack(score, ld_score, P, s, lds, mean, N, D, scales, (__half*)f_hi, (__half*)f_lo,
                         ldp, Cp, norms, s_centred, ld_sc, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const float* s, int64_t lds,
+                          int64_t N, int64_t D, int center, float* scales, void* f_hi, void* f_lo,
+                          int64_t ldp, int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
+                          float* mean_out, float* stats, void* stream) {
+  SIG_CHECK_ARG(s && scales && f_hi && f_lo && stats, "tc_pack_fused: NULL pointer");
+  SIG_CHECK_ARG(aligned16(f_hi) && aligned16(f_lo), "tc_pack_fused: planes must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  SIG_PROPAGATE(launch_tc_stats(s, lds, N, D, score, ld_score, P, stats, 1, st));
+  return launch_tc_pack_stats(score, ld_score, P, s, lds, stats, N, center, N, D, scales, scales + 8,
+                              (__half*)f_hi, (__half*)f_lo, ldp, Cp, norms, s_centred, ld_sc, mean_out,
+                              st);
 }
 
 int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,

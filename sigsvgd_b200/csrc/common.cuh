@@ -81,6 +81,9 @@ struct SigGradSpec {
   int64_t row_offset;    // global index of row 0 (ties hold global indices)
   const sigsvgd_bw_state* state;  // one record
 };
+int select_collect_blocks();
+int launch_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
+                          int64_t cand_cap, unsigned long long* totals, cudaStream_t st);
 bool sig_bwd_fuses_grad(int64_t d, int depth);
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,

@@ -60,6 +60,108 @@ select_hist_kernel(const float* __restrict__ dist, int64_t count, int64_t stride
     if (h[i]) atomicAdd(&g[i], (unsigned long long)h[i]);
 }
 
+// Windowed first pass of the sharded median (dist.py): ONE read of this rank's strip that counts
+// the entries below the window [lo, hi] (bounds from a sample of the global distance
+// distribution, identical on every rank) and compacts the ~5 % of entries inside it into per-block
+// pools.  The exact radix select then runs over the pools only (pool tails are padded with a
+// value above every candidate), so the strip is read once instead of three times.
+// totals[0] += #below, totals[1] += #candidates kept, totals[2] += #pools that overflowed.
+constexpr int kCollectThreads = 512;
+constexpr float kCollectPad = 3.0e38f;
+
+__global__ void __launch_bounds__(kCollectThreads)
+select_collect_kernel(const float* __restrict__ dist, int64_t count, const float* __restrict__ bounds,
+                      float* __restrict__ cand, unsigned int poolcap, int64_t cand_cap,
+                      unsigned long long* __restrict__ totals) {
+  __shared__ unsigned int sh_fill;
+  __shared__ unsigned long long sh_below;
+  if (threadIdx.x == 0) sh_fill = 0u, sh_below = 0ull;
+  __syncthreads();
+  const uint32_t lo = __float_as_uint(__ldg(bounds)) & 0x7fffffffu;
+  const uint32_t span = (__float_as_uint(__ldg(bounds + 1)) & 0x7fffffffu) - lo;
+  float* __restrict__ pool = cand + (size_t)blockIdx.x * poolcap;
+  const int lane = threadIdx.x & 31;
+  unsigned int below = 0;
+  auto push = [&](float v) {
+    const uint32_t bits = __float_as_uint(v) & 0x7fffffffu;
+    below += bits < lo ? 1u : 0u;
+    const bool hit = bits - lo <= span;
+    const unsigned int m = __ballot_sync(0xffffffffu, hit);
+    if (m) {
+      unsigned int base = 0;
+      if (lane == __ffs(m) - 1) base = atomicAdd(&sh_fill, (unsigned int)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+      const unsigned int slot = base + __popc(m & ((1u << lane) - 1u));
+      if (hit && slot < poolcap) pool[slot] = v;
+    }
+  };
+  const bool vec = (reinterpret_cast<uintptr_t>(dist) & 15u) == 0;
+  const int64_t n4 = vec ? count / 4 : 0;
+  const int64_t step = (int64_t)gridDim.x * kCollectThreads;
+  // body: a warp takes 128 consecutive float4 (4 coalesced loads in flight per lane), builds a
+  // 16-bit hit mask per lane, and reserves pool slots with ONE shared-memory atomic per 512 entries
+  const int64_t n_chunks = (n4 + 127) / 128;
+  // consecutive chunks go to different blocks, so small strips still spread over all the pools
+  const int64_t warp_g = (int64_t)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+  const int64_t n_warps = (int64_t)gridDim.x * (kCollectThreads / 32);
+  for (int64_t c = warp_g; c < n_chunks; c += n_warps) {
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t idx = c * 128 + j * 32 + lane;
+      float4 q = make_float4(kCollectPad, kCollectPad, kCollectPad, kCollectPad);
+      if (idx < n4) q = __ldg(reinterpret_cast<const float4*>(dist) + idx);
+      v[4 * j] = q.x, v[4 * j + 1] = q.y, v[4 * j + 2] = q.z, v[4 * j + 3] = q.w;
+    }
+    uint32_t mask = 0;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
+      below += bits < lo ? 1u : 0u;
+      if (bits - lo <= span) mask |= 1u << e;
+    }
+    const int cnt = __popc(mask);
+    int incl = cnt;
+#pragma unroll
+    for (int sft = 1; sft < 32; sft <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, sft);
+      if (lane >= sft) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total) {
+      unsigned int base = 0;
+      if (lane == 31) base = atomicAdd(&sh_fill, (unsigned int)total);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      unsigned int off = base + (unsigned int)(incl - cnt);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        if ((mask >> e) & 1u) {
+          if (off < poolcap) pool[off] = v[e];
+          ++off;
+        }
+      }
+    }
+  }
+  const int64_t tail0 = n4 * 4, ntail = count - tail0;
+  const int64_t ntail_up = (ntail + 31) / 32 * 32;
+  for (int64_t i = (int64_t)blockIdx.x * kCollectThreads + threadIdx.x; i < ntail_up; i += step)
+    push(i < ntail ? __ldg(dist + tail0 + i) : kCollectPad);
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
+  if (lane == 0 && below) atomicAdd(&sh_below, (unsigned long long)below);
+  __syncthreads();
+  const unsigned int fill = sh_fill, kept = min(fill, poolcap);
+  for (unsigned int i = kept + threadIdx.x; i < poolcap; i += kCollectThreads) pool[i] = kCollectPad;
+  if (blockIdx.x == gridDim.x - 1)  // slots beyond the last pool (cand_cap is not a multiple of the pool size)
+    for (int64_t i = (int64_t)gridDim.x * poolcap + threadIdx.x; i < cand_cap; i += kCollectThreads)
+      cand[i] = kCollectPad;
+  if (threadIdx.x == 0) {
+    atomicAdd(&totals[0], sh_below);
+    atomicAdd(&totals[1], (unsigned long long)kept);
+    if (fill > poolcap) atomicAdd(&totals[2], 1ull);
+  }
+}
+
 __global__ void select_begin_kernel(sigsvgd_bw_state* state, unsigned long long* hist,
                                     unsigned long long k) {
   const int b = blockIdx.x;
@@ -260,6 +362,19 @@ int launch_median_select(const float* dist, int64_t count, int64_t batch, int64_
     SIG_PROPAGATE(launch_select_scan(pass, state, hist, batch, st));
   }
   return launch_select_finish(n_log, bw_scale, tol, state, batch, st);
+}
+
+int select_collect_blocks() { return 4 * num_sms(); }
+
+int launch_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
+                          int64_t cand_cap, unsigned long long* totals, cudaStream_t st) {
+  const int blocks = select_collect_blocks();
+  SIG_CHECK_ARG(count >= 0 && cand_cap >= blocks, "select_collect: candidate buffer too small");
+  const unsigned int poolcap = (unsigned int)std::min<int64_t>(cand_cap / blocks, 1ll << 30);
+  SIG_CUDA_OK(cudaMemsetAsync(totals, 0, 3 * sizeof(unsigned long long), st));
+  select_collect_kernel<<<blocks, kCollectThreads, 0, st>>>(dist, count, bounds, cand, poolcap, cand_cap, totals);
+  SIG_LAUNCH_OK("select_collect_kernel");
+  return 0;
 }
 
 }  // namespace sigsvgd

@@ -74,10 +74,10 @@ class CudaBackend:
     def pack(self, s_all, g_all, center, r0, M) -> Features:
         N, D = s_all.shape
         P = g_all.shape[1]
-        mean = ops.col_mean(s_all) if center else None
         if self._use_tc(N):
-            planes, norms, scales, sc = ops.tc_pack_raw(s_all, mean, g_all)
+            planes, norms, scales, sc = ops.tc_pack_fused_raw(s_all, g_all, center)
             return Features(sc, sc[r0:r0 + M], ("tc", planes, norms, scales, D, P, r0, M))
+        mean = ops.col_mean(s_all) if center else None
         v = ops.pack_features(s_all, mean, g_all.contiguous())  # [N, C] = [score | S - mean | 1 | 0]
         return Features(v[:, P:], v[r0:r0 + M, P:], ("simt", v, D, P, r0, M))
 
@@ -129,6 +129,28 @@ class CudaBackend:
     def select_finish(self, n_log, bw_scale, tol, state):
         _lib.call("sigsvgd_select_finish", n_log, float(bw_scale), float(tol), state.data_ptr(), ops._stream())
 
+    # windowed first pass of the sharded median (one read of the strip instead of three)
+    window_min_elems = 1 << 24  # strips smaller than this take the plain three passes
+
+    def select_window(self, sc_all, state):
+        """-> device tensor whose first two floats are [lo, hi]; identical on every rank."""
+        lib = _lib.load()
+        nbytes = lib.sigsvgd_select_window_workspace_bytes()
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=sc_all.device)
+        _lib.call("sigsvgd_select_window", sc_all.data_ptr(), sc_all.stride(0), sc_all.shape[0], sc_all.shape[1],
+                  ws.data_ptr(), nbytes, state.data_ptr(), ops._stream())
+        return ws[:8].view(torch.float32)
+
+    def select_collect(self, dist_loc, bounds):
+        """-> (candidates [cap] fp32 padded with a large value, totals int64[3] = below, kept, overflowed)."""
+        lib = _lib.load()
+        cap = max(int(lib.sigsvgd_select_collect_min_capacity()) * 64, dist_loc.numel() // 8)
+        cand = torch.empty(cap, dtype=torch.float32, device=dist_loc.device)
+        totals = torch.empty(3, dtype=torch.int64, device=dist_loc.device)
+        _lib.call("sigsvgd_select_collect", dist_loc.data_ptr(), dist_loc.numel(), bounds.data_ptr(), cand.data_ptr(),
+                  cap, totals.data_ptr(), ops._stream())
+        return cand, totals
+
     def local_stats(self, state):
         """[sum_kd, n_ties] as one float64 device tensor for the all-reduce."""
         return torch.cat([ops.state_field(state, "sum_kd"), ops.state_field(state, "n_ties").to(torch.float64)])
@@ -160,9 +182,10 @@ def _all_gather_rows(t: torch.Tensor, group) -> torch.Tensor:
 
 def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3,
                 bandwidth: Optional[ops.Bandwidth] = None, want_k: bool = False, center: bool = True,
-                group=None, backend=None) -> ShardedPhi:
+                group=None, backend=None, window: Optional[bool] = None) -> ShardedPhi:
     """Row-block sharded Stein update.  ``x_local [M,T,d]`` / ``score_local [M,T*d]`` are this
-    rank's particles; every rank must hold the same M (N = world * M).  SURVEY.md 8(e)."""
+    rank's particles; every rank must hold the same M (N = world * M).  SURVEY.md 8(e).
+    ``window``: windowed first pass of the median (default: on for large strips)."""
     be = backend or CudaBackend()
     bw = bandwidth or ops.Bandwidth.median()
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -193,9 +216,23 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
         # exact GLOBAL lower median: radix select (11/11/10 bits of the fp32 patterns), one 16 KiB
         # histogram all-reduce per pass; every rank ends with the same median and h
         hist = be.new_hist(x_local.device)
-        be.select_begin(state, hist, (N * N - 1) // 2)
+        k = (N * N - 1) // 2
+        data = k_rows
+        if window is None:
+            window = k_rows.numel() >= getattr(be, "window_min_elems", 1 << 62)
+        if window:
+            # one read of the strip: count the entries below a sampled window around the median and
+            # compact the entries inside it; the select then runs over those candidates only
+            bounds = be.select_window(feat.sc_all, state)
+            cand, totals = be.select_collect(k_rows, bounds)
+            if world > 1:
+                dist.all_reduce(totals, op=dist.ReduceOp.SUM, group=group)
+            below, kept, overflowed = (int(v) for v in totals.tolist())  # host sync; same on every rank
+            if overflowed == 0 and below <= k < below + kept:
+                data, k = cand, k - below
+        be.select_begin(state, hist, k)
         for p in range(3):
-            be.select_hist(k_rows, p, state, hist)
+            be.select_hist(data, p, state, hist)
             if world > 1:
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
             be.select_scan(p, state, hist)

@@ -217,6 +217,23 @@ def tc_pack_raw(s: torch.Tensor, mean: Optional[torch.Tensor], score: Optional[t
     return Planes(fh, fl), norms, scales, sc
 
 
+def tc_pack_fused_raw(s: torch.Tensor, score: Optional[torch.Tensor] = None, center: bool = True):
+    """Same outputs as ``col_mean`` + ``tc_pack_raw`` from one statistics pass and one packing pass."""
+    N, D = s.shape
+    P = 0 if score is None else score.shape[1]
+    Cp = (D + 1 + P + 63) // 64 * 64
+    dev = s.device
+    scales = torch.empty(8 + Cp, dtype=torch.float32, device=dev)
+    stats = torch.empty(D + 2, dtype=torch.float32, device=dev)
+    fh = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+    fl = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+    norms = torch.empty(N, dtype=torch.float32, device=dev)
+    sc = torch.empty(N, D, dtype=torch.float32, device=dev)
+    call("sigsvgd_tc_pack_fused", _p(score), 0 if score is None else score.stride(0), P, _p(s), s.stride(0), N, D,
+         int(center), _p(scales), _p(fh), _p(fl), Cp, Cp, _p(norms), _p(sc), D, None, _p(stats), _stream())
+    return Planes(fh, fl), norms, scales, sc
+
+
 def tc_sqdist_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int, scales: torch.Tensor,
                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
     M, N = a.hi.shape[0], b.hi.shape[0]

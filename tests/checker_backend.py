@@ -76,6 +76,24 @@ class CheckerBackend:
         state["prefix"] |= b << _SHIFT[p]
         hist.zero_()
 
+    def select_window(self, sc_all, state):
+        a = sc_all.double()
+        idx = torch.arange(0, a.shape[0], max(1, a.shape[0] // 16))
+        d = ((a[idx, None, :] - a[None, :, :]) ** 2).sum(-1).reshape(-1)
+        lo, hi = torch.quantile(d, 0.35), torch.quantile(d, 0.65)
+        return torch.tensor([float(lo), float(hi)], dtype=torch.float32)
+
+    def select_collect(self, dist_loc, bounds):
+        flat = dist_loc.reshape(-1)
+        lo, hi = float(bounds[0]), float(bounds[1])
+        inside = flat[(flat >= lo) & (flat <= hi)]
+        cap = max(64, flat.numel() // 2)
+        kept = min(cap, inside.numel())
+        cand = torch.full((cap,), 3.0e38, dtype=torch.float32)
+        cand[:kept] = inside[:kept]
+        totals = torch.tensor([int((flat < lo).sum()), kept, int(inside.numel() > cap)], dtype=torch.int64)
+        return cand, totals
+
     def select_finish(self, n_log, bw_scale, tol, state):
         med = float(np.array([state["prefix"]], dtype=np.uint32).view(np.float32)[0])
         h = bw_scale * math.sqrt(med / math.log(n_log + 1.0))

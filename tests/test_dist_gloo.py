@@ -28,7 +28,7 @@ def _inputs(N, T, d, seed=0):
     return X, G
 
 
-def _worker(rank, world, port, N, T, d, depth, fixed_h, q):
+def _worker(rank, world, port, N, T, d, depth, fixed_h, q, window=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -39,17 +39,17 @@ def _worker(rank, world, port, N, T, d, depth, fixed_h, q):
         M = N // world
         bw = ops.Bandwidth.fixed(fixed_h) if fixed_h else ops.Bandwidth.median()
         res = phi_sharded(X[rank * M:(rank + 1) * M], G[rank * M:(rank + 1) * M], depth=depth, bandwidth=bw,
-                          want_k=True, backend=CheckerBackend())
+                          want_k=True, backend=CheckerBackend(), window=window)
         q.put((rank, res.phi.numpy(), res.k_rows.numpy(), dict(res.state), res.rows))
     finally:
         dist.destroy_process_group()
 
 
-def _run(world, N, T, d, depth, fixed_h=None):
+def _run(world, N, T, d, depth, fixed_h=None, window=None):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, N, T, d, depth, fixed_h, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, N, T, d, depth, fixed_h, q, window)) for r in range(world)]
     for p in procs:
         p.start()
     got = []
@@ -73,12 +73,12 @@ def _run(world, N, T, d, depth, fixed_h=None):
     return got
 
 
-@pytest.mark.parametrize("N,T,d,depth", [(24, 8, 2, 3), (30, 6, 3, 2)])
-def test_sharded_update_matches_single_problem_oracle(N, T, d, depth):
+@pytest.mark.parametrize("N,T,d,depth,window", [(24, 8, 2, 3, None), (30, 6, 3, 2, None), (24, 8, 2, 3, True)])
+def test_sharded_update_matches_single_problem_oracle(N, T, d, depth, window):
     import oracle
     from tests.util import closed_form_with_ties
 
-    got = _run(2, N, T, d, depth)
+    got = _run(2, N, T, d, depth, window=window)
     X, G = _inputs(N, T, d)
     states = [g[3] for g in got]
     # identical global median / bandwidth on every rank, equal to the exact lower median

@@ -44,6 +44,37 @@ def test_world1_matches_closed_form(tc, N, T, d, depth):
     _check(X, G, depth, res.phi.cpu().numpy(), res.k_rows.cpu().numpy(), [ops.read_state(res.state)])
 
 
+@pytest.mark.parametrize("N", [1100, 3000])
+def test_world1_windowed_median_is_exact(N):
+    """The windowed first pass (count below + compact the window, then select among the candidates)
+    must land on the same exact order statistic as the three full passes."""
+    T, d, depth = 16, 3, 3
+    X, G = _inputs(N, T, d, seed=9)
+    dev = torch.device("cuda:0")
+    x, g = torch.as_tensor(X, device=dev), torch.as_tensor(G, device=dev)
+    a = phi_sharded(x, g, depth=depth, want_k=True, window=True)
+    b = phi_sharded(x, g, depth=depth, want_k=True, window=False)
+    ra, rb = ops.read_state(a.state), ops.read_state(b.state)
+    assert abs(ra["median"] - rb["median"]) <= 1e-6 * rb["median"]
+    _check(X, G, depth, a.phi.cpu().numpy(), a.k_rows.cpu().numpy(), [ra])
+    # the collect pass itself: counts and candidates against numpy on the same strip
+    be = CudaBackend()
+    s = ops.signature_fwd_raw(x, depth, True)
+    feat = be.pack(s, g, True, 0, N)
+    dmat = be.gram(feat)
+    st = be.new_state(dev)
+    bounds = be.select_window(feat.sc_all, st)
+    cand, totals = be.select_collect(dmat, bounds)
+    lo, hi = (float(v) for v in bounds.cpu())
+    dn = dmat.cpu().numpy().reshape(-1)
+    below, kept, over = (int(v) for v in totals.cpu())
+    assert over == 0 and below == int((dn < lo).sum()) and kept == int(((dn >= lo) & (dn <= hi)).sum())
+    cn = np.sort(cand.cpu().numpy())
+    assert np.array_equal(cn[:kept], np.sort(dn[(dn >= lo) & (dn <= hi)])) and (cn[kept:] > hi).all()
+    k = (N * N - 1) // 2
+    assert below <= k < below + kept, "sampled window missed the median"
+
+
 def test_world1_default_backend_agrees_with_fused_update():
     N, T, d, depth = 1536, 64, 7, 3  # >= 1024: both take the tcgen05 kernels
     X, G = _inputs(N, T, d, seed=3)
@@ -78,7 +109,7 @@ def _nccl_worker(rank, world, port, N, T, d, depth, tc, q):
         M = N // world
         res = phi_sharded(torch.as_tensor(X[rank * M:(rank + 1) * M], device=dev),
                           torch.as_tensor(G[rank * M:(rank + 1) * M], device=dev), depth=depth, want_k=True,
-                          backend=CudaBackend(tc=tc))
+                          backend=CudaBackend(tc=tc), window=tc)
         torch.cuda.synchronize()
         q.put((rank, res.phi.cpu().numpy(), res.k_rows.cpu().numpy(), ops.read_state(res.state)))
     finally:

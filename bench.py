@@ -283,7 +283,7 @@ def run_ours(args):
             st = ops.bandwidth_raw(d_rows.clone(), ops.Bandwidth.median(), N)
             kpl = ops.tc_rbf_raw(d_rows, st)
             dominant = lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)  # noqa: E731
-            kname = "tc_matmul_kernel (tcgen05 split-fp16, K.[S|1|score])"
+            kname = "gemm3x_kernel<MN-major B> (tcgen05 split-fp16, K.[Sc|1|score])"
         else:
             v_all = ops.pack_features(s_all, ops.col_mean(s_all), Ga.to(dev))
             k_rows = ops.sqdist_raw(v_all[:, P:], v_all[:, P:], D)
@@ -311,11 +311,20 @@ def run_ours(args):
         except Exception:
             pass
         peak = float(peaks.get("bf16_tflops", 1590.0))
+        # DRAM bytes of one launch of this kernel at this shape, from the committed ncu --set full capture
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["gemm3x_kernel"]
+            if use_tc and N == 4096:
+                traffic = tj["dram_bytes_per_launch"]
+        except Exception:
+            pass
         roof = {"bound": "tensor", "kernel": kname, "mma_passes_per_fp32_product": 3 if use_tc else None,
                 "achieved": flops / (ms_k * 1e-3) / 1e12,
                 "peak": peak, "peak_source": ("MEASURED_PEAKS.json bf16_tflops (burst; fp16 and bf16 share the tcgen05 kind::f16 rate)"
                                 if peaks else "fallback 1590 (B200_PROFILING.md)"),
-                "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak, "traffic": None,
+                "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak, "traffic": traffic,
+                "traffic_unit": "DRAM bytes per launch (ncu, profiles/traffic.json); operand planes are 82 MB",
                 "ms_per_launch": ms_k, "algorithmic_flops_per_launch": flops,
                 "step_algorithmic_flops": 2.0 * M * N * (2 * D + P),
                 "step_frac_of_peak": 2.0 * M * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak}

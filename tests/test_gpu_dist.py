@@ -91,6 +91,30 @@ def test_world1_default_backend_agrees_with_fused_update():
     assert rel_max(pa, pb) <= TOL_PHI
 
 
+def test_full_size_two_routes_agree():
+    """N = 16384 (BASELINE configs[3] range; too large for the CPU oracle in a test): the fused
+    update and the strip pipeline are independent routes -- symmetric vs non-symmetric Gram,
+    single-pass window median vs sampled window + radix select -- and must give the same median,
+    bandwidth and phi rows."""
+    N, T, d, depth = 16384, 64, 7, 3
+    g = torch.Generator().manual_seed(11)
+    dev = torch.device("cuda:0")
+    x = torch.cumsum(0.05 * torch.randn(N, T, d, generator=g), dim=1).to(dev)
+    s = torch.randn(N, T * d, generator=g).to(dev)
+    a = ops.phi(x, s, depth=depth)
+    b = phi_sharded(x, s, depth=depth)
+    ra, rb = ops.read_state(a.state), ops.read_state(b.state)
+    assert abs(ra["median"] - rb["median"]) <= 1e-6 * rb["median"]
+    assert abs(ra["h"] - rb["h"]) <= 1e-6 * rb["h"]
+    keep = torch.ones(N, dtype=torch.bool, device=dev)
+    keep[sorted({t[0] for t in ra["ties"]} | {t[0] for t in rb["ties"]})] = False
+    diff = (a.phi[keep] - b.phi[keep]).abs().max().item() / b.phi[keep].abs().max().item()
+    assert diff <= 1e-5
+    assert bool(torch.isfinite(a.phi).all()) and bool(torch.isfinite(b.phi).all())
+    ops._WS_CACHE.clear()
+    torch.cuda.empty_cache()
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))

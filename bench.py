@@ -283,7 +283,7 @@ def run_ours(args):
             st = ops.bandwidth_raw(d_rows.clone(), ops.Bandwidth.median(), N)
             kpl = ops.tc_rbf_raw(d_rows, st)
             dominant = lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)  # noqa: E731
-            kname = "gemm3x_kernel<MN-major B> (tcgen05 split-fp16, K.[Sc|1|score])"
+            kname = "kf_pair_kernel (tcgen05 cta_group::2 split-fp16, K.[Sc|1|score])"
         else:
             v_all = ops.pack_features(s_all, ops.col_mean(s_all), Ga.to(dev))
             k_rows = ops.sqdist_raw(v_all[:, P:], v_all[:, P:], D)
@@ -314,7 +314,7 @@ def run_ours(args):
         # DRAM bytes of one launch of this kernel at this shape, from the committed ncu --set full capture
         traffic = None
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["gemm3x_kernel"]
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["kf_kernel"]
             if use_tc and N == 4096:
                 traffic = tj["dram_bytes_per_launch"]
         except Exception:

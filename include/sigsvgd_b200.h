@@ -219,6 +219,9 @@ int sigsvgd_tc_median_prepare(const float* a, int64_t lda, int64_t M, const floa
  * among the candidates -> state->{median,h,gamma,clamped}.  Falls back to radix passes over the
  * full matrix if the window missed, so the result is always exact. */
 int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
+                             int symmetric /* dist is bit-symmetric with an exact-zero diagonal
+                                              (sigsvgd_tc_gram, symmetric = 1): only the upper
+                                              triangle is read */,
                              int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                              void* stream);
 /* K = exp(state->gamma * dist) (_kernels.py:110) written as planes of K*2^14 and, if k_out is not

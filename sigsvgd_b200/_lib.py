@@ -104,7 +104,7 @@ _SIGNATURES = {
     "sigsvgd_tc_median_prepare": (
         c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
     "sigsvgd_tc_median_select": (
-        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p]),
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int64, c_float, c_float, c_void_p, c_void_p]),
     "sigsvgd_tc_rbf": (
         c_int,
         [c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,

@@ -368,11 +368,11 @@ int sigsvgd_tc_median_prepare(const float* a, int64_t lda, int64_t M, const floa
 }
 
 int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
-                             int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
-                             void* stream) {
+                             int symmetric, int64_t n_log, float bw_scale, float tol,
+                             sigsvgd_bw_state* state, void* stream) {
   SIG_CHECK_ARG(median_ws && dist && state, "tc_median_select: NULL pointer");
   return launch_window_select(median_ws, dist, M, N, ldd, n_log, bw_scale, tol, state,
-                              (cudaStream_t)stream);
+                              (cudaStream_t)stream, symmetric);
 }
 
 int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
@@ -500,7 +500,9 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   }
   // K4: bandwidth
   if (bw_mode == SIGSVGD_BW_MEDIAN && use_tc) {
-    SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, N, N, bw_scale, tol, state, st));
+    // K3 wrote a bit-symmetric matrix with an exact-zero diagonal: the select reads the upper
+    // triangle only
+    SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, N, N, bw_scale, tol, state, st, 1));
   } else if (bw_mode == SIGSVGD_BW_MEDIAN) {
     SIG_PROPAGATE(launch_median_select(K, N * N, B, N * N, N, bw_scale, tol, state, selws,
                                        select_workspace_bytes(N * N, B), st));

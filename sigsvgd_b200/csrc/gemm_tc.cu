@@ -471,6 +471,9 @@ int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const 
   SIG_CHECK_ARG(M >= 1 && K >= 1 && C >= 1 && A.ld >= K && V.ld >= C && ldo >= C,
                 "tc_matmul_nn: bad shape M=%lld K=%lld C=%lld", (long long)M, (long long)K, (long long)C);
   SIG_CHECK_ARG(M < (1ll << 31) && K < (1ll << 31), "tc_matmul_nn: too many rows");
+  // CTA pairs (kf2_tc.cu) when the device can co-schedule them and there are 256-row tiles to fill
+  if (M >= 256 && tc_matmul_pair_available())
+    return tc_matmul_pair(A, V, M, K, C, colscale, out, ldo, st);
   using P = Pipe<true>;
   constexpr int BK = P::BK;
   CUtensorMap ah, al, bh, bl;

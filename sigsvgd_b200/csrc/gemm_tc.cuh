@@ -54,6 +54,10 @@ int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float
 // out[i,c] = colscale[c] * sum_j A[i,j] V[j,c]      i < M, j < K, c < C
 //   A: planes [M x >=K] (K-major), V: planes [K x >=C] (the contraction index is the ROW of V:
 //   MN-major B operand), colscale: DEVICE vector [C] undoing the plane scalings
+// the CTA-pair (cta_group::2) kernel behind tc_matmul_nn (kf2_tc.cu)
+bool tc_matmul_pair_available();
+int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
+                   float* out, int64_t ldo, cudaStream_t st);
 int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
                  float* out, int64_t ldo, cudaStream_t st);
 
@@ -72,7 +76,7 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
 // after tc_gram has filled dist + candidates: exact lower median -> state->{median,h,gamma,clamped}
 int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
                          int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
-                         cudaStream_t st);
+                         cudaStream_t st, int symmetric = 0);
 
 // ---- operand preparation (planes.cu) ---------------------------------------------------------
 // per problem b: tcs[4b..] = {alpha_S, alpha_S^-2, alpha_G, 0}; colscale[b*Cp + c]; mx: 2 uints

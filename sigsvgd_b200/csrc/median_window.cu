@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(1024)
 window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float* shortlist,
                      const float* __restrict__ dist, int64_t M, int64_t N, int64_t ldd,
                      unsigned long long k_total, unsigned long long* ghist2, float log_np1,
-                     float bw_scale, float tol, sigsvgd_bw_state* state) {
+                     float bw_scale, float tol, sigsvgd_bw_state* state, int symmetric) {
   cg::grid_group grid = cg::this_grid();
   __shared__ unsigned int hist[kBins];
   __shared__ unsigned long long scratch[1024];
@@ -282,6 +282,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   unsigned long long* ghist = ghist2 + (size_t)epoch * 3 * kBins;
   unsigned int* short_cnt = pool_cnt + 2 * kMaxPools + epoch;
   const int lane = threadIdx.x & 31;
+  bool tri_scan = false;
   const uint32_t lo_bits = __float_as_uint(win->lo), span_bits = __float_as_uint(win->hi) - lo_bits;
   // radix digits of rel: s1 = shift of the top digit (<= 11 bits), then s2, then 0
   const int nbits = 32 - __clz(span_bits | 1u);
@@ -301,6 +302,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     const bool vec = (N & 3) == 0 && (ldd & 3) == 0 && (reinterpret_cast<uintptr_t>(dist) & 15u) == 0;
     const int64_t nq = vec ? N / 4 : N;  // items per row
     unsigned int nlt = 0;
+    tri_scan = symmetric && vec && M == N && lo_bits > 0u;  // grid-uniform
     // a thread classifies its batch of values locally; the warp then reserves pool space with ONE
     // shared-memory atomic per batch (exclusive scan of the per-thread hit counts)
     auto flush = [&](const float* v, uint32_t hitmask, int nval) {  // warp-collective
@@ -327,54 +329,79 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       }
     };
     constexpr int kRows = 4;  // rows in flight per block (independent loads)
-    for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows) {
-      for (int64_t c0 = threadIdx.x & ~31; c0 < nq; c0 += blockDim.x) {
-        const int64_t c = c0 + lane;
-        float v[16];
-        uint32_t hitmask = 0;
-        if (vec && r0 + kRows <= M && c0 + 32 <= nq) {  // interior: no validity bookkeeping
+    // one warp-chunk: rows r0..r0+3, quads c0..c0+31 (128 columns).  tri: only entries strictly
+    // above the diagonal (column > row) are classified.
+    auto chunk = [&](int64_t r0, int64_t c0, bool tri) {  // warp-collective
+      const int64_t c = c0 + lane;
+      float v[16];
+      uint32_t hitmask = 0;
+      if (vec && r0 + kRows <= M && c0 + 32 <= nq && (!tri || 4 * c0 > r0 + kRows - 1)) {
+        // interior: no validity bookkeeping
 #pragma unroll
-          for (int j = 0; j < kRows; ++j) {
-            const float4 f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
-            v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
-          }
-#pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
-            nlt += bits < lo_bits ? 1u : 0u;
-            if (bits - lo_bits <= span_bits) hitmask |= 1u << e;
-          }
-          flush(v, hitmask, 16);
-          continue;
-        }
-        const bool cin = c < nq;
-        uint32_t validmask = 0;
-        if (vec) {
-#pragma unroll
-          for (int j = 0; j < kRows; ++j) {
-            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (cin && r0 + j < M) {
-              f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
-              validmask |= 0xfu << (4 * j);
-            }
-            v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < kRows; ++j) {
-            v[j] = 0.f;
-            if (cin && r0 + j < M) v[j] = __ldg(dist + (r0 + j) * ldd + c), validmask |= 1u << j;
-          }
+        for (int j = 0; j < kRows; ++j) {
+          const float4 f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
+          v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
         }
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          if (!vec && e >= kRows) break;
           const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
-          const bool ok_e = (validmask >> e) & 1u;
-          nlt += (ok_e && bits < lo_bits) ? 1u : 0u;
-          if (ok_e && bits - lo_bits <= span_bits) hitmask |= 1u << e;
+          nlt += bits < lo_bits ? 1u : 0u;
+          if (bits - lo_bits <= span_bits) hitmask |= 1u << e;
         }
-        flush(v, hitmask, vec ? 16 : kRows);
+        flush(v, hitmask, 16);
+        return;
+      }
+      const bool cin = c < nq;
+      uint32_t validmask = 0;
+      if (vec) {
+#pragma unroll
+        for (int j = 0; j < kRows; ++j) {
+          float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (cin && r0 + j < M) {
+            f = __ldg(reinterpret_cast<const float4*>(dist + (r0 + j) * ldd) + c);
+            uint32_t m4 = 0xfu;
+            if (tri) {  // keep columns 4c+u > r0+j
+              const int64_t first = r0 + j + 1 - 4 * c;  // first valid component
+              m4 = first <= 0 ? 0xfu : first >= 4 ? 0u : (0xfu << first) & 0xfu;
+            }
+            validmask |= m4 << (4 * j);
+          }
+          v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < kRows; ++j) {
+          v[j] = 0.f;
+          if (cin && r0 + j < M) v[j] = __ldg(dist + (r0 + j) * ldd + c), validmask |= 1u << j;
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        if (!vec && e >= kRows) break;
+        const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
+        const bool ok_e = (validmask >> e) & 1u;
+        nlt += (ok_e && bits < lo_bits) ? 1u : 0u;
+        if (ok_e && bits - lo_bits <= span_bits) hitmask |= 1u << e;
+      }
+      flush(v, hitmask, vec ? 16 : kRows);
+    };
+    if (!tri_scan) {
+      for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows)
+        for (int64_t c0 = threadIdx.x & ~31; c0 < nq; c0 += blockDim.x) chunk(r0, c0, false);
+    } else {
+      // bit-symmetric matrix with a zero diagonal: only the strict upper triangle is read.  The
+      // chunks of this block's row groups form one list that its warps walk round-robin, so the
+      // number of sequential chunk steps per warp halves too (not just the bytes).
+      const int wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+      int offset = 0;
+      for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows) {
+        const int64_t q_first = ((r0 + 1) >> 2) & ~(int64_t)31;
+        if (q_first >= nq) continue;
+        const int nch = (int)((nq - q_first + 31) >> 5);
+        int j0 = (wid - offset) % nw;
+        if (j0 < 0) j0 += nw;
+        for (int j = j0; j < nch; j += nw) chunk(r0, q_first + 32 * (int64_t)j, true);
+        offset = (offset + nch) % nw;
       }
     }
     unsigned int tot = nlt;
@@ -400,12 +427,15 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   }
   __syncthreads();
   const unsigned int n_cand = sh_ncand;
-  const unsigned long long below = sh_below;
-  const bool ok = sh_over == 0u && k_total >= below && k_total < below + n_cand;
+  // triangle scan: every counted entry stands for two, and the M diagonal zeros lie below lo > 0
+  const unsigned long long below = tri_scan ? 2ull * sh_below + (unsigned long long)M : sh_below;
+  const unsigned long long n_cand_full = tri_scan ? 2ull * n_cand : (unsigned long long)n_cand;
+  const bool ok = sh_over == 0u && k_total >= below && k_total < below + n_cand_full;
   uint32_t result_bits = 0;
   if (ok) {
     // ---------------------------------------------------------------- window hit
-    unsigned long long k = k_total - below;
+    // (in the doubled candidate list, position k' holds element k'/2 of the single list)
+    unsigned long long k = tri_scan ? (k_total - below) >> 1 : k_total - below;
     block_pick_bucket(ghist, k, &sh_bucket, &sh_k, scratch);
     uint32_t rel_prefix = sh_bucket << s1;
     k = sh_k;
@@ -599,7 +629,7 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
 
 int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int64_t ldd,
                          int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
-                         cudaStream_t st) {
+                         cudaStream_t st, int symmetric) {
   SIG_CHECK_ARG(n_log >= 1, "window_select: n_log must be >= 1");
   SelWindow* win;
   float *sample, *cand;
@@ -610,7 +640,7 @@ int launch_window_select(void* ws, const float* dist, int64_t M, int64_t N, int6
   const float log_np1 = (float)log((double)(float)((double)n_log + 1.0));
   unsigned long long k_total = (unsigned long long)((M * N - 1) / 2);
   void* args[] = {(void*)&win,   (void*)&cand, (void*)&pool_cnt, (void*)&shortlist, (void*)&dist, (void*)&M,   (void*)&N,    (void*)&ldd,
-                  (void*)&k_total, (void*)&ghist, (void*)&log_np1, (void*)&bw_scale, (void*)&tol, (void*)&state};
+                  (void*)&k_total, (void*)&ghist, (void*)&log_np1, (void*)&bw_scale, (void*)&tol, (void*)&state, (void*)&symmetric};
   // one block per SM: co-resident by construction (cooperative launch checks it)
   SIG_CUDA_OK(cudaLaunchCooperativeKernel((const void*)window_select_kernel, dim3((unsigned)num_sms()),
                                           dim3(1024), args, 0, st));

@@ -265,10 +265,12 @@ def tc_gram_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int
     return out
 
 
-def tc_median_select_raw(ws: torch.Tensor, dist: torch.Tensor, n_log: int, bw: "Bandwidth", state: torch.Tensor) -> None:
+def tc_median_select_raw(ws: torch.Tensor, dist: torch.Tensor, n_log: int, bw: "Bandwidth", state: torch.Tensor,
+                         symmetric: bool = False) -> None:
+    """``symmetric``: dist came from ``tc_gram_raw(..., symmetric=True)`` -> only the upper triangle is read."""
     M, N = dist.shape
-    call("sigsvgd_tc_median_select", _p(ws), _p(dist), M, N, dist.stride(0), n_log, bw.bw_scale, bw.tol, _p(state),
-         _stream())
+    call("sigsvgd_tc_median_select", _p(ws), _p(dist), M, N, dist.stride(0), int(symmetric), n_log, bw.bw_scale,
+         bw.tol, _p(state), _stream())
 
 
 def tc_rbf_raw(dist: torch.Tensor, state: torch.Tensor, row_offset: int = 0, want_k: bool = False):

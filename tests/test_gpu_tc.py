@@ -72,6 +72,17 @@ def test_tc_gram_symmetric_and_single_pass_median(N, D, scale):
     lo, hi = np.frombuffer(ws[:8].cpu().numpy().tobytes(), dtype=np.float32)
     assert lo <= want <= hi
     assert int(win[2]) == int(((got >= lo) & (got <= hi)).sum())  # candidates collected exactly once each
+    # triangle scan: the same exact order statistic from the strict upper triangle only
+    state_t = ops.new_state(torch.device(DEV))
+    ops.tc_median_prepare_raw(sc, sc, ws, state_t)
+    ops.tc_median_select_raw(ws, d, N, ops.Bandwidth.median(), state_t, symmetric=True)
+    rec_t = ops.read_state(state_t)
+    assert np.float32(rec_t["median"]) == want and rec_t["h"] == rec["h"]
+    win_t = np.frombuffer(ws[:32].cpu().numpy().tobytes(), dtype=np.uint32)
+    assert win_t[7] == 0, "window missed the median (fallback taken)"
+    if N % 4 == 0 and lo > 0:
+        iu = np.triu_indices(N, 1)
+        assert int(win_t[2]) == int(((got[iu] >= lo) & (got[iu] <= hi)).sum())  # upper entries, once each
     # the non-symmetric kernel (strip of rows) gives the same numbers and the same median machinery
     M = min(N, 200)
     pa = ops.Planes(planes.hi[:M], planes.lo[:M])

@@ -52,6 +52,7 @@ def _gram_win():
     ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist)
 res["prepare+tc_gram_sym_win"] = timeit(_gram_win)
 res["median_window_select"] = timeit(lambda: ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state))
+res["median_window_select_sym"] = timeit(lambda: ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state, True))
 state = ops.bandwidth_raw(dist, ops.Bandwidth.median(), N)
 res["median_select"] = timeit(lambda: ops.bandwidth_raw(dist, ops.Bandwidth.median(), N, state))
 d2 = dist.clone()

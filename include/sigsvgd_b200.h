@@ -188,7 +188,7 @@ int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float
 /* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
  * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack. */
 /* tc_scales + tc_pack (and the column means) in two passes over the data instead of four: one
- * statistics pass (column sums, max |s|, max |score| into stats[D + 2]) and one packing pass that
+ * statistics pass (column sums, max |s|, max |score| into stats[8 * (D + 2)], scratch) and one packing pass that
  * derives the mean (center != 0) and the scales itself.  mean_out [D] / s_centred / norms may be NULL. */
 int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const float* s, int64_t lds,
                           int64_t N, int64_t D, int center, float* scales, void* f_hi, void* f_lo,

@@ -10,6 +10,8 @@
 
 namespace sigsvgd {
 
+static_assert(kStatSlots == 8, "sig3_fwd_kernel (sig_kernels.cu) spreads its statistics over 8 slots");
+
 static thread_local char g_err[512] = "";
 
 void set_error(const char* fmt, ...) {
@@ -136,7 +138,7 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
     L.off_norms = bump(&cur, sizeof(float) * N);
     L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
     L.off_win = bump(&cur, window_workspace_bytes(N, N, nullptr));
-    L.off_stats = bump(&cur, sizeof(float) * (L.D + 2));
+    L.off_stats = bump(&cur, sizeof(float) * kStatSlots * (L.D + 2));
   }
   L.total = cur;
   return L;
@@ -148,7 +150,7 @@ static bool tc_path_enabled(int64_t B, int64_t N, uint32_t flags) {
   if (flags & SIGSVGD_FLAG_FORCE_SIMT) return false;
   if (B != 1 || !tc_available()) return false;
   if (flags & SIGSVGD_FLAG_FORCE_TC) return true;
-  return N >= 1024;
+  return N >= 256;  // measured: 129 us (tcgen05) vs 175 us (SIMT) per update at N = 256
 }
 
 }  // namespace sigsvgd
@@ -448,8 +450,16 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   float* norms = (float*)(w + L.off_norms);
   float* scales = (float*)(w + L.off_scales);
 
-  // K1: signatures of all B*N particles
-  SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
+  // K1: signatures of all B*N particles; on the tensor-core path (depth 3) the same kernel also
+  // accumulates the statistics the operand preparation needs (column sums, max |s|, max |score|)
+  const bool fwd_stats = use_tc && sig_fwd_fuses_stats(d, depth);
+  if (fwd_stats) {
+    float* stats0 = (float*)(w + L.off_stats);
+    SIG_CUDA_OK(cudaMemsetAsync(stats0, 0, sizeof(float) * kStatSlots * (D + 2), st));
+    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st, stats0, hp ? nullptr : score, P, P));
+  } else {
+    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
+  }
   // feature block (centred), its row pitch, and the [K.S | rowsum | K.score] blocks of `out`
   const float* feat;
   int64_t ldf;
@@ -472,16 +482,17 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     // statistics pass (column sums, maxima), then planes F = [S - mean | 1 | score] (fp16 hi/lo)
     // with the centred fp32 features going to the V buffer
     float* stats = (float*)(w + L.off_stats);
+    // the packing pass also zeroes `out`, the target of the K.F reductions
     if (!hp) {
-      SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 1, st));
+      if (!fwd_stats) SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, score, P, P, stats, 1, st));
       SIG_PROPAGATE(launch_tc_pack_stats(score, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales,
-                                         scales + 8, Fh, Fl, C, C, norms, V, D, mean, st));
+                                         scales + 8, Fh, Fl, C, C, norms, V, D, mean, st, 0, -1, out, C));
     } else {
       // feature columns only; the score columns follow once its copy has landed
-      SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, nullptr, P, P, stats, 1, st));
+      if (!fwd_stats) SIG_PROPAGATE(launch_tc_stats(sig, D, N, D, nullptr, P, P, stats, 1, st));
       SIG_PROPAGATE(launch_tc_pack_stats(nullptr, P, P, sig, D, stats, N, center ? 1 : 0, N, D, scales,
                                          scales + 8, Fh, Fl, C, C, norms, V, D, mean, st, 0,
-                                         round_up(D + 1, 2)));
+                                         round_up(D + 1, 2), out, C));
     }
     feat = V, ldf = D;
     out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
@@ -524,7 +535,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
                                          (D + 1) & ~(int64_t)1, C));
     }
     SIG_PROPAGATE(tc_matmul_nn(TcPlanes{Kh, Kl, L.Np}, TcPlanes{Fh, Fl, C}, N, N, D + 1 + P,
-                               scales + 8, out, C, st));
+                               scales + 8, out, C, st, /*out_zeroed=*/true));
   } else {
     SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));
     SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, B, st));

@@ -63,8 +63,12 @@ int num_sms();  // cached cudaDevAttrMultiProcessorCount of the current device
 
 // ---- launchers implemented in the individual .cu files ------------------------------------
 // signature (sig_kernels.cu)
+// stats != NULL (depth 3, d <= 8): also accumulates stats[0..D) += column sums of sig,
+// stats[D] = max |sig| bits, stats[D+1] = max |score| bits (score may be NULL); caller zeroes stats
+bool sig_fwd_fuses_stats(int64_t d, int depth);
 int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
-                   float* sig, cudaStream_t st);
+                   float* sig, cudaStream_t st, float* stats = nullptr, const float* score = nullptr,
+                   int64_t ld_score = 0, int64_t P = 0);
 // Optional producer of the cotangent: instead of reading gsig, the depth-3 backward kernel forms
 //   g_i = -(1/h^2) (sc_i * rowsum_i - ks_i) + median-gradient term on the tie rows
 // (the closed form of autograd.grad(k_xx.sum(), X) in signature space) while it

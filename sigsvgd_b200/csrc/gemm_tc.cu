@@ -467,13 +467,13 @@ int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const flo
 }
 
 int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                 float* out, int64_t ldo, cudaStream_t st) {
+                 float* out, int64_t ldo, cudaStream_t st, bool out_zeroed) {
   SIG_CHECK_ARG(M >= 1 && K >= 1 && C >= 1 && A.ld >= K && V.ld >= C && ldo >= C,
                 "tc_matmul_nn: bad shape M=%lld K=%lld C=%lld", (long long)M, (long long)K, (long long)C);
   SIG_CHECK_ARG(M < (1ll << 31) && K < (1ll << 31), "tc_matmul_nn: too many rows");
   // CTA pairs (kf2_tc.cu) when the device can co-schedule them and there are 256-row tiles to fill
   if (M >= 256 && tc_matmul_pair_available())
-    return tc_matmul_pair(A, V, M, K, C, colscale, out, ldo, st);
+    return tc_matmul_pair(A, V, M, K, C, colscale, out, ldo, st, out_zeroed);
   using P = Pipe<true>;
   constexpr int BK = P::BK;
   CUtensorMap ah, al, bh, bl;
@@ -499,7 +499,7 @@ int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const 
   if (p.streamk) p.kb_per_split = P::kMaxChainKb;
   p.out = out, p.ldo = ldo;
   p.row_vec = nullptr, p.col_vec = colscale, p.scal = nullptr;
-  if (p.nsplit > 1 || p.streamk)
+  if ((p.nsplit > 1 || p.streamk) && !out_zeroed)
     SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, M, st));
   return launch_gemm3x<true, EPI_COLSCALE>(ah, al, bh, bl, p, st);
 }

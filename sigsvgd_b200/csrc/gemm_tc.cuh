@@ -57,9 +57,9 @@ int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float
 // the CTA-pair (cta_group::2) kernel behind tc_matmul_nn (kf2_tc.cu)
 bool tc_matmul_pair_available();
 int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                   float* out, int64_t ldo, cudaStream_t st);
+                   float* out, int64_t ldo, cudaStream_t st, bool out_zeroed = false);
 int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                 float* out, int64_t ldo, cudaStream_t st);
+                 float* out, int64_t ldo, cudaStream_t st, bool out_zeroed = false);
 
 // true when this process can create TMA descriptors (driver entry point resolved)
 bool tc_available();
@@ -89,6 +89,7 @@ int launch_tc_pack(const float* score, int64_t lsc, int64_t P, const float* s, i
                    const float* mean, int64_t N, int64_t D, const float* tcs, __half* fh, __half* fl,
                    int64_t ldp, int64_t Cp, float* norms, float* sc, int64_t ldsc, int64_t batch,
                    cudaStream_t st);
+constexpr int kStatSlots = 8;  // `stats` buffers hold kStatSlots records of D + 2 floats (planes.cu)
 // fused front end: statistics pass (column sums, max |s|, max |score| -> stats[D + 2]) ...
 int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
                     int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st,
@@ -99,7 +100,8 @@ int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float
                          const float* stats, int64_t n_total, int center, int64_t N, int64_t D,
                          float* tcs, float* colscale, __half* fh, __half* fl, int64_t ldp, int64_t Cp,
                          float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st,
-                         int64_t c_lo = 0, int64_t c_hi = -1);  // plane columns [c_lo, c_hi) only
+                         int64_t c_lo = 0, int64_t c_hi = -1,  // plane columns [c_lo, c_hi) only
+                         float* zero_out = nullptr, int64_t ld_zero = 0);  // also zero [N, Cp] of this buffer
 // K = exp(gamma d) as planes of K*2^14 (+ optional fp32 K into kout, may alias d);
 // accumulates state->sum_kd, records median ties (global row = row_offset + i)
 int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,

@@ -291,7 +291,7 @@ static int max_pairs() {
 bool tc_matmul_pair_available() { return max_pairs() > 0 && !getenv("SIGSVGD_KF_NO_PAIRS"); }
 
 int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                   float* out, int64_t ldo, cudaStream_t st) {
+                   float* out, int64_t ldo, cudaStream_t st, bool out_zeroed) {
   const int pairs_max = max_pairs();
   if (pairs_max <= 0) {
     set_error("tc_matmul_pair: 2-CTA clusters cannot be launched on this device");
@@ -317,7 +317,7 @@ int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, cons
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
   p.order = 0;  // row tile slowest (column-tile-slowest measured 12 % slower at N = 8192)
   p.out = out, p.ldo = ldo, p.colscale = colscale;
-  if (p.nsplit > 1)
+  if (p.nsplit > 1 && !out_zeroed)
     SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, M, st));
   const int64_t items = (int64_t)p.tiles_m * p.tiles_n * p.nsplit;
   const int pairs = (int)std::min<int64_t>(items, pairs_max);

@@ -137,6 +137,9 @@ pack_planes_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
 // fused front end of the tensor-core path: one statistics pass + one packing pass
 //   stats[0..D)  = column sums of s (float atomics)      stats[D] = max |s| bits
 //   stats[D+1]   = max |score| bits                       (zeroed by the launcher)
+// The buffer holds kStatSlots such records back to back (slot pitch D + 2): producers that hammer
+// it from a thousand blocks (the fused signature forward) spread their atomics over the slots;
+// the consumer adds the slots up.
 // The pack kernel derives the mean and the scales itself: alpha_S from the bound
 // max|s - mean| <= max|s| + max|mean| (the planes keep >= 22 significant bits as long as the
 // centred features are not 2^17 times smaller than that bound).
@@ -194,14 +197,27 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
                   int64_t n_total, int center, int64_t N, int64_t D, float* __restrict__ tcs,
                   float* __restrict__ colscale, __half* __restrict__ fh, __half* __restrict__ fl,
                   int64_t ldp, int64_t Cp, float* __restrict__ norms, float* __restrict__ sc,
-                  int64_t ldsc, float* __restrict__ mean_out, int64_t c_lo, int64_t c_hi) {
+                  int64_t ldsc, float* __restrict__ mean_out, int64_t c_lo, int64_t c_hi,
+                  float* __restrict__ zero_out, int64_t ld_zero, int mean_in_smem) {
   // columns [c_lo, c_hi) (both even) of the planes are written; a NULL score leaves zeros in its
   // columns (the host-input pipeline packs the feature and the score columns in two launches)
   __shared__ float sh_mm[kThreads / 32];
+  extern __shared__ float sh_mean[];  // [D] when mean_in_smem
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const float inv_n = center ? 1.f / (float)n_total : 0.f;
+  const int64_t slot_pitch = D + 2;
+  auto col_mean_of = [&](int64_t c) {
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < kStatSlots; ++k) sum += stats[k * slot_pitch + c];
+    return sum * inv_n;
+  };
   float mm = 0.f;  // max |mean|
-  for (int64_t c = threadIdx.x; c < D; c += kThreads) mm = fmaxf(mm, fabsf(stats[c] * inv_n));
+  for (int64_t c = threadIdx.x; c < D; c += kThreads) {
+    const float m = col_mean_of(c);
+    if (mean_in_smem) sh_mean[c] = m;
+    mm = fmaxf(mm, fabsf(m));
+  }
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) mm = fmaxf(mm, __shfl_xor_sync(0xffffffffu, mm, o));
   if (lane == 0) sh_mm[wid] = mm;
@@ -209,7 +225,12 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
   mm = 0.f;
 #pragma unroll
   for (int i = 0; i < kThreads / 32; ++i) mm = fmaxf(mm, sh_mm[i]);
-  const unsigned int* mx = reinterpret_cast<const unsigned int*>(stats + D);
+  unsigned int mx[2] = {0u, 0u};
+#pragma unroll
+  for (int k = 0; k < kStatSlots; ++k) {
+    const unsigned int* m = reinterpret_cast<const unsigned int*>(stats + k * slot_pitch + D);
+    mx[0] = max(mx[0], m[0]), mx[1] = max(mx[1], m[1]);  // non-negative float bits order like uints
+  }
   const float as = pow2_scale(__uint_as_float(mx[0]) + mm);
   const float ag = pow2_scale(__uint_as_float(mx[1]));
   if (blockIdx.x == 0) {
@@ -227,10 +248,14 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
       colscale[c] = v;
     }
     if (mean_out)
-      for (int64_t c = threadIdx.x; c < D; c += kThreads) mean_out[c] = stats[c] * inv_n;
+      for (int64_t c = threadIdx.x; c < D; c += kThreads) mean_out[c] = col_mean_of(c);
   }
-  const int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + wid;
-  if (row >= N) return;
+  // warps stride over the rows: the per-block prologue above (means of 8 slots, scales) is paid
+  // once per ~2 blocks per SM instead of once per 8 rows
+  for (int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + wid; row < N;
+       row += (int64_t)gridDim.x * (kThreads / 32)) {
+  if (zero_out)  // this row of the K.F result buffer (reduction target): saves a memset node
+    for (int64_t c = lane; c < Cp; c += 32) zero_out[row * ld_zero + c] = 0.f;
   float nrm = 0.f;
   for (int64_t c0 = c_lo + 2 * lane; c0 < c_hi; c0 += 64) {
     float x[2];
@@ -239,7 +264,7 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
       const int64_t c = c0 + e;
       float v = 0.f;
       if (c < D) {
-        v = __ldg(s + row * lds + c) - stats[c] * inv_n;
+        v = __ldg(s + row * lds + c) - (mean_in_smem ? sh_mean[c] : col_mean_of(c));
         if (sc) sc[row * ldsc + c] = v;
         v *= as;
       } else if (c == D) {
@@ -266,6 +291,7 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
   if (lane == 0 && norms) norms[row] = nrm;
+  }
 }
 
 __device__ __forceinline__ double block_sum_double(double v, double* sm) {
@@ -395,7 +421,7 @@ int launch_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const flo
                     int64_t lsc, int64_t P, float* stats, int zero_first, cudaStream_t st, int do_s) {
   SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && (P == 0 || score == nullptr || lsc >= P),
                 "tc_stats: bad shape N=%lld D=%lld P=%lld", (long long)N, (long long)D, (long long)P);
-  if (zero_first) SIG_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * (D + 2), st));
+  if (zero_first) SIG_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * kStatSlots * (D + 2), st));
   const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)num_sms() * 2, ceil_div(N, 8)));
   const int rows_per_block = (int)ceil_div(N, blocks);
   stats_kernel<<<(unsigned)ceil_div(N, rows_per_block), kStatThreads, 0, st>>>(s, lds, N, D, score, lsc, P,
@@ -408,7 +434,8 @@ int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float
                          const float* stats, int64_t n_total, int center, int64_t N, int64_t D,
                          float* tcs, float* colscale, __half* fh, __half* fl, int64_t ldp, int64_t Cp,
                          float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st,
-                         int64_t c_lo, int64_t c_hi) {
+                         int64_t c_lo, int64_t c_hi, float* zero_out, int64_t ld_zero) {
+  SIG_CHECK_ARG(zero_out == nullptr || ld_zero >= Cp, "tc_pack_stats: ld_zero < Cp");
   if (c_hi < 0) c_hi = Cp;
   SIG_CHECK_ARG(c_lo >= 0 && c_hi <= Cp && (c_lo & 1) == 0 && (c_hi & 1) == 0, "tc_pack_stats: bad column range");
   SIG_CHECK_ARG(N >= 1 && D >= 1 && P >= 0 && lds >= D && Cp >= D + 1 + P && ldp >= Cp && (Cp & 7) == 0 &&
@@ -416,9 +443,11 @@ int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float
                 "tc_pack_stats: bad shape N=%lld D=%lld P=%lld Cp=%lld ldp=%lld", (long long)N, (long long)D,
                 (long long)P, (long long)Cp, (long long)ldp);
   SIG_CHECK_ARG(P == 0 || score == nullptr || lsc >= P, "tc_pack_stats: score pitch < P");
-  pack_stats_kernel<<<(unsigned)ceil_div(N, kThreads / 32), kThreads, 0, st>>>(
+  const int mean_in_smem = D <= 10240 ? 1 : 0;  // 40 KB of dynamic shared memory at most
+  const int64_t blocks = std::min<int64_t>(ceil_div(N, kThreads / 32), (int64_t)num_sms() * 4);
+  pack_stats_kernel<<<(unsigned)blocks, kThreads, mean_in_smem ? sizeof(float) * D : 0, st>>>(
       score, lsc, P, s, lds, stats, n_total, center, N, D, tcs, colscale, fh, fl, ldp, Cp, norms, sc, ldsc,
-      mean_out, c_lo, c_hi);
+      mean_out, c_lo, c_hi, zero_out, ld_zero, mean_in_smem);
   SIG_LAUNCH_OK("pack_stats_kernel");
   return 0;
 }

@@ -98,7 +98,8 @@ __device__ __forceinline__ float group_reduce_scatter(const float (&pd)[d], int 
 template <int d>
 __global__ void __launch_bounds__(kThreads)
 sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, int TC,
-                float* __restrict__ sig) {
+                float* __restrict__ sig, float* __restrict__ stats, const float* __restrict__ score,
+                int64_t ld_score, int P) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   extern __shared__ __align__(16) float smem[];
@@ -201,6 +202,45 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
     }
   }
   __syncthreads();
+  if (stats != nullptr) {
+    // statistics of the tensor-core operand preparation (planes.cu: stats_kernel) while the block's
+    // signatures are still in shared memory: column sums, max |s|, and max |score| of its rows
+    // (one of the 8 slots of the buffer per block: 1024 blocks on the same 399 addresses cost
+    // 9 us of serialised L2 atomics with a single slot)
+    stats += (blockIdx.x & 7) * (D + 2);
+    float ms = 0.f, mg = 0.f;
+    for (int c = tid; c < D; c += kThreads) {
+      float sum = 0.f;
+      for (int q = 0; q < npart; ++q) {
+        const float v = smem[q * D + c];
+        sum += v;
+        ms = fmaxf(ms, fabsf(v));
+      }
+      atomicAdd(stats + c, sum);
+    }
+    if (score != nullptr) {
+      for (int q = 0; q < npart; ++q) {
+        const float* __restrict__ row = score + (p0 + q) * ld_score;
+        for (int i0 = tid; i0 < P; i0 += 8 * kThreads) {
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = i0 + k * kThreads < P ? __ldg(row + i0 + k * kThreads) : 0.f;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) mg = fmaxf(mg, fabsf(v[k]));
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+      ms = fmaxf(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+      mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    }
+    if ((tid & 31) == 0) {
+      unsigned int* mx = reinterpret_cast<unsigned int*>(stats + D);
+      if (ms > 0.f && ms < INFINITY) atomicMax(mx, __float_as_uint(ms));
+      if (mg > 0.f && mg < INFINITY) atomicMax(mx + 1, __float_as_uint(mg));
+    }
+  }
   float* __restrict__ dst = sig + p0 * D;
   const int nout = npart * D;
   if ((nout & 3) == 0 && is_aligned16(dst)) {
@@ -641,7 +681,7 @@ sig_generic_bwd_kernel(const float* __restrict__ x, const float* __restrict__ si
 
 template <int d>
 int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* sig,
-                    cudaStream_t st) {
+                    cudaStream_t st, float* stats, const float* score, int64_t ld_score, int64_t P) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
@@ -649,7 +689,8 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
   int TC = (int)std::min<int64_t>(T, (kBudget / 4 / PPC - kGroupPad) / DP);
   size_t smem = (size_t)std::max(PPC * (TC * DP + kGroupPad), PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
-  sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig);
+  sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig, stats,
+                                                              score, ld_score, (int)P);
   SIG_LAUNCH_OK("sig3_fwd_kernel");
   return 0;
 }
@@ -687,8 +728,13 @@ int make_levels(int64_t d, int depth, LevelInfo* L, int64_t* D) {
 
 }  // namespace
 
+bool sig_fwd_fuses_stats(int64_t d, int depth) { return depth == 3 && d >= 1 && d <= 8; }
+
 int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
-                   float* sig, cudaStream_t st) {
+                   float* sig, cudaStream_t st, float* stats, const float* score, int64_t ld_score,
+                   int64_t P) {
+  SIG_CHECK_ARG(stats == nullptr || sig_fwd_fuses_stats(d, depth),
+                "signature_fwd: fused statistics need depth 3 and d <= 8");
   SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
                 "signature_fwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,
                 (long long)T, (long long)d, depth);
@@ -697,14 +743,14 @@ int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, i
   if (N == 0) return 0;
   if (depth == 3) {
     switch (d) {
-      case 1: return launch_sig3_fwd<1>(x, N, T, basepoint, sig, st);
-      case 2: return launch_sig3_fwd<2>(x, N, T, basepoint, sig, st);
-      case 3: return launch_sig3_fwd<3>(x, N, T, basepoint, sig, st);
-      case 4: return launch_sig3_fwd<4>(x, N, T, basepoint, sig, st);
-      case 5: return launch_sig3_fwd<5>(x, N, T, basepoint, sig, st);
-      case 6: return launch_sig3_fwd<6>(x, N, T, basepoint, sig, st);
-      case 7: return launch_sig3_fwd<7>(x, N, T, basepoint, sig, st);
-      case 8: return launch_sig3_fwd<8>(x, N, T, basepoint, sig, st);
+      case 1: return launch_sig3_fwd<1>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 2: return launch_sig3_fwd<2>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 3: return launch_sig3_fwd<3>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 4: return launch_sig3_fwd<4>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 5: return launch_sig3_fwd<5>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 6: return launch_sig3_fwd<6>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 7: return launch_sig3_fwd<7>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 8: return launch_sig3_fwd<8>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
       default: break;
     }
   }

@@ -224,7 +224,7 @@ def tc_pack_fused_raw(s: torch.Tensor, score: Optional[torch.Tensor] = None, cen
     Cp = (D + 1 + P + 63) // 64 * 64
     dev = s.device
     scales = torch.empty(8 + Cp, dtype=torch.float32, device=dev)
-    stats = torch.empty(D + 2, dtype=torch.float32, device=dev)
+    stats = torch.empty(8 * (D + 2), dtype=torch.float32, device=dev)
     fh = torch.empty(N, Cp, dtype=torch.float16, device=dev)
     fl = torch.empty(N, Cp, dtype=torch.float16, device=dev)
     norms = torch.empty(N, dtype=torch.float32, device=dev)

@@ -81,6 +81,21 @@ int sigsvgd_signature_bwd(const float* x, const float* sig, const float* gsig, i
                           int64_t T, int64_t d, int depth, int basepoint, const float* add,
                           int64_t ld_add, float alpha, float beta, float* out, void* stream);
 
+/* Time-parallel variant of the same pair (same reference statements: _traj_kernels.py:125-126 and
+ * the backward reached from svgd.py:43).  The forward also writes levels 1-2 of the signature of each path up
+ * to the end of time segments 0..2 of ceil(T/4) steps into pref[N][3][d+d*d]; the backward with that
+ * buffer sweeps the 4 segments of every path at once (Chen: S_T = P_q (x) R_q), a 4x shorter
+ * sequential chain.  Available when sigsvgd_signature_prefix_floats(N,T,d,depth) > 0 (depth 3,
+ * d <= 8, T >= 8, T*d a multiple of 4); that many floats is the size of pref.  Results equal the
+ * plain pair up to fp32 rounding. */
+int64_t sigsvgd_signature_prefix_floats(int64_t N, int64_t T, int64_t d, int depth);
+int sigsvgd_signature_fwd_prefix(const float* x, int64_t N, int64_t T, int64_t d, int depth,
+                                 int basepoint, float* sig, float* pref, void* stream);
+int sigsvgd_signature_bwd_prefix(const float* x, const float* sig, const float* pref,
+                                 const float* gsig, int64_t N, int64_t T, int64_t d, int depth,
+                                 int basepoint, const float* add, int64_t ld_add, float alpha,
+                                 float beta, float* out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Pairwise squared distances.  Replaces pw_dist_sq (src/utils/math.py:69-86):
  *   dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j),  a [M,D] (row stride lda), b [N,D] (ldb).

@@ -53,6 +53,14 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_float, c_float,
          c_void_p, c_void_p],
     ),
+    "sigsvgd_signature_prefix_floats": (c_int64, [c_int64, c_int64, c_int64, c_int]),
+    "sigsvgd_signature_fwd_prefix": (
+        c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_signature_bwd_prefix": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_float,
+         c_float, c_void_p, c_void_p],
+    ),
     "sigsvgd_sqdist": (
         c_int,
         [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_int64, c_uint32, c_void_p],

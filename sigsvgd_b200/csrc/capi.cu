@@ -100,7 +100,7 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 
 struct PhiLayout {
   int64_t D, P, C, Np;
-  size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, total;
+  size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, off_pref, total;
   // tensor-core path (B == 1): fp16 planes of F [N x C] and K [N x Np], norms, scales
   size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales, off_win, off_stats;
 };
@@ -128,6 +128,8 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   L.off_mean = bump(&cur, sizeof(float) * B * L.D);
   L.off_part = bump(&cur, sizeof(float) * B * 64 * L.D);
   L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
+  // prefix checkpoints of the time-parallel signature backward (0 floats when not applicable)
+  L.off_pref = bump(&cur, sizeof(float) * sig_prefix_floats(B * N, T, d, depth));
   L.Np = round_up(N, 64);
   L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = L.off_win = L.off_stats = 0;
   if (B == 1) {
@@ -179,6 +181,27 @@ int sigsvgd_signature_bwd(const float* x, const float* sig, const float* gsig, i
   SIG_CHECK_ARG(N == 0 || (x && sig && gsig && out), "signature_bwd: NULL pointer");
   return launch_sig_bwd(x, sig, gsig, N, T, d, depth, basepoint, add, ld_add, alpha, beta, out,
                         (cudaStream_t)stream);
+}
+
+int64_t sigsvgd_signature_prefix_floats(int64_t N, int64_t T, int64_t d, int depth) {
+  if (N < 0 || T < 1 || d < 1 || depth < 1 || depth > 8) return -1;
+  return sig_prefix_floats(N, T, d, depth);
+}
+
+int sigsvgd_signature_fwd_prefix(const float* x, int64_t N, int64_t T, int64_t d, int depth,
+                                 int basepoint, float* sig, float* pref, void* stream) {
+  SIG_CHECK_ARG(N == 0 || (x && sig && pref), "signature_fwd_prefix: NULL pointer");
+  return launch_sig_fwd(x, N, T, d, depth, basepoint, sig, (cudaStream_t)stream, nullptr, nullptr, 0, 0,
+                        pref);
+}
+
+int sigsvgd_signature_bwd_prefix(const float* x, const float* sig, const float* pref,
+                                 const float* gsig, int64_t N, int64_t T, int64_t d, int depth,
+                                 int basepoint, const float* add, int64_t ld_add, float alpha,
+                                 float beta, float* out, void* stream) {
+  SIG_CHECK_ARG(N == 0 || (x && sig && pref && gsig && out), "signature_bwd_prefix: NULL pointer");
+  return launch_sig_bwd(x, sig, gsig, N, T, d, depth, basepoint, add, ld_add, alpha, beta, out,
+                        (cudaStream_t)stream, nullptr, pref);
 }
 
 int sigsvgd_sqdist(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int64_t N,
@@ -436,6 +459,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   float* mean = (float*)(w + L.off_mean);
   float* part = (float*)(w + L.off_part);
   void* selws = (void*)(w + L.off_sel);
+  float* pref = sig_bwd_uses_prefix(T, d, depth) ? (float*)(w + L.off_pref) : nullptr;
   const int64_t D = L.D, P = L.P, C = L.C, R = B * N;
   const bool center = !(flags & SIGSVGD_FLAG_NO_CENTER);
   const bool use_tc = tc_path_enabled(B, N, flags);
@@ -456,9 +480,9 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   if (fwd_stats) {
     float* stats0 = (float*)(w + L.off_stats);
     SIG_CUDA_OK(cudaMemsetAsync(stats0, 0, sizeof(float) * kStatSlots * (D + 2), st));
-    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st, stats0, hp ? nullptr : score, P, P));
+    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st, stats0, hp ? nullptr : score, P, P, pref));
   } else {
-    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st));
+    SIG_PROPAGATE(launch_sig_fwd(x, R, T, d, depth, 1, sig, st, nullptr, nullptr, 0, 0, pref));
   }
   // feature block (centred), its row pitch, and the [K.S | rowsum | K.score] blocks of `out`
   const float* feat;
@@ -550,10 +574,12 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,
                                   g, D, B, st));
   if (gradk_out)
-    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st, spec));
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, nullptr, 0, 0.f, 1.f, gradk_out, st, spec,
+                                 pref));
   const float inv_n = 1.f / (float)N;
   if (!hp) {
-    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st, spec));
+    SIG_PROPAGATE(launch_sig_bwd(x, sig, g, R, T, d, depth, 1, out_kg, C, inv_n, -inv_n, phi, st, spec,
+                                 pref));
     return 0;
   }
   // K2 in row chunks; each chunk's D2H copy overlaps the next chunk's backward sweep
@@ -565,7 +591,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     gc.sc += r0 * ldf, gc.ks += r0 * C, gc.rowsum += r0 * C, gc.row_offset = r0;
     SIG_PROPAGATE(launch_sig_bwd(x + r0 * T * d, sig + r0 * D, g + r0 * D, rows, T, d, depth, 1,
                                  out_kg + r0 * C, C, inv_n, -inv_n, phi + r0 * T * d, st,
-                                 fuse_grad ? &gc : nullptr));
+                                 fuse_grad ? &gc : nullptr, pref ? pref + sig_prefix_floats(r0, T, d, depth) : nullptr));
     SIG_CUDA_OK(cudaEventRecord(hp->chunk[n], st));
     SIG_CUDA_OK(cudaStreamWaitEvent(hp->d2h, hp->chunk[n], 0));
     SIG_CUDA_OK(cudaMemcpyAsync(hp->phi_host + r0 * T * d, phi + r0 * T * d,

@@ -68,7 +68,12 @@ int num_sms();  // cached cudaDevAttrMultiProcessorCount of the current device
 bool sig_fwd_fuses_stats(int64_t d, int depth);
 int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
                    float* sig, cudaStream_t st, float* stats = nullptr, const float* score = nullptr,
-                   int64_t ld_score = 0, int64_t P = 0);
+                   int64_t ld_score = 0, int64_t P = 0, float* pref = nullptr);
+// Prefix checkpoints for the time-parallel backward (sig3_bwd_seg_kernel): pref[N][3][d+d*d] holds
+// levels 1-2 of the signature of each path up to the end of time segments 0..2 of ceil(T/4) steps.  The forward
+// writes them when pref != NULL, the backward with the same pref sweeps the 4 segments at once.
+bool sig_bwd_uses_prefix(int64_t T, int64_t d, int depth);
+int64_t sig_prefix_floats(int64_t N, int64_t T, int64_t d, int depth);  // 0 when not available
 // Optional producer of the cotangent: instead of reading gsig, the depth-3 backward kernel forms
 //   g_i = -(1/h^2) (sc_i * rowsum_i - ks_i) + median-gradient term on the tie rows
 // (the closed form of autograd.grad(k_xx.sum(), X) in signature space) while it
@@ -92,7 +97,7 @@ bool sig_bwd_fuses_grad(int64_t d, int depth);
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
                    float alpha, float beta, float* out, cudaStream_t st,
-                   const SigGradSpec* spec = nullptr);
+                   const SigGradSpec* spec = nullptr, const float* pref = nullptr);
 
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,

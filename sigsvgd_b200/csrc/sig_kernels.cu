@@ -45,7 +45,7 @@ __device__ __forceinline__ void copy_in_f4(float* dst, const float* __restrict__
   for (; i < n4; i += kThreads) d4[i] = __ldg(s4 + i);
 }
 
-__device__ __forceinline__ bool is_aligned16(const void* p) {
+__host__ __device__ __forceinline__ bool is_aligned16(const void* p) {
   return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }
 
@@ -95,11 +95,14 @@ __device__ __forceinline__ float group_reduce_scatter(const float (&pd)[d], int 
 // ------------------------------------------------------------------------------------------
 // depth-3 forward
 // ------------------------------------------------------------------------------------------
+constexpr int kSeg = 4;  // time segments of the time-parallel backward (sig3_bwd_seg_kernel)
+constexpr int kSegThreads = 32 * kSeg;
+
 template <int d>
 __global__ void __launch_bounds__(kThreads)
 sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, int TC,
                 float* __restrict__ sig, float* __restrict__ stats, const float* __restrict__ score,
-                int64_t ld_score, int P) {
+                int64_t ld_score, int P, float* __restrict__ pref, int seg_len) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   extern __shared__ __align__(16) float smem[];
@@ -121,6 +124,7 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
 #pragma unroll
     for (int c = 0; c < d; ++c) S3[j][c] = 0.f;
   }
+  int next_ck = pref != nullptr ? seg_len : T;  // prefix checkpoints for the time-parallel backward
 
   for (int c0 = 0; c0 < T; c0 += TC) {
     const int len = min(TC, T - c0);
@@ -187,6 +191,17 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
 #pragma unroll
       for (int j = 0; j < d; ++j) S2[j] = fmaf(u2, dl[j], S2[j]);
       S1 += di;
+      if (c0 + r + 1 == next_ck && next_ck < T) {  // S after time c0+r = end state of a segment
+        if (active) {
+          // levels 1-2 only: the backward sweep never reads the level-3 state
+          float* __restrict__ o =
+              pref + ((p0 + grp) * (kSeg - 1) + (next_ck / seg_len - 1)) * (int64_t)(d + d * d);
+          o[lane] = S1;
+#pragma unroll
+          for (int j = 0; j < d; ++j) o[d + lane * d + j] = S2[j];
+        }
+        next_ck += seg_len;
+      }
     }
   }
   // stage the result through shared memory for coalesced stores
@@ -252,6 +267,45 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   }
 }
 
+// One reversed time step of the depth-3 VJP for lane i of a particle's group:
+//   levels 1-2 of the state go back  S_{t-1} = S_t (x) exp(-dl)  (level 3 feeds nothing),
+//   the adjoints (A1, A2; A3 = G3 is constant) go back through  S_t = S_{t-1} (x) exp(dl),
+// and the return value is this lane's component of dL/d(dl_t).
+template <int G, int d>
+__device__ __forceinline__ float sig3_bwd_step(const float (&dl)[d], float di, float& S1, float (&S2)[d],
+                                               float& A1, float (&A2)[d], const float (&g3)[d][d],
+                                               int lane) {
+  const float u2r = fmaf(di, -0.5f, S1);
+#pragma unroll
+  for (int j = 0; j < d; ++j) S2[j] = fmaf(-u2r, dl[j], S2[j]);
+  S1 -= di;
+  float hdl[d], pd[d];
+#pragma unroll
+  for (int c = 0; c < d; ++c) {
+    hdl[c] = 0.5f * dl[c];
+    pd[c] = 0.f;
+  }
+  const float u3 = fmaf(di, 1.f / 3.f, S1), u2 = fmaf(di, 0.5f, S1), u3h = 0.5f * u3;
+  float sum_u = 0.f, sum_v = 0.f;  // sum_j rr_j dl_j / 2  and  sum_j A2_j dl_j
+#pragma unroll
+  for (int j = 0; j < d; ++j) {
+    float rr = 0.f;
+#pragma unroll
+    for (int c = 0; c < d; ++c) rr = fmaf(g3[j][c], dl[c], rr);
+    const float B2 = fmaf(u3, hdl[j], S2[j]);
+#pragma unroll
+    for (int c = 0; c < d; ++c) pd[c] = fmaf(g3[j][c], B2, pd[c]);
+    pd[j] = fmaf(rr, u3h, pd[j]);
+    pd[j] = fmaf(A2[j], u2, pd[j]);
+    sum_u = fmaf(rr, hdl[j], sum_u);
+    sum_v = fmaf(A2[j], dl[j], sum_v);
+    A2[j] += rr;
+  }
+  const float dI = fmaf(sum_u, 1.f / 3.f, fmaf(sum_v, 0.5f, A1));
+  A1 += sum_u + sum_v;
+  return group_reduce_scatter<G, d>(pd, lane) + dI;
+}
+
 // ------------------------------------------------------------------------------------------
 // depth-3 backward (VJP) with fused  out = beta * gx + alpha * add
 // ------------------------------------------------------------------------------------------
@@ -275,18 +329,21 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
   const bool vec = TC >= T && ((T * d) & 3) == 0 && is_aligned16(x) && is_aligned16(out) &&
                    (add == nullptr || (is_aligned16(add) && (ld_add & 3) == 0));
 
-  float S1 = 0.f, S2[d], S3[d][d], A1 = 0.f, A2[d], g3[d][d];
-  // ---- load S_T and dL/dS_T (coalesced through smem; both blocks in flight together) ----
+  constexpr int L12 = d + d * d;  // the sweep needs levels 1-2 of the state only (level 3 of S
+                                  // feeds nothing: its adjoint is the constant G3)
+  float S1 = 0.f, S2[d], A1 = 0.f, A2[d], g3[d][d];
+  // ---- load S_T (levels 1-2) and dL/dS_T (coalesced through smem) ----
   {
     const float* __restrict__ src = sig + p0 * D;
     const float* __restrict__ gsrc = gsig + p0 * D;
     float* gstage = smem + PPC * D;
     const int nst = npart * D;
+    for (int i = tid; i < npart * L12; i += kThreads) {
+      const int q = i / L12;
+      smem[i] = __ldg(src + q * D + (i - q * L12));
+    }
     if (gs.sc != nullptr) {
-      // S_T by 16-byte loads where possible, the cotangent computed in place (see SigGradSpec)
-      if ((nst & 3) == 0 && is_aligned16(src)) copy_in_f4(smem, src, nst >> 2, tid);
-      else
-        for (int i = tid; i < nst; i += kThreads) smem[i] = __ldg(src + i);
+      // the cotangent computed in place (see SigGradSpec)
       const float gam2 = 2.f * gs.state->gamma;  // -(1/h^2) = 2*gamma
       for (int i0 = tid; i0 < nst; i0 += 8 * kThreads) {
         float a[8], b[8], r[8];
@@ -323,42 +380,16 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
           __syncthreads();
         }
       }
-    } else if ((nst & 3) == 0 && is_aligned16(src) && is_aligned16(gsrc)) {
-      const float4* __restrict__ a4 = reinterpret_cast<const float4*>(src);
-      const float4* __restrict__ b4 = reinterpret_cast<const float4*>(gsrc);
-      float4* da = reinterpret_cast<float4*>(smem);
-      float4* db = reinterpret_cast<float4*>(gstage);
-      const int n4 = nst >> 2;
-      for (int i0 = tid; i0 < n4; i0 += 4 * kThreads) {
-        float4 va[4], vb[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (i0 + k * kThreads < n4) {
-            va[k] = __ldg(a4 + i0 + k * kThreads);
-            vb[k] = __ldg(b4 + i0 + k * kThreads);
-          }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (i0 + k * kThreads < n4) {
-            da[i0 + k * kThreads] = va[k];
-            db[i0 + k * kThreads] = vb[k];
-          }
-      }
+    } else if ((nst & 3) == 0 && is_aligned16(gsrc)) {
+      copy_in_f4(gstage, gsrc, nst >> 2, tid);
     } else {
-      for (int i = tid; i < nst; i += kThreads) {
-        smem[i] = __ldg(src + i);
-        gstage[i] = __ldg(gsrc + i);
-      }
+      for (int i = tid; i < nst; i += kThreads) gstage[i] = __ldg(gsrc + i);
     }
     __syncthreads();
-    const float* o = smem + gq * D;
+    const float* o = smem + gq * L12;
     S1 = active ? o[il] : 0.f;
 #pragma unroll
-    for (int j = 0; j < d; ++j) {
-      S2[j] = active ? o[d + il * d + j] : 0.f;
-#pragma unroll
-      for (int c = 0; c < d; ++c) S3[j][c] = active ? o[d + d * d + (il * d + j) * d + c] : 0.f;
-    }
+    for (int j = 0; j < d; ++j) S2[j] = active ? o[d + il * d + j] : 0.f;
     const float* og = gstage + gq * D;
     A1 = active ? og[il] : 0.f;
 #pragma unroll
@@ -429,42 +460,7 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
       const float di = rows[r * DP + il] - rows[(r - 1) * DP + il];
 #pragma unroll
       for (int c = 0; c < d; ++c) dl[c] = xt[c] - xp[c];
-      // ---- S_{t-1} = S_t (x) exp(-dl) ----
-      {
-        const float u3 = S1 - di * (1.f / 3.f);
-#pragma unroll
-        for (int j = 0; j < d; ++j) {
-          const float b = S2[j] - u3 * dl[j] * 0.5f;
-#pragma unroll
-          for (int c = 0; c < d; ++c) S3[j][c] = fmaf(-b, dl[c], S3[j][c]);
-        }
-        const float u2 = S1 - di * 0.5f;
-#pragma unroll
-        for (int j = 0; j < d; ++j) S2[j] = fmaf(-u2, dl[j], S2[j]);
-        S1 -= di;
-      }
-      // ---- adjoint of S_t = S_{t-1} (x) exp(dl) ----
-      float pd[d];
-#pragma unroll
-      for (int c = 0; c < d; ++c) pd[c] = 0.f;
-      float dI = A1, a1inc = 0.f;
-      const float u3 = S1 + di * (1.f / 3.f), u2 = S1 + di * 0.5f;
-#pragma unroll
-      for (int j = 0; j < d; ++j) {
-        float rr = 0.f;
-#pragma unroll
-        for (int c = 0; c < d; ++c) rr = fmaf(g3[j][c], dl[c], rr);
-        const float B2 = S2[j] + u3 * dl[j] * 0.5f;
-#pragma unroll
-        for (int c = 0; c < d; ++c) pd[c] = fmaf(g3[j][c], B2, pd[c]);
-        pd[j] += rr * u3 * 0.5f + A2[j] * u2;
-        const float ub = rr * dl[j] * 0.5f, vb = A2[j] * dl[j];
-        a1inc += ub + vb;
-        dI += ub * (1.f / 3.f) + vb * 0.5f;
-        A2[j] += rr;
-      }
-      A1 += a1inc;
-      const float tot = group_reduce_scatter<G, d>(pd, lane) + dI;
+      const float tot = sig3_bwd_step<G, d>(dl, di, S1, S2, A1, A2, g3, lane);
       __syncwarp();  // every lane of the group has consumed row r before it is overwritten
       if (active) rows[r * DP + lane] = tot;
     }
@@ -529,6 +525,239 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
     for (int i = tid; i < npart * DP; i += kThreads) {
       const int q = i / DP, c = i - q * DP;
       carry[i] = smem[q * pstride + DP + c];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// depth-3 backward, time-parallel: the T steps are cut into kSeg segments swept by kSeg warps
+// of one CTA at the same time (Chen: S_T = P_q (x) R_q with P_q the signature up to the end of
+// segment q -- levels 1-2 checkpointed by the forward kernel -- and R_q the signature of the rest).
+//   state at the segment end:    S = P_q
+//   adjoint at the segment end:  A3 = G3,  A2 = G2 + G3 . R1,  A1 = G1 + G2 . R1 + G3 : R2
+//   with R1 = T1 - P1,  R2 = T2 - P2 - P1 (x) R1   (levels of P_q^-1 (x) S_T; T = S_T)
+// The sequential chain per warp is T / kSeg steps instead of T, and there are kSeg times more
+// warps to hide latencies with (N = 4096: 4096 warps instead of 1024).
+// Needs whole paths resident in shared memory and 16-byte aligned rows (the launcher checks).
+// ------------------------------------------------------------------------------------------
+template <int d>
+__global__ void __launch_bounds__(kSegThreads)
+sig3_bwd_seg_kernel(const float* __restrict__ x, const float* __restrict__ sig,
+                    const float* __restrict__ pref, const float* __restrict__ gsig, int64_t N, int T,
+                    int basepoint, int seg_len, const float* __restrict__ add, int64_t ld_add,
+                    float alpha, float beta, float* __restrict__ out, const SigGradSpec gs) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = 32 / G;
+  constexpr int D = d + d * d + d * d * d;
+  constexpr int L12 = d + d * d;  // levels 1-2: all the sweep needs of the state
+  constexpr int RB = DP + d * d;  // R1 (padded) + R2 per (segment, particle)
+  extern __shared__ __align__(16) float smem[];
+  const int tid = threadIdx.x, seg = tid >> 5, l32 = tid & 31, grp = l32 / G, lane = l32 % G;
+  const int il = lane < d ? lane : d - 1;
+  const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const int npart = (int)min((int64_t)PPC, N - p0);
+  const bool active = grp < npart && lane < d;
+  const int gq = grp < npart ? grp : 0;
+  const int pstride = (T + 1) * DP + kGroupPad;
+  float* xrows = smem;                                  // [PPC][pstride]  x, row r <-> time r-1
+  float* regb = smem + PPC * pstride;                   // staging [2][PPC*D], later gDelta rows
+  float* rbuf = regb + max(PPC * pstride, 2 * PPC * D);  // [kSeg][PPC][RB]
+
+  // ---- cooperative loads: waypoints, S_T, cotangent ----
+  {
+    // particle-major so that no index needs a run-time division; 4 loads in flight per thread
+    const float4* __restrict__ s4 = reinterpret_cast<const float4*>(x + p0 * (int64_t)T * d);
+    const int per4 = (T * d) >> 2;
+    for (int q0 = 0; q0 < npart; q0 += 4) {
+      for (int i = tid; i < per4; i += kSegThreads) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (q0 + k < npart) v[k] = __ldg(s4 + (q0 + k) * per4 + i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (q0 + k < npart) {
+            float* dst = xrows + (q0 + k) * pstride + DP;
+            const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (i * 4 + u) / d, c = (i * 4 + u) - t * d;
+              dst[t * DP + c] = f[u];
+            }
+          }
+        }
+      }
+    }
+    for (int i = tid; i < npart * DP; i += kSegThreads) xrows[(i / DP) * pstride + (i % DP)] = 0.f;
+    const float* __restrict__ src = sig + p0 * D;
+    float* gstage = regb + PPC * D;
+    const int nst = npart * D;
+    for (int i = tid; i < npart * L12; i += kSegThreads) {
+      const int q = i / L12;
+      regb[i] = __ldg(src + q * D + (i - q * L12));
+    }
+    if (gs.sc != nullptr) {
+      const float gam2 = 2.f * gs.state->gamma;  // -(1/h^2) = 2*gamma
+      for (int i0 = tid; i0 < nst; i0 += 4 * kSegThreads) {
+        float a[4], b[4], r[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k * kSegThreads;
+          if (i < nst) {
+            const int q = i / D, c = i - q * D;
+            const int64_t row = p0 + q;
+            a[k] = __ldg(gs.sc + row * gs.lds + c);
+            b[k] = __ldg(gs.ks + row * gs.ldks + c);
+            r[k] = __ldg(gs.rowsum + row * gs.ldr);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = i0 + k * kSegThreads;
+          if (i < nst) gstage[i] = gam2 * (a[k] * r[k] - b[k]);
+        }
+      }
+      const float coef = gs.state->coef;
+      if (coef != 0.f) {
+        __syncthreads();
+        const uint32_t nl = min(gs.state->n_ties, (uint32_t)SIGSVGD_MAX_TIES);
+        const float wt = coef / (float)gs.state->n_ties_all;
+        for (uint32_t t = 0; t < nl; ++t) {
+          const int64_t a_loc = (int64_t)gs.state->ties[2 * t] - gs.row_offset - p0;
+          if (a_loc < 0 || a_loc >= npart) continue;  // block-uniform
+          const int64_t jb = gs.state->ties[2 * t + 1];
+          for (int c = tid; c < D; c += kSegThreads)
+            gstage[a_loc * D + c] = fmaf(wt, __ldg(gs.sc + (p0 + a_loc) * gs.lds + c) -
+                                                 __ldg(gs.sc_all + jb * gs.lds_all + c),
+                                         gstage[a_loc * D + c]);
+          __syncthreads();
+        }
+      }
+    } else {
+      const float* __restrict__ gsrc = gsig + p0 * D;
+      for (int i = tid; i < nst; i += kSegThreads) gstage[i] = __ldg(gsrc + i);
+    }
+  }
+  __syncthreads();
+
+  // ---- this warp's segment: state and adjoint at its end ----
+  const int t_lo = seg * seg_len, t_hi = min(T, t_lo + seg_len);
+  const bool nonempty = t_lo < T;
+  const bool last = t_hi == T;
+  float S1 = 0.f, S2[d], A1 = 0.f, A2[d], g3[d][d];
+  {
+    const float* o = regb + gq * L12;           // S_T, levels 1-2
+    const float* og = regb + PPC * D + gq * D;  // G
+    A1 = active ? og[il] : 0.f;
+#pragma unroll
+    for (int j = 0; j < d; ++j) {
+      A2[j] = active ? og[d + il * d + j] : 0.f;
+#pragma unroll
+      for (int c = 0; c < d; ++c) g3[j][c] = active ? og[d + d * d + (il * d + j) * d + c] : 0.f;
+    }
+    if (last || !nonempty) {
+      S1 = active ? o[il] : 0.f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) S2[j] = active ? o[d + il * d + j] : 0.f;
+    } else {
+      const float* __restrict__ pq = pref + ((p0 + gq) * (kSeg - 1) + seg) * (int64_t)L12;
+      S1 = active ? __ldg(pq + il) : 0.f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) S2[j] = active ? __ldg(pq + d + il * d + j) : 0.f;
+      // R1, R2 of the remaining path, shared inside the group through shared memory
+      float* rb = rbuf + (seg * PPC + gq) * RB;
+      const float r1 = (active ? o[il] : 0.f) - S1;
+      __syncwarp();
+      if (active) rb[lane] = r1;
+      __syncwarp();
+      float R1[d];
+#pragma unroll
+      for (int k = 0; k < d; ++k) R1[k] = rb[k];
+      if (active) {
+#pragma unroll
+        for (int k = 0; k < d; ++k) rb[DP + lane * d + k] = o[d + il * d + k] - S2[k] - S1 * R1[k];
+      }
+      __syncwarp();
+      float acc1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) {
+        float row = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < d; ++k) {
+          row = fmaf(g3[j][k], R1[k], row);
+          c2 = fmaf(g3[j][k], rb[DP + j * d + k], c2);
+        }
+        acc1 += A2[j] * R1[j] + c2;  // original G2 here, before it is advanced below
+        A2[j] += row;
+      }
+      A1 += acc1;
+    }
+  }
+  __syncthreads();  // staging consumed: region B becomes the gDelta rows
+
+  // ---- reversible sweep over the segment ----
+  const int t_first = basepoint ? 0 : 1;
+  const float* rows = xrows + gq * pstride;
+  float* grow = regb + gq * pstride;
+  if (nonempty) {
+    float xt[d];
+    load_row<d>(rows + t_hi * DP, xt);
+    float xi = rows[t_hi * DP + il];
+    for (int t = t_hi - 1; t >= t_lo; --t) {
+      const int r = t + 1;
+      if (t < t_first) {  // no increment ends at point 0 without a basepoint
+        if (active) grow[r * DP + lane] = 0.f;
+        continue;
+      }
+      float xp[d], dl[d];
+      load_row<d>(rows + (r - 1) * DP, xp);
+      const float xpi = rows[(r - 1) * DP + il];
+      const float di = xi - xpi;
+      xi = xpi;
+#pragma unroll
+      for (int c = 0; c < d; ++c) {
+        dl[c] = xt[c] - xp[c];
+        xt[c] = xp[c];
+      }
+      const float tot = sig3_bwd_step<G, d>(dl, di, S1, S2, A1, A2, g3, lane);
+      if (active) grow[r * DP + lane] = tot;
+    }
+  }
+  __syncthreads();
+
+  // ---- gx[t] = gDelta[t] - gDelta[t+1], fused epilogue, 16-byte stores ----
+  {
+    const int per4 = (T * d) >> 2;
+    float4* __restrict__ o4 = reinterpret_cast<float4*>(out + p0 * (int64_t)T * d);
+    for (int q0 = 0; q0 < npart; q0 += 4) {
+      for (int i = tid; i < per4; i += kSegThreads) {
+        float4 av[4];
+        if (add) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (q0 + k < npart)
+              av[k] = __ldg(reinterpret_cast<const float4*>(add + (p0 + q0 + k) * ld_add) + i);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (q0 + k < npart) {
+            const float* src = regb + (q0 + k) * pstride;
+            float f[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (i * 4 + u) / d, c = (i * 4 + u) - t * d;
+              const float nxt = (t + 1 < T) ? src[(t + 2) * DP + c] : 0.f;
+              f[u] = beta * (src[(t + 1) * DP + c] - nxt);
+            }
+            if (add) {
+              f[0] = fmaf(alpha, av[k].x, f[0]);
+              f[1] = fmaf(alpha, av[k].y, f[1]);
+              f[2] = fmaf(alpha, av[k].z, f[2]);
+              f[3] = fmaf(alpha, av[k].w, f[3]);
+            }
+            o4[(q0 + k) * per4 + i] = make_float4(f[0], f[1], f[2], f[3]);
+          }
+        }
+      }
     }
   }
 }
@@ -679,9 +908,12 @@ sig_generic_bwd_kernel(const float* __restrict__ x, const float* __restrict__ si
   }
 }
 
+size_t seg_bwd_smem(int64_t T, int64_t d);
+
 template <int d>
 int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* sig,
-                    cudaStream_t st, float* stats, const float* score, int64_t ld_score, int64_t P) {
+                    cudaStream_t st, float* stats, const float* score, int64_t ld_score, int64_t P,
+                    float* pref) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
@@ -690,7 +922,8 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
   size_t smem = (size_t)std::max(PPC * (TC * DP + kGroupPad), PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
   sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig, stats,
-                                                              score, ld_score, (int)P);
+                                                              score, ld_score, (int)P, pref,
+                                                              (int)ceil_div(T, kSeg));
   SIG_LAUNCH_OK("sig3_fwd_kernel");
   return 0;
 }
@@ -698,11 +931,23 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
 template <int d>
 int launch_sig3_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                     int basepoint, const float* add, int64_t ld_add, float alpha, float beta,
-                    float* out, cudaStream_t st, const SigGradSpec& gs) {
+                    float* out, cudaStream_t st, const SigGradSpec& gs, const float* pref) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int kBudget = 40 * 1024;
   static_assert(2 * PPC * D * 4 <= kBudget, "state staging must fit");
+  if (pref != nullptr && is_aligned16(x) && is_aligned16(out) &&
+      (add == nullptr || (is_aligned16(add) && (ld_add & 3) == 0))) {
+    // time-parallel kernel: whole paths resident, kSeg warps per group of particles
+    const size_t smem = seg_bwd_smem(T, d);
+    if (smem > 48 * 1024)
+      SIG_CUDA_OK(cudaFuncSetAttribute(sig3_bwd_seg_kernel<d>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       96 * 1024));
+    sig3_bwd_seg_kernel<d><<<(unsigned)ceil_div(N, PPC), kSegThreads, smem, st>>>(
+        x, sig, pref, gsig, N, (int)T, basepoint, (int)ceil_div(T, kSeg), add, ld_add, alpha, beta, out, gs);
+    SIG_LAUNCH_OK("sig3_bwd_seg_kernel");
+    return 0;
+  }
   int TC = (int)std::min<int64_t>(T, (kBudget / 4 / PPC - kGroupPad) / DP - 1);
   size_t smem = (size_t)std::max(PPC * ((TC + 1) * DP + kGroupPad), 2 * PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
@@ -730,9 +975,28 @@ int make_levels(int64_t d, int depth, LevelInfo* L, int64_t* D) {
 
 bool sig_fwd_fuses_stats(int64_t d, int depth) { return depth == 3 && d >= 1 && d <= 8; }
 
+// The time-parallel backward needs: depth 3, d <= 8, whole paths resident in both kernels,
+// 16-byte rows, and segments of at least two steps.
+namespace {
+size_t seg_bwd_smem(int64_t T, int64_t d) {
+  const int64_t PPC = 32 / group_size((int)d), DP = row_pad((int)d), D = d + d * d + d * d * d;
+  const int64_t pstride = (T + 1) * DP + kGroupPad;
+  return (size_t)(PPC * pstride + std::max(PPC * pstride, 2 * PPC * D) + kSeg * PPC * (DP + d * d)) * 4;
+}
+}  // namespace
+bool sig_bwd_uses_prefix(int64_t T, int64_t d, int depth) {
+  if (depth != 3 || d < 1 || d > 8 || T < 2 * kSeg || T > 4096 || ((T * d) & 3) != 0) return false;
+  return seg_bwd_smem(T, d) <= 96 * 1024;
+}
+int64_t sig_prefix_floats(int64_t N, int64_t T, int64_t d, int depth) {
+  return sig_bwd_uses_prefix(T, d, depth) ? N * (kSeg - 1) * (d + d * d) : 0;
+}
+
 int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, int basepoint,
                    float* sig, cudaStream_t st, float* stats, const float* score, int64_t ld_score,
-                   int64_t P) {
+                   int64_t P, float* pref) {
+  SIG_CHECK_ARG(pref == nullptr || sig_bwd_uses_prefix(T, d, depth),
+                "signature_fwd: prefix checkpoints are not available for this shape");
   SIG_CHECK_ARG(stats == nullptr || sig_fwd_fuses_stats(d, depth),
                 "signature_fwd: fused statistics need depth 3 and d <= 8");
   SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
@@ -743,14 +1007,14 @@ int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, i
   if (N == 0) return 0;
   if (depth == 3) {
     switch (d) {
-      case 1: return launch_sig3_fwd<1>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 2: return launch_sig3_fwd<2>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 3: return launch_sig3_fwd<3>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 4: return launch_sig3_fwd<4>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 5: return launch_sig3_fwd<5>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 6: return launch_sig3_fwd<6>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 7: return launch_sig3_fwd<7>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
-      case 8: return launch_sig3_fwd<8>(x, N, T, basepoint, sig, st, stats, score, ld_score, P);
+      case 1: return launch_sig3_fwd<1>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 2: return launch_sig3_fwd<2>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 3: return launch_sig3_fwd<3>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 4: return launch_sig3_fwd<4>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 5: return launch_sig3_fwd<5>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 6: return launch_sig3_fwd<6>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 7: return launch_sig3_fwd<7>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
+      case 8: return launch_sig3_fwd<8>(x, N, T, basepoint, sig, st, stats, score, ld_score, P, pref);
       default: break;
     }
   }
@@ -775,7 +1039,10 @@ bool sig_bwd_fuses_grad(int64_t d, int depth) { return depth == 3 && d >= 1 && d
 
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
-                   float alpha, float beta, float* out, cudaStream_t st, const SigGradSpec* spec) {
+                   float alpha, float beta, float* out, cudaStream_t st, const SigGradSpec* spec,
+                   const float* pref) {
+  SIG_CHECK_ARG(pref == nullptr || sig_bwd_uses_prefix(T, d, depth),
+                "signature_bwd: prefix checkpoints are not available for this shape");
   SigGradSpec gs{};
   if (spec) {
     gs = *spec;
@@ -793,7 +1060,7 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
     switch (d) {
 #define SIG3_BWD_CASE(dd) \
   case dd:                \
-    return launch_sig3_bwd<dd>(x, sig, gsig, N, T, basepoint, add, ld_add, alpha, beta, out, st, gs);
+    return launch_sig3_bwd<dd>(x, sig, gsig, N, T, basepoint, add, ld_add, alpha, beta, out, st, gs, pref);
       SIG3_BWD_CASE(1)
       SIG3_BWD_CASE(2)
       SIG3_BWD_CASE(3)

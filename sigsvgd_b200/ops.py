@@ -121,6 +121,32 @@ def signature_bwd_raw(x, sig, gsig, depth, basepoint=True, add=None, alpha=0.0, 
     return out
 
 
+def signature_prefix_floats(N: int, T: int, d: int, depth: int) -> int:
+    """Size of the prefix-checkpoint buffer of the time-parallel pair; 0 when the shape does not qualify."""
+    return int(_lib.load().sigsvgd_signature_prefix_floats(N, T, d, depth))
+
+
+def signature_fwd_prefix_raw(x: torch.Tensor, depth: int, basepoint: bool = True):
+    """Forward that also checkpoints the signature at the ends of the first three time segments."""
+    N, T, d = x.shape
+    n = signature_prefix_floats(N, T, d, depth)
+    if n <= 0:
+        raise ValueError(f"no time-parallel signature pair for T={T} d={d} depth={depth}")
+    sig = torch.empty(N, sig_channels(d, depth), dtype=torch.float32, device=x.device)
+    pref = torch.empty(n, dtype=torch.float32, device=x.device)
+    call("sigsvgd_signature_fwd_prefix", _p(x), N, T, d, depth, int(basepoint), _p(sig), _p(pref), _stream())
+    return sig, pref
+
+
+def signature_bwd_prefix_raw(x, sig, pref, gsig, depth, basepoint=True, add=None, alpha=0.0, beta=1.0) -> torch.Tensor:
+    N, T, d = x.shape
+    out = torch.empty_like(x)
+    ld_add = 0 if add is None else add.stride(0)
+    call("sigsvgd_signature_bwd_prefix", _p(x), _p(sig), _p(pref), _p(gsig), N, T, d, depth, int(basepoint), _p(add),
+         ld_add, float(alpha), float(beta), _p(out), _stream())
+    return out
+
+
 def pack_features(s: torch.Tensor, mean: Optional[torch.Tensor], score: Optional[torch.Tensor] = None) -> torch.Tensor:
     """V = [score | s - mean | 1 | 0-pad]  (row stride a multiple of 8 floats)."""
     N, D = s.shape

@@ -58,6 +58,51 @@ def test_signature_fwd_bwd_vs_oracle(N, T, d, depth, basepoint):
     assert rel_max(out, want) <= 2e-5
 
 
+PREFIX_SHAPES = [(17, 64, 7), (130, 30, 2), (20, 12, 4), (40, 10, 8), (100, 10, 2), (33, 9, 4), (9, 11, 4), (16, 8, 1),
+                 (6, 13, 8), (5, 300, 7), (21, 16, 3), (4097, 64, 7)]
+
+
+@pytest.mark.parametrize("N,T,d", PREFIX_SHAPES)
+@pytest.mark.parametrize("basepoint", [True, False])
+def test_signature_time_parallel_pair_vs_oracle(N, T, d, basepoint):
+    """Forward with prefix checkpoints + the backward that sweeps 4 time segments at once
+    (sigsvgd_signature_fwd_prefix / _bwd_prefix) against the float64 oracle."""
+    depth = 3
+    L12 = d + d * d
+    assert ops.signature_prefix_floats(N, T, d, depth) == N * 3 * L12
+    x = make_paths("walk", N, T, d, seed=N + T) * 4.0
+    x64 = x.astype(np.float64)
+    ref = oracle.signature_np(x64, depth, basepoint)
+    sig, pref = ops.signature_fwd_prefix_raw(cu(x), depth, basepoint)
+    assert rel_max(sig.cpu().numpy(), ref) <= TOL_SIG
+    # the checkpoints are levels 1-2 of the signatures of the truncated paths
+    seg = -(-T // 4)
+    pr = pref.cpu().numpy().reshape(N, 3, -1)
+    for q in range(3):
+        if (q + 1) * seg < T:
+            want = oracle.signature_np(x64[:, :(q + 1) * seg], depth, basepoint)
+            assert rel_max(pr[:, q], want[:, :L12]) <= TOL_SIG
+    rng = np.random.default_rng(2)
+    g = rng.standard_normal(ref.shape)
+    gx_ref = oracle.signature_bwd_np(x64, ref, g, depth, basepoint)
+    gx = ops.signature_bwd_prefix_raw(cu(x), sig, pref, cu(g.astype(np.float32)), depth, basepoint).cpu().numpy()
+    assert rel_max(gx, gx_ref) <= 2e-5
+    for pad in (4, 3):  # 16-byte rows of `add`: time-parallel kernel; otherwise the sequential one
+        add = rng.standard_normal((N, T * d + pad)).astype(np.float32)
+        out = ops.signature_bwd_prefix_raw(cu(x), sig, pref, cu(g.astype(np.float32)), depth, basepoint, add=cu(add),
+                                           alpha=0.25, beta=-0.5).cpu().numpy()
+        want = -0.5 * gx_ref + 0.25 * add[:, :T * d].reshape(N, T, d)
+        assert rel_max(out, want) <= 2e-5
+
+
+def test_signature_time_parallel_pair_availability():
+    assert ops.signature_prefix_floats(8, 7, 4, 3) == 0      # fewer than 2 steps per segment
+    assert ops.signature_prefix_floats(8, 9, 3, 3) == 0      # rows not a multiple of 16 bytes
+    assert ops.signature_prefix_floats(8, 16, 4, 4) == 0     # depth 3 only
+    with pytest.raises(ValueError):
+        ops.signature_fwd_prefix_raw(torch.zeros(8, 7, 4, device=DEV), 3)
+
+
 def test_signature_autograd_node_and_empty():
     x = torch.randn(6, 9, 3, device=DEV, requires_grad=True)
     s = ops.signature(x, 3, basepoint=True)

@@ -305,7 +305,10 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     tri_scan = symmetric && vec && M == N && lo_bits > 0u;  // grid-uniform
     // a thread classifies its batch of values locally; the warp then reserves pool space with ONE
     // shared-memory atomic per batch (exclusive scan of the per-thread hit counts)
-    auto flush = [&](const float* v, uint32_t hitmask, int nval) {  // warp-collective
+    constexpr int kRows = 8;  // rows in flight per warp-chunk (independent 16-byte loads per lane)
+    // (hits are re-read from L1 instead of being kept in registers across the scan: 8 rows in flight
+    // per lane fit the 64-register budget of a 1024-thread block only that way)
+    auto flush = [&](uint32_t hitmask, int nval, int64_t r0, int64_t c) {  // warp-collective
       const int hits = __popc(hitmask);
       int incl = hits;
 #pragma unroll
@@ -319,21 +322,21 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       if (lane == 31) base = atomicAdd(&sh_fill, (unsigned int)total);
       base = __shfl_sync(0xffffffffu, base, 31);
       unsigned int off = base + (unsigned int)(incl - hits);
-#pragma unroll
-      for (int e = 0; e < 16; ++e) {
-        if (e < nval && ((hitmask >> e) & 1u)) {
-          if (off < poolcap) pool[off] = v[e];
-          atomicAdd(&hist[((__float_as_uint(v[e]) & 0x7fffffffu) - lo_bits) >> s1], 1u);
-          ++off;
-        }
+      while (hitmask) {
+        const int e = __ffs(hitmask) - 1;
+        hitmask &= hitmask - 1u;
+        if (e >= nval) break;
+        const float val = vec ? __ldg(dist + (r0 + (e >> 2)) * ldd + 4 * c + (e & 3)) : __ldg(dist + (r0 + e) * ldd + c);
+        if (off < poolcap) pool[off] = val;
+        atomicAdd(&hist[((__float_as_uint(val) & 0x7fffffffu) - lo_bits) >> s1], 1u);
+        ++off;
       }
     };
-    constexpr int kRows = 4;  // rows in flight per block (independent loads)
     // one warp-chunk: rows r0..r0+3, quads c0..c0+31 (128 columns).  tri: only entries strictly
     // above the diagonal (column > row) are classified.
     auto chunk = [&](int64_t r0, int64_t c0, bool tri) {  // warp-collective
       const int64_t c = c0 + lane;
-      float v[16];
+      float v[4 * kRows];
       uint32_t hitmask = 0;
       if (vec && r0 + kRows <= M && c0 + 32 <= nq && (!tri || 4 * c0 > r0 + kRows - 1)) {
         // interior: no validity bookkeeping
@@ -343,12 +346,12 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
           v[4 * j] = f.x, v[4 * j + 1] = f.y, v[4 * j + 2] = f.z, v[4 * j + 3] = f.w;
         }
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
+        for (int e = 0; e < 4 * kRows; ++e) {
           const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
           nlt += bits < lo_bits ? 1u : 0u;
           if (bits - lo_bits <= span_bits) hitmask |= 1u << e;
         }
-        flush(v, hitmask, 16);
+        flush(hitmask, 4 * kRows, r0, c);
         return;
       }
       const bool cin = c < nq;
@@ -376,14 +379,14 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
         }
       }
 #pragma unroll
-      for (int e = 0; e < 16; ++e) {
+      for (int e = 0; e < 4 * kRows; ++e) {
         if (!vec && e >= kRows) break;
         const uint32_t bits = __float_as_uint(v[e]) & 0x7fffffffu;
         const bool ok_e = (validmask >> e) & 1u;
         nlt += (ok_e && bits < lo_bits) ? 1u : 0u;
         if (ok_e && bits - lo_bits <= span_bits) hitmask |= 1u << e;
       }
-      flush(v, hitmask, vec ? 16 : kRows);
+      flush(hitmask, vec ? 4 * kRows : kRows, r0, c);
     };
     if (!tri_scan) {
       for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows)
@@ -394,7 +397,13 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       // number of sequential chunk steps per warp halves too (not just the bytes).
       const int wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
       int offset = 0;
-      for (int64_t r0 = (int64_t)blockIdx.x * kRows; r0 < M; r0 += (int64_t)gridDim.x * kRows) {
+      // (row groups dealt in serpentine order: a block's groups from the wide top of the triangle
+      // pair with groups from its narrow bottom)
+      for (int64_t gk = 0;; ++gk) {
+        const int64_t g = (gk & 1) ? (gk + 1) * (int64_t)gridDim.x - 1 - blockIdx.x : gk * (int64_t)gridDim.x + blockIdx.x;
+        if (gk * (int64_t)gridDim.x * kRows >= M) break;
+        const int64_t r0 = g * kRows;
+        if (r0 >= M) continue;
         const int64_t q_first = ((r0 + 1) >> 2) & ~(int64_t)31;
         if (q_first >= nq) continue;
         const int nch = (int)((nq - q_first + 31) >> 5);
@@ -414,16 +423,39 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       pool_cnt[blockIdx.x] = sh_fill;
       pool_cnt[kMaxPools + blockIdx.x] = sh_blt;  // < 2^32: rows are dealt evenly
     }
-    for (int i = threadIdx.x; i < kBins; i += blockDim.x)
+    // blocks finish together: start each one at a different bin so that they do not queue on the
+    // same L2 atomic units
+    for (int i0 = threadIdx.x; i0 < kBins; i0 += blockDim.x) {
+      const int i = (i0 + (int)blockIdx.x * 64) & (kBins - 1);
       if (hist[i]) atomicAdd(&ghist[i], (unsigned long long)hist[i]);
+    }
   }
   __threadfence();
   grid.sync();
-  for (unsigned int i = threadIdx.x; i < npool; i += blockDim.x) {
-    const unsigned int c = pool_cnt[i];
-    atomicAdd(&sh_ncand, min(c, poolcap));
-    atomicAdd(&sh_below, (unsigned long long)pool_cnt[kMaxPools + i]);
-    if (c > poolcap) sh_over = 1u;
+  {
+    // pool totals: warp-reduced first (148 threads on one 64-bit shared atomic -- a CAS loop --
+    // cost 22 % of the kernel)
+    unsigned int my_c = 0, my_over = 0;
+    unsigned long long my_b = 0;
+    for (unsigned int i = threadIdx.x; i < npool; i += blockDim.x) {
+      const unsigned int c = pool_cnt[i];
+      my_c += min(c, poolcap);
+      my_b += (unsigned long long)pool_cnt[kMaxPools + i];
+      my_over |= c > poolcap ? 1u : 0u;
+    }
+    if ((threadIdx.x & ~31u) < npool) {  // warp-uniform: warps that hold any pool
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) {
+        my_c += __shfl_xor_sync(0xffffffffu, my_c, o);
+        my_b += __shfl_xor_sync(0xffffffffu, my_b, o);
+        my_over |= __shfl_xor_sync(0xffffffffu, my_over, o);
+      }
+      if (lane == 0) {
+        atomicAdd(&sh_ncand, my_c);
+        atomicAdd(&sh_below, my_b);
+        if (my_over) sh_over = 1u;
+      }
+    }
   }
   __syncthreads();
   const unsigned int n_cand = sh_ncand;

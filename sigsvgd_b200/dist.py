@@ -68,6 +68,13 @@ class CudaBackend:
         return bool(self.tc)
 
     def sig_fwd(self, x, depth):
+        # with the prefix checkpoints of the time-parallel backward when the shape has them
+        N, T, d = x.shape
+        self._pref = None
+        if N > 0 and ops.signature_prefix_floats(N, T, d, depth) > 0:
+            sig, pref = ops.signature_fwd_prefix_raw(x, depth, True)
+            self._pref = (sig.data_ptr(), pref)
+            return sig
         return ops.signature_fwd_raw(x, depth, True)
 
     # ---- operand preparation / Gram / RBF / contraction ---------------------------------------
@@ -162,6 +169,9 @@ class CudaBackend:
         return ops.sig_grad_raw(sc, sc_all, ks, rowsum, state, row_offset)
 
     def sig_bwd(self, x, sig, g, depth, add, alpha, beta):
+        pref = getattr(self, "_pref", None)
+        if pref is not None and pref[0] == sig.data_ptr():
+            return ops.signature_bwd_prefix_raw(x, sig, pref[1], g, depth, True, add, alpha, beta)
         return ops.signature_bwd_raw(x, sig, g, depth, True, add, alpha, beta)
 
 

@@ -345,6 +345,21 @@ def _is_uniform_cotangent(g: torch.Tensor) -> bool:
     return all(s == 0 for s in g.stride()) or g.numel() == 1
 
 
+def _sig_fwd_saving(x, depth, basepoint):
+    """Forward for an autograd node: also the prefix checkpoints when the time-parallel backward
+    exists for this shape (returns (sig, pref) with pref an empty tensor otherwise)."""
+    N, T, d = x.shape
+    if N > 0 and signature_prefix_floats(N, T, d, depth) > 0:
+        return signature_fwd_prefix_raw(x, depth, basepoint)
+    return signature_fwd_raw(x, depth, basepoint), torch.empty(0, dtype=torch.float32, device=x.device)
+
+
+def _sig_bwd_saved(x, sig, pref, g, depth, basepoint):
+    if pref.numel():
+        return signature_bwd_prefix_raw(x, sig, pref, g, depth, basepoint)
+    return signature_bwd_raw(x, sig, g, depth, basepoint)
+
+
 # ---------------------------------------------------------------------------------------------
 # autograd nodes
 # ---------------------------------------------------------------------------------------------
@@ -354,15 +369,15 @@ class _Signature(torch.autograd.Function):
         x = _prep(path, "signature")
         if x.dim() != 3:
             raise ValueError(f"signature: expected [batch, length, channels], got {tuple(x.shape)}")
-        sig = signature_fwd_raw(x, depth, basepoint)
-        ctx.save_for_backward(x, sig)
+        sig, pref = _sig_fwd_saving(x, depth, basepoint)
+        ctx.save_for_backward(x, sig, pref)
         ctx.depth, ctx.basepoint, ctx.in_dtype = depth, basepoint, path.dtype
         return sig.to(path.dtype)
 
     @staticmethod
     def backward(ctx, g):
-        x, sig = ctx.saved_tensors
-        gx = signature_bwd_raw(x, sig, _prep(g, "signature.backward"), ctx.depth, ctx.basepoint)
+        x, sig, pref = ctx.saved_tensors
+        gx = _sig_bwd_saved(x, sig, pref, _prep(g, "signature.backward"), ctx.depth, ctx.basepoint)
         return gx.to(ctx.in_dtype), None, None
 
 
@@ -431,10 +446,10 @@ class _SigRBFGram(torch.autograd.Function):
         same = _same_data(X, Y)
         x = _prep(X, "PathSigKernel")
         y = x if same else _prep(Y, "PathSigKernel")
-        sx = signature_fwd_raw(x, depth, True)
-        sy = sx if same else signature_fwd_raw(y, depth, True)
+        sx, px = _sig_fwd_saving(x, depth, True)
+        sy, py = (sx, px) if same else _sig_fwd_saving(y, depth, True)
         K, vx, vy, state = _GramCore.forward(sx, sy, same, bw, center)
-        ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state)
+        ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state, px, py)
         ctx.meta = (depth, bw, same, X.dtype)
         ctx.set_materialize_grads(False)
         ctx.bw_state = state
@@ -444,18 +459,18 @@ class _SigRBFGram(torch.autograd.Function):
     def backward(ctx, gK):
         if gK is None:
             return None, None, None, None, None
-        x, y, sx, sy, vx, vy, K, state = ctx.saved_tensors
+        x, y, sx, sy, vx, vy, K, state, px, py = ctx.saved_tensors
         depth, bw, same, in_dtype = ctx.meta
         need_x, need_y = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         D = sx.shape[1]
         gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, need_y, bw)
-        gX = signature_bwd_raw(x, sx, gsx, depth, True).to(in_dtype) if need_x else None
+        gX = _sig_bwd_saved(x, sx, px, gsx, depth, True).to(in_dtype) if need_x else None
         gY = None
         if need_y:
             if gsy is gsx and gX is not None and same:
                 gY = gX
             else:
-                gY = signature_bwd_raw(y, sy, gsy, depth, True).to(in_dtype)
+                gY = _sig_bwd_saved(y, sy, py, gsy, depth, True).to(in_dtype)
         return gX, gY, None, None, None
 
 

@@ -254,39 +254,67 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
   // once per ~2 blocks per SM instead of once per 8 rows
   for (int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + wid; row < N;
        row += (int64_t)gridDim.x * (kThreads / 32)) {
-  if (zero_out)  // this row of the K.F result buffer (reduction target): saves a memset node
-    for (int64_t c = lane; c < Cp; c += 32) zero_out[row * ld_zero + c] = 0.f;
+  if (zero_out) {  // this row of the K.F result buffer (reduction target): saves a memset node
+    float* zr = zero_out + row * ld_zero;
+    if (((ld_zero | Cp) & 3) == 0 && (reinterpret_cast<uintptr_t>(zero_out) & 15u) == 0) {
+      for (int64_t c = 4 * lane; c < Cp; c += 128) *reinterpret_cast<float4*>(zr + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      for (int64_t c = lane; c < Cp; c += 32) zr[c] = 0.f;
+    }
+  }
   float nrm = 0.f;
-  for (int64_t c0 = c_lo + 2 * lane; c0 < c_hi; c0 += 64) {
-    float x[2];
+  // four column pairs per lane and step: their loads are issued together (a warp owns a whole row,
+  // so one pair per step made the row a chain of 14 exposed memory latencies)
+  constexpr int kU = 4;
+  for (int64_t c00 = c_lo + 2 * lane; c00 < c_hi; c00 += 64 * kU) {
+    float raw[kU][2];
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int64_t c = c0 + e;
-      float v = 0.f;
-      if (c < D) {
-        v = __ldg(s + row * lds + c) - (mean_in_smem ? sh_mean[c] : col_mean_of(c));
-        if (sc) sc[row * ldsc + c] = v;
-        v *= as;
-      } else if (c == D) {
-        v = 1.f;
-      } else if (c < D + 1 + P && score) {
-        v = __ldg(score + row * lsc + (c - D - 1)) * ag;
+    for (int u = 0; u < kU; ++u) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int64_t c = c00 + 64 * u + e;
+        float v = 0.f;
+        if (c00 + 64 * u < c_hi) {
+          if (c < D) v = __ldg(s + row * lds + c);
+          else if (c > D && c < D + 1 + P && score) v = __ldg(score + row * lsc + (c - D - 1));
+        }
+        raw[u][e] = v;
       }
-      x[e] = v;
     }
-    __half h0, l0, h1, l1;
-    split_half(x[0], h0, l0);
-    split_half(x[1], h1, l1);
-    if (c0 < D) {
-      const float r0 = __half2float(h0) + __half2float(l0);
-      nrm = fmaf(r0, r0, nrm);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t c0 = c00 + 64 * u;
+      if (c0 >= c_hi) break;
+      float x[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int64_t c = c0 + e;
+        float v = 0.f;
+        if (c < D) {
+          v = raw[u][e] - (mean_in_smem ? sh_mean[c] : col_mean_of(c));
+          if (sc) sc[row * ldsc + c] = v;
+          v *= as;
+        } else if (c == D) {
+          v = 1.f;
+        } else if (c < D + 1 + P && score) {
+          v = raw[u][e] * ag;
+        }
+        x[e] = v;
+      }
+      __half h0, l0, h1, l1;
+      split_half(x[0], h0, l0);
+      split_half(x[1], h1, l1);
+      if (c0 < D) {
+        const float r0 = __half2float(h0) + __half2float(l0);
+        nrm = fmaf(r0, r0, nrm);
+      }
+      if (c0 + 1 < D) {
+        const float r1 = __half2float(h1) + __half2float(l1);
+        nrm = fmaf(r1, r1, nrm);
+      }
+      *reinterpret_cast<__half2*>(fh + row * ldp + c0) = __halves2half2(h0, h1);
+      *reinterpret_cast<__half2*>(fl + row * ldp + c0) = __halves2half2(l0, l1);
     }
-    if (c0 + 1 < D) {
-      const float r1 = __half2float(h1) + __half2float(l1);
-      nrm = fmaf(r1, r1, nrm);
-    }
-    *reinterpret_cast<__half2*>(fh + row * ldp + c0) = __halves2half2(h0, h1);
-    *reinterpret_cast<__half2*>(fl + row * ldp + c0) = __halves2half2(l0, l1);
   }
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
@@ -324,17 +352,9 @@ rbf_planes_kernel(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row
   const int64_t r_end = min(M, r_begin + rows_per_block);
   double acc = 0.0;
   if (c0 < ldp) {  // planes are written up to their padded pitch (zeros beyond N)
-    for (int64_t r = r_begin; r < r_end; ++r) {
-      float dv[4], kv[4];
-      const float* row = d + r * ldd + c0;
-      const int nv = (int)max((int64_t)0, min((int64_t)4, N - c0));
-      if (vec_in) {
-        const float4 q = *reinterpret_cast<const float4*>(row);
-        dv[0] = q.x, dv[1] = q.y, dv[2] = q.z, dv[3] = q.w;
-      } else {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) dv[e] = e < nv ? row[e] : 0.f;
-      }
+    const int nv = (int)max((int64_t)0, min((int64_t)4, N - c0));
+    auto process = [&](int64_t r, const float (&dv)[4]) {
+      float kv[4];
       float part = 0.f;
       __half h[4], l[4];
 #pragma unroll
@@ -352,7 +372,6 @@ rbf_planes_kernel(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row
         }
         split_half(kv[e] * kKScale, h[e], l[e]);
       }
-      acc += (double)part;
       // ldp is a multiple of 8 and c0 a multiple of 4: 8-byte aligned plane stores
       {
         __half2 a = __halves2half2(h[0], h[1]), b2 = __halves2half2(h[2], h[3]);
@@ -375,6 +394,30 @@ rbf_planes_kernel(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row
             if (e < nv) orow[e] = kv[e];
         }
       }
+      return part;
+    };
+    // four rows per step: their loads are issued together (one 16-byte load in flight per thread
+    // left the kernel latency-bound at 63 % of the HBM roofline)
+    for (int64_t r = r_begin; r < r_end; r += 4) {
+      float dv[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (r + j < r_end) {
+          const float* row = d + (r + j) * ldd + c0;
+          if (vec_in) {
+            const float4 q = *reinterpret_cast<const float4*>(row);
+            dv[j][0] = q.x, dv[j][1] = q.y, dv[j][2] = q.z, dv[j][3] = q.w;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) dv[j][e] = e < nv ? row[e] : 0.f;
+          }
+        }
+      }
+      float part = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (r + j < r_end) part += process(r + j, dv[j]);
+      acc += (double)part;
     }
   }
   const double tot = block_sum_double(acc, red);
@@ -462,7 +505,7 @@ int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row
   const int64_t gx = ceil_div(ldp, (int64_t)kThreads * 4);
   int64_t gy = std::min<int64_t>(65535, std::max<int64_t>(1, ceil_div((int64_t)num_sms() * 16, gx)));
   gy = std::min(gy, M);
-  const int rows_per_block = (int)ceil_div(M, gy);
+  const int rows_per_block = (int)round_up(ceil_div(M, gy), 4);
   gy = ceil_div(M, rows_per_block);
   rbf_planes_kernel<<<dim3((unsigned)gx, (unsigned)gy), kThreads, 0, st>>>(
       d, ldd, M, N, row_offset, state, kh, kl, ldp, kout, ldk, rows_per_block);

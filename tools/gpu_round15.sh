@@ -3,4 +3,3 @@ set -x
 mkdir -p gpurun_out
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'window_select' -s 4 -c 1 -o gpurun_out/wsel -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --large-particles 0 > gpurun_out/ncu_wsel.log 2>&1
 tail -n 3 gpurun_out/ncu_wsel.log
-timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_dist.py -m gpu -x -q > gpurun_out/pytest_sub.log 2>&1; tail -n 3 gpurun_out/pytest_sub.log

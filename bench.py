@@ -41,9 +41,9 @@ if ROOT not in sys.path:
 
 T_STEPS, D_CH, DEPTH = 64, 7, 3
 # kernels of libsigsvgd_b200.so launched by one sigsvgd_phi call on the tcgen05 path (sig fwd + stats,
-# window prepare, pack, Gram, window select, rbf planes, median coef, K.F, sig bwd); memset nodes
+# window prepare, pack, Gram, window select, rbf planes, K.F, sig bwd); memset nodes
 # are not counted
-LAUNCHES_PER_UPDATE = 9
+LAUNCHES_PER_UPDATE = 8
 METRIC = "svgd_phi_updates_per_sec"
 UNIT = "phi-updates/s"
 

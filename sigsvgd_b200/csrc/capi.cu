@@ -549,7 +549,10 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
       (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0;
   if (use_tc) {
     SIG_PROPAGATE(launch_tc_rbf(K, N, N, N, 0, state, Kh, Kl, L.Np, k_out ? K : nullptr, N, st));
-    SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
+    // (the coefficient of the median-gradient term is derived by the signature backward itself
+    // when it forms the cotangent: see SigGradSpec::coef_mode)
+    if (!(B == 1 && sig_bwd_fuses_grad(d, depth)))
+      SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
     if (hp) {
       float* stats = (float*)(w + L.off_stats);
       SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->score_ready, 0));
@@ -569,6 +572,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   // (one swarm, depth 3: the backward kernel forms the cotangent itself while staging)
   const bool fuse_grad = B == 1 && sig_bwd_fuses_grad(d, depth);
   SigGradSpec gs{feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, 0, state};
+  gs.coef_mode = use_tc ? (median_grad ? 1 : 2) : 0;
   const SigGradSpec* spec = fuse_grad ? &gs : nullptr;
   if (!fuse_grad)
     SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,

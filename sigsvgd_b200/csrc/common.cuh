@@ -89,6 +89,8 @@ struct SigGradSpec {
   int64_t ldr;
   int64_t row_offset;    // global index of row 0 (ties hold global indices)
   const sigsvgd_bw_state* state;  // one record
+  int coef_mode = 0;     // 0: state->coef / n_ties_all as set by median_coef; 1: derive them from the
+                         // record's own sum_kd / n_ties (and store them); 2: same, gradient term off
 };
 int select_collect_blocks();
 int launch_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,

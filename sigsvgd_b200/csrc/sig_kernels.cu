@@ -267,6 +267,28 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   }
 }
 
+// Median-gradient coefficient for the fused cotangent: either the record's (coef_mode 0: set by
+// median_coef_kernel, e.g. from all-reduced sums on the sharded path) or derived here from the
+// record's own sums, coef = sum_kd / (h^2 median) -- one launch less
+// on the one-swarm path.  The first block of the first row chunk also stores it in the record.
+__device__ __forceinline__ float grad_coef(const SigGradSpec& gs, uint32_t* n_ties_all) {
+  const sigsvgd_bw_state& st = *gs.state;
+  if (gs.coef_mode == 0) {
+    *n_ties_all = st.n_ties_all;
+    return st.coef;
+  }
+  const uint32_t nt = st.n_ties;
+  const bool on = gs.coef_mode == 1 && !st.clamped && st.median > 0.f && nt > 0u;
+  const float coef = on ? (float)st.sum_kd / (st.h * st.h * st.median) : 0.f;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && gs.row_offset == 0) {
+    sigsvgd_bw_state* w = const_cast<sigsvgd_bw_state*>(gs.state);
+    w->coef = coef;
+    w->n_ties_all = nt;
+  }
+  *n_ties_all = nt;
+  return coef;
+}
+
 // One reversed time step of the depth-3 VJP for lane i of a particle's group:
 //   levels 1-2 of the state go back  S_{t-1} = S_t (x) exp(-dl)  (level 3 feeds nothing),
 //   the adjoints (A1, A2; A3 = G3 is constant) go back through  S_t = S_{t-1} (x) exp(dl),
@@ -364,11 +386,12 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
           if (i < nst) gstage[i] = gam2 * (a[k] * r[k] - b[k]);
         }
       }
-      const float coef = gs.state->coef;
+      uint32_t nt_all;
+      const float coef = grad_coef(gs, &nt_all);
       if (coef != 0.f) {
         __syncthreads();
         const uint32_t nl = min(gs.state->n_ties, (uint32_t)SIGSVGD_MAX_TIES);
-        const float wt = coef / (float)gs.state->n_ties_all;
+        const float wt = coef / (float)nt_all;
         for (uint32_t t = 0; t < nl; ++t) {
           const int64_t a_loc = (int64_t)gs.state->ties[2 * t] - gs.row_offset - p0;
           if (a_loc < 0 || a_loc >= npart) continue;  // block-uniform
@@ -616,11 +639,12 @@ sig3_bwd_seg_kernel(const float* __restrict__ x, const float* __restrict__ sig,
           if (i < nst) gstage[i] = gam2 * (a[k] * r[k] - b[k]);
         }
       }
-      const float coef = gs.state->coef;
+      uint32_t nt_all;
+      const float coef = grad_coef(gs, &nt_all);
       if (coef != 0.f) {
         __syncthreads();
         const uint32_t nl = min(gs.state->n_ties, (uint32_t)SIGSVGD_MAX_TIES);
-        const float wt = coef / (float)gs.state->n_ties_all;
+        const float wt = coef / (float)nt_all;
         for (uint32_t t = 0; t < nl; ++t) {
           const int64_t a_loc = (int64_t)gs.state->ties[2 * t] - gs.row_offset - p0;
           if (a_loc < 0 || a_loc >= npart) continue;  // block-uniform

@@ -42,3 +42,31 @@ def test_phi_host_rejects_device_tensors():
     x = torch.zeros(8, 4, 2, device="cuda:0")
     with pytest.raises(RuntimeError):
         ops.phi_host(x, torch.zeros(8, 8, device="cuda:0"))
+
+
+def test_phi_plan_graph_replay_matches_direct_call():
+    """ops.PhiPlan (sigsvgd_phi captured into a CUDA graph) must track new inputs on every replay and
+    agree with the call-by-call update, for the tcgen05 path and the SIMT path."""
+    for N, T, d in [(512, 64, 7), (96, 16, 3)]:
+        plan = ops.PhiPlan(N, T, d, 3, device="cuda:0")
+        for seed in (1, 2, 3):
+            g = torch.Generator().manual_seed(seed)
+            x = torch.cumsum(0.05 * torch.randn(N, T, d, generator=g), dim=1).cuda()
+            s = torch.randn(N, T * d, generator=g).cuda()
+            want = ops.phi(x, s, depth=3)
+            got = plan(x, s)
+            torch.cuda.synchronize()
+            ra, rb = ops.read_state(got.state), ops.read_state(want.state)
+            assert abs(ra["h"] - rb["h"]) <= 1e-6 * rb["h"]
+            assert ra["n_ties_all"] == rb["n_ties_all"]
+            skip = {t[0] for t in ra["ties"]} | {t[0] for t in rb["ties"]}
+            keep = torch.ones(N, dtype=torch.bool, device="cuda:0")
+            keep[sorted(skip)] = False
+            den = want.phi[keep].abs().max().item()
+            assert (got.phi[keep] - want.phi[keep]).abs().max().item() <= 1e-5 * den
+        # in-place use: write into the plan's buffers, replay without arguments
+        plan.x.mul_(1.5)
+        got = plan()
+        want = ops.phi(plan.x.clone(), plan.score.clone(), depth=3)
+        torch.cuda.synchronize()
+        assert abs(ops.read_state(got.state)["h"] - ops.read_state(want.state)["h"]) <= 1e-6 * ops.read_state(want.state)["h"]

@@ -108,7 +108,20 @@ class SVGD:
         if spec is not None and X.dim() == 3:
             score, loss = self._score(X, grad_log_p, kwargs)
             want = self.log_level != "none"
-            res = ops.phi(X.detach(), score.detach(), depth=self.depth, bandwidth=spec, want_k=want, want_grad_k=want)
+            if not want and X.is_cuda and getattr(self, "use_graph", True):
+                # nothing but phi is asked for: replay the update from its CUDA graph (ops.PhiPlan; one
+                # plan per swarm shape and bandwidth rule, inputs copied into the plan's buffers)
+                plans = self.__dict__.setdefault("_plans", {})
+                key = (tuple(X.shape), X.device, self.depth, spec.mode, spec.h, spec.bw_scale, spec.tol, spec.median_grad)
+                plan = plans.get(key)
+                if plan is None:
+                    plan = plans[key] = ops.PhiPlan(X.shape[0], X.shape[1], X.shape[2], self.depth, bandwidth=spec,
+                                                    device=X.device)
+                res = plan(X.detach(), score.detach())
+                res = ops.PhiResult(res.phi.to(X.dtype), res.state)
+            else:
+                res = ops.phi(X.detach(), score.detach(), depth=self.depth, bandwidth=spec, want_k=want,
+                              want_grad_k=want)
             self.last_state = res.state
             velocity = -res.phi.reshape(X.shape)
             k_xx, grad_k = res.k_xx, res.grad_k

@@ -644,7 +644,7 @@ class PhiPlan:
         with torch.cuda.stream(self._stream):
             enqueue()  # warm-up outside the capture: lazy driver-side initialisation (attributes, side stream)
             self._stream.synchronize()
-            with torch.cuda.graph(self.graph, stream=self._stream):
+            with torch.cuda.graph(self.graph, stream=self._stream, capture_error_mode="thread_local"):
                 enqueue()
         torch.cuda.current_stream(dev).wait_stream(self._stream)
 

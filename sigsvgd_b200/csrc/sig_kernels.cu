@@ -267,6 +267,211 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// depth-3 forward, time-parallel: warp q of the CTA sweeps time segment q of the CTA's particles
+// from the identity (R_q = signature of that piece of the path), then Chen's identity stitches
+// them: P_1 = R_0 (x) R_1 and Q = R_2 (x) R_3 on two warps at once, S_T = P_1 (x) Q.  The
+// level-1-2 checkpoints the time-parallel backward wants (P_0, P_1, P_2 = P_1 (x) R_2) fall out
+// of the stitching.  Sequential chain: T/4 steps + two tensor products instead of T steps.
+// ------------------------------------------------------------------------------------------
+// C = A (x) B in place; lane owns the entries of A whose first index is il; B (all D entries of one
+// particle) is read from shared memory.
+template <int d>
+__device__ __forceinline__ void chen_mul(float& A1, float (&A2)[d], float (&A3)[d][d],
+                                         const float* __restrict__ B, int il) {
+  constexpr int L12 = d + d * d;
+  float B1[d];
+#pragma unroll
+  for (int k = 0; k < d; ++k) B1[k] = B[k];
+#pragma unroll
+  for (int j = 0; j < d; ++j) {
+#pragma unroll
+    for (int k = 0; k < d; ++k)
+      A3[j][k] += fmaf(A2[j], B1[k], fmaf(A1, B[d + j * d + k], B[L12 + (il * d + j) * d + k]));
+  }
+#pragma unroll
+  for (int j = 0; j < d; ++j) A2[j] += fmaf(A1, B1[j], B[d + il * d + j]);
+  A1 += B[il];
+}
+
+template <int d>
+__global__ void __launch_bounds__(kSegThreads)
+sig3_fwd_seg_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, int seg_len,
+                    float* __restrict__ sig, float* __restrict__ stats, const float* __restrict__ score,
+                    int64_t ld_score, int P, float* __restrict__ pref) {
+  constexpr int G = group_size(d), DP = row_pad(d), PPC = 32 / G;
+  constexpr int D = d + d * d + d * d * d, L12 = d + d * d;
+  extern __shared__ __align__(16) float smem[];
+  const int tid = threadIdx.x, seg = tid >> 5, l32 = tid & 31, grp = l32 / G, lane = l32 % G;
+  const int il = lane < d ? lane : d - 1;
+  const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const int npart = (int)min((int64_t)PPC, N - p0);
+  const bool active = grp < npart && lane < d;
+  const int gq = grp < npart ? grp : 0;
+  const int pstride = (T + 1) * DP + kGroupPad;
+  float* rbuf = smem;                       // [kSeg][PPC][D]; slot 0 doubles as the output staging
+  float* xrows = smem + kSeg * PPC * D;     // [PPC][pstride], row r <-> time r-1 (row 0 = basepoint)
+
+  {
+    const float4* __restrict__ s4 = reinterpret_cast<const float4*>(x + p0 * (int64_t)T * d);
+    const int per4 = (T * d) >> 2;
+    for (int q0 = 0; q0 < npart; q0 += 4) {
+      for (int i = tid; i < per4; i += kSegThreads) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (q0 + k < npart) v[k] = __ldg(s4 + (q0 + k) * per4 + i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (q0 + k < npart) {
+            float* dst = xrows + (q0 + k) * pstride + DP;
+            const float f[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int t = (i * 4 + u) / d, c = (i * 4 + u) - t * d;
+              dst[t * DP + c] = f[u];
+            }
+          }
+        }
+      }
+    }
+    for (int i = tid; i < npart * DP; i += kSegThreads) xrows[(i / DP) * pstride + (i % DP)] = 0.f;
+  }
+  __syncthreads();
+
+  // ---- R_q: this warp's segment from the identity ----
+  float S1 = 0.f, S2[d], S3[d][d];
+#pragma unroll
+  for (int j = 0; j < d; ++j) {
+    S2[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < d; ++c) S3[j][c] = 0.f;
+  }
+  const int t_lo = seg * seg_len, t_hi = min(T, t_lo + seg_len);
+  if (t_lo < T) {
+    const float* rows = xrows + gq * pstride;
+    float xprev[d];
+    load_row<d>(rows + t_lo * DP, xprev);
+    float xprev_i = rows[t_lo * DP + il];
+    for (int t = t_lo; t < t_hi; ++t) {
+      float xt[d], dl[d];
+      load_row<d>(rows + (t + 1) * DP, xt);
+      const float xi = rows[(t + 1) * DP + il];
+#pragma unroll
+      for (int c = 0; c < d; ++c) {
+        dl[c] = xt[c] - xprev[c];
+        xprev[c] = xt[c];
+      }
+      const float di = xi - xprev_i;
+      xprev_i = xi;
+      if (!basepoint && t == 0) continue;  // first point only seeds xprev
+      const float u3 = S1 + di * (1.f / 3.f);
+#pragma unroll
+      for (int j = 0; j < d; ++j) {
+        const float b = S2[j] + u3 * dl[j] * 0.5f;
+#pragma unroll
+        for (int c = 0; c < d; ++c) S3[j][c] = fmaf(b, dl[c], S3[j][c]);
+      }
+      const float u2 = S1 + di * 0.5f;
+#pragma unroll
+      for (int j = 0; j < d; ++j) S2[j] = fmaf(u2, dl[j], S2[j]);
+      S1 += di;
+    }
+  }
+  auto put = [&](float* o) {  // this lane's entries of (S1, S2, S3) into a D-vector
+    if (active) {
+      o[lane] = S1;
+#pragma unroll
+      for (int j = 0; j < d; ++j) {
+        o[d + lane * d + j] = S2[j];
+#pragma unroll
+        for (int c = 0; c < d; ++c) o[L12 + (lane * d + j) * d + c] = S3[j][c];
+      }
+    }
+  };
+  auto put12 = [&](float* __restrict__ o) {  // levels 1-2 only (a checkpoint)
+    if (active) {
+      o[lane] = S1;
+#pragma unroll
+      for (int j = 0; j < d; ++j) o[d + lane * d + j] = S2[j];
+    }
+  };
+  float* __restrict__ ck = pref ? pref + (p0 + gq) * (int64_t)(kSeg - 1) * L12 : nullptr;
+  if (seg != 0 && seg != 2) put(rbuf + (seg * PPC + gq) * D);  // B operands of the first round
+  if (seg == 2) put(rbuf + (2 * PPC + gq) * D);                // R_2: also needed for P_2
+  if (seg == 0 && ck && seg_len < T) put12(ck);                // P_0 = R_0
+  __syncthreads();
+  // ---- first round: P_1 = R_0 (x) R_1 on warp 0, Q = R_2 (x) R_3 on warp 2 ----
+  if (seg == 0) {
+    chen_mul<d>(S1, S2, S3, rbuf + (1 * PPC + gq) * D, il);
+    if (ck && 2 * seg_len < T) put12(ck + L12);                // P_1
+  } else if (seg == 2) {
+    chen_mul<d>(S1, S2, S3, rbuf + (3 * PPC + gq) * D, il);
+    __syncwarp();
+    put(rbuf + (3 * PPC + gq) * D);                             // Q replaces R_3
+  }
+  __syncthreads();
+  // ---- second round (warp 0): P_2 = P_1 (x) R_2 (levels 1-2), S_T = P_1 (x) Q ----
+  if (seg == 0) {
+    if (ck && 3 * seg_len < T && active) {
+      const float* R2 = rbuf + (2 * PPC + gq) * D;
+      float* __restrict__ o = ck + 2 * L12;
+      o[lane] = S1 + R2[lane];
+#pragma unroll
+      for (int j = 0; j < d; ++j) o[d + lane * d + j] = S2[j] + fmaf(S1, R2[j], R2[d + lane * d + j]);
+    }
+    chen_mul<d>(S1, S2, S3, rbuf + (3 * PPC + gq) * D, il);
+    put(rbuf + gq * D);  // output staging: slot 0, [PPC][D] contiguous
+  }
+  __syncthreads();
+
+  if (stats != nullptr) {
+    // statistics of the operand preparation, as in sig3_fwd_kernel
+    stats += (blockIdx.x & 7) * (D + 2);
+    float ms = 0.f, mg = 0.f;
+    for (int c = tid; c < D; c += kSegThreads) {
+      float sum = 0.f;
+      for (int q = 0; q < npart; ++q) {
+        const float v = rbuf[q * D + c];
+        sum += v;
+        ms = fmaxf(ms, fabsf(v));
+      }
+      atomicAdd(stats + c, sum);
+    }
+    if (score != nullptr) {
+      for (int q = 0; q < npart; ++q) {
+        const float* __restrict__ row = score + (p0 + q) * ld_score;
+        for (int i0 = tid; i0 < P; i0 += 4 * kSegThreads) {
+          float v[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) v[k] = i0 + k * kSegThreads < P ? __ldg(row + i0 + k * kSegThreads) : 0.f;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mg = fmaxf(mg, fabsf(v[k]));
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+      ms = fmaxf(ms, __shfl_xor_sync(0xffffffffu, ms, o));
+      mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    }
+    if (l32 == 0) {
+      unsigned int* mx = reinterpret_cast<unsigned int*>(stats + D);
+      if (ms > 0.f && ms < INFINITY) atomicMax(mx, __float_as_uint(ms));
+      if (mg > 0.f && mg < INFINITY) atomicMax(mx + 1, __float_as_uint(mg));
+    }
+  }
+  float* __restrict__ dst = sig + p0 * D;
+  const int nout = npart * D;
+  if ((nout & 3) == 0 && is_aligned16(dst)) {
+    float4* __restrict__ d4 = reinterpret_cast<float4*>(dst);
+    const float4* s4 = reinterpret_cast<const float4*>(rbuf);
+    for (int i = tid; i < (nout >> 2); i += kSegThreads) d4[i] = s4[i];
+  } else {
+    for (int i = tid; i < nout; i += kSegThreads) dst[i] = rbuf[i];
+  }
+}
+
 // Median-gradient coefficient for the fused cotangent: either the record's (coef_mode 0: set by
 // median_coef_kernel, e.g. from all-reduced sums on the sharded path) or derived here from the
 // record's own sums, coef = sum_kd / (h^2 median) -- one launch less
@@ -945,6 +1150,21 @@ int launch_sig3_fwd(const float* x, int64_t N, int64_t T, int basepoint, float* 
   int TC = (int)std::min<int64_t>(T, (kBudget / 4 / PPC - kGroupPad) / DP);
   size_t smem = (size_t)std::max(PPC * (TC * DP + kGroupPad), PPC * D) * 4;
   const int64_t grid = ceil_div(N, PPC);
+  // the time-parallel forward pays (Chen products, four times the warps) only while the plain
+  // kernel leaves the SMs short of warps: measured 16 -> 10 us at N=256, 16 -> 13 us at N=1024, but
+  // 20 -> 25 us at N=4096 where both are issue-bound
+  if (pref != nullptr && is_aligned16(x) && ((T * d) & 3) == 0 && grid <= 4 * (int64_t)num_sms()) {
+    const size_t smem_seg = (size_t)(kSeg * PPC * D + PPC * ((T + 1) * DP + kGroupPad)) * 4;
+    if (smem_seg <= 96 * 1024) {
+      if (smem_seg > 48 * 1024)
+        SIG_CUDA_OK(cudaFuncSetAttribute(sig3_fwd_seg_kernel<d>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         96 * 1024));
+      sig3_fwd_seg_kernel<d><<<(unsigned)grid, kSegThreads, smem_seg, st>>>(
+          x, N, (int)T, basepoint, (int)ceil_div(T, kSeg), sig, stats, score, ld_score, (int)P, pref);
+      SIG_LAUNCH_OK("sig3_fwd_seg_kernel");
+      return 0;
+    }
+  }
   sig3_fwd_kernel<d><<<(unsigned)grid, kThreads, smem, st>>>(x, N, (int)T, basepoint, TC, sig, stats,
                                                               score, ld_score, (int)P, pref,
                                                               (int)ceil_div(T, kSeg));

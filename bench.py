@@ -338,6 +338,11 @@ def run_ours(args):
                 "ms_per_launch": ms_k, "algorithmic_flops_per_launch": flops,
                 "step_algorithmic_flops": 2.0 * M * N * (2 * D + P),
                 "step_frac_of_peak": 2.0 * M * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak}
+        if use_tc:
+            # fp32-grade products cost three fp16 MMA passes (hi.hi, hi.lo, lo.hi): executed tensor flops
+            # are 3x the algorithmic ones, so `frac` cannot exceed 1/3
+            roof["frac_cap"] = 1.0 / 3.0
+            roof["executed_frac_of_peak"] = 3.0 * roof["frac"]
 
     # ---- one swarm sharded row-block over the ranks (the path's NCCL exchange) ------------------
     sharded = []

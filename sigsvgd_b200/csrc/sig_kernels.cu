@@ -180,14 +180,20 @@ sig3_fwd_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint, in
       const float di = xi - xprev_i;
       xprev_i = xi;
       if (!basepoint && c0 + r == 0) continue;  // first point only seeds xprev
-      const float u3 = S1 + di * (1.f / 3.f);
+      const float u3h = 0.5f * fmaf(di, 1.f / 3.f, S1);
 #pragma unroll
       for (int j = 0; j < d; ++j) {
-        const float b = S2[j] + u3 * dl[j] * 0.5f;
+        // level 3 as packed fp32 FMAs (fma.rn.f32x2): the kernel is issue-bound
+        const float b = fmaf(u3h, dl[j], S2[j]);
+        const float2 b2 = make_float2(b, b);
 #pragma unroll
-        for (int c = 0; c < d; ++c) S3[j][c] = fmaf(b, dl[c], S3[j][c]);
+        for (int c = 0; c + 1 < d; c += 2) {
+          const float2 t = __ffma2_rn(b2, make_float2(dl[c], dl[c + 1]), make_float2(S3[j][c], S3[j][c + 1]));
+          S3[j][c] = t.x, S3[j][c + 1] = t.y;
+        }
+        if (d & 1) S3[j][d - 1] = fmaf(b, dl[d - 1], S3[j][d - 1]);
       }
-      const float u2 = S1 + di * 0.5f;
+      const float u2 = fmaf(di, 0.5f, S1);
 #pragma unroll
       for (int j = 0; j < d; ++j) S2[j] = fmaf(u2, dl[j], S2[j]);
       S1 += di;
@@ -502,32 +508,51 @@ template <int G, int d>
 __device__ __forceinline__ float sig3_bwd_step(const float (&dl)[d], float di, float& S1, float (&S2)[d],
                                                float& A1, float (&A2)[d], const float (&g3)[d][d],
                                                int lane) {
+  // The two 7x7 matrix-vector products with the constant G3 rows dominate the step; they are issued
+  // as packed fp32 FMAs (fma.rn.f32x2: two lanes of the pair per instruction) to halve their issue
+  // slots -- the kernel is issue-bound.
+  constexpr int dh = d / 2;
   const float u2r = fmaf(di, -0.5f, S1);
 #pragma unroll
   for (int j = 0; j < d; ++j) S2[j] = fmaf(-u2r, dl[j], S2[j]);
   S1 -= di;
-  float hdl[d], pd[d];
+  float hdl[d];
+  float2 pd2[dh > 0 ? dh : 1], dl2[dh > 0 ? dh : 1];
+  float pd_last = 0.f;
 #pragma unroll
-  for (int c = 0; c < d; ++c) {
-    hdl[c] = 0.5f * dl[c];
-    pd[c] = 0.f;
+  for (int c = 0; c < d; ++c) hdl[c] = 0.5f * dl[c];
+#pragma unroll
+  for (int c = 0; c < dh; ++c) {
+    pd2[c] = make_float2(0.f, 0.f);
+    dl2[c] = make_float2(dl[2 * c], dl[2 * c + 1]);
   }
   const float u3 = fmaf(di, 1.f / 3.f, S1), u2 = fmaf(di, 0.5f, S1), u3h = 0.5f * u3;
   float sum_u = 0.f, sum_v = 0.f;  // sum_j rr_j dl_j / 2  and  sum_j A2_j dl_j
+  float extra[d];                  // the diagonal terms added to pd[j]
 #pragma unroll
   for (int j = 0; j < d; ++j) {
-    float rr = 0.f;
+    float2 r2 = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int c = 0; c < d; ++c) rr = fmaf(g3[j][c], dl[c], rr);
+    for (int c = 0; c < dh; ++c) r2 = __ffma2_rn(make_float2(g3[j][2 * c], g3[j][2 * c + 1]), dl2[c], r2);
+    float rr = r2.x + r2.y;
+    if (d & 1) rr = fmaf(g3[j][d - 1], dl[d - 1], rr);
     const float B2 = fmaf(u3, hdl[j], S2[j]);
+    const float2 B22 = make_float2(B2, B2);
 #pragma unroll
-    for (int c = 0; c < d; ++c) pd[c] = fmaf(g3[j][c], B2, pd[c]);
-    pd[j] = fmaf(rr, u3h, pd[j]);
-    pd[j] = fmaf(A2[j], u2, pd[j]);
+    for (int c = 0; c < dh; ++c) pd2[c] = __ffma2_rn(make_float2(g3[j][2 * c], g3[j][2 * c + 1]), B22, pd2[c]);
+    if (d & 1) pd_last = fmaf(g3[j][d - 1], B2, pd_last);
+    extra[j] = fmaf(rr, u3h, A2[j] * u2);
     sum_u = fmaf(rr, hdl[j], sum_u);
     sum_v = fmaf(A2[j], dl[j], sum_v);
     A2[j] += rr;
   }
+  float pd[d];
+#pragma unroll
+  for (int c = 0; c < dh; ++c) {
+    pd[2 * c] = pd2[c].x + extra[2 * c];
+    pd[2 * c + 1] = pd2[c].y + extra[2 * c + 1];
+  }
+  if (d & 1) pd[d - 1] = pd_last + extra[d - 1];
   const float dI = fmaf(sum_u, 1.f / 3.f, fmaf(sum_v, 0.5f, A1));
   A1 += sum_u + sum_v;
   return group_reduce_scatter<G, d>(pd, lane) + dI;

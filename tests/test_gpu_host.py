@@ -70,3 +70,23 @@ def test_phi_plan_graph_replay_matches_direct_call():
         want = ops.phi(plan.x.clone(), plan.score.clone(), depth=3)
         torch.cuda.synchronize()
         assert abs(ops.read_state(got.state)["h"] - ops.read_state(want.state)["h"]) <= 1e-6 * ops.read_state(want.state)["h"]
+
+
+def test_phi_plan_batch_of_scenes():
+    """A plan over a batch of independent swarms (B > 1: per-scene medians, SIMT kernels)."""
+    B, N, T, d = 3, 48, 12, 2
+    g = torch.Generator().manual_seed(7)
+    x = torch.cumsum(0.1 * torch.randn(B, N, T, d, generator=g), dim=2).cuda()
+    s = torch.randn(B, N, T * d, generator=g).cuda()
+    plan = ops.PhiPlan(N, T, d, 3, device="cuda:0", batch=B)
+    got = plan(x, s)
+    want = ops.phi(x, s, depth=3)
+    torch.cuda.synchronize()
+    for b in range(B):
+        ra, rb = ops.read_state(got.state, b), ops.read_state(want.state, b)
+        assert abs(ra["h"] - rb["h"]) <= 1e-6 * rb["h"]
+        skip = {t[0] for t in ra["ties"]} | {t[0] for t in rb["ties"]}
+        keep = torch.ones(N, dtype=torch.bool, device="cuda:0")
+        keep[sorted(skip)] = False
+        den = want.phi[b][keep].abs().max().item()
+        assert (got.phi[b][keep] - want.phi[b][keep]).abs().max().item() <= 1e-5 * den

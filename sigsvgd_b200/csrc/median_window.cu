@@ -281,6 +281,10 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   const unsigned int epoch = win->epoch & 1u;
   unsigned long long* ghist = ghist2 + (size_t)epoch * 3 * kBins;
   unsigned int* short_cnt = pool_cnt + 2 * kMaxPools + epoch;
+  // grid totals of phase A (candidates kept, pool overflow flag, entries below the window):
+  // accumulated with three atomics per block BEFORE the grid barrier, double-buffered on the epoch
+  unsigned int* tot32 = pool_cnt + 2 * kMaxPools + 8 + 4 * epoch;
+  unsigned long long* tot_below = reinterpret_cast<unsigned long long*>(tot32 + 2);
   const int lane = threadIdx.x & 31;
   bool tri_scan = false;
   const uint32_t lo_bits = __float_as_uint(win->lo), span_bits = __float_as_uint(win->hi) - lo_bits;
@@ -296,6 +300,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     unsigned long long* other = ghist2 + (size_t)(epoch ^ 1u) * 3 * kBins;
     for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) other[i] = 0ull;
     if (threadIdx.x == 0) pool_cnt[2 * kMaxPools + (epoch ^ 1u)] = 0u;
+    if (threadIdx.x < 4) pool_cnt[2 * kMaxPools + 8 + 4 * (epoch ^ 1u) + threadIdx.x] = 0u;
   }
   __syncthreads();
   {
@@ -422,6 +427,9 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       // plain stores of per-block results (nothing to reset between calls)
       pool_cnt[blockIdx.x] = sh_fill;
       pool_cnt[kMaxPools + blockIdx.x] = sh_blt;  // < 2^32: rows are dealt evenly
+      atomicAdd(&tot32[0], min(sh_fill, poolcap));
+      if (sh_fill > poolcap) atomicOr(&tot32[1], 1u);
+      atomicAdd(tot_below, (unsigned long long)sh_blt);
     }
     // blocks finish together: start each one at a different bin so that they do not queue on the
     // same L2 atomic units
@@ -432,30 +440,10 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   }
   __threadfence();
   grid.sync();
-  {
-    // pool totals: warp-reduced first (148 threads on one 64-bit shared atomic -- a CAS loop --
-    // cost 22 % of the kernel)
-    unsigned int my_c = 0, my_over = 0;
-    unsigned long long my_b = 0;
-    for (unsigned int i = threadIdx.x; i < npool; i += blockDim.x) {
-      const unsigned int c = pool_cnt[i];
-      my_c += min(c, poolcap);
-      my_b += (unsigned long long)pool_cnt[kMaxPools + i];
-      my_over |= c > poolcap ? 1u : 0u;
-    }
-    if ((threadIdx.x & ~31u) < npool) {  // warp-uniform: warps that hold any pool
-#pragma unroll
-      for (int o = 16; o >= 1; o >>= 1) {
-        my_c += __shfl_xor_sync(0xffffffffu, my_c, o);
-        my_b += __shfl_xor_sync(0xffffffffu, my_b, o);
-        my_over |= __shfl_xor_sync(0xffffffffu, my_over, o);
-      }
-      if (lane == 0) {
-        atomicAdd(&sh_ncand, my_c);
-        atomicAdd(&sh_below, my_b);
-        if (my_over) sh_over = 1u;
-      }
-    }
+  if (threadIdx.x == 0) {
+    sh_ncand = __ldcg(&tot32[0]);
+    sh_over = __ldcg(&tot32[1]);
+    sh_below = __ldcg(tot_below);
   }
   __syncthreads();
   const unsigned int n_cand = sh_ncand;

@@ -275,7 +275,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   __shared__ float sl[kShort];
   __shared__ uint32_t sh_bucket;
   __shared__ unsigned long long sh_k;
-  __shared__ unsigned int sh_ncand, sh_over, sh_fill, sh_blt;
+  __shared__ unsigned int sh_ncand, sh_over, sh_fill, sh_blt, sh_last;
   __shared__ unsigned long long sh_below;
   const unsigned int npool = win->npool, poolcap = win->poolcap;
   const unsigned int epoch = win->epoch & 1u;
@@ -283,6 +283,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   unsigned int* short_cnt = pool_cnt + 2 * kMaxPools + epoch;
   // grid totals of phase A (candidates kept, pool overflow flag, entries below the window):
   // accumulated with three atomics per block BEFORE the grid barrier, double-buffered on the epoch
+  unsigned int* done_cnt = pool_cnt + 2 * kMaxPools + 16 + epoch;  // ticket of the short-list finish
   unsigned int* tot32 = pool_cnt + 2 * kMaxPools + 8 + 4 * epoch;
   unsigned long long* tot_below = reinterpret_cast<unsigned long long*>(tot32 + 2);
   const int lane = threadIdx.x & 31;
@@ -301,6 +302,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     for (int i = threadIdx.x; i < 3 * kBins; i += blockDim.x) other[i] = 0ull;
     if (threadIdx.x == 0) pool_cnt[2 * kMaxPools + (epoch ^ 1u)] = 0u;
     if (threadIdx.x < 4) pool_cnt[2 * kMaxPools + 8 + 4 * (epoch ^ 1u) + threadIdx.x] = 0u;
+    if (threadIdx.x == 4) pool_cnt[2 * kMaxPools + 16 + (epoch ^ 1u)] = 0u;
   }
   __syncthreads();
   {
@@ -452,6 +454,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   const unsigned long long n_cand_full = tri_scan ? 2ull * n_cand : (unsigned long long)n_cand;
   const bool ok = sh_over == 0u && k_total >= below && k_total < below + n_cand_full;
   uint32_t result_bits = 0;
+  bool writer = blockIdx.x == 0;  // who stores the result (the finishing block on the short-list path)
   if (ok) {
     // ---------------------------------------------------------------- window hit
     // (in the doubled candidate list, position k' holds element k'/2 of the single list)
@@ -465,6 +468,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       result_bits = lo_bits + rel_prefix;
     } else if (bucket_n <= (unsigned long long)kShort) {
       // phase B: gather the bucket into the short list, one block finishes
+      writer = false;
       const unsigned int cnt = min(pool_cnt[blockIdx.x], poolcap);
       for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
         const unsigned int i = i0 + (unsigned int)lane;
@@ -479,15 +483,23 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
           if (in) shortlist[base + __popc(m & ((1u << lane) - 1u))] = v;
         }
       }
+      // no second grid barrier: the last block to finish its gather (ticket) finishes the select,
+      // the others are done
       __threadfence();
-      grid.sync();
-      if (blockIdx.x == 0) {
+      __syncthreads();
+      if (threadIdx.x == 0) sh_last = atomicAdd(done_cnt, 1u) == gridDim.x - 1 ? 1u : 0u;
+      __syncthreads();
+      if (!sh_last) return;
+      __threadfence();
+      {
         const int n = (int)bucket_n;
         const int npad = (n + 1023) & ~1023;
-        for (int i = threadIdx.x; i < npad; i += blockDim.x) sl[i] = i < n ? shortlist[i] : __uint_as_float(0x7f800000u);
+        for (int i = threadIdx.x; i < npad; i += blockDim.x)
+          sl[i] = i < n ? __ldcg(shortlist + i) : __uint_as_float(0x7f800000u);
         __syncthreads();
         const float med = block_select_smem(sl, npad, k, hist, scratch, &sh_bucket, &sh_k);
         result_bits = __float_as_uint(med) & 0x7fffffffu;
+        writer = true;
       }
     } else {
       // massive ties: keep refining the digits of rel over the pools
@@ -563,7 +575,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     }
     result_bits = prefix;
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+  if (writer && threadIdx.x == 0) {
     sigsvgd_bw_state& s = *state;
     const float med = __uint_as_float(result_bits);
     float h = bw_scale * sqrtf(med / log_np1);  // math.py:31-34

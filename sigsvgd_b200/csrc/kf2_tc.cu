@@ -40,7 +40,8 @@ constexpr int kPMaxChainKb = 1024 / PK;
 struct PairParams {
   int64_t M, N;  // output rows, columns
   int num_k16;
-  int tiles_m, tiles_n;  // tiles of 256 x 256
+  int tiles_m, tiles_n;  // tiles of 256 x tile_n
+  int tile_n;            // columns per pair tile (<= PN, multiple of 16)
   int nsplit, kb_per_split;
   int order;  // 0: row tile slowest, 1: column tile slowest (wide tiles first, the narrow one last)
   float* out;
@@ -114,7 +115,7 @@ kf_pair_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     }
     k.kb0 = sp * p.kb_per_split;
     k.kb1 = min(num_kb_total, k.kb0 + p.kb_per_split);
-    k.ncols = (int)min((int64_t)PN, ((p.N - (int64_t)k.tn * PN) + 15) / 16 * 16);
+    k.ncols = (int)min((int64_t)p.tile_n, ((p.N - (int64_t)k.tn * p.tile_n) + 15) / 16 * 16);
     k.nhalf = k.ncols / 2;  // columns of B staged by each CTA (multiple of 8)
     return k;
   };
@@ -127,7 +128,7 @@ kf_pair_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         const Work wk = decode(w);
         const int nbox = (wk.nhalf + 63) / 64;
         const int row = wk.tm * (2 * PM) + (int)rank * PM;
-        const int col = wk.tn * PN + (int)rank * wk.nhalf;
+        const int col = wk.tn * p.tile_n + (int)rank * wk.nhalf;
         for (int kb = wk.kb0; kb < wk.kb1; ++kb, ++it) {
           const int s = it % kPStages;
           const uint32_t ph = (it / kPStages) & 1u;
@@ -202,7 +203,7 @@ kf_pair_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
       const int64_t row0 = (int64_t)wk.tm * (2 * PM) + (int64_t)rank * PM + q * 32;
 #pragma unroll 1
       for (int c = 0; c < PN / 32; ++c) {
-        const int64_t col0 = (int64_t)wk.tn * PN + c * 32;
+        const int64_t col0 = (int64_t)wk.tn * p.tile_n + c * 32;
         if (c * 32 >= wk.ncols || col0 >= p.N) break;  // warp-uniform
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * PN + c * 32, v);
@@ -306,6 +307,15 @@ int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, cons
   p.M = M, p.N = C;
   p.num_k16 = (int)ceil_div(K, 16);
   p.tiles_m = (int)ceil_div(M, 2 * PM), p.tiles_n = (int)ceil_div(C, PN);
+  p.tile_n = PN;
+  {
+    // experiment knob: column tiles of equal width (848 = 3 x 224 + 176 instead of 3 x 256 + 80)
+    static const int equal_tiles = [] {
+      const char* e = getenv("SIGSVGD_KF_EQUAL_TILES");
+      return e ? atoi(e) : 0;
+    }();
+    if (equal_tiles) p.tile_n = (int)std::min<int64_t>(PN, round_up(ceil_div(C, p.tiles_n), 32));
+  }
   const int num_kb = (p.num_k16 + 1) / 2;
   p.kb_per_split = std::min(num_kb, kPMaxChainKb);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);

@@ -24,7 +24,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
     ts.sort(); print(json.dumps({"us": ts[len(ts) // 2]}))
 else:
     N = sys.argv[1] if len(sys.argv) > 1 else "4096"
-    for env in [{"SIGSVGD_KF_PAIRS": "1", "SIGSVGD_KF_NSPLIT": str(n), "SIGSVGD_KF_ORDER": str(o)} for o in (0, 1) for n in (4, 5, 6, 8)]:
+    for env in [{"SIGSVGD_KF_EQUAL_TILES": str(v)} for v in (0, 1, 0, 1)]:
         e = dict(os.environ); e.update(env); e["SIGSVGD_KF_DEBUG"] = "1"
         r = subprocess.run([sys.executable, __file__, "child", N], env=e, capture_output=True, text=True)
         dbg = [l for l in r.stderr.splitlines() if l.startswith("kf:")]

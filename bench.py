@@ -289,11 +289,10 @@ def run_ours(args):
         if use_tc:
             # the tcgen05 contraction K.[S - mean | 1 | score] exactly as sigsvgd_phi launches it
             planes, norms, scales, sc = ops.tc_pack_raw(s_all, ops.col_mean(s_all), Ga.to(dev))
-            d_rows = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True)
-            st = ops.bandwidth_raw(d_rows.clone(), ops.Bandwidth.median(), N)
-            kpl = ops.tc_rbf_raw(d_rows, st)
-            dominant = lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)  # noqa: E731
-            kname = "kf_pair_kernel (tcgen05 cta_group::2 split-fp16, K.[Sc|1|score])"
+            d_rows = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, out=ops.dist_buffer(N, N, dev))
+            st = ops.bandwidth_raw(d_rows.contiguous(), ops.Bandwidth.median(), N)
+            dominant = lambda: ops.tc_kf_raw(d_rows, planes, D + 1 + P, scales, st)  # noqa: E731
+            kname = "kf_fused_kernel (tcgen05 cta_group::2 split-fp16, exp(gamma d).[Sc|1|score], RBF map fused)"
         else:
             v_all = ops.pack_features(s_all, ops.col_mean(s_all), Ga.to(dev))
             k_rows = ops.sqdist_raw(v_all[:, P:], v_all[:, P:], D)

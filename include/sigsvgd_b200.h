@@ -43,6 +43,10 @@ extern "C" {
 #define SIGSVGD_FLAG_FORCE_SIMT 4u  /* never take the tcgen05 path                          */
 #define SIGSVGD_FLAG_FORCE_TC 8u    /* fail instead of falling back to SIMT                 */
 
+/* A-operand map of sigsvgd_tc_kf */
+#define SIGSVGD_KF_EXP 0      /* a = squared distances: K = exp(state->gamma * a)            */
+#define SIGSVGD_KF_IDENTITY 1 /* a = kernel values already (e.g. a weighted kernel matrix)   */
+
 /* Device-resident result/scratch record of one bandwidth selection (one per problem). */
 typedef struct sigsvgd_bw_state {
   float median;        /* lower median of all squared distances (element (n-1)//2 of the sort) */
@@ -200,8 +204,6 @@ int sigsvgd_tc_pack(const float* score, int64_t ld_score, int64_t P, const float
                     const float* mean, int64_t N, int64_t D, const float* scales, void* f_hi,
                     void* f_lo, int64_t ldp, int64_t Cp, float* norms, float* s_centred,
                     int64_t ld_sc, void* stream);
-/* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
- * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack. */
 /* tc_scales + tc_pack (and the column means) in two passes over the data instead of four: one
  * statistics pass (column sums, max |s|, max |score| into stats[8 * (D + 2)], scratch) and one packing pass that
  * derives the mean (center != 0) and the scales itself.  mean_out [D] / s_centred / norms may be NULL. */
@@ -209,11 +211,9 @@ int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const
                           int64_t N, int64_t D, int center, float* scales, void* f_hi, void* f_lo,
                           int64_t ldp, int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
                           float* mean_out, float* stats, void* stream);
-int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
-                      const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
-                      int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,
-                      void* stream);
-/* Same distances, 128x128 tiles with separate TMEM accumulators for the hi.hi and correction
+/* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
+ * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack.
+ * 128x128 tiles with separate TMEM accumulators for the hi.hi and correction
  * products and a TMA-store epilogue (needs dist 16-byte aligned and ldd % 4 == 0, else a slow
  * per-element epilogue runs); symmetric != 0 (same planes on both sides, M == N) computes the
  * upper triangle and mirrors it: the result is bit-symmetric with an exactly zero diagonal. */
@@ -223,7 +223,7 @@ int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float
                     int64_t ldd, void* stream);
 size_t sigsvgd_tc_median_workspace_bytes(int64_t M, int64_t N);
 /* Single-pass exact median (math.py:28-34).  prepare: a/b = centred fp32 features of the rows /
- * columns (s_centred of sigsvgd_tc_pack); samples 16384 entries of the matrix, sets a candidate
+ * columns (s_centred of sigsvgd_tc_pack); samples 8192 entries of the matrix, sets a candidate
  * window [lo, hi] around the sample median, resets the selection fields of *state.  It does not
  * need the matrix and may run before or after the Gram kernel. */
 int sigsvgd_tc_median_prepare(const float* a, int64_t lda, int64_t M, const float* b, int64_t ldb,
@@ -239,15 +239,20 @@ int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int6
                                               triangle is read */,
                              int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                              void* stream);
-/* K = exp(state->gamma * dist) (_kernels.py:110) written as planes of K*2^14 and, if k_out is not
- * NULL, as fp32 (k_out may alias dist).  Accumulates sum_kd / ties like sigsvgd_rbf_apply. */
-int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
-                   sigsvgd_bw_state* state, void* k_hi, void* k_lo, int64_t ldp, float* k_out,
-                   int64_t ldk, void* stream);
-/* out[M,C] = K[M,N] . F[N,C] in unscaled units: [K.(S-mean) | rowsum(K) | K.score] (svgd.py:82, :43) */
-int sigsvgd_tc_matmul(const void* k_hi, const void* k_lo, int64_t ldk, const void* f_hi,
-                      const void* f_lo, int64_t ldf, int64_t M, int64_t N, int64_t C,
-                      const float* scales, float* out, int64_t ldo, void* stream);
+/* out[M,C] = f(a)[M,K] . F[K,C] in unscaled units: [K.(S-mean) | rowsum(K) | K.score] (svgd.py:82, :43)
+ * with the RBF map fused into the operand path: a = fp32 [M,K] (row pitch lda, a multiple of 4;
+ * 16-byte aligned) holds the squared distances (mode SIGSVGD_KF_EXP: f = exp(state->gamma * .),
+ * _kernels.py:110) or kernel values (SIGSVGD_KF_IDENTITY); the kernel matrix is never written.
+ * stats != 0 (EXP mode): also accumulates state->sum_kd and records the entries equal to
+ * state->median like sigsvgd_rbf_apply (global row index = row_offset + i).  F planes / scales as
+ * produced by sigsvgd_tc_pack*.  out (row pitch ldo >= C) is overwritten. */
+int sigsvgd_tc_kf(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sigsvgd_bw_state* state,
+                  int stats, int64_t row_offset, const void* f_hi, const void* f_lo, int64_t ldf,
+                  int64_t C, const float* scales, float* out, int64_t ldo, void* stream);
+/* k_out[M,N] (row pitch ldk) = exp(state->gamma * dist[M,N]) (_kernels.py:110): the kernel matrix for
+ * callers that ask for k_xx; no statistics.  k_out may alias dist. */
+int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const sigsvgd_bw_state* state,
+                    float* k_out, int64_t ldk, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Fused single-GPU Stein update.  Replaces SVGD._compute_kernel + the arithmetic of

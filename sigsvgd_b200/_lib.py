@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libsigsvgd_b200.so")
 MAX_TIES = 16
 BW_MEDIAN, BW_FIXED = 0, 1
 FLAG_MEDIAN_GRAD, FLAG_NO_CENTER, FLAG_FORCE_SIMT, FLAG_FORCE_TC = 1, 2, 4, 8
+KF_EXP, KF_IDENTITY = 0, 1
 
 
 class BwState(ctypes.Structure):
@@ -98,11 +99,6 @@ _SIGNATURES = {
         [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
          c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p],
     ),
-    "sigsvgd_tc_sqdist": (
-        c_int,
-        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
-         c_void_p, c_void_p, c_int64, c_void_p],
-    ),
     "sigsvgd_tc_gram": (
         c_int,
         [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
@@ -112,17 +108,14 @@ _SIGNATURES = {
     "sigsvgd_tc_median_prepare": (
         c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
     "sigsvgd_tc_median_select": (
-        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int64, c_float, c_float, c_void_p, c_void_p]),
-    "sigsvgd_tc_rbf": (
         c_int,
-        [c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
-         c_void_p],
-    ),
-    "sigsvgd_tc_matmul": (
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int64, c_float, c_float, c_void_p, c_void_p]),
+    "sigsvgd_tc_kf": (
         c_int,
-        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
-         c_int64, c_void_p],
+        [c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_int, c_int64, c_void_p, c_void_p, c_int64, c_int64,
+         c_void_p, c_void_p, c_int64, c_void_p],
     ),
+    "sigsvgd_rbf_out": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p]),
     "sigsvgd_phi_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int, c_int]),
     "sigsvgd_phi": (
         c_int,

@@ -99,10 +99,10 @@ static int host_pipe(HostPipe** out) {
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 struct PhiLayout {
-  int64_t D, P, C, Np;
+  int64_t D, P, C, ldk;
   size_t off_sig, off_v, off_k, off_out, off_g, off_mean, off_part, off_sel, off_pref, total;
-  // tensor-core path (B == 1): fp16 planes of F [N x C] and K [N x Np], norms, scales
-  size_t off_fh, off_fl, off_kh, off_kl, off_norms, off_scales, off_win, off_stats;
+  // tensor-core path (B == 1): fp16 planes of F [N x C], norms, scales, median window
+  size_t off_fh, off_fl, off_norms, off_scales, off_win, off_stats;
 };
 
 static size_t bump(size_t* cur, size_t bytes) {
@@ -122,7 +122,11 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   size_t cur = 0;
   L.off_sig = want_sig ? 0 : bump(&cur, sizeof(float) * B * N * L.D);
   L.off_v = bump(&cur, sizeof(float) * B * N * L.C);
-  L.off_k = want_k ? 0 : bump(&cur, sizeof(float) * B * N * N);
+  // squared distances.  One swarm: always in the workspace, rows padded to whole 128-byte lines (the
+  // fused K.F kernel reads them by TMA; k_xx, if wanted, is a separate output).  Batches (SIMT): the
+  // kernel matrix is formed in place, straight in k_out when the caller wants it.
+  L.ldk = B == 1 ? round_up(N, 32) : N;
+  L.off_k = (want_k && B != 1) ? 0 : bump(&cur, sizeof(float) * B * N * L.ldk);
   L.off_out = bump(&cur, sizeof(float) * B * N * L.C);
   L.off_g = bump(&cur, sizeof(float) * B * N * L.D);
   L.off_mean = bump(&cur, sizeof(float) * B * L.D);
@@ -130,13 +134,10 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   L.off_sel = bump(&cur, select_workspace_bytes(N * N, B));
   // prefix checkpoints of the time-parallel signature backward (0 floats when not applicable)
   L.off_pref = bump(&cur, sizeof(float) * sig_prefix_floats(B * N, T, d, depth));
-  L.Np = round_up(N, 64);
-  L.off_fh = L.off_fl = L.off_kh = L.off_kl = L.off_norms = L.off_scales = L.off_win = L.off_stats = 0;
+  L.off_fh = L.off_fl = L.off_norms = L.off_scales = L.off_win = L.off_stats = 0;
   if (B == 1) {
     L.off_fh = bump(&cur, sizeof(__half) * N * L.C);
     L.off_fl = bump(&cur, sizeof(__half) * N * L.C);
-    L.off_kh = bump(&cur, sizeof(__half) * N * L.Np);
-    L.off_kl = bump(&cur, sizeof(__half) * N * L.Np);
     L.off_norms = bump(&cur, sizeof(float) * N);
     L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
     L.off_win = bump(&cur, window_workspace_bytes(N, N, nullptr));
@@ -208,7 +209,7 @@ int sigsvgd_sqdist(const float* a, int64_t lda, const float* b, int64_t ldb, int
                    int64_t D, float* dist, int64_t ldd, uint32_t flags, void* stream) {
   SIG_CHECK_ARG((M == 0 || N == 0) || (a && b && dist), "sqdist: NULL pointer");
   if (flags & SIGSVGD_FLAG_FORCE_TC) {
-    set_error("sqdist: the tcgen05 path takes fp16 planes; use sigsvgd_tc_sqdist");
+    set_error("sqdist: the tcgen05 path takes fp16 planes; use sigsvgd_tc_gram");
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   return launch_sqdist_simt(a, lda, b, ldb, M, N, D, dist, ldd, 1, 0, 0, 0, (cudaStream_t)stream);
@@ -293,7 +294,7 @@ int sigsvgd_matmul_nn(const float* a, int64_t lda, const float* v, int64_t ldv, 
                       int64_t N, int64_t C, float* out, int64_t ldo, uint32_t flags, void* stream) {
   SIG_CHECK_ARG(M == 0 || (a && v && out), "matmul_nn: NULL pointer");
   if (flags & SIGSVGD_FLAG_FORCE_TC) {
-    set_error("matmul_nn: the tcgen05 path takes fp16 planes; use sigsvgd_tc_matmul");
+    set_error("matmul_nn: the tcgen05 path takes fp16 planes; use sigsvgd_tc_kf");
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   return launch_gemm_nn_simt(a, lda, v, ldv, M, N, C, out, ldo, 1, 0, 0, 0, (cudaStream_t)stream);
@@ -353,16 +354,6 @@ int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const
                               st);
 }
 
-int sigsvgd_tc_sqdist(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
-                      const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
-                      int64_t N, int64_t D, const float* scales, float* dist, int64_t ldd,
-                      void* stream) {
-  SIG_CHECK_ARG(a_hi && a_lo && b_hi && b_lo && na && nb && scales && dist, "tc_sqdist: NULL pointer");
-  return tc_sqdist(TcPlanes{(const __half*)a_hi, (const __half*)a_lo, lda},
-                   TcPlanes{(const __half*)b_hi, (const __half*)b_lo, ldb}, M, N, D, na, nb,
-                   scales + 1, dist, ldd, (cudaStream_t)stream);
-}
-
 int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
                     const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
                     int64_t N, int64_t D, const float* scales, int symmetric, float* dist,
@@ -400,21 +391,19 @@ int sigsvgd_tc_median_select(void* median_ws, const float* dist, int64_t M, int6
                               (cudaStream_t)stream, symmetric);
 }
 
-int sigsvgd_tc_rbf(const float* dist, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
-                   sigsvgd_bw_state* state, void* k_hi, void* k_lo, int64_t ldp, float* k_out,
-                   int64_t ldk, void* stream) {
-  SIG_CHECK_ARG(state && (M == 0 || (dist && k_hi && k_lo)), "tc_rbf: NULL pointer");
-  return launch_tc_rbf(dist, ldd, M, N, row_offset, state, (__half*)k_hi, (__half*)k_lo, ldp, k_out,
-                       ldk, (cudaStream_t)stream);
+int sigsvgd_tc_kf(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sigsvgd_bw_state* state,
+                  int stats, int64_t row_offset, const void* f_hi, const void* f_lo, int64_t ldf,
+                  int64_t C, const float* scales, float* out, int64_t ldo, void* stream) {
+  SIG_CHECK_ARG(a && f_hi && f_lo && scales && out, "tc_kf: NULL pointer");
+  return tc_kf_fused(a, lda, M, K, mode, state, stats, row_offset,
+                     TcPlanes{(const __half*)f_hi, (const __half*)f_lo, ldf}, C, scales + 8, out, ldo,
+                     (cudaStream_t)stream);
 }
 
-int sigsvgd_tc_matmul(const void* k_hi, const void* k_lo, int64_t ldk, const void* f_hi,
-                      const void* f_lo, int64_t ldf, int64_t M, int64_t N, int64_t C,
-                      const float* scales, float* out, int64_t ldo, void* stream) {
-  SIG_CHECK_ARG(k_hi && k_lo && f_hi && f_lo && scales && out, "tc_matmul: NULL pointer");
-  return tc_matmul_nn(TcPlanes{(const __half*)k_hi, (const __half*)k_lo, ldk},
-                      TcPlanes{(const __half*)f_hi, (const __half*)f_lo, ldf}, M, N, C, scales + 8,
-                      out, ldo, (cudaStream_t)stream);
+int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const sigsvgd_bw_state* state,
+                    float* k_out, int64_t ldk, void* stream) {
+  SIG_CHECK_ARG(state && (M == 0 || (dist && k_out)), "rbf_out: NULL pointer");
+  return launch_rbf_out(dist, ldd, M, N, state, k_out, ldk, (cudaStream_t)stream);
 }
 
 size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, int depth,
@@ -453,7 +442,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   char* w = (char*)ws;
   float* sig = sig_out ? sig_out : (float*)(w + L.off_sig);
   float* V = (float*)(w + L.off_v);
-  float* K = k_out ? k_out : (float*)(w + L.off_k);
+  const int64_t ldk = L.ldk;
   float* out = (float*)(w + L.off_out);
   float* g = (float*)(w + L.off_g);
   float* mean = (float*)(w + L.off_mean);
@@ -463,14 +452,15 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   const int64_t D = L.D, P = L.P, C = L.C, R = B * N;
   const bool center = !(flags & SIGSVGD_FLAG_NO_CENTER);
   const bool use_tc = tc_path_enabled(B, N, flags);
+  // squared distances: tcgen05 path -> workspace, pitch ldk (k_xx is a separate output); SIMT path ->
+  // pitch N, turned into the kernel matrix in place, directly in k_out when the caller wants it
+  float* K = (k_out && !use_tc) ? k_out : (float*)(w + L.off_k);
   if ((flags & SIGSVGD_FLAG_FORCE_TC) && !use_tc) {
     set_error("phi: tcgen05 path not available for B=%lld N=%lld", (long long)B, (long long)N);
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   __half* Fh = (__half*)(w + L.off_fh);
   __half* Fl = (__half*)(w + L.off_fl);
-  __half* Kh = (__half*)(w + L.off_kh);
-  __half* Kl = (__half*)(w + L.off_kl);
   float* norms = (float*)(w + L.off_norms);
   float* scales = (float*)(w + L.off_scales);
 
@@ -520,10 +510,9 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     }
     feat = V, ldf = D;
     out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
-    // K3: squared distances into the K buffer (tcgen05, 3 MMAs per product; upper triangle
-    // mirrored)
-    SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms,
-                          scales + 1, 1, K, N, st));
+    // K3: squared distances (tcgen05, 3 MMAs per product; upper triangle mirrored)
+    SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms, scales + 1, 1, K,
+                          ldk, st));
     if (median_tc) SIG_CUDA_OK(cudaStreamWaitEvent(st, side->join, 0));
   } else {
     if (hp) SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->score_ready, 0));
@@ -537,18 +526,18 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   if (bw_mode == SIGSVGD_BW_MEDIAN && use_tc) {
     // K3 wrote a bit-symmetric matrix with an exact-zero diagonal: the select reads the upper
     // triangle only
-    SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, N, N, bw_scale, tol, state, st, 1));
+    SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, ldk, N, bw_scale, tol, state, st, 1));
   } else if (bw_mode == SIGSVGD_BW_MEDIAN) {
     SIG_PROPAGATE(launch_median_select(K, N * N, B, N * N, N, bw_scale, tol, state, selws,
                                        select_workspace_bytes(N * N, B), st));
   } else {
     SIG_PROPAGATE(launch_fixed_bandwidth(h_fixed, state, B, st));
   }
-  // K5: K = exp(gamma d), then one contraction K.[S | 1 | score]
+  // K5: one contraction exp(gamma d).[S | 1 | score]; on the tensor-core path the RBF map runs inside
+  // the contraction's operand path and the kernel matrix is never stored
   const int median_grad =
       (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0;
   if (use_tc) {
-    SIG_PROPAGATE(launch_tc_rbf(K, N, N, N, 0, state, Kh, Kl, L.Np, k_out ? K : nullptr, N, st));
     // (the coefficient of the median-gradient term is derived by the signature backward itself
     // when it forms the cotangent: see SigGradSpec::coef_mode)
     if (!(B == 1 && sig_bwd_fuses_grad(d, depth)))
@@ -561,8 +550,9 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
                                          scales + 8, Fh, Fl, C, C, nullptr, nullptr, D, nullptr, st,
                                          (D + 1) & ~(int64_t)1, C));
     }
-    SIG_PROPAGATE(tc_matmul_nn(TcPlanes{Kh, Kl, L.Np}, TcPlanes{Fh, Fl, C}, N, N, D + 1 + P,
-                               scales + 8, out, C, st, /*out_zeroed=*/true));
+    SIG_PROPAGATE(tc_kf_fused(K, ldk, N, N, SIGSVGD_KF_EXP, state, /*stats=*/1, 0, TcPlanes{Fh, Fl, C},
+                              D + 1 + P, scales + 8, out, C, st, /*out_zeroed=*/true));
+    if (k_out) SIG_PROPAGATE(launch_rbf_out(K, ldk, N, N, state, k_out, N, st));  // k_xx for the caller
   } else {
     SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));
     SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, B, st));

@@ -87,6 +87,39 @@ rbf_apply_kernel(float* __restrict__ k, int64_t ldk, int64_t M, int64_t N, int64
   if (threadIdx.x == 0 && tot != 0.0) atomicAdd(&s.sum_kd, tot);
 }
 
+// k_out = exp(gamma * dist), four columns per thread, no statistics (grid: col blocks x row blocks)
+__global__ void __launch_bounds__(kEwThreads)
+rbf_out_kernel(const float* __restrict__ d, int64_t ldd, int64_t M, int64_t N,
+               const sigsvgd_bw_state* __restrict__ state, float* __restrict__ k, int64_t ldk,
+               int rows_per_block) {
+  const float gamma = state->gamma;
+  const int64_t c0 = ((int64_t)blockIdx.x * kEwThreads + threadIdx.x) * 4;
+  if (c0 >= N) return;
+  const bool vin = ((ldd & 3) == 0) && ((reinterpret_cast<uintptr_t>(d) & 15u) == 0) && (c0 + 3 < N);
+  const bool vout = ((ldk & 3) == 0) && ((reinterpret_cast<uintptr_t>(k) & 15u) == 0) && (c0 + 3 < N);
+  const int nv = (int)min((int64_t)4, N - c0);
+  const int64_t r_end = min(M, ((int64_t)blockIdx.y + 1) * rows_per_block);
+  for (int64_t r = (int64_t)blockIdx.y * rows_per_block; r < r_end; ++r) {
+    float v[4];
+    if (vin) {
+      const float4 q = *reinterpret_cast<const float4*>(d + r * ldd + c0);
+      v[0] = q.x, v[1] = q.y, v[2] = q.z, v[3] = q.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) v[e] = e < nv ? d[r * ldd + c0 + e] : 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[e] = expf(gamma * v[e]);
+    if (vout) {
+      *reinterpret_cast<float4*>(k + r * ldk + c0) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (e < nv) k[r * ldk + c0 + e] = v[e];
+    }
+  }
+}
+
 constexpr int kMeanParts = 64;
 
 // part[b][r][c] = sum over rows n = r, r+64, ... of s[b][n][c]
@@ -186,6 +219,22 @@ int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_of
   rbf_apply_kernel<<<grid, kEwThreads, 0, st>>>(k, ldk, M, N, row_offset, weight, ldw, state,
                                                 stride_k, stride_w, rows_per_block);
   SIG_LAUNCH_OK("rbf_apply_kernel");
+  return 0;
+}
+
+int launch_rbf_out(const float* d, int64_t ldd, int64_t M, int64_t N, const sigsvgd_bw_state* state,
+                   float* k, int64_t ldk, cudaStream_t st) {
+  SIG_CHECK_ARG(M >= 0 && N >= 1 && ldd >= N && ldk >= N, "rbf_out: bad shape M=%lld N=%lld", (long long)M,
+                (long long)N);
+  if (M == 0) return 0;
+  const int64_t gx = ceil_div(N, (int64_t)kEwThreads * 4);
+  int64_t gy = std::min<int64_t>(65535, std::max<int64_t>(1, ceil_div((int64_t)num_sms() * 16, gx)));
+  gy = std::min(gy, M);
+  const int rows_per_block = (int)ceil_div(M, gy);
+  gy = ceil_div(M, rows_per_block);
+  rbf_out_kernel<<<dim3((unsigned)gx, (unsigned)gy), kEwThreads, 0, st>>>(d, ldd, M, N, state, k, ldk,
+                                                                        rows_per_block);
+  SIG_LAUNCH_OK("rbf_out_kernel");
   return 0;
 }
 

@@ -36,14 +36,19 @@ struct SelWindow {
   unsigned int epoch;        // parity selects the histogram / counter buffers of the next select
 };
 constexpr int kMaxPools = 1024;
+// Counter block behind the pools: pool_cnt[0..kMaxPools) fill of pool b, [kMaxPools..2*kMaxPools)
+// entries below the window seen by block b, then 64 words `misc`:
+//   misc[epoch]            fill of the short list          misc[2]            ticket of window_prepare
+//   misc[8 + 4*epoch + 0]  candidates kept (all pools)     misc[8 + 4*epoch + 1]  pool-overflow flag
+//   misc[8 + 4*epoch + 2..3]  entries below the window (u64)
+//   misc[16 + epoch]       ticket of the short-list finish
+// (epoch = SelWindow::epoch & 1 double-buffers what a select leaves behind for the next one)
+constexpr int kWinBins = 2048;      // histogram bins of the select kernel (top 11 bits of bits - lo_bits)
 
 // dist[i,j] = max(0, (na[i] + nb[j] - 2 * sum_c A[i,c] B[j,c]) * scal[0])   i < M, j < N, c < D
 //   A, B: planes [M x >=D], [N x >=D] (features along the row: K-major for both operands)
 //   na, nb: squared row norms in plane units; scal: DEVICE pointer, scal[0] = alpha^-2
-int tc_sqdist(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
-              const float* nb, const float* scal, float* dist, int64_t ldd, cudaStream_t st);
-
-// Same distances with 128 x 128 tiles, separate TMEM accumulators for the hi.hi and the
+// 128 x 128 tiles, separate TMEM accumulators for the hi.hi and the
 // correction products, TMA-store epilogue.
 // symmetric != 0: A and B are the same planes (M == N); only tiles on or above the diagonal are
 // computed, each is stored together with its transpose, and the diagonal is exactly 0.
@@ -51,15 +56,13 @@ int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float
             const float* nb, const float* scal, int symmetric, float* dist, int64_t ldd,
             cudaStream_t st);
 
-// out[i,c] = colscale[c] * sum_j A[i,j] V[j,c]      i < M, j < K, c < C
-//   A: planes [M x >=K] (K-major), V: planes [K x >=C] (the contraction index is the ROW of V:
-//   MN-major B operand), colscale: DEVICE vector [C] undoing the plane scalings
-// the CTA-pair (cta_group::2) kernel behind tc_matmul_nn (kf2_tc.cu)
-bool tc_matmul_pair_available();
-int tc_matmul_pair(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                   float* out, int64_t ldo, cudaStream_t st, bool out_zeroed = false);
-int tc_matmul_nn(TcPlanes A, TcPlanes V, int64_t M, int64_t K, int64_t C, const float* colscale,
-                 float* out, int64_t ldo, cudaStream_t st, bool out_zeroed = false);
+// out[i,c] = colscale[c] * sum_j f(a[i,j]) V[j,c]   (kf3_tc.cu): a = fp32 [M x K] (row pitch lda, a
+// multiple of 4; 16-byte aligned), f = exp(state->gamma * .) (SIGSVGD_KF_EXP) or the identity
+// (SIGSVGD_KF_IDENTITY); V planes [K x >=C] as for tc_matmul_nn.  stats != 0: also state->sum_kd +=
+// sum f(a) a and the entries equal to state->median are recorded (global row = row_offset + i).
+int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sigsvgd_bw_state* state,
+                int stats, int64_t row_offset, TcPlanes V, int64_t C, const float* colscale, float* out,
+                int64_t ldo, cudaStream_t st, bool out_zeroed = false);
 
 // true when this process can create TMA descriptors (driver entry point resolved)
 bool tc_available();
@@ -102,10 +105,5 @@ int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float
                          float* norms, float* sc, int64_t ldsc, float* mean_out, cudaStream_t st,
                          int64_t c_lo = 0, int64_t c_hi = -1,  // plane columns [c_lo, c_hi) only
                          float* zero_out = nullptr, int64_t ld_zero = 0);  // also zero [N, Cp] of this buffer
-// K = exp(gamma d) as planes of K*2^14 (+ optional fp32 K into kout, may alias d);
-// accumulates state->sum_kd, records median ties (global row = row_offset + i)
-int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
-                  sigsvgd_bw_state* state, __half* kh, __half* kl, int64_t ldp, float* kout,
-                  int64_t ldk, cudaStream_t st);
 
 }  // namespace sigsvgd

@@ -5,8 +5,8 @@
 //   1. window_sample : m random entries of the matrix are evaluated directly from the centred fp32
 //                      features (difference form) -- they only steer the search, exactness does
 //                      not depend on them;
-//   2. window_bounds : one block selects two sample order statistics m/2 -+ 6 sigma -> [lo, hi],
-//                      which brackets the true median except with probability ~1e-9;
+//   2. window_bounds : one block selects two sample order statistics m/2 -+ 5.7 sigma -> [lo, hi],
+//                      which brackets the true median except with probability ~1e-8;
 //   3. window_select : one cooperative kernel.  Phase A reads the matrix once (right after the
 //                      Gram kernel wrote it: L2 hits), counts the entries < lo and compacts the
 //                      entries in [lo, hi] (about 5 %) into per-block pools (ballot compaction,
@@ -23,9 +23,9 @@ namespace cg = cooperative_groups;
 namespace sigsvgd {
 namespace {
 
-constexpr int kSample = 16384;      // m
-constexpr int kSampleHalfWin = 384; // 6 sigma, sigma = sqrt(m)/2 = 64 ranks
-constexpr int kBins = 2048;
+constexpr int kSample = 8192;       // m
+constexpr int kSampleHalfWin = 256; // 5.7 sigma, sigma = sqrt(m)/2 = 45 ranks
+constexpr int kBins = kWinBins;
 
 __device__ __forceinline__ uint32_t hash32(uint32_t x) {
   x ^= x >> 16;
@@ -127,11 +127,11 @@ __device__ float block_select_smem(const float* vals, int n, unsigned long long 
   return __uint_as_float(prefix);
 }
 
-// Fused window preparation.  Every block evaluates 128 sample entries d = |a_i - b_j|^2 (one warp
-// per sample, fp32 difference form; the features need not be centred).  The last block to finish
-// (ticket counter) sorts the 16384 samples in shared memory (bitonic) and sets the window to the
-// sample order statistics m/2 -+ 6 sigma; it also resets the window / histogram / bandwidth
-// records.
+// Fused window preparation.  Every warp evaluates two sample entries d = |a_i - b_j|^2 (fp32
+// difference form; the features need not be centred; all loads of a sample in flight at once).  The
+// last block to finish (ticket counter) selects the sample order statistics m/2 -+ 5.7 sigma with two
+// histogram passes (both bounds at once) and sets the window; it also resets the window / histogram /
+// bandwidth records.
 constexpr int kPrepThreads = 1024;
 constexpr int kSamplesPerBlock = 64;
 
@@ -143,13 +143,11 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
                       unsigned int* pool_cnt /*[2*kMaxPools + 64]*/, sigsvgd_bw_state* state) {
   extern __shared__ float sv[];  // kSample floats (last block only)
   __shared__ bool sh_last;
-  __shared__ unsigned int hist[kBins];
+  __shared__ unsigned int hist[2][kBins];
   __shared__ unsigned long long scratch[1024];
   __shared__ float sh_red[64];
-  __shared__ uint32_t sh_bucket;
-  __shared__ unsigned long long sh_k;
-  uint32_t bin0 = 0;
-  float inv_w0 = 0.f;
+  __shared__ uint32_t sh_bucket[2];
+  __shared__ unsigned long long sh_k[2];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll 1
   for (int q = 0; q < kSamplesPerBlock / (kPrepThreads / 32); ++q) {
@@ -159,10 +157,21 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
     const float* __restrict__ ai = a + i * lda;
     const float* __restrict__ bj = b + j * ldb;
     float acc = 0.f;
-#pragma unroll 4
-    for (int64_t c = lane; c < D; c += 32) {
-      const float t = __ldg(ai + c) - __ldg(bj + c);
-      acc = fmaf(t, t, acc);
+    // batches of 8 column pairs: their 16 loads are issued before the first use (one pair per
+    // iteration made a sample a chain of D/32 exposed L2 latencies)
+    for (int64_t c0 = lane; c0 < D; c0 += 32 * 8) {
+      float va[8], vb[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int64_t c = c0 + 32 * u;
+        va[u] = c < D ? __ldg(ai + c) : 0.f;
+        vb[u] = c < D ? __ldg(bj + c) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const float t = va[u] - vb[u];
+        acc = fmaf(t, t, acc);
+      }
     }
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -178,7 +187,7 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
   for (int i = threadIdx.x; i < 2 * 3 * kBins; i += kPrepThreads) ghist[i] = 0ull;
   for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += kPrepThreads) pool_cnt[i] = 0u;  // incl. the ticket
   __syncthreads();
-  // Window bounds = sample order statistics m/2 -+ 6 sigma, located by two levels of 2048 linear
+  // Window bounds = sample order statistics m/2 -+ 5.7 sigma, located by two levels of 2048 linear
   // bins (whole range, then the selected bin) and rounded OUTWARD by one fine bin: the bounds only
   // steer the search, so a slightly wider window is harmless.
   float mn = INFINITY, mx = 0.f;
@@ -199,40 +208,41 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
     mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
     mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   }
-  float bound[2];
-  const int ranks[2] = {kSample / 2 - kSampleHalfWin, kSample / 2 + kSampleHalfWin};
-  for (int which = 0; which < 2; ++which) {
-    float base = mn, width = fmaxf((mx - mn) * (1.f / kBins), 0.f);
-    unsigned long long k = (unsigned long long)ranks[which];
-    for (int level = 0; level < 2; ++level) {
-      const float inv_w = width > 0.f ? 1.f / width : 0.f;
-      for (int i = threadIdx.x; i < kBins; i += kPrepThreads) hist[i] = 0u;
-      __syncthreads();
-      for (int i = threadIdx.x; i < kSample; i += kPrepThreads) {
-        const float v = sv[i];
-        // level 1 keeps only the values that level 0 put into the selected bin
-        bool in = true;
-        if (level == 1) in = min(kBins - 1, (int)((v - mn) * inv_w0)) == (int)bin0;
-        if (in) atomicAdd(&hist[max(0, min(kBins - 1, (int)((v - base) * inv_w)))], 1u);
-      }
-      __syncthreads();
-      block_pick_bucket(hist, k, &sh_bucket, &sh_k, scratch);
-      k = sh_k;
-      if (level == 0) {
-        bin0 = sh_bucket;
-        inv_w0 = inv_w;
-        base = mn + (float)sh_bucket * width;
-        width *= (1.f / kBins);
-      } else {
-        const float edge = base + ((float)sh_bucket + (which == 0 ? -1.f : 2.f)) * width;
-        bound[which] = which == 0 ? fmaxf(edge, 0.f) : edge;
-      }
-      __syncthreads();
-    }
+  const unsigned long long ranks[2] = {kSample / 2 - kSampleHalfWin, kSample / 2 + kSampleHalfWin};
+  const float width0 = fmaxf((mx - mn) * (1.f / kBins), 0.f);
+  const float inv_w0 = width0 > 0.f ? 1.f / width0 : 0.f;
+  auto bin0_of = [&](float v) { return max(0, min(kBins - 1, (int)((v - mn) * inv_w0))); };
+  // level 0: one histogram of the whole range serves both bounds
+  for (int i = threadIdx.x; i < 2 * kBins; i += kPrepThreads) (&hist[0][0])[i] = 0u;
+  __syncthreads();
+  for (int i = threadIdx.x; i < kSample; i += kPrepThreads) atomicAdd(&hist[0][bin0_of(sv[i])], 1u);
+  __syncthreads();
+  block_pick_bucket(hist[0], ranks[0], &sh_bucket[0], &sh_k[0], scratch);
+  block_pick_bucket(hist[0], ranks[1], &sh_bucket[1], &sh_k[1], scratch);
+  const uint32_t b0[2] = {sh_bucket[0], sh_bucket[1]};
+  const unsigned long long k1[2] = {sh_k[0], sh_k[1]};
+  __syncthreads();
+  // level 1: the two selected bins, 2048 finer bins each
+  const float width1 = width0 * (1.f / kBins);
+  const float inv_w1 = width1 > 0.f ? 1.f / width1 : 0.f;
+  const float base1[2] = {mn + (float)b0[0] * width0, mn + (float)b0[1] * width0};
+  for (int i = threadIdx.x; i < kBins; i += kPrepThreads) hist[0][i] = 0u;
+  __syncthreads();
+  for (int i = threadIdx.x; i < kSample; i += kPrepThreads) {
+    const float v = sv[i];
+    const uint32_t bv = (uint32_t)bin0_of(v);
+#pragma unroll
+    for (int which = 0; which < 2; ++which)
+      if (bv == b0[which]) atomicAdd(&hist[which][max(0, min(kBins - 1, (int)((v - base1[which]) * inv_w1)))], 1u);
   }
+  __syncthreads();
+  block_pick_bucket(hist[0], k1[0], &sh_bucket[0], &sh_k[0], scratch);
+  block_pick_bucket(hist[1], k1[1], &sh_bucket[1], &sh_k[1], scratch);
   if (threadIdx.x == 0) {
-    win->lo = fminf(bound[0], bound[1]);
-    win->hi = fmaxf(bound[0], bound[1]);
+    const float lo_e = fmaxf(base1[0] + ((float)sh_bucket[0] - 1.f) * width1, 0.f);
+    const float hi_e = base1[1] + ((float)sh_bucket[1] + 2.f) * width1;
+    win->lo = fminf(lo_e, hi_e);
+    win->hi = fmaxf(lo_e, hi_e);
     win->n_cand = 0u;
     win->cap = cap;
     win->below = 0ull;
@@ -253,7 +263,7 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
   }
 }
 
-constexpr int kShort = 4096;  // capacity of the short list finished by a single block
+constexpr int kShort = 6144;  // capacity of the short list finished by a single block
 
 // cooperative: exact order statistic k_total of the M x N matrix `dist`
 //   phase A  one pass over the matrix: count entries < lo, compact entries in [lo, hi] into this
@@ -469,7 +479,12 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     } else if (bucket_n <= (unsigned long long)kShort) {
       // phase B: gather the bucket into the short list, one block finishes
       writer = false;
-      const unsigned int cnt = min(pool_cnt[blockIdx.x], poolcap);
+      // (matches are gathered in shared memory first: ONE global reservation per block instead of one
+      // round trip per warp and step)
+      const unsigned int cnt = blockIdx.x < npool ? min(pool_cnt[blockIdx.x], poolcap) : 0u;
+      __shared__ unsigned int sh_base;
+      if (threadIdx.x == 0) sh_fill = 0u;
+      __syncthreads();
       for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
         const unsigned int i = i0 + (unsigned int)lane;
         const float v = i < cnt ? pool[i] : 0.f;
@@ -478,11 +493,17 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
         const unsigned m = __ballot_sync(0xffffffffu, in);
         if (m) {
           unsigned int base = 0;
-          if (lane == 0) base = atomicAdd(short_cnt, (unsigned int)__popc(m));
+          if (lane == 0) base = atomicAdd(&sh_fill, (unsigned int)__popc(m));
           base = __shfl_sync(0xffffffffu, base, 0);
-          if (in) shortlist[base + __popc(m & ((1u << lane) - 1u))] = v;
+          const unsigned int at = base + __popc(m & ((1u << lane) - 1u));
+          if (in && at < (unsigned int)kShort) sl[at] = v;  // (a block holds at most bucket_n <= kShort)
         }
       }
+      __syncthreads();
+      const unsigned int nloc = min(sh_fill, (unsigned int)kShort);
+      if (threadIdx.x == 0 && nloc) sh_base = atomicAdd(short_cnt, nloc);
+      __syncthreads();
+      for (unsigned int i = threadIdx.x; i < nloc; i += blockDim.x) shortlist[sh_base + i] = sl[i];
       // no second grid barrier: the last block to finish its gather (ticket) finishes the select,
       // the others are done
       __threadfence();
@@ -493,7 +514,7 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       __threadfence();
       {
         const int n = (int)bucket_n;
-        const int npad = (n + 1023) & ~1023;
+        const int npad = (n + 1023) & ~1023;  // <= kShort (a multiple of 1024)
         for (int i = threadIdx.x; i < npad; i += blockDim.x)
           sl[i] = i < n ? __ldcg(shortlist + i) : __uint_as_float(0x7f800000u);
         __syncthreads();
@@ -602,11 +623,11 @@ size_t window_workspace_bytes(int64_t M, int64_t N, unsigned int* cap_out) {
   if (cap_out) *cap_out = cap;
   return (size_t)round_up((int64_t)sizeof(SelWindow), 256) + (size_t)round_up(sizeof(float) * kSample, 256) +
          (size_t)round_up(sizeof(unsigned long long) * 2 * 3 * kBins, 256) +
-         sizeof(unsigned int) * (2 * kMaxPools + 64) + sizeof(float) * 4096 + sizeof(float) * (size_t)cap;
+         sizeof(unsigned int) * (2 * kMaxPools + 64) + sizeof(float) * kShort + sizeof(float) * (size_t)cap;
 }
 
 // ws layout: [SelWindow | sample | ghist x2 | pool_cnt[kMaxPools] + below_cnt[kMaxPools] + misc[64] |
-//             shortlist[4096] | cand]
+//             shortlist[kShort] | cand]
 static void window_carve(void* ws, SelWindow** win, float** sample, unsigned long long** ghist,
                          unsigned int** pool_cnt, float** cand, float** shortlist = nullptr) {
   char* w = (char*)ws;
@@ -619,7 +640,7 @@ static void window_carve(void* ws, SelWindow** win, float** sample, unsigned lon
   *pool_cnt = (unsigned int*)w;
   w += sizeof(unsigned int) * (2 * kMaxPools + 64);
   if (shortlist) *shortlist = (float*)w;
-  w += sizeof(float) * 4096;
+  w += sizeof(float) * kShort;
   *cand = (float*)w;
 }
 

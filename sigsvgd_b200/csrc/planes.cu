@@ -1,12 +1,10 @@
 // Operand preparation for the split-fp16 tensor-core GEMMs (gemm_tc.cu): power-of-two scaling,
-// hi/lo fp16 planes, row norms, and the RBF map that writes K directly as planes.
+// hi/lo fp16 planes, row norms.  (The RBF map is fused into the K.F kernel's operand path, kf3_tc.cu.)
 //
 //   tc_scales   : alpha_S, alpha_G (powers of two placing the largest |value| in [2^13, 2^14)),
 //                 alpha_S^-2 for the distance epilogue, colscale[] for the K.V epilogue
 //   tc_pack     : F = [ (S - mean)*alpha_S | 1 | score*alpha_G | 0.. ] as fp16 hi/lo planes,
 //                 |F_S|^2 row norms (plane units), and the centred fp32 features
-//   tc_rbf      : K = exp(gamma d) -> hi/lo planes of K*2^14 (+ optional fp32 K, sum K*d, ties)
-//                 reference: src/kernels/_kernels.py:110
 #include "gemm_tc.cuh"
 
 namespace sigsvgd {
@@ -14,12 +12,6 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr float kKScale = 16384.f;  // 2^14: K in [0,1] -> [0, 2^14]
-
-__device__ __forceinline__ float exp2f_fast(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 __device__ __forceinline__ void split_half(float x, __half& hi, __half& lo) {
   hi = __float2half_rn(x);
@@ -328,111 +320,6 @@ pack_stats_kernel(const float* __restrict__ score, int64_t lsc, int64_t P,
   }
 }
 
-__device__ __forceinline__ double block_sum_double(double v, double* sm) {
-#pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  if (l == 0) sm[w] = v;
-  __syncthreads();
-  double s = 0.0;
-  if (threadIdx.x == 0)
-    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += sm[i];
-  return s;
-}
-
-// grid: (col blocks, row blocks); each thread handles 4 consecutive columns of `rows_per_block` rows
-__global__ void __launch_bounds__(kThreads)
-rbf_planes_kernel(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
-                  sigsvgd_bw_state* __restrict__ state, __half* __restrict__ kh,
-                  __half* __restrict__ kl, int64_t ldp, float* kout, int64_t ldk,
-                  int rows_per_block) {
-  __shared__ double red[kThreads / 32];
-  sigsvgd_bw_state& s = *state;
-  const float gamma = s.gamma;
-  const uint32_t med_bits = __float_as_uint(s.median);
-  const bool track_ties = s.median > 0.f;
-  const int64_t c0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
-  const bool vec_in = ((ldd & 3) == 0) && ((reinterpret_cast<uintptr_t>(d) & 15u) == 0) && (c0 + 3 < N);
-  const bool vec_out = kout && ((ldk & 3) == 0) && ((reinterpret_cast<uintptr_t>(kout) & 15u) == 0) && (c0 + 3 < N);
-  const int64_t r_begin = (int64_t)blockIdx.y * rows_per_block;
-  const int64_t r_end = min(M, r_begin + rows_per_block);
-  double acc = 0.0;
-  if (c0 < ldp) {  // planes are written up to their padded pitch (zeros beyond N)
-    const int nv = (int)max((int64_t)0, min((int64_t)4, N - c0));
-    const float gamma2 = gamma * 1.4426950408889634f;  // log2(e)
-    auto process = [&](int64_t r, const float (&dv)[4]) {
-      float kv[4];
-      float part = 0.f;
-      __half h[4], l[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        // ex2.approx of (gamma*log2e)*d: relative error 2^-22 + 1.2e-7*|gamma d|, i.e. < 5e-8 absolute
-        // on K in (0, 1]; the full-range expf costs a third of this kernel's issue slots
-        kv[e] = e < nv ? exp2f_fast(gamma2 * dv[e]) : 0.f;
-        if (e < nv) {
-          part = fmaf(kv[e], dv[e], part);
-          if (track_ties && (__float_as_uint(dv[e]) & 0x7fffffffu) == med_bits) {
-            const uint32_t slot = atomicAdd(&s.n_ties, 1u);
-            if (slot < SIGSVGD_MAX_TIES) {
-              s.ties[2 * slot] = (int32_t)(row_offset + r);
-              s.ties[2 * slot + 1] = (int32_t)(c0 + e);
-            }
-          }
-        }
-        split_half(kv[e] * kKScale, h[e], l[e]);
-      }
-      // ldp is a multiple of 8 and c0 a multiple of 4: 8-byte aligned plane stores
-      {
-        __half2 a = __halves2half2(h[0], h[1]), b2 = __halves2half2(h[2], h[3]);
-        __half2 c = __halves2half2(l[0], l[1]), e2 = __halves2half2(l[2], l[3]);
-        uint2 uh, ul;
-        uh.x = *reinterpret_cast<uint32_t*>(&a);
-        uh.y = *reinterpret_cast<uint32_t*>(&b2);
-        ul.x = *reinterpret_cast<uint32_t*>(&c);
-        ul.y = *reinterpret_cast<uint32_t*>(&e2);
-        *reinterpret_cast<uint2*>(kh + r * ldp + c0) = uh;
-        *reinterpret_cast<uint2*>(kl + r * ldp + c0) = ul;
-      }
-      if (kout) {
-        float* orow = kout + r * ldk + c0;
-        if (vec_out) {
-          *reinterpret_cast<float4*>(orow) = make_float4(kv[0], kv[1], kv[2], kv[3]);
-        } else {
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (e < nv) orow[e] = kv[e];
-        }
-      }
-      return part;
-    };
-    // four rows per step: their loads are issued together (one 16-byte load in flight per thread
-    // left the kernel latency-bound at 63 % of the HBM roofline)
-    for (int64_t r = r_begin; r < r_end; r += 4) {
-      float dv[4][4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (r + j < r_end) {
-          const float* row = d + (r + j) * ldd + c0;
-          if (vec_in) {
-            const float4 q = *reinterpret_cast<const float4*>(row);
-            dv[j][0] = q.x, dv[j][1] = q.y, dv[j][2] = q.z, dv[j][3] = q.w;
-          } else {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) dv[j][e] = e < nv ? row[e] : 0.f;
-          }
-        }
-      }
-      float part = 0.f;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (r + j < r_end) part += process(r + j, dv[j]);
-      acc += (double)part;
-    }
-  }
-  const double tot = block_sum_double(acc, red);
-  if (threadIdx.x == 0 && tot != 0.0) atomicAdd(&s.sum_kd, tot);
-}
-
 }  // namespace
 
 int launch_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, int64_t D,
@@ -501,24 +388,6 @@ int launch_tc_pack_stats(const float* score, int64_t lsc, int64_t P, const float
       score, lsc, P, s, lds, stats, n_total, center, N, D, tcs, colscale, fh, fl, ldp, Cp, norms, sc, ldsc,
       mean_out, c_lo, c_hi, zero_out, ld_zero, mean_in_smem);
   SIG_LAUNCH_OK("pack_stats_kernel");
-  return 0;
-}
-
-int launch_tc_rbf(const float* d, int64_t ldd, int64_t M, int64_t N, int64_t row_offset,
-                  sigsvgd_bw_state* state, __half* kh, __half* kl, int64_t ldp, float* kout,
-                  int64_t ldk, cudaStream_t st) {
-  SIG_CHECK_ARG(M >= 0 && N >= 1 && ldd >= N && ldp >= N && (ldp & 7) == 0 && (kout == nullptr || ldk >= N),
-                "tc_rbf: bad shape M=%lld N=%lld ldd=%lld ldp=%lld", (long long)M, (long long)N,
-                (long long)ldd, (long long)ldp);
-  if (M == 0) return 0;
-  const int64_t gx = ceil_div(ldp, (int64_t)kThreads * 4);
-  int64_t gy = std::min<int64_t>(65535, std::max<int64_t>(1, ceil_div((int64_t)num_sms() * 16, gx)));
-  gy = std::min(gy, M);
-  const int rows_per_block = (int)round_up(ceil_div(M, gy), 4);
-  gy = ceil_div(M, rows_per_block);
-  rbf_planes_kernel<<<dim3((unsigned)gx, (unsigned)gy), kThreads, 0, st>>>(
-      d, ldd, M, N, row_offset, state, kh, kl, ldp, kout, ldk, rows_per_block);
-  SIG_LAUNCH_OK("rbf_planes_kernel");
   return 0;
 }
 

@@ -82,6 +82,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       : "memory");
 }
 
+// 2-D tiled prefetch into L2 (no shared-memory destination, no completion tracking)
+__device__ __forceinline__ void tma_prefetch_2d(const void* tmap, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+               :
+               : "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1)
+               : "memory");
+}
+
 // 2-D tiled store smem -> global (bulk async-group completion); out-of-bounds parts are clipped
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -173,6 +181,11 @@ __device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
                : "memory");
+}
+// Arrive on a barrier of another CTA of the cluster with the default (.release.cta) semantics: the
+// form for per-stage signalling (the cluster-scope release above costs ~1000 cycles per arrive).
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair: data lands in the issuing CTA's shared memory, the
 // transaction bytes are counted on the barrier of the pair's even CTA (peer bit cleared)

@@ -92,22 +92,29 @@ class CudaBackend:
         if f.data[0] == "tc":
             _, planes, norms, scales, D, P, r0, M = f.data
             rows = ops.Planes(planes.hi[r0:r0 + M], planes.lo[r0:r0 + M])
-            return ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False)
+            # (contiguous when N % 4 == 0: the flat select kernels and the TMA-fed contraction both take it)
+            N = planes.hi.shape[0]
+            out = torch.empty(M, N, dtype=torch.float32, device=planes.hi.device) if N % 4 == 0 else \
+                ops.dist_buffer(M, N, planes.hi.device)
+            return ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False, out=out)
         _, v, D, P, r0, M = f.data
         return ops.sqdist_raw(v[r0:r0 + M, P:], v[:, P:], D)
 
     def rbf(self, k_rows, state, row_offset, f: Features, want_k: bool):
-        """exp in place (SIMT) or into fp16 planes (tcgen05).  Adds this strip's sum K*d / ties to
-        ``state``.  Returns the contraction operand."""
+        """SIMT: exp in place, adding this strip's sum K*d / ties to ``state``.  tcgen05: nothing to
+        do here -- the RBF map and its statistics run inside the contraction's operand path.
+        Returns (contraction operand, k_xx rows or None)."""
         if f.data[0] == "tc":
-            return ops.tc_rbf_raw(k_rows, state, row_offset, want_k)
-        return ops.rbf_apply_raw(k_rows, state, row_offset)
+            return k_rows, (ops.rbf_out_raw(k_rows, state) if want_k else None)
+        k = ops.rbf_apply_raw(k_rows, state, row_offset)
+        return k, (k if want_k else None)
 
-    def contract(self, kmat, f: Features):
-        """-> (K.Sc [M,D], rowsum [M], K.score [M,P]) views of one [M, C] result."""
+    def contract(self, kmat, f: Features, state, row_offset):
+        """-> (K.Sc [M,D], rowsum [M], K.score [M,P]) views of one [M, C] result.  After it ``state``
+        holds this strip's sum K*d / ties on either path."""
         if f.data[0] == "tc":
             _, planes, norms, scales, D, P, r0, M = f.data
-            out = ops.tc_matmul_raw(kmat, planes, planes.hi.shape[0], D + 1 + P, scales)
+            out = ops.tc_kf_raw(kmat, planes, D + 1 + P, scales, state, _lib.KF_EXP, True, row_offset)
             return out[:, :D], out[:, D], out[:, D + 1:D + 1 + P]
         _, v, D, P, r0, M = f.data
         out = ops.matmul_nn_raw(kmat, v)
@@ -227,14 +234,14 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
         # histogram all-reduce per pass; every rank ends with the same median and h
         hist = be.new_hist(x_local.device)
         k = (N * N - 1) // 2
-        data = k_rows
+        data = k_rows if k_rows.is_contiguous() else k_rows.contiguous()  # the select kernels take flat arrays
         if window is None:
             window = k_rows.numel() >= getattr(be, "window_min_elems", 1 << 62)
         if window:
             # one read of the strip: count the entries below a sampled window around the median and
             # compact the entries inside it; the select then runs over those candidates only
             bounds = be.select_window(feat.sc_all, state)
-            cand, totals = be.select_collect(k_rows, bounds)
+            cand, totals = be.select_collect(data, bounds)
             if world > 1:
                 dist.all_reduce(totals, op=dist.ReduceOp.SUM, group=group)
             below, kept, overflowed = (int(v) for v in totals.tolist())  # host sync; same on every rank
@@ -247,16 +254,15 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
             be.select_scan(p, state, hist)
         be.select_finish(N, bw.bw_scale, bw.tol, state)
-    kmat = be.rbf(k_rows, state, r0, feat, want_k)
+    kmat, k_out = be.rbf(k_rows, state, r0, feat, want_k)
+    ks, rowsum, kg = be.contract(kmat, feat, state, r0)  # K.Sc [M,D], row sums [M], K.score [M,P]
     stats = be.local_stats(state)
     if world > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
     be.median_coef(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad, stats)
-
-    ks, rowsum, kg = be.contract(kmat, feat)  # K.Sc [M,D], row sums [M], K.score [M,P]
     g = be.sig_grad(feat.sc_loc, feat.sc_all, ks, rowsum, state, r0)
     phi = be.sig_bwd(x_local, s_local, g, depth, kg, 1.0 / N, -1.0 / N)
-    return ShardedPhi(phi, state, k_rows if want_k else None, (r0, r0 + M))
+    return ShardedPhi(phi, state, k_out, (r0, r0 + M))
 
 
 __all__ = ["phi_sharded", "shard_range", "shard_scenes", "CudaBackend", "ShardedPhi"]

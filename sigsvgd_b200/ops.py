@@ -260,16 +260,6 @@ def tc_pack_fused_raw(s: torch.Tensor, score: Optional[torch.Tensor] = None, cen
     return Planes(fh, fl), norms, scales, sc
 
 
-def tc_sqdist_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int, scales: torch.Tensor,
-                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    M, N = a.hi.shape[0], b.hi.shape[0]
-    if out is None:
-        out = torch.empty(M, N, dtype=torch.float32, device=a.hi.device)
-    call("sigsvgd_tc_sqdist", _p(a.hi), _p(a.lo), a.ld, _p(na), _p(b.hi), _p(b.lo), b.ld, _p(nb), M, N, D, _p(scales),
-         _p(out), out.stride(0), _stream())
-    return out
-
-
 def tc_median_workspace(M: int, N: int, device) -> torch.Tensor:
     nbytes = _lib.load().sigsvgd_tc_median_workspace_bytes(M, N)
     return torch.empty(nbytes, dtype=torch.uint8, device=device)
@@ -291,6 +281,12 @@ def tc_gram_raw(a: Planes, na: torch.Tensor, b: Planes, nb: torch.Tensor, D: int
     return out
 
 
+def dist_buffer(M: int, N: int, device) -> torch.Tensor:
+    """[M, N] fp32 view whose rows are padded to whole 128-byte lines (what the TMA-fed kernels like)."""
+    ld = (N + 31) // 32 * 32
+    return torch.empty(M, ld, dtype=torch.float32, device=device)[:, :N]
+
+
 def tc_median_select_raw(ws: torch.Tensor, dist: torch.Tensor, n_log: int, bw: "Bandwidth", state: torch.Tensor,
                          symmetric: bool = False) -> None:
     """``symmetric``: dist came from ``tc_gram_raw(..., symmetric=True)`` -> only the upper triangle is read."""
@@ -299,23 +295,26 @@ def tc_median_select_raw(ws: torch.Tensor, dist: torch.Tensor, n_log: int, bw: "
          bw.tol, _p(state), _stream())
 
 
-def tc_rbf_raw(dist: torch.Tensor, state: torch.Tensor, row_offset: int = 0, want_k: bool = False):
-    """-> (K planes [M, Np]); if want_k, ``dist`` is overwritten with the fp32 kernel values."""
+def tc_kf_raw(a: torch.Tensor, f: Planes, C: int, scales: torch.Tensor, state: Optional[torch.Tensor] = None,
+              mode: int = _lib.KF_EXP, stats: bool = True, row_offset: int = 0) -> torch.Tensor:
+    """out [M, Cp] = f(a)[M, K] . F[K, :C] with the RBF map fused into the operand path (columns >= C are
+    not written).  ``a``: fp32 squared distances (``KF_EXP``) or kernel values (``KF_IDENTITY``); its row
+    pitch must be a multiple of 4 floats."""
+    M, K = a.shape
+    if a.stride(1) != 1 or a.stride(0) % 4 or a.data_ptr() % 16:
+        a = dist_buffer(M, K, a.device).copy_(a)
+    out = torch.empty(M, f.hi.shape[1], dtype=torch.float32, device=a.device)
+    call("sigsvgd_tc_kf", _p(a), a.stride(0), M, K, int(mode), _p(state), int(stats and mode == _lib.KF_EXP),
+         row_offset, _p(f.hi), _p(f.lo), f.ld, C, _p(scales), _p(out), out.stride(0), _stream())
+    return out
+
+
+def rbf_out_raw(dist: torch.Tensor, state: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K = exp(gamma * dist) as a contiguous fp32 matrix (no statistics)."""
     M, N = dist.shape
-    Np = (N + 63) // 64 * 64
-    kh = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
-    kl = torch.empty(M, Np, dtype=torch.float16, device=dist.device)
-    call("sigsvgd_tc_rbf", _p(dist), dist.stride(0), M, N, row_offset, _p(state), _p(kh), _p(kl), Np,
-         _p(dist) if want_k else None, dist.stride(0), _stream())
-    return Planes(kh, kl)
-
-
-def tc_matmul_raw(k: Planes, f: Planes, N: int, C: int, scales: torch.Tensor) -> torch.Tensor:
-    """out [M, Cp] = K[M, N] . F[N, :C] (columns >= C are not written)."""
-    M = k.hi.shape[0]
-    out = torch.empty(M, f.hi.shape[1], dtype=torch.float32, device=k.hi.device)
-    call("sigsvgd_tc_matmul", _p(k.hi), _p(k.lo), k.ld, _p(f.hi), _p(f.lo), f.ld, M, N, C, _p(scales), _p(out),
-         out.stride(0), _stream())
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=dist.device)
+    call("sigsvgd_rbf_out", _p(dist), dist.stride(0), M, N, _p(state), _p(out), out.stride(0), _stream())
     return out
 
 

@@ -109,7 +109,7 @@ class CheckerBackend:
         idx = torch.nonzero(d == float(med)) if state["median"] > 0 else torch.zeros(0, 2, dtype=torch.int64)
         state["n_ties"] = int(idx.shape[0])
         state["ties"] = [(int(i) + row_offset, int(j)) for i, j in idx[:16]]
-        return k
+        return k, (k if want_k else None)
 
     def local_stats(self, state):
         return torch.tensor([state["sum_kd"], float(state["n_ties"])], dtype=torch.float64)
@@ -119,7 +119,7 @@ class CheckerBackend:
         ok = enable and not state["clamped"] and state["median"] > 0
         state["coef"] = float(stats[0]) / (state["h"] ** 2 * state["median"]) if ok else 0.0
 
-    def contract(self, kmat, f):
+    def contract(self, kmat, f, state=None, row_offset=0):
         v, D, P, r0, M = f.data
         out = (kmat.double() @ v.double()).float()
         return out[:, P:P + D], out[:, P + D], out[:, :P]

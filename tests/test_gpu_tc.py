@@ -1,4 +1,4 @@
-"""GPU tests of the tcgen05 split-fp16 path (gemm_tc.cu / planes.cu) through the C ABI: each
+"""GPU tests of the tcgen05 split-fp16 path (gram_tc.cu / kf3_tc.cu / planes.cu) through the C ABI: each
 building block against float64 numpy, and the fused update forced onto the tensor-core path
 against the CPU oracle.  Tolerances as in tests/util.py (fp32-grade: the path must be as accurate
 as the fp32 SIMT kernels it replaces)."""
@@ -37,7 +37,7 @@ def test_tc_sqdist_vs_float64(M, N, D, scale):
     assert torch.equal(sc, allrows)
     pa = ops.Planes(planes.hi[:M], planes.lo[:M])
     pb = ops.Planes(planes.hi[M:], planes.lo[M:])
-    got = ops.tc_sqdist_raw(pa, norms[:M], pb, norms[M:], D, scales).cpu().numpy()
+    got = ops.tc_gram_raw(pa, norms[:M], pb, norms[M:], D, scales, symmetric=False).cpu().numpy()
     a64, b64 = a.astype(np.float64), b.astype(np.float64)
     ref = np.maximum((a64 ** 2).sum(1)[:, None] + (b64 ** 2).sum(1)[None] - 2 * a64 @ b64.T, 0)
     assert got.shape == ref.shape
@@ -113,8 +113,11 @@ def test_single_pass_median_falls_back_when_window_misses():
     assert np.float32(ops.read_state(state)["median"]) == np.sort(got.reshape(-1))[(N * N - 1) // 2]
 
 
-@pytest.mark.parametrize("M,N,D,P", [(128, 128, 14, 20), (130, 200, 39, 27), (512, 512, 399, 448), (300, 1000, 399, 448), (128, 4100, 399, 448)])
-def test_tc_rbf_and_matmul_vs_float64(M, N, D, P):
+@pytest.mark.parametrize("M,N,D,P", [(128, 128, 14, 20), (130, 200, 39, 27), (512, 512, 399, 448), (300, 1000, 399, 448),
+                                     (128, 4100, 399, 448), (1024, 2048, 399, 448)])
+def test_tc_kf_fused_vs_float64(M, N, D, P):
+    """K.[Sc | 1 | score] with the RBF map fused into the operand path (kf3_tc.cu): pair kernel for
+    M > 128, single-CTA kernel otherwise; exp and identity modes; sum K*d and the tie records."""
     rng = np.random.default_rng(M * 3 + N)
     s = (rng.standard_normal((N, D)) * np.exp(rng.uniform(-5, 0, size=D))).astype(np.float32)
     g = (rng.standard_normal((N, P)) * 30).astype(np.float32)
@@ -124,21 +127,35 @@ def test_tc_rbf_and_matmul_vs_float64(M, N, D, P):
     planes, norms, scales, sc = ops.tc_pack_raw(cu(s), mean, cu(g))
     state = ops.new_state(torch.device(DEV))
     _lib.call("sigsvgd_fixed_bandwidth", 1.3, state.data_ptr(), ops._stream())
-    d_dev = cu(dist)
-    kpl = ops.tc_rbf_raw(d_dev, state, want_k=True)
+    # plant a "median" so that the tie detection has something to find: two entries of the strip
+    med = np.float32(2.5)
+    dist[dist == med] = np.float32(2.25)
+    dist[M // 2, N // 3] = med
+    dist[M - 1, N - 1] = med
+    ops.state_field(state, "median").fill_(float(med))
+    d_dev = ops.dist_buffer(M, N, DEV).copy_(cu(dist))
     K64 = np.exp(-0.5 / np.float64(np.float32(1.3)) ** 2 * dist.astype(np.float64))
-    assert np.abs(d_dev.cpu().numpy() - K64).max() <= 1e-6
+    assert np.abs(ops.rbf_out_raw(d_dev, state).cpu().numpy() - K64).max() <= 1e-6
+    C = D + 1 + P
+    out = ops.tc_kf_raw(d_dev, planes, C, scales, state, _lib.KF_EXP, True, row_offset=1000).cpu().numpy()
+    assert np.array_equal(d_dev.cpu().numpy(), dist)  # the operand is read-only
     rec = ops.read_state(state)
     assert abs(rec["sum_kd"] - (K64 * dist).sum()) <= 1e-5 * (K64 * dist).sum()
-    C = D + 1 + P
-    out = ops.tc_matmul_raw(kpl, planes, N, C, scales).cpu().numpy()
+    assert rec["n_ties"] == 2 and sorted(rec["ties"]) == sorted([(1000 + M // 2, N // 3), (1000 + M - 1, N - 1)])
     sc64 = s.astype(np.float64) - mean.cpu().numpy().astype(np.float64)
-    ref = np.concatenate([K64 @ sc64, K64.sum(1, keepdims=True), K64 @ g.astype(np.float64)], axis=1)
+    F64 = np.concatenate([sc64, np.ones((N, 1)), g.astype(np.float64)], axis=1)
+    ref = K64 @ F64
     for lo, hi in ((0, D), (D, D + 1), (D + 1, C)):
         blk = ref[:, lo:hi]
         # TMEM accumulation truncates (round toward zero): the bias grows with the chain length,
-        # which tc_matmul bounds at 192 MMAs per partial sum
+        # which the kernel bounds at 192 MMAs per partial sum
         assert np.abs(out[:, lo:hi] - blk).max() <= 1e-5 * np.abs(blk).max(), (lo, hi)
+    # identity mode: the operand already holds kernel values (autograd backward with a saved K)
+    k_dev = ops.dist_buffer(M, N, DEV).copy_(cu(K64.astype(np.float32)))
+    out_i = ops.tc_kf_raw(k_dev, planes, C, scales, None, _lib.KF_IDENTITY).cpu().numpy()
+    ref_i = K64.astype(np.float32).astype(np.float64) @ F64
+    for lo, hi in ((0, D), (D, D + 1), (D + 1, C)):
+        assert np.abs(out_i[:, lo:hi] - ref_i[:, lo:hi]).max() <= 1e-5 * np.abs(ref_i[:, lo:hi]).max(), (lo, hi)
 
 
 @pytest.mark.parametrize("kind,N,T,d,depth", [("walk", 256, 64, 7, 3), ("panda", 256, 64, 7, 3), ("walk", 1000, 20, 7, 3),

@@ -38,36 +38,38 @@ mean = ops.col_mean(sig)
 res["col_mean"] = timeit(lambda: ops.col_mean(sig))
 planes, norms, scales, sc = ops.tc_pack_raw(sig, mean, G)
 res["tc_pack(+scales)"] = timeit(lambda: ops.tc_pack_raw(sig, mean, G))
-dist = torch.empty(N, N, device=dev)
-res["tc_sqdist"] = timeit(lambda: ops.tc_sqdist_raw(planes, norms, planes, norms, D, scales, out=dist))
-res["tc_sqdist_noflush"] = timeit(lambda: ops.tc_sqdist_raw(planes, norms, planes, norms, D, scales, out=dist), do_flush=False)
+dist = ops.dist_buffer(N, N, dev)
 state = ops.new_state(dev)
 ws = ops.tc_median_workspace(N, N, dev)
 ops.tc_median_prepare_raw(sc, sc, ws, state)
-res["median_prepare"] = timeit(lambda: ops.tc_median_prepare_raw(sc, sc, ws, state))
-res["tc_gram_sym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist))
-res["tc_gram_nonsym_nowin"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, False, dist))
-def _gram_win():
-    ops.tc_median_prepare_raw(sc, sc, ws, state)
-    ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist)
-res["prepare+tc_gram_sym_win"] = timeit(_gram_win)
-res["median_window_select"] = timeit(lambda: ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state))
-res["median_window_select_sym"] = timeit(lambda: ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state, True))
-state = ops.bandwidth_raw(dist, ops.Bandwidth.median(), N)
-res["median_select"] = timeit(lambda: ops.bandwidth_raw(dist, ops.Bandwidth.median(), N, state))
-d2 = dist.clone()
-kpl = ops.tc_rbf_raw(d2, state)
-res["tc_rbf"] = timeit(lambda: ops.tc_rbf_raw(d2, state))
-out = ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales)
-res["tc_matmul"] = timeit(lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales))
-res["tc_matmul_noflush"] = timeit(lambda: ops.tc_matmul_raw(kpl, planes, N, D + 1 + P, scales), do_flush=False)
+res["median_prepare"] = timeit(lambda: ops.tc_median_prepare_raw(sig, sig, ws, state))
+res["tc_gram_sym"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist))
+res["tc_gram_sym_noflush"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist), do_flush=False)
+res["tc_gram_nonsym"] = timeit(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, False, dist))
+ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, dist)
+def _sel():
+    ops.tc_median_prepare_raw(sig, sig, ws, state)
+    ops.tc_median_select_raw(ws, dist, N, ops.Bandwidth.median(), state, True)
+res["prepare+select_sym"] = timeit(_sel)
+_sel()
+print("median", ops.read_state(state)["median"], "h", ops.read_state(state)["h"], file=sys.stderr)
+out = ops.tc_kf_raw(dist, planes, D + 1 + P, scales, state)
+res["tc_kf_fused"] = timeit(lambda: ops.tc_kf_raw(dist, planes, D + 1 + P, scales, state))
+res["tc_kf_fused_noflush"] = timeit(lambda: ops.tc_kf_raw(dist, planes, D + 1 + P, scales, state), do_flush=False)
+res["tc_kf_fused_nostats"] = timeit(lambda: ops.tc_kf_raw(dist, planes, D + 1 + P, scales, state, stats=False))
+kmat = ops.rbf_out_raw(dist, state, ops.dist_buffer(N, N, dev))
+res["rbf_out"] = timeit(lambda: ops.rbf_out_raw(dist, state, kmat))
+res["tc_kf_identity"] = timeit(lambda: ops.tc_kf_raw(kmat, planes, D + 1 + P, scales, None, _lib.KF_IDENTITY))
 gs = ops.sig_grad_raw(sc, sc, out[:, :D], out[:, D], state)
 res["sig_grad"] = timeit(lambda: ops.sig_grad_raw(sc, sc, out[:, :D], out[:, D], state))
 res["sig_bwd"] = timeit(lambda: ops.signature_bwd_raw(X, sig, gs, depth, True, add=out[:, D + 1:], alpha=1.0 / N, beta=-1.0 / N))
 res["phi_total"] = timeit(lambda: ops.phi(X, G, depth=depth))
 res["phi_total_noflush"] = timeit(lambda: ops.phi(X, G, depth=depth), do_flush=False)
-res["phi_simt"] = timeit(lambda: ops.phi(X, G, depth=depth, flags=_lib.FLAG_FORCE_SIMT), n=5)
+res["phi_total_want_k"] = timeit(lambda: ops.phi(X, G, depth=depth, want_k=True))
+plan = ops.PhiPlan(N, T, d, depth, device=dev)
+plan.x.copy_(X); plan.score.copy_(G)
+res["phi_plan"] = timeit(lambda: plan())
 fl_gram, fl_kv = 2.0 * N * N * D, 2.0 * N * N * (D + P)
-res["TFLOPs_alg_sqdist"] = fl_gram / res["tc_sqdist"] / 1e6
-res["TFLOPs_alg_matmul"] = fl_kv / res["tc_matmul"] / 1e6
+res["TFLOPs_alg_gram"] = fl_gram / res["tc_gram_sym"] / 1e6
+res["TFLOPs_alg_kf"] = fl_kv / res["tc_kf_fused"] / 1e6
 print(json.dumps({"N": N, "us": res}, indent=1))

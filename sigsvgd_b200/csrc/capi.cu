@@ -111,6 +111,9 @@ static size_t bump(size_t* cur, size_t bytes) {
   return o;
 }
 
+// batches of independent scenes take the tcgen05 kernels when no tile straddles two scenes
+static bool tc_batch_shape(int64_t B, int64_t N) { return B > 1 && N >= 128 && N % 128 == 0; }
+
 static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int depth, bool want_sig,
                             bool want_k) {
   PhiLayout L;
@@ -135,11 +138,14 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   // prefix checkpoints of the time-parallel signature backward (0 floats when not applicable)
   L.off_pref = bump(&cur, sizeof(float) * sig_prefix_floats(B * N, T, d, depth));
   L.off_fh = L.off_fl = L.off_norms = L.off_scales = L.off_win = L.off_stats = 0;
+  if (B == 1 || tc_batch_shape(B, N)) {
+    L.off_fh = bump(&cur, sizeof(__half) * B * N * L.C);
+    L.off_fl = bump(&cur, sizeof(__half) * B * N * L.C);
+    L.off_norms = bump(&cur, sizeof(float) * B * N);
+    // per problem: {alpha_S, alpha_S^-2, alpha_G, 0} | 4 words of scratch ; then the colscale vectors
+    L.off_scales = bump(&cur, sizeof(float) * B * (8 + L.C));
+  }
   if (B == 1) {
-    L.off_fh = bump(&cur, sizeof(__half) * N * L.C);
-    L.off_fl = bump(&cur, sizeof(__half) * N * L.C);
-    L.off_norms = bump(&cur, sizeof(float) * N);
-    L.off_scales = bump(&cur, sizeof(float) * (8 + L.C));
     L.off_win = bump(&cur, window_workspace_bytes(N, N, nullptr));
     L.off_stats = bump(&cur, sizeof(float) * kStatSlots * (L.D + 2));
   }
@@ -147,11 +153,13 @@ static PhiLayout phi_layout(int64_t B, int64_t N, int64_t T, int64_t d, int dept
   return L;
 }
 
-// The tcgen05 path serves one swarm (B == 1) whose N^2 work dwarfs the fixed costs; small swarms
-// and batches of small scenes stay on the exact-fp32 SIMT kernels (launch-bound regime).
+// The tcgen05 path serves one swarm (B == 1) whose N^2 work dwarfs the fixed costs, and batches of
+// scenes whose particle count is a multiple of the 128-row tile (one grouped Gram / K.F launch for
+// all scenes); small swarms and odd-sized scenes stay on the exact-fp32 SIMT kernels.
 static bool tc_path_enabled(int64_t B, int64_t N, uint32_t flags) {
   if (flags & SIGSVGD_FLAG_FORCE_SIMT) return false;
-  if (B != 1 || !tc_available()) return false;
+  if (!tc_available()) return false;
+  if (B != 1) return tc_batch_shape(B, N);
   if (flags & SIGSVGD_FLAG_FORCE_TC) return true;
   return N >= 256;  // measured: 129 us (tcgen05) vs 175 us (SIMT) per update at N = 256
 }
@@ -454,7 +462,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   const bool use_tc = tc_path_enabled(B, N, flags);
   // squared distances: tcgen05 path -> workspace, pitch ldk (k_xx is a separate output); SIMT path ->
   // pitch N, turned into the kernel matrix in place, directly in k_out when the caller wants it
-  float* K = (k_out && !use_tc) ? k_out : (float*)(w + L.off_k);
+  float* K = (k_out && !(use_tc && B == 1)) ? k_out : (float*)(w + L.off_k);
   if ((flags & SIGSVGD_FLAG_FORCE_TC) && !use_tc) {
     set_error("phi: tcgen05 path not available for B=%lld N=%lld", (long long)B, (long long)N);
     return SIGSVGD_ERR_UNSUPPORTED;
@@ -466,7 +474,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
 
   // K1: signatures of all B*N particles; on the tensor-core path (depth 3) the same kernel also
   // accumulates the statistics the operand preparation needs (column sums, max |s|, max |score|)
-  const bool fwd_stats = use_tc && sig_fwd_fuses_stats(d, depth);
+  const bool fwd_stats = use_tc && B == 1 && sig_fwd_fuses_stats(d, depth);
   if (fwd_stats) {
     float* stats0 = (float*)(w + L.off_stats);
     SIG_CUDA_OK(cudaMemsetAsync(stats0, 0, sizeof(float) * kStatSlots * (D + 2), st));
@@ -479,8 +487,22 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   int64_t ldf;
   const float *out_ks, *out_rowsum, *out_kg;
   SideStream* side = nullptr;
-  const bool median_tc = use_tc && bw_mode == SIGSVGD_BW_MEDIAN;
-  if (use_tc) {
+  const bool median_tc = use_tc && B == 1 && bw_mode == SIGSVGD_BW_MEDIAN;
+  const bool tc_batch = use_tc && B > 1;
+  if (tc_batch) {
+    // grouped path: every scene is one 128-row tile row of the stacked operands
+    float* tcs = scales;
+    unsigned int* mx = (unsigned int*)(scales + 4 * B);
+    float* colscale = scales + 8 * B;
+    if (center) SIG_PROPAGATE(launch_col_mean(sig, D, N, D, part, mean, B, N * D, st));
+    SIG_PROPAGATE(launch_tc_scales(sig, D, center ? mean : nullptr, N, D, score, P, P, C, mx, tcs, colscale, B, st));
+    SIG_PROPAGATE(launch_tc_pack(score, P, P, sig, D, center ? mean : nullptr, N, D, tcs, Fh, Fl, C, C, norms, V, D,
+                                 B, st));
+    feat = V, ldf = D;
+    out_ks = out, out_rowsum = out + D, out_kg = out + D + 1;
+    SIG_PROPAGATE(tc_gram(TcPlanes{Fh, Fl, C}, TcPlanes{Fh, Fl, C}, N, N, D, norms, norms, tcs + 1, 1, K, N, st, B,
+                          4));
+  } else if (use_tc) {
     if (median_tc) {
       // K4a on the side stream: sample the distance matrix straight from the raw signatures
       // (distances are translation invariant) and set the candidate window of the median
@@ -523,7 +545,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     SIG_PROPAGATE(launch_sqdist_simt(V + P, C, V + P, C, N, N, D, K, N, B, N * C, N * C, N * N, st));
   }
   // K4: bandwidth
-  if (bw_mode == SIGSVGD_BW_MEDIAN && use_tc) {
+  if (bw_mode == SIGSVGD_BW_MEDIAN && use_tc && B == 1) {
     // K3 wrote a bit-symmetric matrix with an exact-zero diagonal: the select reads the upper
     // triangle only
     SIG_PROPAGATE(launch_window_select(w + L.off_win, K, N, N, ldk, N, bw_scale, tol, state, st, 1));
@@ -537,7 +559,14 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   // the contraction's operand path and the kernel matrix is never stored
   const int median_grad =
       (bw_mode == SIGSVGD_BW_MEDIAN) && (flags & SIGSVGD_FLAG_MEDIAN_GRAD) ? 1 : 0;
-  if (use_tc) {
+  if (tc_batch) {
+    SIG_PROPAGATE(tc_kf_fused(K, N, N, N, SIGSVGD_KF_EXP, state, /*stats=*/1, 0, TcPlanes{Fh, Fl, C}, D + 1 + P,
+                              scales + 8 * B, out, C, st, /*out_zeroed=*/false, B, C));
+    SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, B, st));
+    if (k_out)  // the distances were formed in k_out: turn them into the kernel values in place
+      for (int64_t b = 0; b < B; ++b)
+        SIG_PROPAGATE(launch_rbf_out(K + b * N * N, N, N, N, state + b, K + b * N * N, N, st));
+  } else if (use_tc) {
     // (the coefficient of the median-gradient term is derived by the signature backward itself
     // when it forms the cotangent: see SigGradSpec::coef_mode)
     if (!(B == 1 && sig_bwd_fuses_grad(d, depth)))

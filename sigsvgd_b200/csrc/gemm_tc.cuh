@@ -52,17 +52,23 @@ constexpr int kWinBins = 2048;      // histogram bins of the select kernel (top 
 // correction products, TMA-store epilogue.
 // symmetric != 0: A and B are the same planes (M == N); only tiles on or above the diagonal are
 // computed, each is stored together with its transpose, and the diagonal is exactly 0.
+// batch > 1: `batch` independent problems stacked along the rows of A, B, na, nb and dist
+// [batch*M x N] (needs M, N multiples of 128), scale record of problem b at scal + b * scal_stride.
 int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
             const float* nb, const float* scal, int symmetric, float* dist, int64_t ldd,
-            cudaStream_t st);
+            cudaStream_t st, int64_t batch = 1, int64_t scal_stride = 0);
 
 // out[i,c] = colscale[c] * sum_j f(a[i,j]) V[j,c]   (kf3_tc.cu): a = fp32 [M x K] (row pitch lda, a
 // multiple of 4; 16-byte aligned), f = exp(state->gamma * .) (SIGSVGD_KF_EXP) or the identity
 // (SIGSVGD_KF_IDENTITY); V planes [K x >=C] as for tc_matmul_nn.  stats != 0: also state->sum_kd +=
 // sum f(a) a and the entries equal to state->median are recorded (global row = row_offset + i).
+// batch > 1: `batch` independent problems stacked along the rows of a [batch*M x K], V [batch*K x C]
+// and out [batch*M x C] (needs M % 128 == 0, K % 32 == 0), state[b] and colscale + b * colscale_stride
+// per problem.
 int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sigsvgd_bw_state* state,
                 int stats, int64_t row_offset, TcPlanes V, int64_t C, const float* colscale, float* out,
-                int64_t ldo, cudaStream_t st, bool out_zeroed = false);
+                int64_t ldo, cudaStream_t st, bool out_zeroed = false, int64_t batch = 1,
+                int64_t colscale_stride = 0);
 
 // true when this process can create TMA descriptors (driver entry point resolved)
 bool tc_available();

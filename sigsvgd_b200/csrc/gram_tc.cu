@@ -37,6 +37,10 @@ struct GramParams {
   const float* na;
   const float* nb;
   const float* scal;
+  // batch of independent problems stacked along the rows of A, B and out (batch == 1: one problem);
+  // scal + b * scal_stride is the scale record of problem b
+  int batch;
+  int64_t scal_stride;
 };
 
 __device__ __forceinline__ void decode_sym(int t, int T, int& tm, int& tn) {
@@ -94,7 +98,9 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
   const uint32_t tmem_base = *tmem_slot;
 
   const int num_kb = (p.num_k16 + 3) / 4;
+  const int work_per_problem = p.num_work / p.batch;
   auto decode = [&](int w, int& tm, int& tn) {
+    w %= work_per_problem;
     if constexpr (kSym) {
       decode_sym(w, p.tiles_m, tm, tn);
     } else {
@@ -110,16 +116,18 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
       for (int w = blockIdx.x; w < p.num_work; w += gridDim.x) {
         int tm, tn;
         decode(w, tm, tn);
+        const int b = w / work_per_problem;
+        const int ra = (int)(b * p.M) + tm * GM, rb = (int)(b * p.N) + tn * GN;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
           ptx::mbar_wait(empty_bar(s), ph ^ 1u);
           const uint32_t st = sbase + s * kStageBytes;
           ptx::mbar_expect_tx(full_bar(s), kStageBytes);
-          ptx::tma_load_2d(st, &tmAh, full_bar(s), kb * GK, tm * GM);
-          ptx::tma_load_2d(st + kPlaneBytes, &tmAl, full_bar(s), kb * GK, tm * GM);
-          ptx::tma_load_2d(st + 2 * kPlaneBytes, &tmBh, full_bar(s), kb * GK, tn * GN);
-          ptx::tma_load_2d(st + 3 * kPlaneBytes, &tmBl, full_bar(s), kb * GK, tn * GN);
+          ptx::tma_load_2d(st, &tmAh, full_bar(s), kb * GK, ra);
+          ptx::tma_load_2d(st + kPlaneBytes, &tmAl, full_bar(s), kb * GK, ra);
+          ptx::tma_load_2d(st + 2 * kPlaneBytes, &tmBh, full_bar(s), kb * GK, rb);
+          ptx::tma_load_2d(st + 3 * kPlaneBytes, &tmBl, full_bar(s), kb * GK, rb);
         }
       }
     }
@@ -167,8 +175,6 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
     //  slow path (unaligned output): per-element guarded stores.
     const int q = warp & 3;
     uint32_t tcount = 0;
-    const float scal0 = __ldg(p.scal);  // alpha^-2, a power of two: scaling commutes with rounding
-    const float m2s = -2.f * scal0;
     uint8_t* const stg0 = smem + kStages * kStageBytes + q * (2 * kOutTileBytes);
     const uint32_t stg0_u = sbase + kStages * kStageBytes + q * (2 * kOutTileBytes);
     float* xp = reinterpret_cast<float*>(stg0);  // slow path: 32 x 32 transpose tile, XOR-swizzled
@@ -178,20 +184,26 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
     for (int w = blockIdx.x; w < p.num_work; w += gridDim.x, ++tcount) {
       int tm, tn;
       decode(w, tm, tn);
+      const int64_t pb = w / work_per_problem;  // problem of this tile
+      const float scal0 = __ldg(p.scal + pb * p.scal_stride);  // alpha^-2, a power of two: scaling commutes with rounding
+      const float m2s = -2.f * scal0;
+      const float* const na_b = p.na + pb * p.M;
+      const float* const nb_b = p.nb + pb * p.N;
+      float* const out_b = p.out + pb * p.M * p.ldo;
       const int a = tcount & 1;
       const uint32_t aph = (tcount >> 1) & 1u;
-      const int64_t row0 = (int64_t)tm * GM + q * 32;  // first row of this warp
+      const int64_t row0 = (int64_t)tm * GM + q * 32;  // first row of this warp (within the problem)
       const int64_t row = row0 + lane;
       const bool row_ok = row < p.M;
       const bool diag = kSym && tm == tn;
       // norms of this thread's row and of the tile's columns (lane-strided), fetched while the
       // accumulator is still being produced
-      const float rvs = row_ok ? __ldg(p.na + row) * scal0 : 0.f;
+      const float rvs = row_ok ? __ldg(na_b + row) * scal0 : 0.f;
       float cnv[GN / 32];
 #pragma unroll
       for (int k = 0; k < GN / 32; ++k) {
         const int64_t col = (int64_t)tn * GN + k * 32 + lane;
-        cnv[k] = col < p.N ? __ldg(p.nb + col) * scal0 : 0.f;
+        cnv[k] = col < p.N ? __ldg(nb_b + col) * scal0 : 0.f;
       }
       ptx::mbar_wait(tfull_bar(a), aph);
       ptx::tc_fence_after();
@@ -262,13 +274,13 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
           ptx::fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            ptx::tma_store_2d(&tmOut, stg_u, col0, (int)row0);  // clipped at the matrix edges
+            ptx::tma_store_2d(&tmOut, stg_u, col0, (int)(pb * p.M + row0));  // clipped at the matrix edges
             ptx::bulk_commit();
           }
           ++nstore;
           if (kSym && blk == 0) {
             // mirrored block: entry (row, col0 + e) -> out[col0 + e][row]; one coalesced line per e
-            float* mp = p.out + (int64_t)col0 * p.ldo + row;
+            float* mp = out_b + (int64_t)col0 * p.ldo + row;
             if (ncol == 32 && row0 + 32 <= p.M) {
 #pragma unroll
               for (int e = 0; e < 32; ++e) mp[(int64_t)e * p.ldo] = o[e];
@@ -327,7 +339,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
           if (kSym && upmask) {
 #pragma unroll
             for (int e = 0; e < 32; ++e)
-              if ((upmask >> e) & 1u) p.out[(col0 + e) * p.ldo + row] = o[e];
+              if ((upmask >> e) & 1u) out_b[(col0 + e) * p.ldo + row] = o[e];
           }
           // direct block through a 32 x 32 shared-memory transpose so that each store instruction
           // writes 32 consecutive columns of one row (a thread owns a row in TMEM)
@@ -339,7 +351,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CU
 #pragma unroll 8
           for (int r = 0; r < 32; ++r) {
             const int64_t rr = row0 + r;
-            if (rr < p.M && col_ok && (!diag || col >= rr)) p.out[rr * p.ldo + col] = xp[r * 32 + (lane ^ r)];
+            if (rr < p.M && col_ok && (!diag || col >= rr)) out_b[rr * p.ldo + col] = xp[r * 32 + (lane ^ r)];
           }
           __syncwarp();
         }
@@ -367,30 +379,36 @@ int make_tmap_f32(CUtensorMap* tm, const float* base, int64_t inner, int64_t out
 
 int tc_gram(TcPlanes A, TcPlanes B, int64_t M, int64_t N, int64_t D, const float* na,
             const float* nb, const float* scal, int symmetric, float* dist, int64_t ldd,
-            cudaStream_t st) {
+            cudaStream_t st, int64_t batch, int64_t scal_stride) {
+  SIG_CHECK_ARG(batch >= 1 && (batch == 1 || (M % GM == 0 && N % GN == 0)),
+                "tc_gram: batched problems need M and N to be multiples of 128 (M=%lld N=%lld)", (long long)M,
+                (long long)N);
   SIG_CHECK_ARG(M >= 1 && N >= 1 && D >= 1 && A.ld >= D && B.ld >= D && ldd >= N,
                 "tc_gram: bad shape M=%lld N=%lld D=%lld", (long long)M, (long long)N, (long long)D);
   SIG_CHECK_ARG(M < (1ll << 30) && N < (1ll << 30), "tc_gram: too many rows");
   SIG_CHECK_ARG(!symmetric || (M == N && A.hi == B.hi && A.lo == B.lo && na == nb),
                 "tc_gram: symmetric mode needs identical operands");
   CUtensorMap ah, al, bh, bl;
-  SIG_PROPAGATE(make_tmap_f16(&ah, A.hi, D, M, A.ld, GK, GM));
-  SIG_PROPAGATE(make_tmap_f16(&al, A.lo, D, M, A.ld, GK, GM));
-  SIG_PROPAGATE(make_tmap_f16(&bh, B.hi, D, N, B.ld, GK, GN));
-  SIG_PROPAGATE(make_tmap_f16(&bl, B.lo, D, N, B.ld, GK, GN));
+  SIG_PROPAGATE(make_tmap_f16(&ah, A.hi, D, batch * M, A.ld, GK, GM));
+  SIG_PROPAGATE(make_tmap_f16(&al, A.lo, D, batch * M, A.ld, GK, GM));
+  SIG_PROPAGATE(make_tmap_f16(&bh, B.hi, D, batch * N, B.ld, GK, GN));
+  SIG_PROPAGATE(make_tmap_f16(&bl, B.lo, D, batch * N, B.ld, GK, GN));
   GramParams p;
   p.M = M, p.N = N;
   p.num_k16 = (int)ceil_div(D, 16);
   p.tiles_m = (int)ceil_div(M, GM), p.tiles_n = (int)ceil_div(N, GN);
-  const int64_t work = symmetric ? (int64_t)p.tiles_m * (p.tiles_m + 1) / 2 : (int64_t)p.tiles_m * p.tiles_n;
+  const int64_t work =
+      batch * (symmetric ? (int64_t)p.tiles_m * (p.tiles_m + 1) / 2 : (int64_t)p.tiles_m * p.tiles_n);
   SIG_CHECK_ARG(work < (1ll << 31) && (!symmetric || p.tiles_m <= 2048), "tc_gram: too many tiles");
   p.num_work = (int)work;
   p.out = dist, p.ldo = ldd;
   p.na = na, p.nb = nb, p.scal = scal;
+  p.batch = (int)batch, p.scal_stride = scal_stride;
   // TMA-store epilogue needs a 16-byte aligned output with a 16-byte row pitch
   const bool tma_out = (reinterpret_cast<uintptr_t>(dist) & 15u) == 0 && (ldd & 3) == 0;
   CUtensorMap to = ah;  // placeholder when unused
-  if (tma_out) SIG_PROPAGATE(make_tmap_f32(&to, dist, N, M, ldd, 32, 32));
+  SIG_CHECK_ARG(batch == 1 || tma_out, "tc_gram: batched problems need a 16-byte aligned output with ldd %% 4 == 0");
+  if (tma_out) SIG_PROPAGATE(make_tmap_f32(&to, dist, N, batch * M, ldd, 32, 32));
   static thread_local int configured_dev = -1;
   int dev = 0;
   SIG_CUDA_OK(cudaGetDevice(&dev));

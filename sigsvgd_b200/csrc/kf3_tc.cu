@@ -72,6 +72,11 @@ struct FusedParams {
   int64_t ldo;
   const float* colscale;
   sigsvgd_bw_state* state;
+  // batch of independent problems stacked along the rows of every operand (batch == 1: one problem)
+  int batch;
+  int64_t a_batch_rows;    // rows of A per problem (= M)
+  int64_t v_batch_rows;    // rows of V per problem (= K)
+  int64_t colscale_stride; // floats between the colscale vectors of consecutive problems
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -139,13 +144,16 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   // work item w -> (row tile, column tile, K chunk), row tile slowest; dealt round-robin (units that
   // run side by side then walk the same K blocks in phase and L2 merges their operand requests)
-  const int num_work = p.tiles_m * p.tiles_n * p.nsplit;
+  const int work_per_problem = p.tiles_m * p.tiles_n * p.nsplit;
+  const int num_work = p.batch * work_per_problem;
   const int num_kb_total = (p.num_k16 + 1) / 2;
   struct Work {
-    int tm, tn, kb0, kb1, ncols;
+    int b, tm, tn, kb0, kb1, ncols;
   };
   auto decode = [&](int w) {
     Work k;
+    k.b = w / work_per_problem;
+    w -= k.b * work_per_problem;
     k.tm = w / (p.tiles_n * p.nsplit);
     const int rem = w - k.tm * (p.tiles_n * p.nsplit);
     k.tn = rem / p.nsplit;
@@ -165,8 +173,9 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const Work wk = decode(w);
         const int ncta_cols = kPair ? wk.ncols / 2 : wk.ncols;  // columns of B this CTA stages
         const int nbox = (ncta_cols + 63) / 64;
-        const int row = wk.tm * kRowsPerUnit + (int)rank * FM;
+        const int row = (int)(wk.b * p.a_batch_rows) + wk.tm * kRowsPerUnit + (int)rank * FM;
         const int col = wk.tn * FN + (int)rank * ncta_cols;
+        const int vrow0 = (int)(wk.b * p.v_batch_rows);
         for (int kb = wk.kb0; kb < wk.kb1; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
@@ -182,11 +191,11 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (q >= nbox) break;
             const uint32_t dh = st + kFABytes + q * (FK * 128), dl = dh + kBBytes;
             if constexpr (kPair) {
-              ptx::tma_load_2d_pair(dh, &tmBh, full_bar(s), col + q * 64, kb * FK);
-              ptx::tma_load_2d_pair(dl, &tmBl, full_bar(s), col + q * 64, kb * FK);
+              ptx::tma_load_2d_pair(dh, &tmBh, full_bar(s), col + q * 64, vrow0 + kb * FK);
+              ptx::tma_load_2d_pair(dl, &tmBl, full_bar(s), col + q * 64, vrow0 + kb * FK);
             } else {
-              ptx::tma_load_2d(dh, &tmBh, full_bar(s), col + q * 64, kb * FK);
-              ptx::tma_load_2d(dl, &tmBl, full_bar(s), col + q * 64, kb * FK);
+              ptx::tma_load_2d(dh, &tmBh, full_bar(s), col + q * 64, vrow0 + kb * FK);
+              ptx::tma_load_2d(dl, &tmBl, full_bar(s), col + q * 64, vrow0 + kb * FK);
             }
           }
         }
@@ -253,15 +262,37 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t row_off = (uint32_t)row * 128u;
     float g2 = 0.f;
     uint32_t med_bits = 0xffffffffu;  // never matches a non-negative finite distance
-    if (p.mode == SIGSVGD_KF_EXP) {
-      g2 = p.state->gamma * 1.4426950408889634f;  // log2(e)
-      if (p.stats && p.state->median > 0.f) med_bits = __float_as_uint(p.state->median);
-    }
-    double acc = 0.0;
+    int cur_b = -1;                   // problem whose bandwidth record is loaded
+    double acc = 0.0;                 // sum K*d of problem cur_b gathered by this thread
+    double* red = reinterpret_cast<double*>(smem + kStages * kStageBytes + kFBarBytes + kFXposeBytes);
+    // sum K*d of one problem, this CTA's converter threads -> one atomic (all 256 threads call it)
+    auto flush_stats = [&](int b) {
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) red[warp - kWarpConv0] = acc;
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight converter warps
+      if (ct == 0) {
+        double tot = 0.0;
+#pragma unroll
+        for (int i = 0; i < kConvWarps; ++i) tot += red[i];
+        if (tot != 0.0) atomicAdd(&p.state[b].sum_kd, tot * (1.0 / (double)kKScale));
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      acc = 0.0;
+    };
     uint32_t it = 0;
     const uint32_t leader_full0 = kPair ? ptx::mapa(full_bar(0), 0) : full_bar(0);
     for (int w = unit; w < num_work; w += nunits) {
       const Work wk = decode(w);
+      if (wk.b != cur_b) {  // CTA-uniform: every converter thread walks the same items
+        if (p.stats && cur_b >= 0) flush_stats(cur_b);
+        cur_b = wk.b;
+        if (p.mode == SIGSVGD_KF_EXP) {
+          g2 = p.state[cur_b].gamma * 1.4426950408889634f;  // log2(e)
+          med_bits = (p.stats && p.state[cur_b].median > 0.f) ? __float_as_uint(p.state[cur_b].median) : 0xffffffffu;
+        }
+      }
+      sigsvgd_bw_state* const st_b = p.state + (p.state ? cur_b : 0);
       const int64_t grow = p.row_offset + (int64_t)wk.tm * kRowsPerUnit + (int64_t)rank * FM + row;
       float part = 0.f;
       for (int kb = wk.kb0; kb < wk.kb1; ++kb, ++it) {
@@ -313,10 +344,10 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
                 if (__float_as_uint(d[e]) == med_bits) {
-                  const uint32_t slot = atomicAdd(&p.state->n_ties, 1u);
+                  const uint32_t slot = atomicAdd(&st_b->n_ties, 1u);
                   if (slot < SIGSVGD_MAX_TIES) {
-                    p.state->ties[2 * slot] = (int32_t)grow;
-                    p.state->ties[2 * slot + 1] = (int32_t)(kb * FK + 16 * half + e);
+                    st_b->ties[2 * slot] = (int32_t)grow;
+                    st_b->ties[2 * slot + 1] = (int32_t)(kb * FK + 16 * half + e);
                   }
                 }
               }
@@ -336,20 +367,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
       acc += (double)part;
     }
-    if (p.stats) {
-      // sum K*d of this CTA -> one atomic
-      double* red = reinterpret_cast<double*>(smem + kStages * kStageBytes + kFBarBytes + kFXposeBytes);
-#pragma unroll
-      for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (lane == 0) red[warp - kWarpConv0] = acc;
-      asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight converter warps
-      if (ct == 0) {
-        double tot = 0.0;
-#pragma unroll
-        for (int i = 0; i < kConvWarps; ++i) tot += red[i];
-        if (tot != 0.0) atomicAdd(&p.state->sum_kd, tot * (1.0 / (double)kKScale));
-      }
-    }
+    if (p.stats && cur_b >= 0) flush_stats(cur_b);
   } else if (warp >= kWarpEpi0 && warp < kWarpEpi0 + 4) {
     // ------------------------------------------------------------------ epilogue (own 128 rows)
     const int q = warp & 3;
@@ -365,7 +383,9 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t aph = (tcount >> 1) & 1u;
       ptx::mbar_wait(tfull_bar(a), aph);
       ptx::tc_fence_after();
-      const int64_t row0 = (int64_t)wk.tm * kRowsPerUnit + (int64_t)rank * FM + q * 32;
+      const int64_t row0 = (int64_t)wk.tm * kRowsPerUnit + (int64_t)rank * FM + q * 32;  // within the problem
+      float* const outb = p.out + (int64_t)wk.b * p.M * p.ldo;
+      const float* const csb = p.colscale + (int64_t)wk.b * p.colscale_stride;
 #pragma unroll 1
       for (int c = 0; c < FN / 32; ++c) {
         const int64_t col0 = (int64_t)wk.tn * FN + c * 32;
@@ -373,7 +393,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * FN + c * 32, v);
         const bool col_ok = col0 + lane < p.N;
-        const float cvl = col_ok ? __ldg(p.colscale + col0 + lane) : 0.f;
+        const float cvl = col_ok ? __ldg(csb + col0 + lane) : 0.f;
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; ++e) xp[lane * kFPitch + e] = __uint_as_float(v[e]);
@@ -388,7 +408,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               const int r = rr + (lane >> 3);
               if (row0 + r < p.M) {
                 const float* src = xp + r * kFPitch + cg;
-                ptx::red_add_v4(p.out + (row0 + r) * p.ldo + col0 + cg, src[0] * s0, src[1] * s1,
+                ptx::red_add_v4(outb + (row0 + r) * p.ldo + col0 + cg, src[0] * s0, src[1] * s1,
                                 src[2] * s2, src[3] * s3);
               }
             }
@@ -398,7 +418,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           for (int r = 0; r < 32; ++r) {
             if (row0 + r < p.M && col_ok) {
               const float val = xp[r * kFPitch + lane] * cvl;
-              float* dst = p.out + (row0 + r) * p.ldo + col0 + lane;
+              float* dst = outb + (row0 + r) * p.ldo + col0 + lane;
               if (accumulate_out) atomicAdd(dst, val);
               else *dst = val;
             }
@@ -469,7 +489,7 @@ int max_pairs() {
 
 int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sigsvgd_bw_state* state,
                 int stats, int64_t row_offset, TcPlanes V, int64_t C, const float* colscale, float* out,
-                int64_t ldo, cudaStream_t st, bool out_zeroed) {
+                int64_t ldo, cudaStream_t st, bool out_zeroed, int64_t batch, int64_t colscale_stride) {
   SIG_CHECK_ARG(M >= 1 && K >= 1 && C >= 1 && lda >= K && V.ld >= C && ldo >= C,
                 "tc_kf: bad shape M=%lld K=%lld C=%lld", (long long)M, (long long)K, (long long)C);
   SIG_CHECK_ARG(M < (1ll << 31) && K < (1ll << 31), "tc_kf: too many rows");
@@ -477,12 +497,17 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
   SIG_CHECK_ARG(state != nullptr || (mode == SIGSVGD_KF_IDENTITY && !stats), "tc_kf: state is NULL");
   SIG_CHECK_ARG((lda & 3) == 0 && (reinterpret_cast<uintptr_t>(a) & 15u) == 0,
                 "tc_kf: the fp32 operand must be 16-byte aligned with a row pitch that is a multiple of 4");
+  // a batch stacks the problems along the rows of a, V and out; tiles must not straddle two problems
+  SIG_CHECK_ARG(batch >= 1 && (batch == 1 || (M % FM == 0 && K % FK == 0)),
+                "tc_kf: batched problems need M %% 128 == 0 and K %% 32 == 0 (M=%lld K=%lld)", (long long)M,
+                (long long)K);
+  SIG_CHECK_ARG(batch * M < (1ll << 31) && batch * K < (1ll << 31), "tc_kf: batch too large");
   const int pairs_max = max_pairs();
-  const bool pair = M > FM && pairs_max > 0;
+  const bool pair = M > FM && pairs_max > 0 && (batch == 1 || M % (2 * FM) == 0);
   CUtensorMap ta, bh, bl;
-  SIG_PROPAGATE(make_tmap_f32(&ta, a, K, M, lda, FK, FM));  // 128-byte rows: SWIZZLE_128B
-  SIG_PROPAGATE(make_tmap_f16(&bh, V.hi, C, K, V.ld, 64, FK));
-  SIG_PROPAGATE(make_tmap_f16(&bl, V.lo, C, K, V.ld, 64, FK));
+  SIG_PROPAGATE(make_tmap_f32(&ta, a, K, batch * M, lda, FK, FM));  // 128-byte rows: SWIZZLE_128B
+  SIG_PROPAGATE(make_tmap_f16(&bh, V.hi, C, batch * K, V.ld, 64, FK));
+  SIG_PROPAGATE(make_tmap_f16(&bl, V.lo, C, batch * K, V.ld, 64, FK));
   FusedParams p;
   p.M = M, p.N = C, p.row_offset = row_offset;
   p.num_k16 = (int)ceil_div(K, 16);
@@ -493,15 +518,17 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
   // ones while there are fewer than ~6 items per unit, never below 8 K blocks
   p.kb_per_split = std::min(num_kb, kFMaxChainKb);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
-  while ((int64_t)p.tiles_m * p.tiles_n * p.nsplit < 6ll * units_max && num_kb / (2 * p.nsplit) >= 8)
+  while (batch * p.tiles_m * p.tiles_n * p.nsplit < 6ll * units_max && num_kb / (2 * p.nsplit) >= 8)
     p.nsplit *= 2;
   p.kb_per_split = (int)ceil_div(num_kb, p.nsplit);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
   p.mode = mode, p.stats = stats ? 1 : 0;
   p.out = out, p.ldo = ldo, p.colscale = colscale, p.state = state;
+  p.batch = (int)batch, p.a_batch_rows = M, p.v_batch_rows = K, p.colscale_stride = colscale_stride;
   if (p.nsplit > 1 && !out_zeroed)
-    SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, M, st));
-  const int64_t items = (int64_t)p.tiles_m * p.tiles_n * p.nsplit;
+    SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, batch * M, st));
+  const int64_t items = batch * p.tiles_m * p.tiles_n * p.nsplit;
+  SIG_CHECK_ARG(items < (1ll << 31), "tc_kf: too many work items");
   const int units = (int)std::min<int64_t>(items, units_max);
   if (!pair) {
     if (pairs_max <= 0) {  // attributes were not set by max_pairs()

@@ -391,12 +391,33 @@ def signature(path, depth, stream=False, basepoint=False, inverse=False, initial
     return _Signature.apply(path, int(depth), bool(basepoint))
 
 
+#: swarms at least this large take the tcgen05 kernels in the autograd nodes (like ``sigsvgd_phi``)
+TC_MIN_ROWS = 256
+
+
+def _use_tc(n_rows: int) -> bool:
+    return n_rows >= TC_MIN_ROWS and tc_available()
+
+
+def _square_buffer(M: int, N: int, device) -> torch.Tensor:
+    """[M, N] fp32 for distances / kernel values that the TMA-fed kernels can read: contiguous when
+    the pitch N is already a multiple of 4 floats, else a padded view."""
+    return torch.empty(M, N, dtype=torch.float32, device=device) if N % 4 == 0 else dist_buffer(M, N, device)
+
+
 class _GramCore:
-    """Shared forward/backward of the two Gram nodes, operating on fp32 feature matrices."""
+    """Shared forward/backward of the two Gram nodes, operating on fp32 feature matrices.
+
+    ``forward`` returns ``(K, fx, fy, state, extra)``: ``fx`` / ``fy`` are 2-D fp32 tensors whose first
+    D columns are the centred features of the rows / columns, ``extra`` is ``()`` on the exact-fp32
+    SIMT route and ``(f_hi, f_lo, scales, norms)`` -- the split-fp16 planes of ``[fy | 1]`` (and of
+    ``fx`` above them when the two arguments differ) with their row norms -- on the tcgen05 route."""
 
     @staticmethod
     def forward(sx, sy, same, bw: Bandwidth, center: bool):
         N, D = sx.shape
+        if _use_tc(N):
+            return _GramCore._forward_tc(sx, sy, same, bw, center)
         mean = col_mean(sx) if center else None
         vx = pack_features(sx, mean)
         vy = vx if same else pack_features(sy, mean)
@@ -404,11 +425,51 @@ class _GramCore:
         state = bandwidth_raw(K, bw, N)
         rbf_apply_raw(K, state)
         median_coef_raw(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad)
-        return K, vx, vy, state
+        return K, vx, vy, state, ()
 
     @staticmethod
-    def backward(gK, K, vx, vy, state, same, D, need_y, bw: Bandwidth):
+    def _forward_tc(sx, sy, same, bw: Bandwidth, center: bool):
+        """tcgen05 route: Gram on the tensor cores (symmetric when both arguments are the same data),
+        windowed exact median, exp in place with the statistics of the median-gradient term."""
+        N, D = sx.shape
+        dev = sx.device
+        rows = sx if same else torch.cat([sx, sy], dim=0)
+        planes, norms, scales, sc = tc_pack_fused_raw(rows, None, center)
+        if same:
+            px = py = planes
+            nx = ny = norms
+            fx = fy = sc
+        else:
+            px, py = Planes(planes.hi[:N], planes.lo[:N]), Planes(planes.hi[N:], planes.lo[N:])
+            nx, ny = norms[:N], norms[N:]
+            fx, fy = sc[:N], sc[N:]
+        K = tc_gram_raw(px, nx, py, ny, D, scales, symmetric=same, out=_square_buffer(N, N, dev))
+        state = new_state(dev)
+        if bw.mode == _lib.BW_FIXED:
+            call("sigsvgd_fixed_bandwidth", bw.h, _p(state), _stream())
+        else:
+            ws = tc_median_workspace(N, N, dev)
+            tc_median_prepare_raw(fx, fy, ws, state)
+            tc_median_select_raw(ws, K, N, bw, state, symmetric=same)
+        rbf_apply_raw(K, state)  # in place; accumulates sum K*d and the tie records
+        median_coef_raw(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad)
+        return K, fx, fy, state, (planes.hi, planes.lo, scales, norms)
+
+    @staticmethod
+    def _contract(A, fy_planes: "Planes", scales, D):
+        """[A . fy | rowsum(A)] on the tensor cores; A holds kernel values (identity operand map)."""
+        out = tc_kf_raw(A, fy_planes, D + 1, scales, None, _lib.KF_IDENTITY)
+        return out[:, :D], out[:, D]
+
+    @staticmethod
+    def backward(gK, K, vx, vy, state, same, D, need_y, bw: Bandwidth, extra=()):
         """Returns (g_x [N,D], g_y [N,D] or None): gradients wrt the feature matrices."""
+        tc = len(extra) == 4
+        N = K.shape[0]
+        if tc:
+            f_hi, f_lo, scales, norms = extra
+            px = Planes(f_hi[:N], f_lo[:N])
+            py = px if same else Planes(f_hi[N:], f_lo[N:])
         if _is_uniform_cotangent(gK):
             scale = gK[(0,) * gK.dim()].reshape(1).to(torch.float32)  # device scalar, applied at the end
             A, st = K, state
@@ -416,21 +477,34 @@ class _GramCore:
             # generic cotangent W: weighted kernel A = W o K with its own statistics
             W = _prep(gK, "gram.backward")
             scale = None
-            A = sqdist_raw(vx, vy, D)
+            if tc:
+                # distances again from the planes (the forward's matrix now holds K)
+                A = tc_gram_raw(px, norms[:N], py, norms[:N] if same else norms[N:], D, scales, symmetric=False,
+                                out=_square_buffer(N, py.hi.shape[0], K.device))
+            else:
+                A = sqdist_raw(vx, vy, D)
             st = state.clone()
             st[:, 4:8] = 0  # sum_kd, n_ties, n_ties_all
             rbf_apply_raw(A, st, weight=W)
             median_coef_raw(st, bw.mode == _lib.BW_MEDIAN and bw.median_grad)
-        out = matmul_nn_raw(A, vy)
-        gx = sig_grad_raw(vx, vy, out[:, :D], out[:, D], st)
+        if tc:
+            ks, rowsum = _GramCore._contract(A, py, scales, D)
+        else:
+            out = matmul_nn_raw(A, vy)
+            ks, rowsum = out[:, :D], out[:, D]
+        gx = sig_grad_raw(vx, vy, ks, rowsum, st)
         gy = None
         if need_y:
             if same and scale is not None:
-                gy = gx  # K and the tie set are bit-symmetric (see gemm_simt.cu), so g^Y == g^X
+                gy = gx  # K and the tie set are bit-symmetric (see gemm_simt.cu / gram_tc.cu), so g^Y == g^X
             else:
                 At = A.t().contiguous()
-                out_t = matmul_nn_raw(At, vx)
-                gy = sig_grad_raw(vy, vx, out_t[:, :D], out_t[:, D], _swap_ties(st))
+                if tc:
+                    ks_t, rowsum_t = _GramCore._contract(At, px, scales, D)
+                else:
+                    out_t = matmul_nn_raw(At, vx)
+                    ks_t, rowsum_t = out_t[:, :D], out_t[:, D]
+                gy = sig_grad_raw(vy, vx, ks_t, rowsum_t, _swap_ties(st))
         if scale is not None:
             gx = gx * scale
             gy = None if gy is None else (gx if gy is gx else gy * scale)
@@ -447,8 +521,8 @@ class _SigRBFGram(torch.autograd.Function):
         y = x if same else _prep(Y, "PathSigKernel")
         sx, px = _sig_fwd_saving(x, depth, True)
         sy, py = (sx, px) if same else _sig_fwd_saving(y, depth, True)
-        K, vx, vy, state = _GramCore.forward(sx, sy, same, bw, center)
-        ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state, px, py)
+        K, vx, vy, state, extra = _GramCore.forward(sx, sy, same, bw, center)
+        ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state, px, py, *extra)
         ctx.meta = (depth, bw, same, X.dtype)
         ctx.set_materialize_grads(False)
         ctx.bw_state = state
@@ -458,11 +532,11 @@ class _SigRBFGram(torch.autograd.Function):
     def backward(ctx, gK):
         if gK is None:
             return None, None, None, None, None
-        x, y, sx, sy, vx, vy, K, state, px, py = ctx.saved_tensors
+        x, y, sx, sy, vx, vy, K, state, px, py, *extra = ctx.saved_tensors
         depth, bw, same, in_dtype = ctx.meta
         need_x, need_y = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         D = sx.shape[1]
-        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, need_y, bw)
+        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, need_y, bw, tuple(extra))
         gX = _sig_bwd_saved(x, sx, px, gsx, depth, True).to(in_dtype) if need_x else None
         gY = None
         if need_y:
@@ -481,8 +555,8 @@ class _RBFGram(torch.autograd.Function):
         same = _same_data(X, Y)
         sx = _prep(X, "GaussianKernel")
         sy = sx if same else _prep(Y, "GaussianKernel")
-        K, vx, vy, state = _GramCore.forward(sx, sy, same, bw, center)
-        ctx.save_for_backward(vx, vy, K, state)
+        K, vx, vy, state, extra = _GramCore.forward(sx, sy, same, bw, center)
+        ctx.save_for_backward(vx, vy, K, state, *extra)
         ctx.meta = (bw, same, X.dtype, sx.shape[1])
         ctx.set_materialize_grads(False)
         ctx.bw_state = state
@@ -492,9 +566,9 @@ class _RBFGram(torch.autograd.Function):
     def backward(ctx, gK):
         if gK is None:
             return None, None, None, None
-        vx, vy, K, state = ctx.saved_tensors
+        vx, vy, K, state, *extra = ctx.saved_tensors
         bw, same, in_dtype, D = ctx.meta
-        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, ctx.needs_input_grad[1], bw)
+        gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, ctx.needs_input_grad[1], bw, tuple(extra))
         gX = gsx.to(in_dtype) if ctx.needs_input_grad[0] else None
         gY = gsy.to(in_dtype) if (ctx.needs_input_grad[1] and gsy is not None) else None
         return gX, gY, None, None
@@ -521,9 +595,15 @@ def rbf_gram_with_grad(X, Y, bandwidth: Optional[Bandwidth] = None, center: bool
     sy = sx if same else _prep(Y, "GaussianKernel")
     D = sx.shape[1]
     bw_nograd = Bandwidth(bw.mode, bw.h, bw.bw_scale, bw.tol, False)
-    K, vx, vy, state = _GramCore.forward(sx, sy, same, bw_nograd, center)
-    out = matmul_nn_raw(K, vy)
-    dK = sig_grad_raw(vx, vy, out[:, :D], out[:, D], state)
+    K, vx, vy, state, extra = _GramCore.forward(sx, sy, same, bw_nograd, center)
+    if len(extra) == 4:
+        N = K.shape[0]
+        py = Planes(extra[0][:N], extra[1][:N]) if same else Planes(extra[0][N:], extra[1][N:])
+        ks, rowsum = _GramCore._contract(K, py, extra[2], D)
+    else:
+        out = matmul_nn_raw(K, vy)
+        ks, rowsum = out[:, :D], out[:, D]
+    dK = sig_grad_raw(vx, vy, ks, rowsum, state)
     return K.to(X.dtype), dK.to(X.dtype), state
 
 

@@ -23,6 +23,19 @@ def cu(a):
     return torch.as_tensor(np.ascontiguousarray(a), device=DEV)
 
 
+def _kernel_names(fn):
+    """Names of the CUDA kernels `fn` launches (torch profiler / CUPTI); None if unavailable."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        return [e.key for e in prof.key_averages()]
+    except Exception:
+        return None
+
+
 # ---------------------------------------------------------------------------------------------
 # K1 / K2 signature forward + VJP
 # ---------------------------------------------------------------------------------------------
@@ -276,7 +289,7 @@ def test_phi_median_grad_off_and_linearity():
 
 
 def test_phi_batched_matches_loop():
-    B, N, T, d = 5, 128, 16, 7
+    B, N, T, d = 5, 96, 16, 7  # N not a multiple of 128: exact-fp32 SIMT kernels, batched in the grid
     X = np.stack([make_paths("walk", N, T, d, seed=10 + b) for b in range(B)])
     G = np.random.default_rng(7).standard_normal((B, N, T * d)).astype(np.float32)
     res = ops.phi(cu(X), cu(G), want_k=True)
@@ -285,6 +298,30 @@ def test_phi_batched_matches_loop():
         assert torch.equal(one.phi, res.phi[b])
         assert torch.equal(one.k_xx, res.k_xx[b])
         assert ops.read_state(one.state)["median"] == ops.read_state(res.state, b)["median"]
+
+
+@pytest.mark.parametrize("B,N,T,d", [(6, 128, 64, 7), (3, 256, 20, 7), (9, 128, 10, 2)])
+def test_phi_batched_scenes_on_tensor_cores(B, N, T, d):
+    """Independent scenes whose particle count is a multiple of the 128-row tile run as ONE grouped
+    tcgen05 Gram / K.F launch (BASELINE.json configs[4]); every scene keeps its own median."""
+    X = np.stack([make_paths("walk", N, T, d, seed=40 + b) * (1.0 + 0.3 * b) for b in range(B)])
+    G = np.random.default_rng(8).standard_normal((B, N, T * d)).astype(np.float32)
+    res = ops.phi(cu(X), cu(G), want_k=True, want_grad_k=True)
+    names = _kernel_names(lambda: ops.phi(cu(X), cu(G)))
+    if names is not None and len(names):
+        assert any("gram_kernel" in n for n in names) and any("kf_fused_kernel" in n for n in names), names
+    nok = ops.phi(cu(X), cu(G))  # k_xx not requested: same phi
+    assert rel_max(nok.phi.cpu().numpy(), res.phi.cpu().numpy()) <= 1e-6
+    simt = ops.phi(cu(X), cu(G), want_k=True, flags=_lib.FLAG_FORCE_SIMT)
+    for b in range(B):
+        rec = ops.read_state(res.state, b)
+        cf = closed_form_with_ties(X[b].astype(np.float64), G[b].astype(np.float64), 3, rec["ties"])
+        assert abs(rec["h"] - cf["h"]) <= TOL_H * cf["h"]
+        assert np.abs(res.k_xx[b].cpu().numpy() - cf["K"]).max() <= TOL_K
+        assert rel_max(res.grad_k[b].cpu().numpy(), cf["grad_k"]) <= TOL_PHI
+        assert rel_max(res.phi[b].cpu().numpy(), cf["phi"]) <= TOL_PHI
+        assert float((simt.k_xx[b] - res.k_xx[b]).abs().max()) <= 2e-5
+        assert ops.read_state(simt.state, b)["h"] == pytest.approx(rec["h"], rel=1e-6)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -332,6 +369,83 @@ def test_pathsig_kernel_two_sample_and_generic_cotangent():
     assert np.abs(K.detach().cpu().numpy() - Kc.detach().numpy()).max() <= TOL_K
     assert rel_max(gX.cpu().numpy(), gXc.numpy()) <= TOL_PHI
     assert rel_max(gY.cpu().numpy(), gYc.numpy()) <= TOL_PHI
+
+
+@pytest.mark.parametrize("N", [1024, 4096])
+def test_reference_autograd_statements_run_on_tensor_cores(N):
+    """The literal drop-in -- the reference's own statements at svgd.py:41-43 / score.py:54-55 --
+    reaches the tcgen05 Gram and K.F kernels and agrees with the fused update."""
+    X = cu(make_paths("walk", N, 64, 7, seed=21))
+    G = cu(np.random.default_rng(22).standard_normal((N, 448)).astype(np.float32))
+    kernel = PathSigKernel()
+    out = {}
+
+    def statements():
+        Xr = X.detach().requires_grad_(True)
+        k_xx = kernel(Xr, Xr.detach(), compute_grad=False)
+        out["k_xx"], out["grad_k"] = k_xx.detach(), torch.autograd.grad(k_xx.sum(), Xr)[0].flatten(1)
+
+    statements()
+    names = _kernel_names(statements)
+    if names is not None and len(names):
+        assert any("gram_kernel" in n for n in names), names
+        assert any("kf_fused_kernel" in n for n in names), names
+        assert not any("sqdist_nt_kernel" in n or "gemm_nn_kernel" in n for n in names), names
+    fused = ops.phi(X, G, want_k=True, want_grad_k=True)
+    rf, ra = ops.read_state(fused.state), None
+    assert float((out["k_xx"] - fused.k_xx).abs().max()) <= 2e-6
+    # same median / h; the tie pair is the same because both routes select on the same Gram matrix
+    assert rel_max(out["grad_k"].cpu().numpy(), fused.grad_k.cpu().numpy()) <= 1e-5
+    # velocity = (k_xx @ score - grad_k) / N as the reference forms it (svgd.py:82), vs phi
+    vel = (out["k_xx"].double() @ G.double() - out["grad_k"].double()) / N
+    assert rel_max(vel.cpu().numpy(), fused.phi.reshape(N, -1).cpu().numpy()) <= 1e-5
+    # both arguments carry grad (script_planning_robot.py:107): twice the one-sided gradient
+    Xb = X.detach().requires_grad_(True)
+    g2 = torch.autograd.grad(kernel(Xb, Xb, compute_grad=False).sum(), Xb)[0].flatten(1)
+    assert rel_max(g2.cpu().numpy(), 2 * fused.grad_k.cpu().numpy()) <= 1e-5
+    if N <= 1024:  # float64 closed form with the reported tie pair(s)
+        cf = closed_form_with_ties(X.cpu().numpy().astype(np.float64), G.cpu().numpy().astype(np.float64), 3, rf["ties"])
+        assert np.abs(out["k_xx"].cpu().numpy() - cf["K"]).max() <= TOL_K
+        assert rel_max(out["grad_k"].cpu().numpy(), cf["grad_k"]) <= TOL_PHI
+
+
+def test_two_sample_and_generic_cotangent_on_tensor_cores():
+    N = 300  # >= ops.TC_MIN_ROWS: tcgen05 route, non-symmetric Gram, weighted kernel in the backward
+    X = cu(make_paths("walk", N, 12, 3, seed=8)).requires_grad_(True)
+    Y = cu(make_paths("walk", N, 12, 3, seed=9)).requires_grad_(True)
+    W = torch.rand(N, N, device=DEV)
+    K = PathSigKernel()(X, Y, compute_grad=False)
+    gX, gY = torch.autograd.grad((K * W).sum(), (X, Y), retain_graph=True)
+    Xc, Yc = X.detach().cpu().double().requires_grad_(True), Y.detach().cpu().double().requires_grad_(True)
+    sx, sy = oracle.signature_torch(Xc, 3, basepoint=True), oracle.signature_torch(Yc, 3, basepoint=True)
+    sq = ((sx[:, None] - sy[None]) ** 2).sum(-1)
+    h = torch.sqrt(torch.median(sq) / torch.tensor(N + 1.0).log())
+    Kc = torch.exp(-0.5 / h ** 2 * sq)
+    gXc, gYc = torch.autograd.grad((Kc * W.cpu().double()).sum(), (Xc, Yc), retain_graph=True)
+    assert np.abs(K.detach().cpu().numpy() - Kc.detach().numpy()).max() <= TOL_K
+    assert rel_max(gX.cpu().numpy(), gXc.numpy()) <= TOL_PHI
+    assert rel_max(gY.cpu().numpy(), gYc.numpy()) <= TOL_PHI
+    # uniform cotangent, gradient wrt both (distinct) arguments
+    gX1, gY1 = torch.autograd.grad(K.sum(), (X, Y))
+    gX1c, gY1c = torch.autograd.grad(Kc.sum(), (Xc, Yc))
+    assert rel_max(gX1.cpu().numpy(), gX1c.numpy()) <= TOL_PHI
+    assert rel_max(gY1.cpu().numpy(), gY1c.numpy()) <= TOL_PHI
+
+
+def test_gaussian_kernel_large_on_tensor_cores():
+    rng = np.random.default_rng(5)
+    A = (rng.standard_normal((512, 40)) * np.exp(rng.uniform(-3, 0, 40))).astype(np.float32)
+    B = (rng.standard_normal((512, 40)) * np.exp(rng.uniform(-3, 0, 40))).astype(np.float32)
+    K, dK = GaussianKernel()(cu(A), cu(B))
+    A64, B64 = A.astype(np.float64), B.astype(np.float64)
+    Kr, sq, h, med = oracle.gaussian_gram(A64, B64, None, 1.0)
+    dKr = -(A64 * Kr.sum(1, keepdims=True) - Kr @ B64) / h ** 2  # _kernels.py:112-113, constant h
+    assert np.abs(K.cpu().numpy() - Kr).max() <= TOL_K
+    assert rel_max(dK.cpu().numpy(), dKr) <= TOL_PHI
+    a_dev = cu(A)
+    Ks, dKs = GaussianKernel()(a_dev, a_dev)  # same data: symmetric Gram, exact-zero diagonal distances
+    Krs, _, hs, _ = oracle.gaussian_gram(A64, A64, None, 1.0)
+    assert np.abs(Ks.cpu().numpy() - Krs).max() <= TOL_K and float(Ks.diagonal().min()) == 1.0
 
 
 def test_svgd_mirror_velocity_and_optimize_vs_reference_golden():

@@ -31,7 +31,14 @@ extern "C" {
 #define SIGSVGD_ERR_WORKSPACE 3   /* workspace too small                         */
 #define SIGSVGD_ERR_CUDA 4        /* CUDA runtime error (launch / attribute)     */
 
-#define SIGSVGD_MAX_TIES 16
+/* Entries equal to the median that are RECORDED (the support of torch.median's backward).  A generic
+ * swarm has 2 (the symmetric pair); duplicated / lattice-placed particles can have more.  If more than
+ * SIGSVGD_MAX_TIES entries tie, n_ties / n_ties_all still hold the true count, every recorded entry
+ * keeps the reference's weight coef / n_ties_all, and the entries beyond the cap (which ones is
+ * unspecified) get no median-gradient term: a documented truncation of a term that is itself an
+ * artefact of differentiating through the median; callers detect it by
+ * n_ties_all > SIGSVGD_MAX_TIES. */
+#define SIGSVGD_MAX_TIES 64
 
 /* bandwidth modes (src/kernels/_kernels.py:106-109: h = get_bandwidth(sq_dists) | float(h)) */
 #define SIGSVGD_BW_MEDIAN 0 /* src/utils/math.py:28-34 bw_median                        */

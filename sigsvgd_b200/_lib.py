@@ -13,7 +13,7 @@ from ctypes import c_double, c_float, c_int, c_int64, c_size_t, c_uint32, c_uint
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsigsvgd_b200.so")
 
-MAX_TIES = 16
+MAX_TIES = 64
 BW_MEDIAN, BW_FIXED = 0, 1
 FLAG_MEDIAN_GRAD, FLAG_NO_CENTER, FLAG_FORCE_SIMT, FLAG_FORCE_TC = 1, 2, 4, 8
 KF_EXP, KF_IDENTITY = 0, 1
@@ -38,7 +38,7 @@ class BwState(ctypes.Structure):
 
 
 STATE_BYTES = ctypes.sizeof(BwState)
-assert STATE_BYTES == 176, STATE_BYTES
+assert STATE_BYTES == 48 + 8 * MAX_TIES, STATE_BYTES
 # byte offsets used by the host code to address fields of a device copy
 OFF_MEDIAN, OFF_H, OFF_GAMMA, OFF_COEF, OFF_SUM_KD, OFF_N_TIES, OFF_N_TIES_ALL, OFF_CLAMPED = 0, 4, 8, 12, 16, 24, 28, 32
 OFF_TIES = BwState.ties.offset

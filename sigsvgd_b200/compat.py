@@ -10,22 +10,32 @@ CUDA library, so the reference's UNMODIFIED files run on the new kernels:
   the north-star kernel -- truncated signature + RBF with the median heuristic -- as an autograd
   node; the Goursat-PDE kernel of the real package is SURVEY.md 8(f)-1 ("next").
 
-``install()`` registers both in ``sys.modules`` (only if the real packages are absent, unless
-``force=True``).
+``install()`` registers ``signatory`` in ``sys.modules`` (only if the real package is absent, unless
+``force=True``).  The ``sigkernel`` stand-in computes a DIFFERENT kernel from the package whose name it
+takes (truncated signature + RBF, not the Goursat-PDE signature kernel), so it is registered only on
+request -- ``install(sigkernel_truncated=True)`` -- and says so with a warning.
 """
 from __future__ import annotations
 
 import sys
 import types
+import warnings
 
 import torch
 
 from . import ops
 
 
+_SUBSTITUTION = ("sigsvgd_b200.compat.SigKernel is NOT the Goursat-PDE signature kernel of the `sigkernel` package: "
+                 "compute_Gram returns exp(-|S(x) - S(y)|^2 / (2 h^2)) on depth-%d truncated signatures, h from the median "
+                 "heuristic (RBFKernel(sigma, fixed=True): h = sigma).  `dyadic_order` has no meaning here.")
+
+
 class RBFKernel:
-    """``sigkernel.RBFKernel(sigma)``; sigma is kept for API compatibility.  The truncated-signature
-    adapter uses the median heuristic on signature features unless ``fixed=True``."""
+    """``sigkernel.RBFKernel(sigma)`` shaped.  In the real package sigma is the width of a static kernel
+    between path POINTS; the truncated-signature adapter has no such kernel, so sigma is only used
+    when the caller opts in with ``fixed=True`` (then it is the bandwidth h on signature features);
+    otherwise the bandwidth is the median heuristic, as in the reference's ``PathSigKernel``."""
 
     def __init__(self, sigma: float = 1.0, fixed: bool = False):
         self.sigma = float(sigma)
@@ -35,10 +45,15 @@ class RBFKernel:
 class SigKernel:
     """``sigkernel.SigKernel(static_kernel, dyadic_order)`` shaped adapter."""
 
+    _warned = False
+
     def __init__(self, static_kernel=None, dyadic_order: int = 0, depth: int = 3):
         self.static_kernel = static_kernel
         self.dyadic_order = dyadic_order
         self.depth = int(depth)
+        if not SigKernel._warned:
+            SigKernel._warned = True
+            warnings.warn(_SUBSTITUTION % self.depth, stacklevel=2)
 
     def _bandwidth(self):
         sk = self.static_kernel
@@ -64,13 +79,17 @@ def signature_channels(channels: int, depth: int, scalar_term: bool = False) -> 
     return ops.sig_channels(channels, depth) + (1 if scalar_term else 0)
 
 
-def install(force: bool = False) -> dict:
-    """Register ``signatory`` / ``sigkernel`` stand-ins.  Returns {name: module} of what was set."""
+def install(force: bool = False, sigkernel_truncated: bool = False) -> dict:
+    """Register the ``signatory`` stand-in and, only with ``sigkernel_truncated=True``, a module named
+    ``sigkernel`` whose ``SigKernel`` is the truncated-signature RBF kernel (see the module docstring).
+    Returns {name: module} of what was set."""
     done = {}
-    for name, attrs in (
-        ("signatory", dict(signature=signature, signature_channels=signature_channels, __version__="sigsvgd_b200")),
-        ("sigkernel", dict(SigKernel=SigKernel, RBFKernel=RBFKernel, __version__="sigsvgd_b200")),
-    ):
+    wanted = [("signatory", dict(signature=signature, signature_channels=signature_channels, __version__="sigsvgd_b200"))]
+    if sigkernel_truncated:
+        warnings.warn("registering a module named `sigkernel`: " + _SUBSTITUTION % 3, stacklevel=2)
+        wanted.append(("sigkernel", dict(SigKernel=SigKernel, RBFKernel=RBFKernel, __version__="sigsvgd_b200-truncated",
+                                         __doc__=_SUBSTITUTION % 3)))
+    for name, attrs in wanted:
         if not force:
             try:
                 __import__(name)

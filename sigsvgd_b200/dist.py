@@ -128,20 +128,20 @@ class CudaBackend:
         return torch.zeros(2048, dtype=torch.int64, device=device)
 
     def fixed_bandwidth(self, h, state):
-        _lib.call("sigsvgd_fixed_bandwidth", float(h), state.data_ptr(), ops._stream())
+        ops.call("sigsvgd_fixed_bandwidth", float(h), ops._p(state), ops._stream())
 
     def select_begin(self, state, hist, k):
-        _lib.call("sigsvgd_select_begin", state.data_ptr(), hist.data_ptr(), int(k), ops._stream())
+        ops.call("sigsvgd_select_begin", ops._p(state), ops._p(hist), int(k), ops._stream())
 
     def select_hist(self, dist_loc, p, state, hist):
-        _lib.call("sigsvgd_select_hist", dist_loc.data_ptr(), dist_loc.numel(), p, state.data_ptr(), hist.data_ptr(),
+        ops.call("sigsvgd_select_hist", ops._p(dist_loc), dist_loc.numel(), p, ops._p(state), ops._p(hist),
                   ops._stream())
 
     def select_scan(self, p, state, hist):
-        _lib.call("sigsvgd_select_scan", p, state.data_ptr(), hist.data_ptr(), ops._stream())
+        ops.call("sigsvgd_select_scan", p, ops._p(state), ops._p(hist), ops._stream())
 
     def select_finish(self, n_log, bw_scale, tol, state):
-        _lib.call("sigsvgd_select_finish", n_log, float(bw_scale), float(tol), state.data_ptr(), ops._stream())
+        ops.call("sigsvgd_select_finish", n_log, float(bw_scale), float(tol), ops._p(state), ops._stream())
 
     # windowed first pass of the sharded median (one read of the strip instead of three)
     window_min_elems = 1 << 24  # strips smaller than this take the plain three passes
@@ -151,8 +151,8 @@ class CudaBackend:
         lib = _lib.load()
         nbytes = lib.sigsvgd_select_window_workspace_bytes()
         ws = torch.empty(nbytes, dtype=torch.uint8, device=sc_all.device)
-        _lib.call("sigsvgd_select_window", sc_all.data_ptr(), sc_all.stride(0), sc_all.shape[0], sc_all.shape[1],
-                  ws.data_ptr(), nbytes, state.data_ptr(), ops._stream())
+        ops.call("sigsvgd_select_window", ops._p(sc_all), sc_all.stride(0), sc_all.shape[0], sc_all.shape[1],
+                  ops._p(ws), nbytes, ops._p(state), ops._stream())
         return ws[:8].view(torch.float32)
 
     def select_collect(self, dist_loc, bounds):
@@ -161,8 +161,8 @@ class CudaBackend:
         cap = max(int(lib.sigsvgd_select_collect_min_capacity()) * 64, dist_loc.numel() // 8)
         cand = torch.empty(cap, dtype=torch.float32, device=dist_loc.device)
         totals = torch.empty(3, dtype=torch.int64, device=dist_loc.device)
-        _lib.call("sigsvgd_select_collect", dist_loc.data_ptr(), dist_loc.numel(), bounds.data_ptr(), cand.data_ptr(),
-                  cap, totals.data_ptr(), ops._stream())
+        ops.call("sigsvgd_select_collect", ops._p(dist_loc), dist_loc.numel(), ops._p(bounds), ops._p(cand),
+                  cap, ops._p(totals), ops._stream())
         return cand, totals
 
     def local_stats(self, state):

@@ -15,24 +15,57 @@ result is cast back.  No CPU path exists: CPU tensors raise.
 from __future__ import annotations
 
 import math
+import threading
 from dataclasses import dataclass
 from typing import Optional
 
 import torch
 
 from . import _lib
-from ._lib import call
 
 
 # ---------------------------------------------------------------------------------------------
 # helpers
 # ---------------------------------------------------------------------------------------------
+# The C library launches on the CURRENT device and takes the stream as an argument, while the
+# reference's only multi-GPU idiom is ``device=f"cuda:{i}"`` with no ``set_device`` anywhere
+# (examples/script_planning_robot.py:486).  So every C call here runs with the device of its tensor
+# arguments made current and on that device's current stream: ``_p`` notes the device of each pointer
+# it hands out, ``_stream`` (always the last argument) and ``call`` use it.  Tensors on two different
+# devices in one call raise.
+_pending = threading.local()
+
+
+def _note_device(dev) -> None:
+    cur = getattr(_pending, "device", None)
+    if cur is None:
+        _pending.device = dev
+    elif cur != dev:
+        _pending.device = None
+        raise RuntimeError(f"sigsvgd_b200: tensors of one call live on different devices ({cur} and {dev})")
+
+
 def _p(t: Optional[torch.Tensor]):
-    return None if t is None else t.data_ptr()
+    if t is None:
+        return None
+    if t.is_cuda:
+        _note_device(t.device)
+    return t.data_ptr()
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    dev = getattr(_pending, "device", None)
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def call(name: str, *args) -> None:
+    dev = getattr(_pending, "device", None)
+    _pending.device = None
+    if dev is None or dev.index == torch.cuda.current_device():
+        _lib.call(name, *args)
+    else:
+        with torch.cuda.device(dev):
+            _lib.call(name, *args)
 
 
 def _prep(t: torch.Tensor, what: str) -> torch.Tensor:

@@ -108,7 +108,7 @@ class CheckerBackend:
         state["sum_kd"] = float((k.double() * d.double()).sum())
         idx = torch.nonzero(d == float(med)) if state["median"] > 0 else torch.zeros(0, 2, dtype=torch.int64)
         state["n_ties"] = int(idx.shape[0])
-        state["ties"] = [(int(i) + row_offset, int(j)) for i, j in idx[:16]]
+        state["ties"] = [(int(i) + row_offset, int(j)) for i, j in idx[:64]]
         return k, (k if want_k else None)
 
     def local_stats(self, state):

@@ -45,8 +45,8 @@ def test_header_cites_reference_for_every_group():
 
 def test_state_struct_layout_matches_header():
     text = open(HEADER).read()
-    assert "#define SIGSVGD_MAX_TIES 16" in text
-    assert _lib.STATE_BYTES == 176 and _lib.OFF_SUM_KD == 16 and _lib.OFF_TIES == 48
+    assert f"#define SIGSVGD_MAX_TIES {_lib.MAX_TIES}" in text and _lib.MAX_TIES == 64
+    assert _lib.STATE_BYTES == 48 + 8 * _lib.MAX_TIES and _lib.OFF_SUM_KD == 16 and _lib.OFF_TIES == 48
 
 
 def test_channels_and_version(lib):
@@ -115,7 +115,10 @@ def test_kernel_classes_keep_reference_conventions():
 
 def test_cpu_tensors_are_refused_not_emulated():
     from sigsvgd_b200 import ops
-    from sigsvgd_b200.inference import SVGD
+    from sigsvgd_b200.inference import make_fused
+    from tests import ref_mirror
+
+    SVGD = make_fused(ref_mirror.SVGD)
     from sigsvgd_b200.kernels import PathSigKernel
 
     X, G = torch.zeros(4, 5, 2), torch.zeros(4, 10)
@@ -133,7 +136,8 @@ def test_cpu_tensors_are_refused_not_emulated():
 
 def test_bandwidth_spec_and_fused_dispatch():
     from sigsvgd_b200 import ops
-    from sigsvgd_b200.inference import FixedBandwidth, ScoreEstimator, _fused_spec
+    from sigsvgd_b200.inference import FixedBandwidth, _fused_spec
+    from tests.ref_mirror import ScoreEstimator
     from sigsvgd_b200.kernels import GaussianKernel, PathSigKernel
 
     assert _fused_spec(PathSigKernel()).mode == _lib.BW_MEDIAN
@@ -157,7 +161,9 @@ def test_compat_install_registers_stand_ins():
 
     saved = {k: sys.modules.get(k) for k in ("signatory", "sigkernel")}
     try:
-        done = compat.install(force=True)
+        assert set(compat.install(force=True)) == {"signatory"}  # `sigkernel` is opt-in: different mathematics
+        with pytest.warns(UserWarning, match="NOT the Goursat-PDE"):
+            done = compat.install(force=True, sigkernel_truncated=True)
         assert set(done) == {"signatory", "sigkernel"}
         import signatory
         import sigkernel

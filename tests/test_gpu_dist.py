@@ -161,3 +161,26 @@ def test_world2_nccl(tc, N):
     recs = [g[3] for g in got]
     assert recs[0]["median"] == recs[1]["median"] and recs[0]["h"] == recs[1]["h"]
     _check(X, G, depth, np.concatenate([g[1] for g in got]), np.concatenate([g[2] for g in got]), recs)
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_calls_follow_the_device_of_their_tensors():
+    """The reference's multi-GPU idiom is ``device=f"cuda:{i}"`` with no ``set_device``
+    (examples/script_planning_robot.py:486): tensors on cuda:1 while cuda:0 is the current device."""
+    from sigsvgd_b200.kernels import PathSigKernel
+
+    assert torch.cuda.current_device() == 0
+    X, G = _inputs(300, 16, 3, seed=2)
+    d0, d1 = torch.device("cuda:0"), torch.device("cuda:1")
+    r0 = ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d0), want_k=True)
+    r1 = ops.phi(torch.as_tensor(X, device=d1), torch.as_tensor(G, device=d1), want_k=True)
+    assert r1.phi.device == d1 and torch.cuda.current_device() == 0
+    assert torch.equal(r0.phi.cpu(), r1.phi.cpu()) and torch.equal(r0.k_xx.cpu(), r1.k_xx.cpu())
+    x1 = torch.as_tensor(X, device=d1).requires_grad_(True)
+    k = PathSigKernel()(x1, x1.detach(), compute_grad=False)
+    gk = torch.autograd.grad(k.sum(), x1)[0]
+    assert gk.device == d1 and torch.isfinite(gk).all()
+    with pytest.raises(RuntimeError, match="different devices"):
+        ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d1))
+    r0b = ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d0))  # the guard left no stale state
+    assert torch.equal(r0b.phi, r0.phi)

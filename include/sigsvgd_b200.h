@@ -150,6 +150,11 @@ int sigsvgd_select_window(const float* feat, int64_t ld, int64_t N, int64_t D, v
 int64_t sigsvgd_select_collect_min_capacity(void);
 int sigsvgd_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
                            int64_t cand_cap, uint64_t* totals, void* stream);
+/* select_begin for a select over the candidates, with the bookkeeping kept on the device (no host
+ * read of totals): rank = k_total - totals[0]; *ok (device int32) = 1 if the window holds the rank and
+ * no pool overflowed, else 0 (the caller then repeats the select over the full strips). */
+int sigsvgd_select_begin_window(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k_total,
+                                const uint64_t* totals, int32_t* ok, void* stream);
 int sigsvgd_select_finish(int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                           void* stream);
 

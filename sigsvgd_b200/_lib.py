@@ -71,6 +71,7 @@ _SIGNATURES = {
         c_int, [c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),
     "sigsvgd_fixed_bandwidth": (c_int, [c_float, c_void_p, c_void_p]),
     "sigsvgd_select_begin": (c_int, [c_void_p, c_void_p, c_uint64, c_void_p]),
+    "sigsvgd_select_begin_window": (c_int, [c_void_p, c_void_p, c_uint64, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_select_hist": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_select_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_select_finish": (c_int, [c_int64, c_float, c_float, c_void_p, c_void_p]),

@@ -243,6 +243,12 @@ int sigsvgd_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, vo
   return launch_select_begin(state, hist, k, 1, (cudaStream_t)stream);
 }
 
+int sigsvgd_select_begin_window(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k_total,
+                                const uint64_t* totals, int32_t* ok, void* stream) {
+  SIG_CHECK_ARG(state && hist && totals && ok, "select_begin_window: NULL pointer");
+  return launch_select_begin_window(state, hist, k_total, totals, ok, (cudaStream_t)stream);
+}
+
 int sigsvgd_select_hist(const float* dist, int64_t count, int pass, const sigsvgd_bw_state* state,
                         uint64_t* hist, void* stream) {
   SIG_CHECK_ARG(state && hist && (count == 0 || dist), "select_hist: NULL pointer");

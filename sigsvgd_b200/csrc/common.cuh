@@ -113,6 +113,8 @@ int launch_gemm_nn_simt(const float* a, int64_t lda, const float* v, int64_t ldv
 size_t select_workspace_bytes(int64_t count, int64_t batch);
 int launch_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, int64_t batch,
                         cudaStream_t st);
+int launch_select_begin_window(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k_total,
+                               const uint64_t* totals, int* ok, cudaStream_t st);
 int launch_select_hist(const float* dist, int64_t count, int64_t batch, int64_t stride, int pass,
                        const sigsvgd_bw_state* state, uint64_t* hist, cudaStream_t st);
 int launch_select_scan(int pass, sigsvgd_bw_state* state, uint64_t* hist, int64_t batch,

@@ -61,13 +61,12 @@ __device__ __forceinline__ void hist_add(unsigned int* hist, uint32_t bin, bool 
 
 // Block-wide (1024 threads, 2 bins each): find the bucket holding rank k of hist[kBins] and the
 // rank inside it.  Parallel prefix sum: warp shuffles + one shared array of 32 warp totals.
-template <typename CountT>
-__device__ __forceinline__ void block_pick_bucket(const CountT* hist, unsigned long long k,
-                                                  uint32_t* bucket_out, unsigned long long* k_out,
-                                                  unsigned long long* scratch /*[>= 32]*/) {
+__device__ __forceinline__ void block_pick_bucket_vals(unsigned long long h0, unsigned long long h1,
+                                                       unsigned long long k, uint32_t* bucket_out,
+                                                       unsigned long long* k_out,
+                                                       unsigned long long* scratch /*[>= 33]*/,
+                                                       unsigned long long* count_out = nullptr) {
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-  const unsigned long long h0 = (unsigned long long)hist[2 * t];
-  const unsigned long long h1 = (unsigned long long)hist[2 * t + 1];
   unsigned long long incl = h0 + h1;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -78,6 +77,7 @@ __device__ __forceinline__ void block_pick_bucket(const CountT* hist, unsigned l
   if (t == 0) {
     *bucket_out = kBins - 1;  // only reached if k is past the total (callers never ask for that)
     *k_out = 0ull;
+    if (count_out) *count_out = 0ull;
   }
   __syncthreads();
   if (wid == 0) {
@@ -95,12 +95,22 @@ __device__ __forceinline__ void block_pick_bucket(const CountT* hist, unsigned l
     if (k < excl + h0) {
       *bucket_out = 2 * t;
       *k_out = k - excl;
+      if (count_out) *count_out = h0;
     } else {
       *bucket_out = 2 * t + 1;
       *k_out = k - excl - h0;
+      if (count_out) *count_out = h1;
     }
   }
   __syncthreads();
+}
+
+template <typename CountT>
+__device__ __forceinline__ void block_pick_bucket(const CountT* hist, unsigned long long k,
+                                                  uint32_t* bucket_out, unsigned long long* k_out,
+                                                  unsigned long long* scratch /*[>= 32]*/) {
+  block_pick_bucket_vals((unsigned long long)hist[2 * threadIdx.x], (unsigned long long)hist[2 * threadIdx.x + 1], k,
+                         bucket_out, k_out, scratch);
 }
 
 // exact order statistic `k` of n floats (>= 0) held in shared memory; one block of 1024 threads
@@ -452,6 +462,19 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
   }
   __threadfence();
   grid.sync();
+  // everything the tail needs from global memory is requested here, in ONE round trip: the grid
+  // totals, this thread's two bins of the global histogram, and this block's first pool entries
+  // (the pool is scanned again once the bucket is known; its values do not depend on the bucket)
+  __shared__ unsigned long long sh_bn;
+  const unsigned int my_cnt = blockIdx.x < npool ? min(sh_fill, poolcap) : 0u;
+  const unsigned long long gh0 = __ldcg(ghist + 2 * threadIdx.x), gh1 = __ldcg(ghist + 2 * threadIdx.x + 1);
+  constexpr int kPre = 4;  // pool entries per thread kept in registers (pools hold ~3.5k at N = 4096)
+  float pv[kPre];
+#pragma unroll
+  for (int j = 0; j < kPre; ++j) {
+    const unsigned int i = threadIdx.x + j * blockDim.x;
+    pv[j] = i < my_cnt ? pool[i] : 0.f;
+  }
   if (threadIdx.x == 0) {
     sh_ncand = __ldcg(&tot32[0]);
     sh_over = __ldcg(&tot32[1]);
@@ -469,10 +492,10 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
     // ---------------------------------------------------------------- window hit
     // (in the doubled candidate list, position k' holds element k'/2 of the single list)
     unsigned long long k = tri_scan ? (k_total - below) >> 1 : k_total - below;
-    block_pick_bucket(ghist, k, &sh_bucket, &sh_k, scratch);
+    block_pick_bucket_vals(gh0, gh1, k, &sh_bucket, &sh_k, scratch, &sh_bn);
     uint32_t rel_prefix = sh_bucket << s1;
     k = sh_k;
-    const unsigned long long bucket_n = ghist[sh_bucket];
+    const unsigned long long bucket_n = sh_bn;
     __syncthreads();
     if (s1 == 0) {
       result_bits = lo_bits + rel_prefix;
@@ -481,15 +504,14 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
       writer = false;
       // (matches are gathered in shared memory first: ONE global reservation per block instead of one
       // round trip per warp and step)
-      const unsigned int cnt = blockIdx.x < npool ? min(pool_cnt[blockIdx.x], poolcap) : 0u;
+      const unsigned int cnt = my_cnt;
       __shared__ unsigned int sh_base;
+      __syncthreads();  // (my_cnt was read from sh_fill by every thread)
       if (threadIdx.x == 0) sh_fill = 0u;
       __syncthreads();
-      for (unsigned int i0 = threadIdx.x & ~31u; i0 < cnt; i0 += blockDim.x) {
-        const unsigned int i = i0 + (unsigned int)lane;
-        const float v = i < cnt ? pool[i] : 0.f;
+      auto keep = [&](float v, bool inb) {  // warp-collective
         const uint32_t rel = (__float_as_uint(v) & 0x7fffffffu) - lo_bits;
-        const bool in = i < cnt && (rel >> s1) == (rel_prefix >> s1);
+        const bool in = inb && (rel >> s1) == (rel_prefix >> s1);
         const unsigned m = __ballot_sync(0xffffffffu, in);
         if (m) {
           unsigned int base = 0;
@@ -498,6 +520,12 @@ window_select_kernel(SelWindow* win, float* cand, unsigned int* pool_cnt, float*
           const unsigned int at = base + __popc(m & ((1u << lane) - 1u));
           if (in && at < (unsigned int)kShort) sl[at] = v;  // (a block holds at most bucket_n <= kShort)
         }
+      };
+#pragma unroll
+      for (int j = 0; j < kPre; ++j) keep(pv[j], threadIdx.x + j * blockDim.x < cnt);
+      for (unsigned int i0 = kPre * blockDim.x + (threadIdx.x & ~31u); i0 < cnt; i0 += blockDim.x) {
+        const unsigned int i = i0 + (unsigned int)lane;
+        keep(i < cnt ? pool[i] : 0.f, i < cnt);
       }
       __syncthreads();
       const unsigned int nloc = min(sh_fill, (unsigned int)kShort);

@@ -179,6 +179,29 @@ __global__ void select_begin_kernel(sigsvgd_bw_state* state, unsigned long long*
   }
 }
 
+// same, for a select over the candidates of a window (sigsvgd_select_collect): the rank is taken
+// relative to the entries below the window, all on the device -- totals = {#below, #kept, #overflowed}
+// summed over the ranks; *ok = 1 if the wanted rank lies inside the window and no pool overflowed
+__global__ void select_begin_window_kernel(sigsvgd_bw_state* state, unsigned long long* hist,
+                                           unsigned long long k_total, const unsigned long long* totals,
+                                           int* ok) {
+  for (int i = threadIdx.x; i < kBins; i += blockDim.x) hist[i] = 0ull;
+  if (threadIdx.x == 0) {
+    const unsigned long long below = totals[0], kept = totals[1], over = totals[2];
+    const bool hit = over == 0ull && k_total >= below && k_total < below + kept;
+    *ok = hit ? 1 : 0;
+    sigsvgd_bw_state& s = state[0];
+    s.prefix = 0u;
+    s.k_rem = hit ? k_total - below : 0ull;
+    s.median = 0.f;
+    s.sum_kd = 0.0;
+    s.n_ties = 0u;
+    s.n_ties_all = 0u;
+    s.clamped = 0u;
+    s.coef = 0.f;
+  }
+}
+
 // one block of 256 threads per problem
 __global__ void __launch_bounds__(256)
 select_scan_kernel(int pass, sigsvgd_bw_state* state, unsigned long long* hist) {
@@ -295,6 +318,14 @@ int launch_select_begin(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k, int
                         cudaStream_t st) {
   select_begin_kernel<<<(unsigned)batch, 256, 0, st>>>(state, (unsigned long long*)hist, k);
   SIG_LAUNCH_OK("select_begin_kernel");
+  return 0;
+}
+
+int launch_select_begin_window(sigsvgd_bw_state* state, uint64_t* hist, uint64_t k_total,
+                               const uint64_t* totals, int* ok, cudaStream_t st) {
+  select_begin_window_kernel<<<1, 256, 0, st>>>(state, (unsigned long long*)hist, k_total,
+                                                (const unsigned long long*)totals, ok);
+  SIG_LAUNCH_OK("select_begin_window_kernel");
   return 0;
 }
 

@@ -78,6 +78,56 @@ class CudaBackend:
         return ops.signature_fwd_raw(x, depth, True)
 
     # ---- operand preparation / Gram / RBF / contraction ---------------------------------------
+    def prepare(self, s_local, g_local, center, group, rank, world) -> Optional[Features]:
+        """tcgen05 route: every rank packs the split-fp16 operand planes of ITS OWN rows only and the
+        planes are what is exchanged (same bytes as the fp32 [S | score] rows they stand for), instead
+        of every rank packing all N rows after the exchange.  The mean and the power-of-two scales
+        that all ranks must share come from one all-gather of a (D + 2)-float statistics vector.
+        Returns None when this backend wants the generic gather-then-pack route."""
+        M, D = s_local.shape
+        P = g_local.shape[1]
+        N = world * M
+        if not self._use_tc(N):
+            return None
+        dev = s_local.device
+        Cp = (D + 1 + P + 63) // 64 * 64
+        # 1. global statistics: column sums, max |s|, max |score|
+        vec = torch.cat([s_local.sum(0), s_local.abs().amax().reshape(1), g_local.abs().amax().reshape(1)])
+        if world > 1:
+            allv = torch.empty(world, D + 2, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(allv, vec, group=group)
+        else:
+            allv = vec[None]
+        mean = allv[:, :D].sum(0) / N if center else torch.zeros(D, dtype=torch.float32, device=dev)
+        max_s = allv[:, D].amax() + mean.abs().amax()  # bound on max |s - mean| (as the fused one-GPU pack)
+        max_g = allv[:, D + 1].amax()
+
+        def pow2_scale(m):  # power of two placing m in [2^13, 2^14)
+            _, e = torch.frexp(torch.where(m > 0, m, torch.ones_like(m)))  # m = mant * 2^e, mant in [0.5, 1)
+            return torch.ldexp(torch.ones_like(m), 14 - e.clamp(-99, 101))
+
+        a_s, a_g = pow2_scale(max_s), pow2_scale(max_g)
+        scales = torch.zeros(8 + Cp, dtype=torch.float32, device=dev)
+        scales[0], scales[1], scales[2] = a_s, 1.0 / (a_s * a_s), a_g
+        scales[8:8 + D] = 1.0 / (16384.0 * a_s)
+        scales[8 + D] = 1.0 / 16384.0
+        scales[8 + D + 1:8 + D + 1 + P] = 1.0 / (16384.0 * a_g)
+        # 2. planes / norms / centred features of this rank's rows
+        fh = torch.empty(M, Cp, dtype=torch.float16, device=dev)
+        fl = torch.empty(M, Cp, dtype=torch.float16, device=dev)
+        norms = torch.empty(M, dtype=torch.float32, device=dev)
+        sc = torch.empty(M, D, dtype=torch.float32, device=dev)
+        ops.call("sigsvgd_tc_pack", ops._p(g_local), g_local.stride(0), P, ops._p(s_local), s_local.stride(0),
+                 ops._p(mean) if center else None, M, D, ops._p(scales), ops._p(fh), ops._p(fl), Cp, Cp, ops._p(norms),
+                 ops._p(sc), D, ops._stream())
+        # 3. the one real exchange step of the path
+        if world > 1:
+            fh, fl, norms, sc_all = (_all_gather_rows(t, group) for t in (fh, fl, norms, sc))
+        else:
+            sc_all = sc
+        r0 = rank * M
+        return Features(sc_all, sc_all[r0:r0 + M], ("tc", ops.Planes(fh, fl), norms, scales, D, P, r0, M))
+
     def pack(self, s_all, g_all, center, r0, M) -> Features:
         N, D = s_all.shape
         P = g_all.shape[1]
@@ -132,6 +182,14 @@ class CudaBackend:
 
     def select_begin(self, state, hist, k):
         ops.call("sigsvgd_select_begin", ops._p(state), ops._p(hist), int(k), ops._stream())
+
+    def select_begin_window(self, state, hist, k_total, totals):
+        """``select_begin`` for a select over window candidates with the rank taken relative to the
+        all-rank totals ON THE DEVICE.  Returns a device int32 flag: 1 = the window held the rank."""
+        ok = torch.zeros(1, dtype=torch.int32, device=state.device)
+        ops.call("sigsvgd_select_begin_window", ops._p(state), ops._p(hist), int(k_total), ops._p(totals), ops._p(ok),
+                 ops._stream())
+        return ok
 
     def select_hist(self, dist_loc, p, state, hist):
         ops.call("sigsvgd_select_hist", ops._p(dist_loc), dist_loc.numel(), p, ops._p(state), ops._p(hist),
@@ -216,17 +274,19 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
     g_local = score_local.reshape(M, P).contiguous()
 
     s_local = be.sig_fwd(x_local, depth)
-    if world > 1:
-        # the one real exchange step of the path: [S | score] rows of every rank
-        packed = torch.cat([s_local, g_local], dim=1)
-        allp = _all_gather_rows(packed, group)
-        s_all, g_all = allp[:, :D], allp[:, D:]
-    else:
-        s_all, g_all = s_local, g_local
-    feat = be.pack(s_all, g_all, center, r0, M)
+    feat = be.prepare(s_local, g_local, center, group, rank, world) if hasattr(be, "prepare") else None
+    if feat is None:
+        if world > 1:
+            # the one real exchange step of the path: [S | score] rows of every rank
+            allp = _all_gather_rows(torch.cat([s_local, g_local], dim=1), group)
+            s_all, g_all = allp[:, :D], allp[:, D:]
+        else:
+            s_all, g_all = s_local, g_local
+        feat = be.pack(s_all, g_all, center, r0, M)
     k_rows = be.gram(feat)  # [M, N] squared distances of this rank's rows
 
     state = be.new_state(x_local.device)
+    window_ok = None  # device flag of an optimistic windowed select (checked once, at the end)
     if bw.mode == _lib.BW_FIXED:
         be.fixed_bandwidth(bw.h, state)
     else:
@@ -239,15 +299,16 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
             window = k_rows.numel() >= getattr(be, "window_min_elems", 1 << 62)
         if window:
             # one read of the strip: count the entries below a sampled window around the median and
-            # compact the entries inside it; the select then runs over those candidates only
+            # compact the entries inside it; the select then runs over those candidates only.  Whether
+            # the window held the median is decided on the device (no host read in the middle of the
+            # step); in the ~1e-8 case that it did not, the step is repeated with the plain passes.
             bounds = be.select_window(feat.sc_all, state)
-            cand, totals = be.select_collect(data, bounds)
+            data, totals = be.select_collect(data, bounds)
             if world > 1:
                 dist.all_reduce(totals, op=dist.ReduceOp.SUM, group=group)
-            below, kept, overflowed = (int(v) for v in totals.tolist())  # host sync; same on every rank
-            if overflowed == 0 and below <= k < below + kept:
-                data, k = cand, k - below
-        be.select_begin(state, hist, k)
+            window_ok = be.select_begin_window(state, hist, k, totals)
+        else:
+            be.select_begin(state, hist, k)
         for p in range(3):
             be.select_hist(data, p, state, hist)
             if world > 1:
@@ -262,6 +323,8 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
     be.median_coef(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad, stats)
     g = be.sig_grad(feat.sc_loc, feat.sc_all, ks, rowsum, state, r0)
     phi = be.sig_bwd(x_local, s_local, g, depth, kg, 1.0 / N, -1.0 / N)
+    if window_ok is not None and not bool(window_ok.item()):  # identical on every rank (all-reduced totals)
+        return phi_sharded(x_local, score_local, depth, bandwidth, want_k, center, group, backend, window=False)
     return ShardedPhi(phi, state, k_out, (r0, r0 + M))
 
 

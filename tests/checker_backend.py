@@ -61,6 +61,12 @@ class CheckerBackend:
         state.update(prefix=0, k_rem=int(k))
         hist.zero_()
 
+    def select_begin_window(self, state, hist, k_total, totals):
+        below, kept, over = (int(v) for v in totals.tolist())
+        hit = over == 0 and below <= k_total < below + kept
+        self.select_begin(state, hist, k_total - below if hit else 0)
+        return torch.tensor([1 if hit else 0], dtype=torch.int32)
+
     def select_hist(self, dist_loc, p, state, hist):
         bits = dist_loc.contiguous().view(torch.int32).reshape(-1).to(torch.int64)
         if p > 0:

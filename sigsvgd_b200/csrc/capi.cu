@@ -585,6 +585,9 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
                                          scales + 8, Fh, Fl, C, C, nullptr, nullptr, D, nullptr, st,
                                          (D + 1) & ~(int64_t)1, C));
     }
+    // (Host-input pipeline: running the [Sc | 1] columns as a launch of their own, beside the score's
+    // H2D copy, was measured and dropped: the front half ends just as the score lands, so nothing
+    // overlaps, and two launches of the contraction cost 27 us more than one.)
     SIG_PROPAGATE(tc_kf_fused(K, ldk, N, N, SIGSVGD_KF_EXP, state, /*stats=*/1, 0, TcPlanes{Fh, Fl, C},
                               D + 1 + P, scales + 8, out, C, st, /*out_zeroed=*/true));
     if (k_out) SIG_PROPAGATE(launch_rbf_out(K, ldk, N, N, state, k_out, N, st));  // k_xx for the caller
@@ -611,10 +614,14 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
                                  pref));
     return 0;
   }
-  // K2 in row chunks; each chunk's D2H copy overlaps the next chunk's backward sweep
-  const int64_t per = round_up(ceil_div(R, kHostChunks), 32);
+  // K2 in row chunks; each chunk's D2H copy overlaps the next chunk's backward sweep.  The copies are
+  // the long pole (PCIe), so the first chunk is small -- phi starts to leave early -- and the later
+  // ones grow (1/8, 1/4, 5/8 of the rows): each finishes before the copy in front of it does.
+  const int64_t unit = round_up(ceil_div(R, 8), 32);
+  const int64_t sizes[kHostChunks] = {unit, 2 * unit, 5 * unit, R};
   int n = 0;
-  for (int64_t r0 = 0; r0 < R; r0 += per, ++n) {
+  for (int64_t r0 = 0; r0 < R && n < kHostChunks; ++n) {
+    const int64_t per = n + 1 < kHostChunks ? sizes[n] : R - r0;
     const int64_t rows = std::min(per, R - r0);
     SigGradSpec gc = gs;
     gc.sc += r0 * ldf, gc.ks += r0 * C, gc.rowsum += r0 * C, gc.row_offset = r0;
@@ -625,6 +632,7 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     SIG_CUDA_OK(cudaStreamWaitEvent(hp->d2h, hp->chunk[n], 0));
     SIG_CUDA_OK(cudaMemcpyAsync(hp->phi_host + r0 * T * d, phi + r0 * T * d,
                                 sizeof(float) * rows * T * d, cudaMemcpyDeviceToHost, hp->d2h));
+    r0 += rows;
   }
   SIG_CUDA_OK(cudaEventRecord(hp->done, hp->d2h));
   SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->done, 0));

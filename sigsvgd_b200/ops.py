@@ -670,6 +670,7 @@ def rbf_gram_with_grad(X, Y, bandwidth: Optional[Bandwidth] = None, center: bool
 # fused Stein update
 # ---------------------------------------------------------------------------------------------
 _WS_CACHE: dict = {}
+_HOST_CACHE: dict = {}  # phi_host: (device, shape) -> (state record, workspace)
 
 
 def _workspace(device, nbytes: int) -> torch.Tensor:
@@ -802,7 +803,8 @@ def phi_host(X: torch.Tensor, score: torch.Tensor, depth: int = 3, bandwidth: Op
     (pinned memory makes the copies asynchronous), result in ``out`` (CPU, pinned if given that
     way).  One ``sigsvgd_phi_host`` call: H2D of X, the score's H2D beside the front half of the
     update, chunked D2H of phi beside the signature backward.  The result is complete once the
-    current stream of ``device`` has finished (``torch.cuda.current_stream().synchronize()``)."""
+    current stream of ``device`` has finished (``torch.cuda.current_stream().synchronize()``).  The
+    returned ``state`` record is reused by the next ``phi_host`` call of the same shape on that device."""
     bw = bandwidth or Bandwidth.median()
     if X.is_cuda or score.is_cuda:
         raise RuntimeError("phi_host takes CPU tensors; use ops.phi for device-resident inputs")
@@ -819,17 +821,23 @@ def phi_host(X: torch.Tensor, score: torch.Tensor, depth: int = 3, bandwidth: Op
     if out.is_cuda or out.dtype != torch.float32 or not out.is_contiguous() or out.shape != x.shape:
         raise ValueError("phi_host: out must be a contiguous fp32 CPU tensor shaped like X")
     lib = _lib.load()
-    with torch.cuda.device(dev):
-        state = new_state(dev, 1)
+    key = (dev.index, N, T, d, depth)
+    cached = _HOST_CACHE.get(key)
+    if cached is None:
         nbytes = lib.sigsvgd_phi_host_workspace_bytes(N, T, d, depth)
         if nbytes == 0:
             raise ValueError("phi_host: bad shape")
-        ws = _workspace(dev, nbytes)
-        fl = int(flags) | (_lib.FLAG_MEDIAN_GRAD if (bw.mode == _lib.BW_MEDIAN and bw.median_grad) else 0)
-        if not center:
-            fl |= _lib.FLAG_NO_CENTER
-        call("sigsvgd_phi_host", _p(x), _p(g), N, T, d, depth, bw.mode, bw.h, bw.bw_scale, bw.tol, fl, _p(out),
-             _p(state), _p(ws), ws.numel(), _stream())
+        with torch.cuda.device(dev):
+            # one state record and one workspace per (device, shape), reused by later calls: the pipeline
+            # rewrites every field of the record, and calls on one device are stream-ordered
+            cached = _HOST_CACHE[key] = (new_state(dev, 1), torch.empty(nbytes, dtype=torch.uint8, device=dev))
+    state, ws = cached
+    fl = int(flags) | (_lib.FLAG_MEDIAN_GRAD if (bw.mode == _lib.BW_MEDIAN and bw.median_grad) else 0)
+    if not center:
+        fl |= _lib.FLAG_NO_CENTER
+    _note_device(dev)
+    call("sigsvgd_phi_host", x.data_ptr(), g.data_ptr(), N, T, d, depth, bw.mode, bw.h, bw.bw_scale, bw.tol, fl,
+         out.data_ptr(), _p(state), _p(ws), ws.numel(), _stream())
     res = PhiResult(out, state)
     res._keep = (x, g)  # the asynchronous copies read these host buffers until the stream drains
     return res

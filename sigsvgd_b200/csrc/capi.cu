@@ -573,10 +573,6 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
       for (int64_t b = 0; b < B; ++b)
         SIG_PROPAGATE(launch_rbf_out(K + b * N * N, N, N, N, state + b, K + b * N * N, N, st));
   } else if (use_tc) {
-    // (the coefficient of the median-gradient term is derived by the signature backward itself
-    // when it forms the cotangent: see SigGradSpec::coef_mode)
-    if (!(B == 1 && sig_bwd_fuses_grad(d, depth)))
-      SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
     if (hp) {
       float* stats = (float*)(w + L.off_stats);
       SIG_CUDA_OK(cudaStreamWaitEvent(st, hp->score_ready, 0));
@@ -590,6 +586,11 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
     // overlaps, and two launches of the contraction cost 27 us more than one.)
     SIG_PROPAGATE(tc_kf_fused(K, ldk, N, N, SIGSVGD_KF_EXP, state, /*stats=*/1, 0, TcPlanes{Fh, Fl, C},
                               D + 1 + P, scales + 8, out, C, st, /*out_zeroed=*/true));
+    // the coefficient of the median-gradient term needs sum(k*d), which the contraction has just
+    // accumulated; at depth 3 the signature backward derives it itself while forming the cotangent
+    // (SigGradSpec::coef_mode)
+    if (!(B == 1 && sig_bwd_fuses_grad(d, depth)))
+      SIG_PROPAGATE(launch_median_coef(state, nullptr, nullptr, median_grad, 1, st));
     if (k_out) SIG_PROPAGATE(launch_rbf_out(K, ldk, N, N, state, k_out, N, st));  // k_xx for the caller
   } else {
     SIG_PROPAGATE(launch_rbf_apply(K, N, N, N, 0, nullptr, 0, state, B, N * N, 0, st));

@@ -92,6 +92,28 @@ struct SigGradSpec {
   int coef_mode = 0;     // 0: state->coef / n_ties_all as set by median_coef; 1: derive them from the
                          // record's own sum_kd / n_ties (and store them); 2: same, gradient term off
 };
+// Median-gradient coefficient for the fused cotangent: either the record's (coef_mode 0: set by
+// median_coef_kernel, e.g. from all-reduced sums on the sharded path) or derived here from the
+// record's own sums, coef = sum_kd / (h^2 median) -- one launch less
+// on the one-swarm path.  The first block of the first row chunk also stores it in the record.
+__device__ __forceinline__ float grad_coef(const SigGradSpec& gs, uint32_t* n_ties_all) {
+  const sigsvgd_bw_state& st = *gs.state;
+  if (gs.coef_mode == 0) {
+    *n_ties_all = st.n_ties_all;
+    return st.coef;
+  }
+  const uint32_t nt = st.n_ties;
+  const bool on = gs.coef_mode == 1 && !st.clamped && st.median > 0.f && nt > 0u;
+  const float coef = on ? (float)st.sum_kd / (st.h * st.h * st.median) : 0.f;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && gs.row_offset == 0) {
+    sigsvgd_bw_state* w = const_cast<sigsvgd_bw_state*>(gs.state);
+    w->coef = coef;
+    w->n_ties_all = nt;
+  }
+  *n_ties_all = nt;
+  return coef;
+}
+
 int select_collect_blocks();
 int launch_select_collect(const float* dist, int64_t count, const float* bounds, float* cand,
                           int64_t cand_cap, unsigned long long* totals, cudaStream_t st);
@@ -100,6 +122,13 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
                    float alpha, float beta, float* out, cudaStream_t st,
                    const SigGradSpec* spec = nullptr, const float* pref = nullptr);
+
+// depth 4, 2 <= d <= 8 (sig4_kernels.cu): d^2 threads per particle, level 4 in registers
+bool sig4_available(int64_t d);
+int launch_sig4_fwd(const float* x, int64_t N, int64_t T, int64_t d, int basepoint, float* sig, cudaStream_t st);
+int launch_sig4_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T, int64_t d,
+                    int basepoint, const float* add, int64_t ld_add, float alpha, float beta, float* out,
+                    cudaStream_t st, const SigGradSpec* spec = nullptr);
 
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,

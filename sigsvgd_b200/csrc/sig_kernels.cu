@@ -478,28 +478,6 @@ sig3_fwd_seg_kernel(const float* __restrict__ x, int64_t N, int T, int basepoint
   }
 }
 
-// Median-gradient coefficient for the fused cotangent: either the record's (coef_mode 0: set by
-// median_coef_kernel, e.g. from all-reduced sums on the sharded path) or derived here from the
-// record's own sums, coef = sum_kd / (h^2 median) -- one launch less
-// on the one-swarm path.  The first block of the first row chunk also stores it in the record.
-__device__ __forceinline__ float grad_coef(const SigGradSpec& gs, uint32_t* n_ties_all) {
-  const sigsvgd_bw_state& st = *gs.state;
-  if (gs.coef_mode == 0) {
-    *n_ties_all = st.n_ties_all;
-    return st.coef;
-  }
-  const uint32_t nt = st.n_ties;
-  const bool on = gs.coef_mode == 1 && !st.clamped && st.median > 0.f && nt > 0u;
-  const float coef = on ? (float)st.sum_kd / (st.h * st.h * st.median) : 0.f;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && gs.row_offset == 0) {
-    sigsvgd_bw_state* w = const_cast<sigsvgd_bw_state*>(gs.state);
-    w->coef = coef;
-    w->n_ties_all = nt;
-  }
-  *n_ties_all = nt;
-  return coef;
-}
-
 // One reversed time step of the depth-3 VJP for lane i of a particle's group:
 //   levels 1-2 of the state go back  S_{t-1} = S_t (x) exp(-dl)  (level 3 feeds nothing),
 //   the adjoints (A1, A2; A3 = G3 is constant) go back through  S_t = S_{t-1} (x) exp(dl),
@@ -1287,6 +1265,7 @@ int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, i
       default: break;
     }
   }
+  if (depth == 4 && sig4_available(d)) return launch_sig4_fwd(x, N, T, d, basepoint, sig, st);
   LevelInfo L;
   int64_t D;
   if (make_levels(d, depth, &L, &D) != 0 || (D + d) * 4 > 200 * 1024) {
@@ -1304,7 +1283,9 @@ int launch_sig_fwd(const float* x, int64_t N, int64_t T, int64_t d, int depth, i
   return 0;
 }
 
-bool sig_bwd_fuses_grad(int64_t d, int depth) { return depth == 3 && d >= 1 && d <= 8; }
+bool sig_bwd_fuses_grad(int64_t d, int depth) {
+  return (depth == 3 && d >= 1 && d <= 8) || (depth == 4 && sig4_available(d));
+}
 
 int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t N, int64_t T,
                    int64_t d, int depth, int basepoint, const float* add, int64_t ld_add,
@@ -1316,7 +1297,7 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
   if (spec) {
     gs = *spec;
     SIG_CHECK_ARG(sig_bwd_fuses_grad(d, depth) && gs.sc && gs.sc_all && gs.ks && gs.rowsum && gs.state,
-                  "signature_bwd: fused gradient needs depth 3, d <= 8 and a complete spec");
+                  "signature_bwd: fused gradient needs depth 3 (d <= 8) or depth 4 (2 <= d <= 8) and a complete spec");
   }
   SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
                 "signature_bwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,
@@ -1342,6 +1323,8 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
       default: break;
     }
   }
+  if (depth == 4 && sig4_available(d))
+    return launch_sig4_bwd(x, sig, gsig, N, T, d, basepoint, add, ld_add, alpha, beta, out, st, spec ? &gs : nullptr);
   LevelInfo L;
   int64_t D;
   if (make_levels(d, depth, &L, &D) != 0 || (2 * D + 2 * d + 33 * d) * 4 > 200 * 1024) {

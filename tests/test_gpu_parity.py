@@ -47,7 +47,10 @@ SIG_SHAPES = [
     # N, T, d, depth
     (1, 1, 7, 3), (3, 2, 7, 3), (17, 64, 7, 3), (130, 30, 2, 3), (16, 5, 1, 3), (33, 9, 3, 3), (20, 12, 4, 3),
     (9, 7, 5, 3), (11, 6, 6, 3), (40, 10, 8, 3), (100, 10, 2, 3), (5, 300, 7, 3),  # T > one staging chunk
-    (7, 8, 3, 4), (6, 9, 7, 4), (5, 6, 2, 5), (8, 7, 5, 2), (4, 5, 3, 1), (3, 4, 10, 3),  # generic kernels
+    (5, 6, 2, 5), (8, 7, 5, 2), (4, 5, 3, 1), (3, 4, 10, 3), (3, 4, 1, 4), (3, 5, 9, 4),  # generic kernels
+    # depth 4, 2 <= d <= 8: sig4 kernels (d^2 threads per particle; chunks of 8 steps; 256/d^2 particles per CTA)
+    (7, 8, 3, 4), (6, 9, 7, 4), (2, 1, 7, 4), (11, 17, 7, 4), (13, 20, 2, 4), (9, 10, 4, 4), (6, 9, 5, 4),
+    (15, 8, 6, 4), (6, 9, 8, 4), (4, 100, 7, 4),
 ]
 
 
@@ -73,6 +76,22 @@ def test_signature_fwd_bwd_vs_oracle(N, T, d, depth, basepoint):
                                 beta=-0.5).cpu().numpy()
     want = -0.5 * gx_ref + 0.25 * add[:, :T * d].reshape(N, T, d)
     assert rel_max(out, want) <= 2e-5
+
+
+def test_signature_depth4_full_size_rows_vs_oracle():
+    """BASELINE.json configs[3] shape (4096, 64, 7, depth 4): every row computed, a row sample checked
+    against the float64 oracle (forward and VJP)."""
+    N, T, d, depth = 4096, 64, 7, 4
+    x = make_paths("walk", N, T, d, seed=11)
+    rows = np.arange(0, N, 97)
+    sig = ops.signature_fwd_raw(cu(x), depth, True)
+    assert sig.shape == (N, 2800)
+    ref = oracle.signature_np(x[rows].astype(np.float64), depth, True)
+    assert rel_max(sig[rows].cpu().numpy(), ref) <= TOL_SIG
+    g = np.random.default_rng(2).standard_normal((N, 2800)).astype(np.float32)
+    gx = ops.signature_bwd_raw(cu(x), sig, cu(g), depth, True).cpu().numpy()
+    gx_ref = oracle.signature_bwd_np(x[rows].astype(np.float64), ref, g[rows].astype(np.float64), depth, True)
+    assert rel_max(gx[rows], gx_ref) <= 2e-5
 
 
 PREFIX_SHAPES = [(17, 64, 7), (130, 30, 2), (20, 12, 4), (40, 10, 8), (100, 10, 2), (33, 9, 4), (9, 11, 4), (16, 8, 1),
@@ -261,7 +280,8 @@ def test_phi_vs_reference_golden(name):
 
 
 @pytest.mark.parametrize("kind,N,T,d,depth", [("walk", 256, 64, 7, 3), ("panda", 256, 64, 7, 3), ("field", 100, 10, 2, 3),
-                                              ("walk", 35, 30, 2, 3), ("walk", 513, 20, 7, 3), ("walk", 64, 12, 3, 4)])
+                                              ("walk", 35, 30, 2, 3), ("walk", 513, 20, 7, 3), ("walk", 64, 12, 3, 4),
+                                              ("walk", 384, 64, 7, 4)])
 @pytest.mark.parametrize("center", [True, False])
 def test_phi_vs_oracle_seeded(kind, N, T, d, depth, center):
     X = make_paths(kind, N, T, d, seed=3)

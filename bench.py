@@ -24,7 +24,8 @@ Extras in the same line (skipped with --skip-extras):
   record (median / h identical on every rank and equal to the one-GPU route's, max deviation of phi over
   a row sample) and the one-GPU time of the same swarm measured in the SAME run -> `sharded_efficiency`;
 * `batched_scenes`: BASELINE.json configs[4], 1024 scenes x 128 particles split over the ranks;
-* `mpc_step`: the "ms/MPC step" half of the metric (configs[2]) at the particle-maze shapes.
+* `mpc_step`: the "ms/MPC step" half of the metric (configs[2]) at the particle-maze shapes;
+* `depth4_swarm`: configs[3]'s depth-4 end (N = 4096, D = 2800 signature channels), same update call.
 
 N > 1 (torchrun): headline `value` ("scaling": "weak") = every rank updates its OWN independent swarm
 of `--particles` particles, no communication (north_star: "batches of independent planning problems
@@ -394,6 +395,25 @@ def run_ours(args):
             torch.cuda.empty_cache()
             return {"scenes": n_scenes, "error": f"{type(e).__name__}: {e}"[:300]}
 
+    def depth4_swarm(Ns, steps, warmup):
+        """BASELINE.json configs[3], depth 4: the same update call with 2800 signature channels (the
+        dedicated depth-4 signature kernels, tcgen05 Gram / K.F over D = 2800)."""
+        try:
+            xs, gs = (t.to(dev) for t in make_inputs(Ns, seed=5))
+            ms = timed(lambda: ops.phi(xs, gs, depth=4).phi, steps, warmup, reduce_max=False)
+            res = ops.phi(xs, gs, depth=4)
+            rec = ops.read_state(res.state)
+            ok = bool(torch.isfinite(res.phi).all().item())
+            del xs, gs, res
+            ops._WS_CACHE.clear()
+            torch.cuda.empty_cache()
+            return {"particles": Ns, "depth": 4, "sig_channels": ops.sig_channels(D_CH, 4), "ms_per_step": ms,
+                    "updates_per_s": 1e3 / ms, "steps": steps, "finite": ok, "median": rec["median"], "h": rec["h"],
+                    "n_ties": rec["n_ties"]}
+        except Exception as e:
+            torch.cuda.empty_cache()
+            return {"particles": Ns, "depth": 4, "error": f"{type(e).__name__}: {e}"[:300]}
+
     def mpc_step(steps, warmup):
         """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
         opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
@@ -600,7 +620,7 @@ def run_ours(args):
                 "achieved": flops / (ms_k * 1e-3) / 1e12, "peak": peak_tf,
                 "peak_source": peak_src + " bf16_tflops (burst; fp16 and bf16 share the tcgen05 kind::f16 rate)",
                 "unit": "TFLOP/s", "frac": flops / (ms_k * 1e-3) / 1e12 / peak_tf, "traffic": traffic,
-                "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per launch; algorithmic operand bytes are 82 MB",
+                "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per launch; algorithmic operand bytes are 96 MB (fp32 distances 67, fp16 planes 15, fp32 output 15)",
                 "ms_per_launch": ms_k, "algorithmic_flops_per_launch": flops,
                 "step_algorithmic_flops": 2.0 * N * N * (2 * D + P),
                 "step_frac_of_peak": 2.0 * N * N * (2 * D + P) / (ms_dev * 1e-3) / 1e12 / peak_tf,
@@ -614,7 +634,7 @@ def run_ours(args):
         torch.cuda.empty_cache()
 
     # ---- extras: one swarm sharded over the ranks, batched scenes, the MPC step -----------------
-    sharded, scenes, mpc = [], None, None
+    sharded, scenes, mpc, deep = [], None, None, None
     if not args.skip_extras:
         if world > 1:
             sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
@@ -623,6 +643,7 @@ def run_ours(args):
         scenes = batched_scenes(1024, 128, 10, 3)
         if rank == 0:
             mpc = mpc_step(20, 5)
+            deep = depth4_swarm(N, 10, 3)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -656,6 +677,7 @@ def run_ours(args):
             "sharded_swarm": sharded,
             "batched_scenes": scenes,
             "mpc_step": mpc,
+            "depth4_swarm": deep,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

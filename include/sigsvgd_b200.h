@@ -223,6 +223,19 @@ int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const
                           int64_t N, int64_t D, int center, float* scales, void* f_hi, void* f_lo,
                           int64_t ldp, int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
                           float* mean_out, float* stats, void* stream);
+/* The two passes of sigsvgd_tc_pack_fused as separate calls, for rows that are ONE SHARD of a larger
+ * swarm (row-block sharded update): sigsvgd_tc_stats fills stats[8 * (D + 2)] (8 slots
+ * of: D column sums, max |s|, max |score|; the slots add / max together) for this shard's N rows; the
+ * caller combines the shards' records (sums add, maxima max) into one 8-slot record, and
+ * sigsvgd_tc_pack_from_stats packs the shard's rows with the mean (n_total = particles of the whole
+ * swarm) and the power-of-two scales derived from it -- bit-identical on every shard. */
+int sigsvgd_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
+                     int64_t ld_score, int64_t P, float* stats, void* stream);
+int sigsvgd_tc_pack_from_stats(const float* score, int64_t ld_score, int64_t P, const float* s,
+                               int64_t lds, const float* stats, int64_t n_total, int64_t N, int64_t D,
+                               int center, float* scales, void* f_hi, void* f_lo, int64_t ldp,
+                               int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
+                               float* mean_out, void* stream);
 /* dist[i,j] = max(0, |a_i|^2 + |b_j|^2 - 2 a_i.b_j) over the first D plane columns, in the
  * units of the unscaled features (math.py:69-86); na/nb = norms from sigsvgd_tc_pack.
  * 128x128 tiles with separate TMEM accumulators for the hi.hi and correction

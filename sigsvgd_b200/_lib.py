@@ -128,6 +128,12 @@ _SIGNATURES = {
         [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
          c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     ),
+    "sigsvgd_tc_stats": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "sigsvgd_tc_pack_from_stats": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p,
+         c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p],
+    ),
     "sigsvgd_select_window_workspace_bytes": (c_size_t, []),
     "sigsvgd_select_window": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
     "sigsvgd_select_collect_min_capacity": (c_int64, []),

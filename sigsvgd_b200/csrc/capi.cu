@@ -368,6 +368,29 @@ int sigsvgd_tc_pack_fused(const float* score, int64_t ld_score, int64_t P, const
                               st);
 }
 
+/* The two passes of sigsvgd_tc_pack_fused as separate calls, for rows that are one shard of a larger
+ * swarm: the statistics of every shard are combined by the caller (column sums add, maxima take the
+ * max) into the 8-slot record, and the packing pass derives the mean (with n_total = all particles)
+ * and the scales from it -- identical on every shard. */
+int sigsvgd_tc_stats(const float* s, int64_t lds, int64_t N, int64_t D, const float* score,
+                     int64_t ld_score, int64_t P, float* stats, void* stream) {
+  SIG_CHECK_ARG(s && stats, "tc_stats: NULL pointer");
+  return launch_tc_stats(s, lds, N, D, score, ld_score, P, stats, 1, (cudaStream_t)stream);
+}
+
+int sigsvgd_tc_pack_from_stats(const float* score, int64_t ld_score, int64_t P, const float* s,
+                               int64_t lds, const float* stats, int64_t n_total, int64_t N, int64_t D,
+                               int center, float* scales, void* f_hi, void* f_lo, int64_t ldp,
+                               int64_t Cp, float* norms, float* s_centred, int64_t ld_sc,
+                               float* mean_out, void* stream) {
+  SIG_CHECK_ARG(s && scales && f_hi && f_lo && stats, "tc_pack_from_stats: NULL pointer");
+  SIG_CHECK_ARG(aligned16(f_hi) && aligned16(f_lo), "tc_pack_from_stats: planes must be 16-byte aligned");
+  SIG_CHECK_ARG(n_total >= N && N >= 0, "tc_pack_from_stats: n_total < N");
+  return launch_tc_pack_stats(score, ld_score, P, s, lds, stats, n_total, center, N, D, scales, scales + 8,
+                              (__half*)f_hi, (__half*)f_lo, ldp, Cp, norms, s_centred, ld_sc, mean_out,
+                              (cudaStream_t)stream);
+}
+
 int sigsvgd_tc_gram(const void* a_hi, const void* a_lo, int64_t lda, const float* na,
                     const void* b_hi, const void* b_lo, int64_t ldb, const float* nb, int64_t M,
                     int64_t N, int64_t D, const float* scales, int symmetric, float* dist,

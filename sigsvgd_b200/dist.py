@@ -47,6 +47,7 @@ class Features:
     sc_all: torch.Tensor
     sc_loc: torch.Tensor
     data: object
+    pending: object = None  # exchanges still in flight (CudaBackend.prepare -> CudaBackend.gram)
 
 
 class CudaBackend:
@@ -91,42 +92,49 @@ class CudaBackend:
             return None
         dev = s_local.device
         Cp = (D + 1 + P + 63) // 64 * 64
-        # 1. global statistics: column sums, max |s|, max |score|
-        vec = torch.cat([s_local.sum(0), s_local.abs().amax().reshape(1), g_local.abs().amax().reshape(1)])
+        # 1. global statistics (column sums, max |s|, max |score|): one pass over this rank's rows into
+        #    the library's 8-slot record, one all-gather of a (D + 2)-float vector per rank
+        stats = torch.empty(8, D + 2, dtype=torch.float32, device=dev)
+        ops.call("sigsvgd_tc_stats", ops._p(s_local), s_local.stride(0), M, D, ops._p(g_local), g_local.stride(0), P,
+                 ops._p(stats), ops._stream())
+        vec = torch.cat([stats[:, :D].sum(0), stats[:, D:].amax(0)])
         if world > 1:
             allv = torch.empty(world, D + 2, dtype=torch.float32, device=dev)
             dist.all_gather_into_tensor(allv, vec, group=group)
         else:
             allv = vec[None]
-        mean = allv[:, :D].sum(0) / N if center else torch.zeros(D, dtype=torch.float32, device=dev)
-        max_s = allv[:, D].amax() + mean.abs().amax()  # bound on max |s - mean| (as the fused one-GPU pack)
-        max_g = allv[:, D + 1].amax()
-
-        def pow2_scale(m):  # power of two placing m in [2^13, 2^14)
-            _, e = torch.frexp(torch.where(m > 0, m, torch.ones_like(m)))  # m = mant * 2^e, mant in [0.5, 1)
-            return torch.ldexp(torch.ones_like(m), 14 - e.clamp(-99, 101))
-
-        a_s, a_g = pow2_scale(max_s), pow2_scale(max_g)
-        scales = torch.zeros(8 + Cp, dtype=torch.float32, device=dev)
-        scales[0], scales[1], scales[2] = a_s, 1.0 / (a_s * a_s), a_g
-        scales[8:8 + D] = 1.0 / (16384.0 * a_s)
-        scales[8 + D] = 1.0 / 16384.0
-        scales[8 + D + 1:8 + D + 1 + P] = 1.0 / (16384.0 * a_g)
-        # 2. planes / norms / centred features of this rank's rows
-        fh = torch.empty(M, Cp, dtype=torch.float16, device=dev)
-        fl = torch.empty(M, Cp, dtype=torch.float16, device=dev)
-        norms = torch.empty(M, dtype=torch.float32, device=dev)
-        sc = torch.empty(M, D, dtype=torch.float32, device=dev)
-        ops.call("sigsvgd_tc_pack", ops._p(g_local), g_local.stride(0), P, ops._p(s_local), s_local.stride(0),
-                 ops._p(mean) if center else None, M, D, ops._p(scales), ops._p(fh), ops._p(fl), Cp, Cp, ops._p(norms),
-                 ops._p(sc), D, ops._stream())
-        # 3. the one real exchange step of the path
-        if world > 1:
-            fh, fl, norms, sc_all = (_all_gather_rows(t, group) for t in (fh, fl, norms, sc))
+        rec = torch.zeros(8, D + 2, dtype=torch.float32, device=dev)  # every rank builds the same record
+        if world <= 8:
+            rec[:world] = allv
         else:
-            sc_all = sc
+            rec[:7] = allv[:7]
+            rec[7, :D] = allv[7:, :D].sum(0)
+            rec[7, D:] = allv[7:, D:].amax(0)
+        # 2. planes / norms / centred features of this rank's rows, packed in place into the buffers that
+        #    will hold every rank's rows; the packing pass derives the mean (over all N particles) and the
+        #    power-of-two scales from the record, exactly as the one-GPU update does
         r0 = rank * M
-        return Features(sc_all, sc_all[r0:r0 + M], ("tc", ops.Planes(fh, fl), norms, scales, D, P, r0, M))
+        scales = torch.zeros(8 + Cp, dtype=torch.float32, device=dev)
+        fh = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+        fl = torch.empty(N, Cp, dtype=torch.float16, device=dev)
+        norms = torch.empty(N, dtype=torch.float32, device=dev)
+        sc_all = torch.empty(N, D, dtype=torch.float32, device=dev)
+        ops.call("sigsvgd_tc_pack_from_stats", ops._p(g_local), g_local.stride(0), P, ops._p(s_local),
+                 s_local.stride(0), ops._p(rec), N, M, D, int(bool(center)), ops._p(scales), ops._p(fh[r0:]),
+                 ops._p(fl[r0:]), Cp, Cp, ops._p(norms[r0:]), ops._p(sc_all[r0:]), D, None, ops._stream())
+        # 3. the one real exchange step of the path: all-gather of the operand planes (what the Gram strip
+        #    waits for) and, behind them and asynchronous, of the centred fp32 features (needed only after
+        #    the Gram -- median sample, tie partners -- so their transfer runs under it).
+        #    (Measured on 8 GPUs, N = 65536: splitting the exchange into one broadcast per source rank
+        #    and computing the Gram strip block by block as the blocks land was NOT faster -- 16
+        #    collective launches cost the host more than the overlap gains: 7.31 vs 7.17 ms per update.)
+        pending = None
+        if world > 1:
+            # (in place: every rank's rows already sit at their offset in the gathered buffer)
+            works = [dist.all_gather_into_tensor(t, t[r0:r0 + M], group=group, async_op=True) for t in (fh, fl, norms)]
+            sc_work = dist.all_gather_into_tensor(sc_all, sc_all[r0:r0 + M], group=group, async_op=True)
+            pending = (works, sc_work)
+        return Features(sc_all, sc_all[r0:r0 + M], ("tc", ops.Planes(fh, fl), norms, scales, D, P, r0, M), pending)
 
     def pack(self, s_all, g_all, center, r0, M) -> Features:
         N, D = s_all.shape
@@ -146,7 +154,15 @@ class CudaBackend:
             N = planes.hi.shape[0]
             out = torch.empty(M, N, dtype=torch.float32, device=planes.hi.device) if N % 4 == 0 else \
                 ops.dist_buffer(M, N, planes.hi.device)
-            return ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False, out=out)
+            if f.pending is None:
+                return ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False, out=out)
+            works, sc_work = f.pending
+            for w in works:
+                w.wait()  # the compute stream waits; the host does not
+            ops.tc_gram_raw(rows, norms[r0:r0 + M], planes, norms, D, scales, False, out=out)
+            sc_work.wait()
+            f.pending = None
+            return out
         _, v, D, P, r0, M = f.data
         return ops.sqdist_raw(v[r0:r0 + M, P:], v[:, P:], D)
 
@@ -246,6 +262,7 @@ class ShardedPhi:
     state: torch.Tensor  # bandwidth record (identical median / h on every rank)
     k_rows: Optional[torch.Tensor] = None  # [M, N] this rank's rows of k_xx (if requested)
     rows: Tuple[int, int] = (0, 0)
+    window_ok: Optional[torch.Tensor] = None  # device flag of the windowed median (ShardedPlan only)
 
 
 def _all_gather_rows(t: torch.Tensor, group) -> torch.Tensor:
@@ -257,11 +274,22 @@ def _all_gather_rows(t: torch.Tensor, group) -> torch.Tensor:
 
 def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3,
                 bandwidth: Optional[ops.Bandwidth] = None, want_k: bool = False, center: bool = True,
-                group=None, backend=None, window: Optional[bool] = None) -> ShardedPhi:
+                group=None, backend=None, window: Optional[bool] = None,
+                timings: Optional[dict] = None, _defer_window_check: bool = False) -> ShardedPhi:
     """Row-block sharded Stein update.  ``x_local [M,T,d]`` / ``score_local [M,T*d]`` are this
     rank's particles; every rank must hold the same M (N = world * M).  SURVEY.md 8(e).
-    ``window``: windowed first pass of the median (default: on for large strips)."""
+    ``window``: windowed first pass of the median (default: on for large strips).
+    ``timings``: if a dict, filled with this rank's milliseconds per phase (CUDA events on the current
+    stream, read after the step; the collectives are inside the phase that issues them)."""
     be = backend or CudaBackend()
+    marks = []
+
+    def mark(name):
+        if timings is not None and x_local.is_cuda:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(x_local.device))
+            marks.append((name, ev))
+
     bw = bandwidth or ops.Bandwidth.median()
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -273,7 +301,9 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
     x_local = x_local.contiguous()
     g_local = score_local.reshape(M, P).contiguous()
 
+    mark("start")
     s_local = be.sig_fwd(x_local, depth)
+    mark("signature_fwd")
     feat = be.prepare(s_local, g_local, center, group, rank, world) if hasattr(be, "prepare") else None
     if feat is None:
         if world > 1:
@@ -283,7 +313,9 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
         else:
             s_all, g_all = s_local, g_local
         feat = be.pack(s_all, g_all, center, r0, M)
+    mark("pack_and_all_gather")
     k_rows = be.gram(feat)  # [M, N] squared distances of this rank's rows
+    mark("gram_strip")
 
     state = be.new_state(x_local.device)
     window_ok = None  # device flag of an optimistic windowed select (checked once, at the end)
@@ -315,17 +347,70 @@ def phi_sharded(x_local: torch.Tensor, score_local: torch.Tensor, depth: int = 3
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
             be.select_scan(p, state, hist)
         be.select_finish(N, bw.bw_scale, bw.tol, state)
+    mark("global_median")
     kmat, k_out = be.rbf(k_rows, state, r0, feat, want_k)
     ks, rowsum, kg = be.contract(kmat, feat, state, r0)  # K.Sc [M,D], row sums [M], K.score [M,P]
+    mark("kf_strip")
     stats = be.local_stats(state)
     if world > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
     be.median_coef(state, bw.mode == _lib.BW_MEDIAN and bw.median_grad, stats)
     g = be.sig_grad(feat.sc_loc, feat.sc_all, ks, rowsum, state, r0)
     phi = be.sig_bwd(x_local, s_local, g, depth, kg, 1.0 / N, -1.0 / N)
+    mark("coef_and_signature_bwd")
+    if _defer_window_check:  # (ShardedPlan: the flag is read after the graph replay)
+        return ShardedPhi(phi, state, k_out, (r0, r0 + M), window_ok)
     if window_ok is not None and not bool(window_ok.item()):  # identical on every rank (all-reduced totals)
-        return phi_sharded(x_local, score_local, depth, bandwidth, want_k, center, group, backend, window=False)
+        return phi_sharded(x_local, score_local, depth, bandwidth, want_k, center, group, backend, window=False,
+                           timings=timings)
+    if marks:
+        marks[-1][1].synchronize()
+        timings.clear()
+        timings.update({b[0]: a[1].elapsed_time(b[1]) for a, b in zip(marks[:-1], marks[1:])})
     return ShardedPhi(phi, state, k_out, (r0, r0 + M))
 
 
-__all__ = ["phi_sharded", "shard_range", "shard_scenes", "CudaBackend", "ShardedPhi"]
+class ShardedPlan:
+    """``phi_sharded`` of one shard shape captured ONCE into a CUDA graph -- kernels AND the NCCL
+    collectives -- and replayed: the sharded step is ~40 launches and 9 collectives, and at 8 ranks
+    the host's enqueue time (not the GPUs) is a sixth of the step.  Every rank must build and call
+    the plan in lock-step (the capture itself runs the collectives).
+
+    The plan owns static buffers: pass this rank's rows to ``__call__`` (copied in) and read
+    ``.phi`` / ``.state`` of the returned ``ShardedPhi``.  The windowed median's "window held the
+    median" flag is read after the replay; in the ~1e-8 case that it did not, the step is repeated
+    eagerly with the plain three passes.  Delete the plan before ``dist.destroy_process_group()``: a
+    live graph that holds NCCL work keeps the communicator's teardown waiting."""
+
+    def __init__(self, M: int, T: int, d: int, depth: int = 3, bandwidth: Optional[ops.Bandwidth] = None,
+                 center: bool = True, group=None, device=None):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.args = (depth, bandwidth, False, center, group)
+        gen = torch.Generator().manual_seed(1234 + (dist.get_rank(group) if dist.is_initialized() else 0))
+        self.x = torch.cumsum(0.05 * torch.randn(M, T, d, generator=gen), dim=1).to(dev)
+        self.score = torch.randn(M, T * d, generator=gen).to(dev)
+        self._stream = torch.cuda.Stream(device=dev)
+        self._stream.wait_stream(torch.cuda.current_stream(dev))
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(self._stream):
+            for _ in range(2):  # warm-up outside the capture: communicator set-up, lazy initialisation
+                phi_sharded(self.x, self.score, *self.args, _defer_window_check=True)
+            self._stream.synchronize()
+            with torch.cuda.graph(self.graph, stream=self._stream, capture_error_mode="thread_local"):
+                self.res = phi_sharded(self.x, self.score, *self.args, _defer_window_check=True)
+        torch.cuda.current_stream(dev).wait_stream(self._stream)
+
+    def __call__(self, x_local: torch.Tensor, score_local: torch.Tensor) -> ShardedPhi:
+        if x_local.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x_local.reshape(self.x.shape))
+        if score_local.data_ptr() != self.score.data_ptr():
+            self.score.copy_(score_local.reshape(self.score.shape))
+        self.graph.replay()
+        ok = self.res.window_ok
+        if ok is not None and not bool(ok.item()):
+            depth, bw, want_k, center, group = self.args
+            return phi_sharded(self.x, self.score, depth, bw, want_k, center, group, window=False)
+        return self.res
+
+
+__all__ = ["phi_sharded", "shard_range", "shard_scenes", "CudaBackend", "ShardedPhi", "ShardedPlan"]

@@ -135,7 +135,19 @@ def _nccl_worker(rank, world, port, N, T, d, depth, tc, q):
                           torch.as_tensor(G[rank * M:(rank + 1) * M], device=dev), depth=depth, want_k=True,
                           backend=CudaBackend(tc=tc), window=tc)
         torch.cuda.synchronize()
-        q.put((rank, res.phi.cpu().numpy(), res.k_rows.cpu().numpy(), ops.read_state(res.state)))
+        out = [rank, res.phi.cpu().numpy(), res.k_rows.cpu().numpy(), ops.read_state(res.state), None]
+        if tc:
+            # the same step (kernels + NCCL collectives) replayed from one CUDA graph
+            from sigsvgd_b200.dist import ShardedPlan
+
+            plan = ShardedPlan(M, T, d, depth)
+            for _ in range(2):
+                rg = plan(torch.as_tensor(X[rank * M:(rank + 1) * M], device=dev),
+                          torch.as_tensor(G[rank * M:(rank + 1) * M], device=dev))
+            torch.cuda.synchronize()
+            out[4] = (rg.phi.cpu().numpy(), ops.read_state(rg.state))
+            del plan, rg  # (a live graph holding NCCL work must go before the process group does)
+        q.put(tuple(out))
     finally:
         dist.destroy_process_group()
 
@@ -161,6 +173,14 @@ def test_world2_nccl(tc, N):
     recs = [g[3] for g in got]
     assert recs[0]["median"] == recs[1]["median"] and recs[0]["h"] == recs[1]["h"]
     _check(X, G, depth, np.concatenate([g[1] for g in got]), np.concatenate([g[2] for g in got]), recs)
+    if tc:
+        grecs = [g[4][1] for g in got]
+        assert grecs[0]["median"] == recs[0]["median"] and grecs[1]["h"] == recs[1]["h"]
+        skip = {t[0] for r in recs + grecs for t in r["ties"]}
+        keep = np.array([i for i in range(N) if i not in skip])
+        phi_e = np.concatenate([g[1] for g in got]).reshape(N, -1)[keep]
+        phi_g = np.concatenate([g[4][0] for g in got]).reshape(N, -1)[keep]
+        assert rel_max(phi_g, phi_e) <= 1e-5
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
@@ -175,7 +195,10 @@ def test_calls_follow_the_device_of_their_tensors():
     r0 = ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d0), want_k=True)
     r1 = ops.phi(torch.as_tensor(X, device=d1), torch.as_tensor(G, device=d1), want_k=True)
     assert r1.phi.device == d1 and torch.cuda.current_device() == 0
-    assert torch.equal(r0.phi.cpu(), r1.phi.cpu()) and torch.equal(r0.k_xx.cpu(), r1.k_xx.cpu())
+    # (same arithmetic on both devices; the column statistics are accumulated with floating-point
+    # atomics, so the last bits may differ from launch to launch)
+    assert rel_max(r1.phi.cpu().numpy(), r0.phi.cpu().numpy()) < 1e-5
+    assert float((r0.k_xx.cpu() - r1.k_xx.cpu()).abs().max()) < 1e-6
     x1 = torch.as_tensor(X, device=d1).requires_grad_(True)
     k = PathSigKernel()(x1, x1.detach(), compute_grad=False)
     gk = torch.autograd.grad(k.sum(), x1)[0]
@@ -183,4 +206,4 @@ def test_calls_follow_the_device_of_their_tensors():
     with pytest.raises(RuntimeError, match="different devices"):
         ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d1))
     r0b = ops.phi(torch.as_tensor(X, device=d0), torch.as_tensor(G, device=d0))  # the guard left no stale state
-    assert torch.equal(r0b.phi, r0.phi)
+    assert rel_max(r0b.phi.cpu().numpy(), r0.phi.cpu().numpy()) < 1e-5

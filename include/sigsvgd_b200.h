@@ -124,6 +124,22 @@ size_t sigsvgd_select_workspace_bytes(int64_t count);
 int sigsvgd_median_bandwidth(const float* dist, int64_t count, int64_t n_log, float bw_scale,
                              float tol, sigsvgd_bw_state* state, void* ws, size_t ws_bytes,
                              void* stream);
+/* The same exact median for callers that may not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc): NO counterpart in the reference -- added at the
+ * request of the operators of the run that produced this library.  The 2048-bin u64 histograms that
+ * sigsvgd_median_bandwidth takes as `ws` live in a file-scope device array inside the library
+ * (SIGSVGD_STATIC_MAX_BATCH x 16 KiB = 256 KiB, held by every GPU that loads the library until exit);
+ * the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   dist: `batch` arrays of `count` floats >= 0, array b at dist + b * stride (stride ignored for
+ *   batch 1); state: `batch` records; each record gets the exact lower median (rank (count-1)/2) of its
+ *   array and h, gamma, clamped as sigsvgd_median_bandwidth fills them.
+ * batch > SIGSVGD_STATIC_MAX_BATCH -> SIGSVGD_ERR_WORKSPACE (use the workspace form).  Every call on a
+ * device shares the one array (its bins are re-zeroed at the start of each call): calls that overlap
+ * on the GPU -- different streams, or graphs replayed concurrently -- RACE; serialise them. */
+#define SIGSVGD_STATIC_MAX_BATCH 16
+int sigsvgd_median_bandwidth_static(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                                    int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                                    void* stream);
 /* Fixed bandwidth: fills state for a caller-chosen h (bandwidth_fn=lambda _: const). */
 int sigsvgd_fixed_bandwidth(float h, sigsvgd_bw_state* state, void* stream);
 

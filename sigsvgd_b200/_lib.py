@@ -69,6 +69,8 @@ _SIGNATURES = {
     "sigsvgd_select_workspace_bytes": (c_size_t, [c_int64]),
     "sigsvgd_median_bandwidth": (
         c_int, [c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "sigsvgd_median_bandwidth_static": (
+        c_int, [c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p]),
     "sigsvgd_fixed_bandwidth": (c_int, [c_float, c_void_p, c_void_p]),
     "sigsvgd_select_begin": (c_int, [c_void_p, c_void_p, c_uint64, c_void_p]),
     "sigsvgd_select_begin_window": (c_int, [c_void_p, c_void_p, c_uint64, c_void_p, c_void_p, c_void_p]),

@@ -233,6 +233,14 @@ int sigsvgd_median_bandwidth(const float* dist, int64_t count, int64_t n_log, fl
                               (cudaStream_t)stream);
 }
 
+int sigsvgd_median_bandwidth_static(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                                    int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                                    void* stream) {
+  SIG_CHECK_ARG(dist && state, "median_bandwidth_static: NULL pointer");
+  return launch_median_select_static(dist, count, batch, stride, n_log, bw_scale, tol, state,
+                                     (cudaStream_t)stream);
+}
+
 int sigsvgd_fixed_bandwidth(float h, sigsvgd_bw_state* state, void* stream) {
   SIG_CHECK_ARG(state, "fixed_bandwidth: NULL pointer");
   return launch_fixed_bandwidth(h, state, 1, (cudaStream_t)stream);

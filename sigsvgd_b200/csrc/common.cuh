@@ -156,6 +156,10 @@ int launch_median_coef(sigsvgd_bw_state* state, const double* sum_kd_all,
 int launch_median_select(const float* dist, int64_t count, int64_t batch, int64_t stride,
                          int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
                          void* ws, size_t ws_bytes, cudaStream_t st);
+// same, scratch in a file-scope device array (select.cu); batch <= SIGSVGD_STATIC_MAX_BATCH
+int launch_median_select_static(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                                int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                                cudaStream_t st);
 
 // elementwise / packing (elementwise.cu)
 int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,

@@ -7,6 +7,8 @@
 //
 // The passes are separate launches so a row-block-sharded run can all-reduce the 2048-bin
 // histogram between `hist` and `scan`; batched problems use blockIdx.y.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace sigsvgd {
@@ -393,6 +395,60 @@ int launch_median_select(const float* dist, int64_t count, int64_t batch, int64_
     SIG_PROPAGATE(launch_select_scan(pass, state, hist, batch, st));
   }
   return launch_select_finish(n_log, bw_scale, tol, state, batch, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// The same exact median with its histogram scratch in a file-scope device array, for callers that
+// may not allocate (sigsvgd_median_bandwidth_static; no counterpart in the reference).
+// kStaticMaxBatch records x 2048 bins x 8 bytes = 256 KiB, held by every GPU that loads the library.
+// In host code `g_static_hist` is only a stand-in for the symbol: the device address is looked up
+// once per device (that device current) and that pointer is what the kernels get.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_static_hist[SIGSVGD_STATIC_MAX_BATCH * kBins];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {};
+}  // namespace
+
+static int static_hist_address(uint64_t** out) {
+  int dev = -1;
+  SIG_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("median_bandwidth_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    SIG_CUDA_OK(cudaGetSymbolAddress(&p, g_static_hist));  // of the CURRENT device's copy
+    if (p == nullptr) {
+      set_error("median_bandwidth_static: cudaGetSymbolAddress returned NULL on device %d", dev);
+      return SIGSVGD_ERR_CUDA;
+    }
+    g_static_ptr[dev] = p;
+  }
+  *out = (uint64_t*)g_static_ptr[dev];
+  return 0;
+}
+
+int launch_median_select_static(const float* dist, int64_t count, int64_t batch, int64_t stride,
+                                int64_t n_log, float bw_scale, float tol, sigsvgd_bw_state* state,
+                                cudaStream_t st) {
+  SIG_CHECK_ARG(batch >= 1, "median_bandwidth_static: batch must be >= 1");
+  if (batch > SIGSVGD_STATIC_MAX_BATCH) {
+    set_error("median_bandwidth_static: batch %lld exceeds the static scratch (SIGSVGD_STATIC_MAX_BATCH = %d "
+              "records of %d x 8 bytes); use sigsvgd_median_bandwidth with a caller workspace",
+              (long long)batch, SIGSVGD_STATIC_MAX_BATCH, kBins);
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  SIG_CHECK_ARG(batch == 1 || stride >= count, "median_bandwidth_static: stride < count");
+  uint64_t* hist = nullptr;
+  SIG_PROPAGATE(static_hist_address(&hist));
+  // (select_begin zeroes the bins of the records in use: the array keeps the previous call's contents)
+  return launch_median_select(dist, count, batch, stride, n_log, bw_scale, tol, state, hist,
+                              (size_t)SIGSVGD_STATIC_MAX_BATCH * kBins * sizeof(uint64_t), st);
 }
 
 int select_collect_blocks() { return 4 * num_sms(); }

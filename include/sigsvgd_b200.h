@@ -296,6 +296,25 @@ int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const 
                     float* k_out, int64_t ldk, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Fused optimiser step on the particles.  Replaces the update statements of
+ * SVGD.step (src/inference/svgd.py:93-116): `optimizer.step()` of torch.optim.SGD / torch.optim.Adam
+ * (default flags: no weight decay, no amsgrad, no nesterov, dampening 0) and the hand-written Adagrad
+ * (svgd.py:110-113), as ONE elementwise launch over the n = N*T*d particle coordinates.
+ *   g = sign * dir[i]   (dir = phi with sign = -1: the reference minimises with X.grad = -phi)
+ *   SGD:     m != NULL: buf = first ? g : beta1*buf + g (beta1 = momentum; buf in m);  x -= lr * (buf | g)
+ *   ADAGRAD: v += g^2;  g' = g / sqrt(v + 1e-12);  x -= lr * g'
+ *   ADAM:    m += (g - m)(1 - beta1);  v = beta2*v + (1 - beta2) g^2;  x -= c1 * m / (sqrt(v)/c2 + eps)
+ *            with c1 = lr / (1 - beta1^t), c2 = sqrt(1 - beta2^t) formed by the caller for step t; the betas are
+ *            doubles so that 1 - beta is formed as torch forms it (in double, then rounded to fp32)
+ * grad_out (may be NULL) receives what the reference logs as the step's "grad" (g; g' for Adagrad). */
+#define SIGSVGD_OPT_SGD 0
+#define SIGSVGD_OPT_ADAGRAD 1
+#define SIGSVGD_OPT_ADAM 2
+int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
+                     int kind, float lr, double beta1, double beta2, float eps, float c1, float c2, int first,
+                     void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Fused single-GPU Stein update.  Replaces SVGD._compute_kernel + the arithmetic of
  * SVGD._velocity (src/inference/svgd.py:36-44, 82-83) for kernel = PathSigKernel(GaussianKernel):
  *   phi = ( K . score - grad_k ) / N ,   the reference's velocity is -phi.

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libsigsvgd_b200.so")
 MAX_TIES = 64
 BW_MEDIAN, BW_FIXED = 0, 1
 FLAG_MEDIAN_GRAD, FLAG_NO_CENTER, FLAG_FORCE_SIMT, FLAG_FORCE_TC = 1, 2, 4, 8
+OPT_SGD, OPT_ADAGRAD, OPT_ADAM = 0, 1, 2
 KF_EXP, KF_IDENTITY = 0, 1
 
 
@@ -136,6 +137,9 @@ _SIGNATURES = {
         [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p,
          c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p],
     ),
+    "sigsvgd_opt_step": (
+        c_int, [c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_double, c_double,
+                c_float, c_float, c_float, c_int, c_void_p]),
     "sigsvgd_select_window_workspace_bytes": (c_size_t, []),
     "sigsvgd_select_window": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
     "sigsvgd_select_collect_min_capacity": (c_int64, []),

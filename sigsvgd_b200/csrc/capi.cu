@@ -451,6 +451,14 @@ int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const 
   return launch_rbf_out(dist, ldd, M, N, state, k_out, ldk, (cudaStream_t)stream);
 }
 
+int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
+                     int kind, float lr, double beta1, double beta2, float eps, float c1, float c2, int first,
+                     void* stream) {
+  SIG_CHECK_ARG(n == 0 || (x && dir), "opt_step: NULL pointer");
+  return launch_opt_step(x, dir, sign, m, v, grad_out, n, kind, lr, beta1, beta2, eps, c1, c2, first,
+                         (cudaStream_t)stream);
+}
+
 size_t sigsvgd_phi_workspace_bytes(int64_t B, int64_t N, int64_t T, int64_t d, int depth,
                                    int want_k) {
   if (B < 1 || N < 1 || T < 1 || d < 1 || depth < 1 || depth > 8) return 0;

@@ -165,6 +165,9 @@ int launch_median_select_static(const float* dist, int64_t count, int64_t batch,
 int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
                      const float* weight, int64_t ldw, sigsvgd_bw_state* state, int64_t batch,
                      int64_t stride_k, int64_t stride_w, cudaStream_t st);
+int launch_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
+                    int kind, float lr, double b1, double b2, float eps, float c1, float c2, int first,
+                    cudaStream_t st);
 int launch_rbf_out(const float* d, int64_t ldd, int64_t M, int64_t N, const sigsvgd_bw_state* state,
                    float* k, int64_t ldk, cudaStream_t st);
 int launch_col_mean(const float* s, int64_t lds, int64_t N, int64_t D, float* part, float* mean,

@@ -199,6 +199,46 @@ sig_grad_kernel(const float* __restrict__ sc, int64_t lds, const float* __restri
   g[row * ldg + c] = val;
 }
 
+// ------------------------------------------------------------------------------------------
+// Fused optimiser step on the particles: x <- update(x, g) with g = sign * dir
+// (dir = phi with sign -1: the reference minimises with X.grad = -phi, svgd.py:82-83, 93-116).
+//   SGD      : [buf <- mu*buf + g (buf = g on the first step)]  x -= lr * (buf | g)        torch.optim.SGD
+//   ADAGRAD  : inertia += g^2;  g' = g / sqrt(inertia + 1e-12);  x -= lr * g'             svgd.py:110-113
+//   ADAM     : m <- m + (g - m)(1 - b1);  v <- b2 v + (1 - b2) g^2;
+//              x -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)                           torch.optim.Adam
+// grad_out (optional) receives what the reference logs as the step's "grad" (g, or g' for Adagrad).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kEwThreads)
+opt_step_kernel(float* __restrict__ x, const float* __restrict__ dir, float sign, float* __restrict__ m,
+                float* __restrict__ v, float* __restrict__ grad_out, int64_t n, int kind, float lr, float b1,
+                float b2, float omb1, float omb2, float eps, float c1, float c2, int first) {
+  for (int64_t i = (int64_t)blockIdx.x * kEwThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kEwThreads) {
+    const float g = sign * dir[i];
+    float xi = x[i], logged = g;
+    if (kind == SIGSVGD_OPT_SGD) {
+      float step = g;
+      if (m != nullptr) {
+        step = first ? g : fmaf(b1, m[i], g);
+        m[i] = step;
+      }
+      xi = fmaf(-lr, step, xi);
+    } else if (kind == SIGSVGD_OPT_ADAGRAD) {
+      const float acc = fmaf(g, g, v[i]);
+      v[i] = acc;
+      logged = g / sqrtf(acc + 1e-12f);
+      xi = fmaf(-lr, logged, xi);
+    } else {  // Adam; c1 = lr / (1 - b1^t), c2 = sqrt(1 - b2^t)
+      const float mi = fmaf(g - m[i], omb1, m[i]);
+      const float vi = fmaf(b2, v[i], omb2 * g * g);
+      m[i] = mi;
+      v[i] = vi;
+      xi -= c1 * (mi / (sqrtf(vi) / c2 + eps));
+    }
+    x[i] = xi;
+    if (grad_out != nullptr) grad_out[i] = logged;
+  }
+}
+
 }  // namespace
 
 int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_offset,
@@ -219,6 +259,22 @@ int launch_rbf_apply(float* k, int64_t ldk, int64_t M, int64_t N, int64_t row_of
   rbf_apply_kernel<<<grid, kEwThreads, 0, st>>>(k, ldk, M, N, row_offset, weight, ldw, state,
                                                 stride_k, stride_w, rows_per_block);
   SIG_LAUNCH_OK("rbf_apply_kernel");
+  return 0;
+}
+
+int launch_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
+                    int kind, float lr, double b1, double b2, float eps, float c1, float c2, int first,
+                    cudaStream_t st) {
+  SIG_CHECK_ARG(kind == SIGSVGD_OPT_SGD || kind == SIGSVGD_OPT_ADAGRAD || kind == SIGSVGD_OPT_ADAM,
+                "opt_step: unknown optimiser kind %d", kind);
+  SIG_CHECK_ARG(kind != SIGSVGD_OPT_ADAGRAD || v != nullptr, "opt_step: Adagrad needs the inertia buffer v");
+  SIG_CHECK_ARG(kind != SIGSVGD_OPT_ADAM || (m != nullptr && v != nullptr), "opt_step: Adam needs m and v");
+  if (n <= 0) return 0;
+  const int64_t grid = std::min<int64_t>(ceil_div(n, (int64_t)kEwThreads), (int64_t)num_sms() * 16);
+  opt_step_kernel<<<(unsigned)grid, kEwThreads, 0, st>>>(
+      x, dir, sign, m, v, grad_out, n, kind, lr, (float)b1, (float)b2, (float)(1.0 - b1), (float)(1.0 - b2), eps, c1,
+      c2, first);
+  SIG_LAUNCH_OK("opt_step_kernel");
   return 0;
 }
 

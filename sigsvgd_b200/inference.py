@@ -71,6 +71,61 @@ def _target_score(sampler, X, grad_log_p, kwargs):
     return score, loss
 
 
+def _plain(x) -> bool:
+    return isinstance(x, (int, float)) and not isinstance(x, bool)
+
+
+def _fused_optimizer_step(optimizer, X: torch.Tensor, grad: torch.Tensor) -> bool:
+    """``optimizer.step()`` for ``X.grad = grad`` as ONE library launch (``sigsvgd_opt_step``) when the
+    optimizer is a stock ``torch.optim.Adam`` / ``torch.optim.SGD`` over ``[X]`` with the flags the
+    reference uses (src/inference/svgd.py:131: ``optimizer_class(params=[X], **opt_args)``); the state
+    dictionary keeps torch's own layout, so ``state_dict()`` / ``load_state_dict`` work unchanged.
+    Returns False (nothing done) for anything else."""
+    from . import _lib
+
+    if not (X.is_cuda and X.dtype == torch.float32 and X.is_contiguous() and grad.is_contiguous()):
+        return False
+    groups = optimizer.param_groups
+    if len(groups) != 1 or len(groups[0]["params"]) != 1 or groups[0]["params"][0] is not X:
+        return False
+    g = groups[0]
+    if g.get("weight_decay", 0) != 0 or g.get("maximize", False) or g.get("differentiable", False) \
+            or g.get("capturable", False) or g.get("fused", None) or not _plain(g["lr"]):
+        return False
+    if type(optimizer) is torch.optim.Adam:
+        if g.get("amsgrad", False) or not all(_plain(b) for b in g["betas"]):
+            return False
+        st = optimizer.state[X]
+        if len(st) == 0:
+            st["step"] = torch.tensor(0.0, dtype=torch.float32)
+            st["exp_avg"] = torch.zeros_like(X, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(X, memory_format=torch.preserve_format)
+        if st["step"].is_cuda or not st["exp_avg"].is_contiguous() or not st["exp_avg_sq"].is_contiguous():
+            return False
+        st["step"] += 1
+        t = float(st["step"])
+        b1, b2 = g["betas"]
+        ops.opt_step_raw(X, grad, _lib.OPT_ADAM, g["lr"], 1.0, st["exp_avg"], st["exp_avg_sq"], None, b1, b2, g["eps"],
+                         g["lr"] / (1.0 - b1 ** t), (1.0 - b2 ** t) ** 0.5)
+        return True
+    if type(optimizer) is torch.optim.SGD:
+        if g.get("nesterov", False) or g.get("dampening", 0) != 0 or not _plain(g.get("momentum", 0)):
+            return False
+        mom = g.get("momentum", 0)
+        buf, first = None, False
+        if mom != 0:
+            st = optimizer.state[X]
+            buf = st.get("momentum_buffer")
+            if buf is None:
+                buf, first = torch.empty_like(X), True
+                st["momentum_buffer"] = buf
+            elif not buf.is_contiguous():
+                return False
+        ops.opt_step_raw(X, grad, _lib.OPT_SGD, g["lr"], 1.0, buf, None, None, mom, first=first)
+        return True
+    return False
+
+
 def make_fused(base_cls):
     """Subclass of ``base_cls`` (an ``SVGD`` class with the reference's interface) whose ``_velocity``
     takes the fused CUDA path when it can.  Class attributes of the result:
@@ -78,6 +133,9 @@ def make_fused(base_cls):
     * ``log_level``: ``"full"`` (reference behaviour: every entry of the step's dictionary copied to
       the CPU), ``"device"`` (same entries, left on the device: no blocking D2H of the [N,N] matrix),
       ``"none"`` (``k_xx`` / ``grad_k`` are not materialised at all; the update replays a CUDA graph);
+    * ``fused_optimizer``: with ``log_level`` other than "full", the particle update of ``step`` (stock
+      ``torch.optim.Adam`` / ``SGD`` over ``[X]``, or the base class's hand-written Adagrad) runs as one
+      ``sigsvgd_opt_step`` launch; the optimizer's state dictionary keeps torch's layout;
     * ``depth``: signature depth of the fused path (the reference hard-wires PathSigKernel's default 3);
     * ``last_state``: device record of the last fused update (median, h, tie pairs)."""
     root = next(c for c in reversed(base_cls.__mro__) if "_velocity" in vars(c))
@@ -88,6 +146,7 @@ def make_fused(base_cls):
         log_level = "full"
         depth = 3
         use_graph = True
+        fused_optimizer = True  # Adam / SGD / Adagrad update as one library launch (log_level != "full")
         last_state = None
 
         def _velocity(self, X: torch.Tensor, grad_log_p: torch.Tensor, **kwargs) -> Tuple[torch.Tensor, dict]:
@@ -132,9 +191,25 @@ def make_fused(base_cls):
             if self.log_level == "full":
                 return super().step(X, grad_log_p, optimizer, **kwargs)
             grad, iter_dict = self._velocity(X, grad_log_p, **kwargs)
+            fuse = self.fused_optimizer and X.is_cuda and X.dtype == torch.float32
             if isinstance(optimizer, torch.optim.Optimizer):
                 X.grad = grad
-                optimizer.step()
+                if not (fuse and _fused_optimizer_step(optimizer, X, grad.contiguous())):
+                    optimizer.step()
+            elif fuse and X.is_contiguous():
+                # the base class's hand-written update rules (svgd.py:110-115) as one launch; X is a new
+                # tensor as in the base class
+                from . import _lib
+
+                X, grad = X.detach().clone(), grad.contiguous()
+                if self.opt_adagrad:
+                    if not isinstance(self.opt_inertia, torch.Tensor):
+                        self.opt_inertia = torch.full_like(X, float(self.opt_inertia))
+                    logged = torch.empty_like(X)
+                    ops.opt_step_raw(X, grad, _lib.OPT_ADAGRAD, self.opt_args["lr"], 1.0, None, self.opt_inertia, logged)
+                    grad = logged
+                else:
+                    ops.opt_step_raw(X, grad, _lib.OPT_SGD, self.opt_args["lr"])
             else:
                 if self.opt_adagrad:  # the base class's hand-written Adagrad, on the device
                     self.opt_inertia = self.opt_inertia + grad * grad

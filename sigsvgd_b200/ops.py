@@ -351,6 +351,19 @@ def rbf_out_raw(dist: torch.Tensor, state: torch.Tensor, out: Optional[torch.Ten
     return out
 
 
+def opt_step_raw(x: torch.Tensor, direction: torch.Tensor, kind: int, lr: float, sign: float = 1.0,
+                 m: Optional[torch.Tensor] = None, v: Optional[torch.Tensor] = None,
+                 grad_out: Optional[torch.Tensor] = None, beta1: float = 0.0, beta2: float = 0.0, eps: float = 0.0,
+                 c1: float = 0.0, c2: float = 1.0, first: bool = False) -> None:
+    """One fused optimiser step IN PLACE on ``x`` (``sigsvgd_opt_step``; kinds ``_lib.OPT_*``)."""
+    for t in (x, direction, m, v, grad_out):
+        if t is not None and (not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous()
+                              or t.numel() != x.numel()):
+            raise ValueError("opt_step: contiguous float32 CUDA tensors of one size expected")
+    call("sigsvgd_opt_step", _p(x), _p(direction), float(sign), _p(m), _p(v), _p(grad_out), x.numel(), int(kind),
+         float(lr), float(beta1), float(beta2), float(eps), float(c1), float(c2), int(bool(first)), _stream())
+
+
 def sig_grad_raw(sc, sc_all, ks, rowsum, state, row_offset: int = 0) -> torch.Tensor:
     """sc/sc_all/ks: 2-D views (features in the first D columns of ks.shape[1]); rowsum: 1-D view."""
     M, D = ks.shape

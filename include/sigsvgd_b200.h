@@ -296,6 +296,39 @@ int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const 
                     float* k_out, int64_t ldk, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Signature-PDE (Goursat) kernel, SURVEY.md 8(f)-1.  Replaces
+ *   sigkernel.SigKernel(static_kernel, dyadic_order).compute_Gram(X.double(), Y.double())
+ * (third party sigkernel @ 3b2373982e12, absent; call sites src/kernels/_traj_kernels.py:198-206,
+ * src/inference/trajectory_svgd.py:55-69, src/inference/score.py:64-76) with the reference's static kernel
+ * BatchGaussianKernel.Gram_matrix = exp(-|x_s - y_t|^2 / h) (src/kernels/_traj_kernels.py:176-195; note
+ * "/ h") or sigkernel.LinearKernel (<x_s, y_t> * h), and its backward w.r.t. the FIRST argument.
+ * x [A,M,D], y [B,N,D] fp64 row-major; k_out [A,B] fp64.  order = dyadic refinement (2^order fine cells
+ * per segment and side).  The bandwidth is state->h when state != NULL (RBF), else the argument h.
+ * One warp per path pair with the pair's [M,N] static Gram in shared memory: shapes whose pair state
+ * exceeds 200 KB (roughly M*N > 12000) return SIGSVGD_ERR_UNSUPPORTED.
+ *
+ * sigsvgd_sigpde_bandwidth: the reference's default bandwidth for that static kernel -- bw_median
+ * (src/utils/math.py:28-34) over ALL A*B*M*N point-pair distances, h = sqrt(median / ln(A + 1)) -- by the
+ * exact radix select with the distances recomputed on the fly (no [A,B,M,N] tensor); fills
+ * state->{median,h,clamped}; hist: 2048 x 8 bytes of scratch.
+ * sigsvgd_sigpde_gram_bwd: grad_x [A,M,D] = sum_b gout[a,b] d k[a,b] / d x^a by the package's formula
+ * (reverse-direction solve, products of the two solutions summed per coarse cell, analytic derivative of
+ * the increments at a fixed bandwidth); ws from sigsvgd_sigpde_bwd_workspace_bytes.
+ * ------------------------------------------------------------------------------------------- */
+#define SIGSVGD_PDE_RBF 0
+#define SIGSVGD_PDE_LINEAR 1
+int sigsvgd_sigpde_bandwidth(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N,
+                             int64_t D, float bw_scale, float tol, sigsvgd_bw_state* state, uint64_t* hist,
+                             void* stream);
+int sigsvgd_sigpde_gram(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N, int64_t D,
+                        int order, int kind, double h, const sigsvgd_bw_state* state, double* k_out,
+                        void* stream);
+size_t sigsvgd_sigpde_bwd_workspace_bytes(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, int order);
+int sigsvgd_sigpde_gram_bwd(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N,
+                            int64_t D, int order, int kind, double h, const sigsvgd_bw_state* state,
+                            const double* gout, double* grad_x, void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Fused optimiser step on the particles.  Replaces the update statements of
  * SVGD.step (src/inference/svgd.py:93-116): `optimizer.step()` of torch.optim.SGD / torch.optim.Adam
  * (default flags: no weight decay, no amsgrad, no nesterov, dampening 0) and the hand-written Adagrad

@@ -17,6 +17,7 @@ MAX_TIES = 64
 BW_MEDIAN, BW_FIXED = 0, 1
 FLAG_MEDIAN_GRAD, FLAG_NO_CENTER, FLAG_FORCE_SIMT, FLAG_FORCE_TC = 1, 2, 4, 8
 OPT_SGD, OPT_ADAGRAD, OPT_ADAM = 0, 1, 2
+PDE_RBF, PDE_LINEAR = 0, 1
 KF_EXP, KF_IDENTITY = 0, 1
 
 
@@ -137,6 +138,16 @@ _SIGNATURES = {
         [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p,
          c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p],
     ),
+    "sigsvgd_sigpde_bandwidth": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p,
+                c_void_p]),
+    "sigsvgd_sigpde_gram": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_double, c_void_p,
+                c_void_p, c_void_p]),
+    "sigsvgd_sigpde_bwd_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int64, c_int]),
+    "sigsvgd_sigpde_gram_bwd": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_double, c_void_p,
+                c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "sigsvgd_opt_step": (
         c_int, [c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_double, c_double,
                 c_float, c_float, c_float, c_int, c_void_p]),

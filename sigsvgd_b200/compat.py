@@ -84,6 +84,46 @@ class SigKernel:
         return self.compute_Gram(X, Y).diagonal()
 
 
+class LinearKernel:
+    """``sigkernel.LinearKernel`` shaped: static kernel ``<x_s, y_t> * scale``."""
+
+    def __init__(self, scale: float = 1.0):
+        self.scale = float(scale)
+
+
+class PdeSigKernel:
+    """``sigkernel.SigKernel(static_kernel, dyadic_order)`` computing the package's OWN kernel: the
+    Goursat-PDE signature kernel (``ops.sigpde_gram``), in float64 on the GPU.
+    ``static_kernel``: ``RBFKernel(sigma)`` (``exp(-|x - y|^2 / sigma)``, the package's convention),
+    ``LinearKernel(scale)``, or the reference's ``BatchGaussianKernel`` (``sigsvgd_b200.kernels``)."""
+
+    def __init__(self, static_kernel=None, dyadic_order: int = 0, _naive_solver: bool = False):
+        if _naive_solver:
+            raise NotImplementedError("PdeSigKernel: only the package's default (second-order) solver is built")
+        self.static_kernel = static_kernel if static_kernel is not None else RBFKernel(1.0)
+        self.dyadic_order = int(dyadic_order)
+
+    def _spec(self):
+        from . import _lib
+
+        sk = self.static_kernel
+        if isinstance(sk, LinearKernel):
+            return _lib.PDE_LINEAR, sk.scale
+        if isinstance(sk, RBFKernel):
+            return _lib.PDE_RBF, sk.sigma
+        if hasattr(sk, "bandwidth_spec"):
+            return _lib.PDE_RBF, sk.bandwidth_spec()
+        raise TypeError(f"PdeSigKernel: unsupported static kernel {type(sk).__name__}")
+
+    def compute_Gram(self, X: torch.Tensor, Y: torch.Tensor, sym: bool = False) -> torch.Tensor:
+        """[A,M,D] x [B,N,D] -> [A,B] in X's dtype; gradient w.r.t. X (trajectory_svgd.py:55-69)."""
+        kind, h = self._spec()
+        return ops.sigpde_gram(X, Y, self.dyadic_order, kind, h)
+
+    def compute_kernel(self, X: torch.Tensor, Y: torch.Tensor) -> torch.Tensor:
+        return self.compute_Gram(X, Y).diagonal()
+
+
 def signature(path, depth, stream=False, basepoint=False, inverse=False, initial=None, scalar_term=False):
     return ops.signature(path, depth, stream=stream, basepoint=basepoint, inverse=inverse, initial=initial,
                          scalar_term=scalar_term)
@@ -93,13 +133,17 @@ def signature_channels(channels: int, depth: int, scalar_term: bool = False) -> 
     return ops.sig_channels(channels, depth) + (1 if scalar_term else 0)
 
 
-def install(force: bool = False, sigkernel_truncated: bool = False) -> dict:
-    """Register the ``signatory`` stand-in and, only with ``sigkernel_truncated=True``, a module named
-    ``sigkernel`` whose ``SigKernel`` is the truncated-signature RBF kernel (see the module docstring).
-    Returns {name: module} of what was set."""
+def install(force: bool = False, sigkernel_truncated: bool = False, sigkernel_pde: bool = False) -> dict:
+    """Register the ``signatory`` stand-in and, on request, a module named ``sigkernel``: with
+    ``sigkernel_pde=True`` its ``SigKernel`` is ``PdeSigKernel`` (the package's own Goursat-PDE kernel on the
+    CUDA library); with ``sigkernel_truncated=True`` it is the truncated-signature RBF kernel of the north
+    star (see the module docstring; warns).  Returns {name: module} of what was set."""
     done = {}
     wanted = [("signatory", dict(signature=signature, signature_channels=signature_channels, __version__="sigsvgd_b200"))]
-    if sigkernel_truncated:
+    if sigkernel_pde:
+        wanted.append(("sigkernel", dict(SigKernel=PdeSigKernel, RBFKernel=RBFKernel, LinearKernel=LinearKernel,
+                                         __version__="sigsvgd_b200-pde")))
+    elif sigkernel_truncated:
         warnings.warn("registering a module named `sigkernel`: " + _SUBSTITUTION % 3, stacklevel=2)
         wanted.append(("sigkernel", dict(SigKernel=SigKernel, RBFKernel=RBFKernel, __version__="sigsvgd_b200-truncated",
                                          __doc__=_SUBSTITUTION % 3)))
@@ -119,4 +163,4 @@ def install(force: bool = False, sigkernel_truncated: bool = False) -> dict:
     return done
 
 
-__all__ = ["SigKernel", "RBFKernel", "signature", "signature_channels", "install"]
+__all__ = ["SigKernel", "PdeSigKernel", "RBFKernel", "LinearKernel", "signature", "signature_channels", "install"]

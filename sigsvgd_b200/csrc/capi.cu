@@ -451,6 +451,29 @@ int sigsvgd_rbf_out(const float* dist, int64_t ldd, int64_t M, int64_t N, const 
   return launch_rbf_out(dist, ldd, M, N, state, k_out, ldk, (cudaStream_t)stream);
 }
 
+int sigsvgd_sigpde_bandwidth(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N,
+                             int64_t D, float bw_scale, float tol, sigsvgd_bw_state* state, uint64_t* hist,
+                             void* stream) {
+  return launch_sigpde_bandwidth(x, y, A, B, M, N, D, bw_scale, tol, state, hist, (cudaStream_t)stream);
+}
+
+int sigsvgd_sigpde_gram(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N, int64_t D,
+                        int order, int kind, double h, const sigsvgd_bw_state* state, double* k_out,
+                        void* stream) {
+  return launch_sigpde_fwd(x, y, A, B, M, N, D, order, kind, h, state, k_out, (cudaStream_t)stream);
+}
+
+size_t sigsvgd_sigpde_bwd_workspace_bytes(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, int order) {
+  return sigpde_bwd_workspace_bytes(A, B, M, N, D, order);
+}
+
+int sigsvgd_sigpde_gram_bwd(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N,
+                            int64_t D, int order, int kind, double h, const sigsvgd_bw_state* state,
+                            const double* gout, double* grad_x, void* ws, size_t ws_bytes, void* stream) {
+  return launch_sigpde_bwd(x, y, A, B, M, N, D, order, kind, h, state, gout, grad_x, ws, ws_bytes,
+                           (cudaStream_t)stream);
+}
+
 int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
                      int kind, float lr, double beta1, double beta2, float eps, float c1, float c2, int first,
                      void* stream) {

@@ -130,6 +130,18 @@ int launch_sig4_bwd(const float* x, const float* sig, const float* gsig, int64_t
                     int basepoint, const float* add, int64_t ld_add, float alpha, float beta, float* out,
                     cudaStream_t st, const SigGradSpec* spec = nullptr);
 
+// signature-PDE kernel (sigpde.cu)
+int launch_sigpde_bandwidth(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N,
+                            int64_t D, float bw_scale, float tol, sigsvgd_bw_state* state, uint64_t* hist,
+                            cudaStream_t st);
+int launch_sigpde_fwd(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N, int64_t D,
+                      int order, int kind, double h, const sigsvgd_bw_state* state, double* k_out,
+                      cudaStream_t st);
+size_t sigpde_bwd_workspace_bytes(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, int order);
+int launch_sigpde_bwd(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N, int64_t D,
+                      int order, int kind, double h, const sigsvgd_bw_state* state, const double* gout,
+                      double* grad_x, void* ws, size_t ws_bytes, cudaStream_t st);
+
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,
                        int64_t N, int64_t D, float* dist, int64_t ldd, int64_t batch,

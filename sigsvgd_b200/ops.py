@@ -646,6 +646,78 @@ class _RBFGram(torch.autograd.Function):
         return gX, gY, None, None
 
 
+# ---------------------------------------------------------------------------------------------
+# signature-PDE kernel: sigkernel.SigKernel.compute_Gram and its backward
+# ---------------------------------------------------------------------------------------------
+def _prep64(t: torch.Tensor, what: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{what}: CUDA tensors only; sigsvgd_b200 has no CPU fallback")
+    if t.dim() != 3:
+        raise ValueError(f"{what}: expected [batch, length, dim] paths, got {tuple(t.shape)}")
+    return t.detach().to(torch.float64).contiguous()
+
+
+def sigpde_bandwidth_raw(x: torch.Tensor, y: torch.Tensor, bw_scale: float = 1.0, tol: float = 1e-8) -> torch.Tensor:
+    """State record with the reference's default bandwidth of ``BatchGaussianKernel.Gram_matrix``: bw_median over
+    all A*B*M*N point-pair distances, ln(A + 1).  x, y: float64 [A,M,D], [B,N,D]."""
+    (A, M, D), (B, N, _) = x.shape, y.shape
+    state = new_state(x.device)
+    hist = torch.empty(2048, dtype=torch.int64, device=x.device)
+    call("sigsvgd_sigpde_bandwidth", _p(x), _p(y), A, B, M, N, D, float(bw_scale), float(tol), _p(state), _p(hist),
+         _stream())
+    return state
+
+
+def sigpde_gram_raw(x, y, order: int, kind: int = _lib.PDE_RBF, h: float = 1.0, state=None) -> torch.Tensor:
+    (A, M, D), (B, N, D2) = x.shape, y.shape
+    if D != D2:
+        raise ValueError("sigpde_gram: paths of different dimension")
+    k = torch.empty(A, B, dtype=torch.float64, device=x.device)
+    call("sigsvgd_sigpde_gram", _p(x), _p(y), A, B, M, N, D, int(order), int(kind), float(h), _p(state), _p(k), _stream())
+    return k
+
+
+def sigpde_gram_bwd_raw(x, y, gout, order: int, kind: int = _lib.PDE_RBF, h: float = 1.0, state=None) -> torch.Tensor:
+    (A, M, D), (B, N, _) = x.shape, y.shape
+    nbytes = int(_lib.load().sigsvgd_sigpde_bwd_workspace_bytes(A, B, M, N, D, int(order)))
+    ws = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=x.device)
+    gx = torch.empty_like(x)
+    call("sigsvgd_sigpde_gram_bwd", _p(x), _p(y), A, B, M, N, D, int(order), int(kind), float(h), _p(state), _p(gout),
+         _p(gx), _p(ws), ws.numel(), _stream())
+    return gx
+
+
+class _SigPdeGram(torch.autograd.Function):
+    """k[a,b] = Goursat-PDE signature kernel of paths X_a, Y_b; gradient w.r.t. X only (as the package)."""
+
+    @staticmethod
+    def forward(ctx, X, Y, order, kind, h, bw_scale, tol):
+        x, y = _prep64(X, "SigKernel.compute_Gram"), _prep64(Y, "SigKernel.compute_Gram")
+        state = sigpde_bandwidth_raw(x, y, bw_scale, tol) if (h is None and kind == _lib.PDE_RBF) else None
+        k = sigpde_gram_raw(x, y, order, kind, 1.0 if h is None else h, state)
+        ctx.saved = (x, y, state)
+        ctx.cfg = (order, kind, 1.0 if h is None else h, X.dtype)
+        ctx.state = state
+        return k.to(X.dtype)
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, y, state = ctx.saved
+        order, kind, h, dtype = ctx.cfg
+        gx = None
+        if ctx.needs_input_grad[0]:
+            gx = sigpde_gram_bwd_raw(x, y, gout.to(torch.float64).contiguous(), order, kind, h, state).to(dtype)
+        return gx, None, None, None, None, None, None
+
+
+def sigpde_gram(X, Y, order: int = 0, kind: int = _lib.PDE_RBF, h: Optional[float] = None, bw_scale: float = 1.0,
+                tol: float = 1e-8) -> torch.Tensor:
+    """Signature-PDE Gram matrix [A,B] of X [A,M,D] and Y [B,N,D] (any float dtype; computed in float64 as
+    the reference does), differentiable w.r.t. X.  ``h=None`` (RBF): the reference's median heuristic over
+    all point pairs; else ``exp(-d/h)`` (RBF) or ``<x,y> * h`` (linear)."""
+    return _SigPdeGram.apply(X, Y, int(order), int(kind), None if h is None else float(h), float(bw_scale), float(tol))
+
+
 def sig_rbf_gram(X, Y, depth: int = 3, bandwidth: Optional[Bandwidth] = None, center: bool = True) -> torch.Tensor:
     if X.shape != Y.shape:
         raise AssertionError("X and Y must have the same dimensions.")

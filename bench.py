@@ -25,7 +25,8 @@ Extras in the same line (skipped with --skip-extras):
   a row sample) and the one-GPU time of the same swarm measured in the SAME run -> `sharded_efficiency`;
 * `batched_scenes`: BASELINE.json configs[4], 1024 scenes x 128 particles split over the ranks;
 * `mpc_step`: the "ms/MPC step" half of the metric (configs[2]) at the particle-maze shapes;
-* `depth4_swarm`: configs[3]'s depth-4 end (N = 4096, D = 2800 signature channels), same update call.
+* `depth4_swarm`: configs[3]'s depth-4 end (N = 4096, D = 2800 signature channels), same update call;
+* `sigpde`: the signature-PDE Gram matrix / gradient at the maze and Panda shapes, fp64.
 
 N > 1 (torchrun): headline `value` ("scaling": "weak") = every rank updates its OWN independent swarm
 of `--particles` particles, no communication (north_star: "batches of independent planning problems
@@ -440,6 +441,29 @@ def run_ours(args):
             torch.cuda.empty_cache()
             return {"particles": Ns, "depth": 4, "error": f"{type(e).__name__}: {e}"[:300]}
 
+    def sigpde_leg(steps, warmup):
+        """the signature-PDE Gram matrix and its gradient (what the reference's example
+        scripts call through ``sigkernel``) at the particle-maze shapes (35 x 30 x 2, dyadic order 3,
+        examples/particle_maze_config.yaml:20) and at Panda-shaped paths (256 x 64 x 7, order 0), fp64."""
+        try:
+            out = {}
+            for name, A, M, Dp, order in (("maze_35x30x2_order3", 35, 30, 2, 3), ("panda_256x64x7_order0", 256, 64, 7, 0)):
+                g = torch.Generator().manual_seed(3)
+                xp = torch.cumsum(0.1 * torch.randn(A, M, Dp, generator=g, dtype=torch.float64), 1).to(dev)
+                go = torch.ones(A, A, dtype=torch.float64, device=dev)
+                st = ops.sigpde_bandwidth_raw(xp, xp)
+                cells = A * A * ((M - 1) << order) ** 2
+                ms_bw = timed(lambda: ops.sigpde_bandwidth_raw(xp, xp), steps, warmup, reduce_max=False)
+                ms_f = timed(lambda: ops.sigpde_gram_raw(xp, xp, order, _lib.PDE_RBF, 1.0, st), steps, warmup, reduce_max=False)
+                ms_b = timed(lambda: ops.sigpde_gram_bwd_raw(xp, xp, go, order, _lib.PDE_RBF, 1.0, st), steps, warmup,
+                             reduce_max=False)
+                out[name] = {"median_bandwidth_ms": ms_bw, "gram_ms": ms_f, "gram_bwd_ms": ms_b, "fine_cells": cells,
+                             "gram_gcells_per_s": cells / ms_f / 1e6, "dtype": "f64"}
+            return out
+        except Exception as e:
+            torch.cuda.empty_cache()
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+
     def mpc_step(steps, warmup):
         """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
         opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
@@ -660,7 +684,7 @@ def run_ours(args):
         torch.cuda.empty_cache()
 
     # ---- extras: one swarm sharded over the ranks, batched scenes, the MPC step -----------------
-    sharded, scenes, mpc, deep = [], None, None, None
+    sharded, scenes, mpc, deep, pde = [], None, None, None, None
     if not args.skip_extras:
         if world > 1:
             sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
@@ -670,6 +694,7 @@ def run_ours(args):
         if rank == 0:
             mpc = mpc_step(20, 5)
             deep = depth4_swarm(N, 10, 3)
+            pde = sigpde_leg(5, 2)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -704,6 +729,7 @@ def run_ours(args):
             "batched_scenes": scenes,
             "mpc_step": mpc,
             "depth4_swarm": deep,
+            "sigpde": pde,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

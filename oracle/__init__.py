@@ -11,6 +11,10 @@ Parity status
   ``PathSigKernel``, ``SVGD._compute_kernel/_velocity``): pinned by golden vectors generated in
   the build container by running the reference's own *unmodified* Python
   (``oracle/make_golden.py`` -> ``tests/golden/*.npz``).
+* signature-PDE kernel (``sigkernel`` @ 3b23739, third party, absent): **parity unpinned** for the Goursat
+  solver and its backward (closed-form known answers, ``sigpde_oracle.py``); the static kernel and the
+  bandwidth convention are the reference's own code and are pinned by ``tests/golden/sigpde_static.npz``
+  (``oracle/make_golden_sigpde.py``).
 """
 from .signature import signature_np, signature_bwd_np, sig_channels, OracleSignature, signature_torch  # noqa: F401
 from .phi_oracle import (  # noqa: F401

@@ -58,7 +58,12 @@ def bw_median_points(dist, bw_scale=1.0, tol=1e-8):
     """``bw_median`` on the [A,B,M,N] tensor: lower median of all entries, ln(A + 1) (math.py:28-34)."""
     flat = np.sort(dist.reshape(-1))
     med = flat[(flat.size - 1) // 2]
-    return max(bw_scale * np.sqrt(med / np.log(dist.shape[0] + 1.0)), tol), med
+    # (the reference evaluates ln(A + 1) on a default-dtype, i.e. float32, 0-dim tensor: math.py:32; torch's
+    # float32 log itself is used here, it can differ from libm's by an ulp)
+    import torch
+
+    log_a1 = float(torch.tensor(dist.shape[0] + 1.0, dtype=torch.float32).log())
+    return max(bw_scale * np.sqrt(med / log_a1), tol), med
 
 
 def _solve(inc, order):

@@ -361,6 +361,15 @@ static BwdPlan bwd_plan(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, i
   if (pl.warps < 1) return pl;
   const int64_t want_blocks = 4 * (int64_t)num_sms();
   int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(ceil_div(B, pl.warps), ceil_div(want_blocks, A)));
+  // the reverse solve of every resident pair is parked in global memory: keep that scratch under 4 GiB
+  const double per = 8.0 * ((double)((M - 1) << order) * (double)((N - 1) << order) + (double)(M - 1) * (N - 1));
+  const double cap = 4.0 * 1024 * 1024 * 1024;
+  while (chunks > 1 && per * A * chunks * pl.warps > cap) --chunks;
+  while (pl.warps > 1 && per * A * chunks * pl.warps > cap) --pl.warps;
+  if (per * A * chunks * pl.warps > 4 * cap) {
+    pl.warps = -1;  // refined grid too large for the parked reverse solve
+    return pl;
+  }
   pl.b_per_block = (int)(ceil_div(ceil_div(B, chunks), pl.warps) * pl.warps);
   pl.chunks = (int)ceil_div(B, pl.b_per_block);
   return pl;
@@ -369,8 +378,9 @@ static BwdPlan bwd_plan(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, i
 size_t sigpde_bwd_workspace_bytes(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, int order) {
   if (A < 1 || B < 1 || M < 2 || N < 2 || D < 1 || order < 0 || order > 10) return 0;
   const BwdPlan pl = bwd_plan(A, B, M, N, D, order);
+  if (pl.warps < 1) return 0;
   const size_t per = (size_t)((M - 1) << order) * (size_t)((N - 1) << order) + (size_t)(M - 1) * (N - 1);
-  return (size_t)A * std::max(1, pl.chunks) * std::max(1, pl.warps) * per * 8;
+  return (size_t)A * pl.chunks * pl.warps * per * 8;
 }
 
 int launch_sigpde_bwd(const double* x, const double* y, int64_t A, int64_t B, int64_t M, int64_t N, int64_t D,
@@ -382,8 +392,9 @@ int launch_sigpde_bwd(const double* x, const double* y, int64_t A, int64_t B, in
   SIG_CHECK_ARG(A <= 65535, "sigpde_gram_bwd: A > 65535");
   const BwdPlan pl = bwd_plan(A, B, M, N, D, order);
   if (pl.warps < 1) {
-    set_error("sigpde_gram_bwd: M=%lld N=%lld D=%lld order=%d does not fit the shared-memory resident pair state",
-              (long long)M, (long long)N, (long long)D, order);
+    set_error(pl.warps < 0 ? "sigpde_gram_bwd: A=%lld M=%lld N=%lld order=%d: the parked reverse solves exceed 16 GiB of scratch"
+                           : "sigpde_gram_bwd: A=%lld M=%lld N=%lld order=%d does not fit the shared-memory resident pair state",
+              (long long)A, (long long)M, (long long)N, order);
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   if (ws_bytes < sigpde_bwd_workspace_bytes(A, B, M, N, D, order)) {

@@ -74,6 +74,20 @@ def test_median_bandwidth_over_all_point_pairs(A, B, M, N, D):
     assert rel_max(got.cpu().numpy(), want) <= TOL
 
 
+@pytest.mark.parametrize("name", ["maze", "small", "panda"])
+def test_vs_reference_golden_static_kernel(name):
+    """The reference's own BatchGaussianKernel.Gram_matrix output (median heuristic and a constant
+    bandwidth), pushed through the solver restatement: tests/golden/sigpde_static.npz."""
+    from tests.util import load_golden
+
+    g = load_golden("sigpde_static")
+    X, Y, order = g[f"{name}_X"], g[f"{name}_Y"], int(g[f"{name}_order"])
+    k_fix = ops.sigpde_gram(cu(X), cu(Y), order, _lib.PDE_RBF, 0.75)
+    assert rel_max(k_fix.cpu().numpy(), g[f"{name}_k_fix"]) <= TOL
+    k_med = ops.sigpde_gram(cu(X), cu(Y), order)  # h=None: the median heuristic over all point pairs
+    assert rel_max(k_med.cpu().numpy(), g[f"{name}_k_med"]) <= 1e-6  # (the bandwidth record is float32)
+
+
 def test_signature_kernel_class_runs_the_reference_statements():
     """score.py:64-76: k_xx = kernel(x, x.detach()); grad_k = ag(k_xx.sum(), x)[0] (fp32 in, fp32 out)."""
     X = _paths(12, 10, 2, 6).astype(np.float32)

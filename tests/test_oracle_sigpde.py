@@ -46,7 +46,7 @@ def test_median_bandwidth_convention():
     _, dist = so.static_gram(X, Y, so.RBF, 1.0)
     h, med = so.bw_median_points(dist)
     ref = torch.median(torch.as_tensor(dist))  # lower median of all A*B*M*N entries
-    assert med == float(ref) and h == pytest.approx(np.sqrt(med / np.log(4 + 1.0)))
+    assert med == float(ref) and h == pytest.approx(np.sqrt(med / np.log(4 + 1.0)), rel=1e-7)
 
 
 @pytest.mark.parametrize("kind,h", [(so.RBF, 0.9), (so.LINEAR, 0.7)])
@@ -65,3 +65,18 @@ def test_backward_formula_approaches_the_exact_discrete_derivative(kind, h):
         errs.append(np.abs(got - exact).max() / np.abs(exact).max())
     # first-order convergence (the formula pairs K at a cell's lower corner with K_rev at its upper corner)
     assert errs[1] < 0.4 * errs[0] and errs[2] < 0.3 * errs[1] and errs[2] < 3e-2
+
+
+@pytest.mark.parametrize("name", ["maze", "small", "panda"])
+def test_static_kernel_and_bandwidth_convention_vs_reference_golden(name):
+    """tests/golden/sigpde_static.npz: the reference's own BatchGaussianKernel.Gram_matrix (median
+    heuristic over the [A,B,M,N] tensor with ln(A + 1); ``exp(-dist / h)``), pushed through the solver."""
+    from tests.util import load_golden
+
+    g = load_golden("sigpde_static")
+    X, Y, order = g[f"{name}_X"], g[f"{name}_Y"], int(g[f"{name}_order"])
+    _, dist = so.static_gram(X, Y, so.RBF, 1.0)
+    h, _ = so.bw_median_points(dist)
+    assert h == pytest.approx(float(g[f"{name}_h_med"]), rel=1e-9)
+    assert np.allclose(so.sigpde_gram(X, Y, order, so.RBF, h), g[f"{name}_k_med"], rtol=1e-9)
+    assert np.allclose(so.sigpde_gram(X, Y, order, so.RBF, 0.75), g[f"{name}_k_fix"], rtol=1e-12)

@@ -181,3 +181,41 @@ def test_mpc_golden_is_reproducible_from_the_unmodified_controller():
     assert np.abs(record["tau"][1] - g["tau"][1]).max() < 1e-5
     assert rel_max(data[1]["grad_k"].numpy(), g["grad_k"][1]) < 1e-4
     assert rel_max(a_seq.numpy(), g["a_seq"][0]) < 1e-4
+
+
+def test_unmodified_reference_signature_kernel_over_the_oracle_solver():
+    """src/kernels/_traj_kernels.py:198-206 ``SignatureKernel`` UNMODIFIED, with a ``sigkernel`` stand-in whose
+    ``compute_Gram`` = the reference's own ``static_kernel.Gram_matrix`` + the oracle's Goursat recursion:
+    what ``sigsvgd_b200.kernels.SignatureKernel`` must reproduce (checked on the GPU against the same
+    oracle functions in tests/test_gpu_sigpde.py)."""
+    import sys
+    import types
+
+    from oracle import sigpde_oracle as so
+
+    sk = types.ModuleType("sigkernel")
+
+    class SigKernel:
+        def __init__(self, static_kernel, dyadic_order=0):
+            self.static_kernel, self.dyadic_order = static_kernel, dyadic_order
+
+        def compute_Gram(self, X, Y, sym=False):
+            G = self.static_kernel.Gram_matrix(X, Y).numpy()
+            return torch.as_tensor(so._solve(so.increments(G), self.dyadic_order)[..., -1, -1])
+
+    sk.SigKernel, sk.RBFKernel = SigKernel, object
+    ref_shim.import_reference(sigkernel_module=sk)
+    import src.kernels._traj_kernels as tk
+
+    old = tk.sigkernel
+    tk.sigkernel = sk
+    try:
+        X, _ = _inputs(N=6, T=7, d=2, seed=11)
+        X = X.float()
+        k_ref = tk.SignatureKernel(depth=2)(X, X)  # median heuristic, dyadic_order = depth
+        assert k_ref.dtype == torch.float32 and k_ref.shape == (6, 6)
+        X64 = X.double().numpy()
+        h, _ = so.bw_median_points(so.static_gram(X64, X64, so.RBF, 1.0)[1])
+        assert rel_max(k_ref.numpy(), so.sigpde_gram(X64, X64, 2, so.RBF, h)) < 1e-6
+    finally:
+        tk.sigkernel = old

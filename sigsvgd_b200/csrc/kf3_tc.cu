@@ -49,22 +49,31 @@ constexpr uint32_t kFRedBytes = 128;
 constexpr int kFMaxChainKb = 1024 / FK;
 constexpr float kKScale = 16384.f;  // K in [0,1] -> [0, 2^14] (planes.cu uses the same scaling)
 
-template <bool kPair>
+// kWide (pairs only): an item is up to 512 columns wide -- both halves of TMEM as ONE accumulator set
+// (columns 0-255 and 256-511, two MMAs per pass sharing the converted A stage), so every distance tile is
+// fetched and converted once per 512 output columns instead of once per 256; the price is that the
+// epilogue of an item no longer overlaps the MMAs of the next.
+template <bool kPair, bool kWide = false>
 struct FCfg {
-  static constexpr int kStages = kPair ? 6 : 4;
-  static constexpr int kBCols = kPair ? FN / 2 : FN;             // columns of B staged per CTA
+  static_assert(kPair || !kWide, "wide items need CTA pairs");
+  static constexpr int kTileCols = kWide ? 2 * FN : FN;          // columns per item (upper bound)
+  static constexpr int kStages = kWide ? 4 : (kPair ? 6 : 4);
+  static constexpr int kBCols = kPair ? kTileCols / 2 : kTileCols;  // columns of B staged per CTA
   static constexpr uint32_t kBBytes = kBCols * FK * 2;           // per plane
   static constexpr uint32_t kStageBytes = kFABytes + 2 * kBBytes;
   static constexpr uint32_t kSmemBytes = kStages * kStageBytes + kFBarBytes + kFXposeBytes + kFRedBytes + 1024;
   static constexpr int kCtas = kPair ? 2 : 1;
 };
-static_assert(FCfg<true>::kSmemBytes <= 232448 && FCfg<false>::kSmemBytes <= 232448, "shared memory");
+static_assert(FCfg<true>::kSmemBytes <= 232448 && FCfg<false>::kSmemBytes <= 232448 &&
+                  FCfg<true, true>::kSmemBytes <= 232448,
+              "shared memory");
 
 struct FusedParams {
   int64_t M, N;          // output rows, columns
   int64_t row_offset;    // global index of row 0 (tie records)
   int num_k16;
   int tiles_m, tiles_n;
+  int tile_cols;         // columns per item (multiple of 32; <= 256, or <= 512 for the wide kernel)
   int nsplit, kb_per_split;
   int mode;              // SIGSVGD_KF_EXP: A = exp(gamma * a) ; SIGSVGD_KF_IDENTITY: A = a
   int stats;             // accumulate state->sum_kd / ties (first column tile only)
@@ -85,11 +94,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
-template <bool kPair>
+template <bool kPair, bool kWide>
 __global__ void __launch_bounds__(kFThreads, 1)
 kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                 const __grid_constant__ CUtensorMap tmBl, const FusedParams p) {
-  using Cfg = FCfg<kPair>;
+  using Cfg = FCfg<kPair, kWide>;
   constexpr int kStages = Cfg::kStages;
   constexpr uint32_t kBBytes = Cfg::kBBytes, kStageBytes = Cfg::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
@@ -160,7 +169,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int sp = rem - k.tn * p.nsplit;
     k.kb0 = sp * p.kb_per_split;
     k.kb1 = min(num_kb_total, k.kb0 + p.kb_per_split);
-    k.ncols = (int)min((int64_t)FN, ((p.N - (int64_t)k.tn * FN) + 15) / 16 * 16);
+    k.ncols = (int)min((int64_t)p.tile_cols, ((p.N - (int64_t)k.tn * p.tile_cols) + 15) / 16 * 16);
     return k;
   };
   constexpr int kRowsPerUnit = FM * Cfg::kCtas;
@@ -171,10 +180,14 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       uint32_t it = 0;
       for (int w = unit; w < num_work; w += nunits) {
         const Work wk = decode(w);
-        const int ncta_cols = kPair ? wk.ncols / 2 : wk.ncols;  // columns of B this CTA stages
+        // columns of B this CTA stages: its half of the item, or (wide) its halves of the item's two parts
+        const int n0 = min(wk.ncols, FN), n1 = wk.ncols - n0;
+        const int ncta_cols = kPair ? n0 / 2 : n0;
         const int nbox = (ncta_cols + 63) / 64;
+        const int nbox1 = kWide ? (n1 / 2 + 63) / 64 : 0;
         const int row = (int)(wk.b * p.a_batch_rows) + wk.tm * kRowsPerUnit + (int)rank * FM;
-        const int col = wk.tn * FN + (int)rank * ncta_cols;
+        const int col = wk.tn * p.tile_cols + (int)rank * ncta_cols;
+        const int col1 = wk.tn * p.tile_cols + FN + (int)rank * (n1 / 2);
         const int vrow0 = (int)(wk.b * p.v_batch_rows);
         for (int kb = wk.kb0; kb < wk.kb1; ++kb, ++it) {
           const int s = it % kStages;
@@ -185,9 +198,17 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           ptx::mbar_expect_tx(raw_bar(s), kFABytes);
           ptx::tma_load_2d(st, &tmA, raw_bar(s), kb * FK, row);
           // B: completion counted on the leader's barrier (bytes of every CTA of the unit)
-          if (leader) ptx::mbar_expect_tx(full_bar(s), Cfg::kCtas * 2 * nbox * (FK * 128));
+          if (leader) ptx::mbar_expect_tx(full_bar(s), Cfg::kCtas * 2 * (nbox + nbox1) * (FK * 128));
+          if constexpr (kWide) {
+            // second part of the item (columns 256..ncols): boxes 2, 3 of the stage
+            for (int q = 0; q < nbox1; ++q) {
+              const uint32_t dh = st + kFABytes + (2 + q) * (FK * 128), dl = dh + kBBytes;
+              ptx::tma_load_2d_pair(dh, &tmBh, full_bar(s), col1 + q * 64, vrow0 + kb * FK);
+              ptx::tma_load_2d_pair(dl, &tmBl, full_bar(s), col1 + q * 64, vrow0 + kb * FK);
+            }
+          }
 #pragma unroll
-          for (int q = 0; q < Cfg::kBCols / 64; ++q) {
+          for (int q = 0; q < (kWide ? 2 : Cfg::kBCols / 64); ++q) {
             if (q >= nbox) break;
             const uint32_t dh = st + kFABytes + q * (FK * 128), dl = dh + kBBytes;
             if constexpr (kPair) {
@@ -207,9 +228,11 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       uint32_t it = 0, tcount = 0;
       for (int w = unit; w < num_work; w += nunits, ++tcount) {
         const Work wk = decode(w);
-        const uint32_t idesc = ptx::make_idesc_f16(kRowsPerUnit, wk.ncols, false, true);
-        const int a = tcount & 1;
-        const uint32_t aph = (tcount >> 1) & 1u;
+        const int n0 = min(wk.ncols, FN), n1 = wk.ncols - n0;
+        const uint32_t idesc = ptx::make_idesc_f16(kRowsPerUnit, n0, false, true);
+        const uint32_t idesc1 = ptx::make_idesc_f16(kRowsPerUnit, max(n1, 16), false, true);
+        const int a = kWide ? 0 : (int)(tcount & 1);
+        const uint32_t aph = kWide ? (tcount & 1u) : ((tcount >> 1) & 1u);
         ptx::mbar_wait(tempty_bar(a), aph ^ 1u);
         ptx::tc_fence_after();
         const uint32_t tacc = tmem_base + a * FN;
@@ -229,7 +252,20 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const uint64_t bh = ptx::make_smem_desc(st + kFABytes + k * 2048, FK * 128, 1024, ptx::kLayoutSw128);
             const uint64_t bl =
                 ptx::make_smem_desc(st + kFABytes + kBBytes + k * 2048, FK * 128, 1024, ptx::kLayoutSw128);
-            if constexpr (kPair) {
+            if constexpr (kWide) {
+              ptx::umma_f16_pair(tacc, ah, bh, idesc, accumulate);
+              ptx::umma_f16_pair(tacc, ah, bl, idesc, 1u);
+              ptx::umma_f16_pair(tacc, al, bh, idesc, 1u);
+              if (n1 > 0) {
+                const uint64_t bh1 = ptx::make_smem_desc(st + kFABytes + 2 * (FK * 128) + k * 2048, FK * 128, 1024,
+                                                         ptx::kLayoutSw128);
+                const uint64_t bl1 = ptx::make_smem_desc(st + kFABytes + kBBytes + 2 * (FK * 128) + k * 2048, FK * 128,
+                                                         1024, ptx::kLayoutSw128);
+                ptx::umma_f16_pair(tacc + FN, ah, bh1, idesc1, accumulate);
+                ptx::umma_f16_pair(tacc + FN, ah, bl1, idesc1, 1u);
+                ptx::umma_f16_pair(tacc + FN, al, bh1, idesc1, 1u);
+              }
+            } else if constexpr (kPair) {
               ptx::umma_f16_pair(tacc, ah, bh, idesc, accumulate);
               ptx::umma_f16_pair(tacc, ah, bl, idesc, 1u);
               ptx::umma_f16_pair(tacc, al, bh, idesc, 1u);
@@ -379,16 +415,16 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t leader_tempty0 = kPair ? ptx::mapa(tempty_bar(0), 0) : tempty_bar(0);
     for (int w = unit; w < num_work; w += nunits, ++tcount) {
       const Work wk = decode(w);
-      const int a = tcount & 1;
-      const uint32_t aph = (tcount >> 1) & 1u;
+      const int a = kWide ? 0 : (int)(tcount & 1);
+      const uint32_t aph = kWide ? (tcount & 1u) : ((tcount >> 1) & 1u);
       ptx::mbar_wait(tfull_bar(a), aph);
       ptx::tc_fence_after();
       const int64_t row0 = (int64_t)wk.tm * kRowsPerUnit + (int64_t)rank * FM + q * 32;  // within the problem
       float* const outb = p.out + (int64_t)wk.b * p.M * p.ldo;
       const float* const csb = p.colscale + (int64_t)wk.b * p.colscale_stride;
 #pragma unroll 1
-      for (int c = 0; c < FN / 32; ++c) {
-        const int64_t col0 = (int64_t)wk.tn * FN + c * 32;
+      for (int c = 0; c < Cfg::kTileCols / 32; ++c) {
+        const int64_t col0 = (int64_t)wk.tn * p.tile_cols + c * 32;
         if (c * 32 >= wk.ncols || col0 >= p.N) break;  // warp-uniform
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * FN + c * 32, v);
@@ -461,9 +497,11 @@ int max_pairs() {
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
   if (dev == cached_dev) return cached;
   cached_dev = dev, cached = 0;
-  if (cudaFuncSetAttribute(kf_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  if (cudaFuncSetAttribute(kf_fused_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)FCfg<true>::kSmemBytes) != cudaSuccess ||
-      cudaFuncSetAttribute(kf_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaFuncSetAttribute(kf_fused_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)FCfg<true, true>::kSmemBytes) != cudaSuccess ||
+      cudaFuncSetAttribute(kf_fused_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)FCfg<false>::kSmemBytes) != cudaSuccess) {
     cudaGetLastError();
     return 0;
@@ -477,7 +515,7 @@ int max_pairs() {
   attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr, cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, kf_fused_kernel<true>, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&n, kf_fused_kernel<true, false>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     n = 0;
   }
@@ -511,14 +549,25 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
   FusedParams p;
   p.M = M, p.N = C, p.row_offset = row_offset;
   p.num_k16 = (int)ceil_div(K, 16);
-  p.tiles_m = (int)ceil_div(M, pair ? 2 * FM : FM), p.tiles_n = (int)ceil_div(C, FN);
+  // wide items (<= 512 columns, pairs only) when there is more than one 256-column tile: the fp32 operand is
+  // fetched and converted once per item, so halving the number of column tiles halves that traffic.
+  // Columns are dealt evenly over the tiles (widths a multiple of 32).
+  // Their epilogue does not overlap the next item's MMAs, so they only pay while there are few, long
+  // chains: enough items of full (1024-index) chains to occupy every pair.  Measured at N = 4096, C = 848
+  // (us, L2 flushed): narrow 101; wide with chains of 256 / 512 / 1024 indices 132 / 112 / 93
+  // (chains of 2048: 83, but twice the truncation error of the TMEM accumulation).
   const int units_max = pair ? pairs_max : num_sms();
-  const int num_kb = (p.num_k16 + 1) / 2;
+  const int num_kb = (int)ceil_div(ceil_div(K, 16), 2);
+  const bool wide = pair && batch == 1 && C > FN &&
+                    ceil_div(M, 2 * FM) * ceil_div(C, 2 * FN) * ceil_div(num_kb, kFMaxChainKb) >= units_max;
+  const int64_t max_cols = wide ? 2 * FN : FN;
+  p.tiles_m = (int)ceil_div(M, pair ? 2 * FM : FM), p.tiles_n = (int)ceil_div(C, max_cols);
+  p.tile_cols = wide ? (int)round_up(ceil_div(C, p.tiles_n), 32) : FN;
   // chains of at most 1024 contraction indices (the TMEM accumulator adds with truncation); shorter
   // ones while there are fewer than ~6 items per unit, never below 8 K blocks
   p.kb_per_split = std::min(num_kb, kFMaxChainKb);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
-  while (batch * p.tiles_m * p.tiles_n * p.nsplit < 6ll * units_max && num_kb / (2 * p.nsplit) >= 8)
+  while (!wide && batch * p.tiles_m * p.tiles_n * p.nsplit < 6ll * units_max && num_kb / (2 * p.nsplit) >= 8)
     p.nsplit *= 2;
   p.kb_per_split = (int)ceil_div(num_kb, p.nsplit);
   p.nsplit = (int)ceil_div(num_kb, p.kb_per_split);
@@ -532,23 +581,24 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
   const int units = (int)std::min<int64_t>(items, units_max);
   if (!pair) {
     if (pairs_max <= 0) {  // attributes were not set by max_pairs()
-      SIG_CUDA_OK(cudaFuncSetAttribute(kf_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      SIG_CUDA_OK(cudaFuncSetAttribute(kf_fused_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)FCfg<false>::kSmemBytes));
     }
-    kf_fused_kernel<false><<<units, kFThreads, FCfg<false>::kSmemBytes, st>>>(ta, bh, bl, p);
+    kf_fused_kernel<false, false><<<units, kFThreads, FCfg<false>::kSmemBytes, st>>>(ta, bh, bl, p);
     SIG_LAUNCH_OK("kf_fused_kernel<single>");
     return 0;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * (unsigned)units);
   cfg.blockDim = dim3(kFThreads);
-  cfg.dynamicSmemBytes = FCfg<true>::kSmemBytes;
+  cfg.dynamicSmemBytes = wide ? FCfg<true, true>::kSmemBytes : FCfg<true>::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr, cfg.numAttrs = 1;
-  SIG_CUDA_OK(cudaLaunchKernelEx(&cfg, kf_fused_kernel<true>, ta, bh, bl, p));
+  if (wide) SIG_CUDA_OK(cudaLaunchKernelEx(&cfg, kf_fused_kernel<true, true>, ta, bh, bl, p));
+  else SIG_CUDA_OK(cudaLaunchKernelEx(&cfg, kf_fused_kernel<true, false>, ta, bh, bl, p));
   SIG_LAUNCH_OK("kf_fused_kernel<pair>");
   return 0;
 }

@@ -14,6 +14,11 @@
  *    synchronisation and no allocation, and is CUDA-graph capturable;
  *  - return value 0 = success; otherwise an SIGSVGD_ERR_* code, message via
  *    sigsvgd_last_error() (thread-local).  There is no CPU fallback: unsupported shapes fail.
+ *  - host threads: every entry point may be called from several threads.  sigsvgd_phi and
+ *    sigsvgd_phi_host share one internal side stream / copy-stream set (and its events) per device, so
+ *    their ENQUEUE phase is serialised per device inside the library (a mutex held for the ~50 us of
+ *    host work); the GPU work of concurrent calls on different caller streams is ordered correctly but
+ *    passes through that one side stream.  sigsvgd_median_bandwidth_static shares its scratch (see there).
  */
 #ifndef SIGSVGD_B200_H_
 #define SIGSVGD_B200_H_

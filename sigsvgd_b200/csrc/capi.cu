@@ -702,12 +702,23 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   return 0;
 }
 
+// sigsvgd_phi / sigsvgd_phi_host fork work onto ONE side stream / copy-stream set per device and order it
+// with one set of events: the record / wait pairs of a call must not interleave with another host
+// thread's, so the enqueue phase of these two entry points is serialised per device.
+static std::mutex& enqueue_mutex() {
+  static std::mutex table[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  return table[dev];
+}
+
 extern "C" {
 
 int sigsvgd_phi(const float* x, const float* score, int64_t B, int64_t N, int64_t T, int64_t d,
                 int depth, int bw_mode, float h_fixed, float bw_scale, float tol, uint32_t flags,
                 float* phi, float* k_out, float* gradk_out, float* sig_out,
                 sigsvgd_bw_state* state, void* ws, size_t ws_bytes, void* stream) {
+  std::lock_guard<std::mutex> lock(enqueue_mutex());
   return phi_pipeline(x, score, B, N, T, d, depth, bw_mode, h_fixed, bw_scale, tol, flags, phi, k_out,
                       gradk_out, sig_out, state, ws, ws_bytes, stream, nullptr);
 }
@@ -733,6 +744,7 @@ int sigsvgd_phi_host(const float* x_host, const float* score_host, int64_t N, in
               sigsvgd_phi_host_workspace_bytes(N, T, d, depth));
     return SIGSVGD_ERR_WORKSPACE;
   }
+  std::lock_guard<std::mutex> lock(enqueue_mutex());
   HostPipe* hp = nullptr;
   SIG_PROPAGATE(host_pipe(&hp));
   const size_t bytes = sizeof(float) * (size_t)(N * T * d);

@@ -90,3 +90,38 @@ def test_phi_plan_batch_of_scenes():
         keep[sorted(skip)] = False
         den = want.phi[b][keep].abs().max().item()
         assert (got.phi[b][keep] - want.phi[b][keep]).abs().max().item() <= 1e-5 * den
+
+
+def test_two_host_threads_on_one_device():
+    """sigsvgd_phi shares one side stream and event set per device; the library serialises the enqueue
+    phase per device (include/sigsvgd_b200.h, "host threads"), so concurrent callers on their own streams
+    get the results of sequential calls."""
+    import threading
+
+    N, T, d = 512, 16, 3
+    gen = torch.Generator().manual_seed(21)
+    inputs = [(torch.cumsum(0.1 * torch.randn(N, T, d, generator=gen), 1).to("cuda:0"),
+               torch.randn(N, T * d, generator=gen).to("cuda:0")) for _ in range(2)]
+    want = [ops.phi(x, g).phi.clone() for x, g in inputs]
+    torch.cuda.synchronize()
+    got, errs = [None, None], []
+
+    def work(i):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(25):
+                    r = ops.phi(*inputs[i])
+                got[i] = r.phi.clone()
+            st.synchronize()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errs, errs
+    for i in range(2):
+        assert float((got[i] - want[i]).abs().max() / want[i].abs().max()) < 1e-5

@@ -54,7 +54,12 @@ static int side_stream(SideStream** out) {
   std::lock_guard<std::mutex> lock(mu);
   SideStream& s = table[dev];
   if (!s.stream) {
-    SIG_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    // highest priority: the side work (the median's sampling pass) is small and latency-bound; it should
+    // take its SMs as soon as it is ready instead of queueing behind the main stream's wide kernels and
+    // then running beside -- and slowing -- the Gram
+    int prio_lo = 0, prio_hi = 0;
+    SIG_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    SIG_CUDA_OK(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_hi));
     SIG_CUDA_OK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
     SIG_CUDA_OK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
   }

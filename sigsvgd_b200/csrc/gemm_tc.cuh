@@ -38,7 +38,7 @@ struct SelWindow {
 constexpr int kMaxPools = 1024;
 // Counter block behind the pools: pool_cnt[0..kMaxPools) fill of pool b, [kMaxPools..2*kMaxPools)
 // entries below the window seen by block b, then 64 words `misc`:
-//   misc[epoch]            fill of the short list          misc[2]            ticket of window_prepare
+//   misc[epoch]            fill of the short list          misc[2]            (unused)
 //   misc[8 + 4*epoch + 0]  candidates kept (all pools)     misc[8 + 4*epoch + 1]  pool-overflow flag
 //   misc[8 + 4*epoch + 2..3]  entries below the window (u64)
 //   misc[16 + epoch]       ticket of the short-list finish

@@ -137,31 +137,26 @@ __device__ float block_select_smem(const float* vals, int n, unsigned long long 
   return __uint_as_float(prefix);
 }
 
-// Fused window preparation.  Every warp evaluates two sample entries d = |a_i - b_j|^2 (fp32
-// difference form; the features need not be centred; all loads of a sample in flight at once).  The
-// last block to finish (ticket counter) selects the sample order statistics m/2 -+ 5.7 sigma with two
-// histogram passes (both bounds at once) and sets the window; it also resets the window / histogram /
-// bandwidth records.
+// Window preparation, two launches on the side stream:
+//  window_sample_kernel  every warp evaluates two sample entries d = |a_i - b_j|^2 (fp32 difference
+//    form; the features need not be centred; all loads of a sample in flight at once).  Small blocks
+//    (256 threads): they find room on SMs that the main stream's packing pass is still using, instead of
+//    waiting for it to drain and then running beside -- and slowing -- the Gram (which cost it 4-5 us
+//    when sampling and bounds were one kernel of 1024-thread blocks);
+//  window_bounds_kernel  one block selects the sample order statistics m/2 -+ kSampleHalfWin with two
+//    histogram passes (both bounds at once) and sets the window; it also resets the window /
+//    histogram / bandwidth records.
 constexpr int kPrepThreads = 1024;
-constexpr int kSamplesPerBlock = 64;
+constexpr int kSampleThreads = 256;
+constexpr int kSamplesPerBlock = 2 * (kSampleThreads / 32);
 
-__global__ void __launch_bounds__(kPrepThreads)
-window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
-                      const float* __restrict__ b, int64_t ldb, int64_t N, int64_t D,
-                      float* __restrict__ sample, unsigned int* ticket, SelWindow* win,
-                      unsigned int cap, unsigned int npool, unsigned long long* ghist /*[2*3*kBins]*/,
-                      unsigned int* pool_cnt /*[2*kMaxPools + 64]*/, sigsvgd_bw_state* state) {
-  extern __shared__ float sv[];  // kSample floats (last block only)
-  __shared__ bool sh_last;
-  __shared__ unsigned int hist[2][kBins];
-  __shared__ unsigned long long scratch[1024];
-  __shared__ float sh_red[64];
-  __shared__ uint32_t sh_bucket[2];
-  __shared__ unsigned long long sh_k[2];
+__global__ void __launch_bounds__(kSampleThreads)
+window_sample_kernel(const float* __restrict__ a, int64_t lda, int64_t M, const float* __restrict__ b,
+                     int64_t ldb, int64_t N, int64_t D, float* __restrict__ sample) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll 1
-  for (int q = 0; q < kSamplesPerBlock / (kPrepThreads / 32); ++q) {
-    const int sidx = blockIdx.x * kSamplesPerBlock + q * (kPrepThreads / 32) + wid;
+  for (int q = 0; q < kSamplesPerBlock / (kSampleThreads / 32); ++q) {
+    const int sidx = blockIdx.x * kSamplesPerBlock + q * (kSampleThreads / 32) + wid;
     const int64_t i = (int64_t)(((uint64_t)hash32(2u * sidx + 1u) * (uint64_t)M) >> 32);
     const int64_t j = (int64_t)(((uint64_t)hash32(2u * sidx + 0x9e3779b9u) * (uint64_t)N) >> 32);
     const float* __restrict__ ai = a + i * lda;
@@ -187,15 +182,22 @@ window_prepare_kernel(const float* __restrict__ a, int64_t lda, int64_t M,
     for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0) sample[sidx] = acc;
   }
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) sh_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!sh_last) return;
-  __threadfence();
+}
+
+__global__ void __launch_bounds__(kPrepThreads)
+window_bounds_kernel(const float* __restrict__ sample, SelWindow* win, unsigned int cap, unsigned int npool,
+                     unsigned long long* ghist /*[2*3*kBins]*/, unsigned int* pool_cnt /*[2*kMaxPools + 64]*/,
+                     sigsvgd_bw_state* state) {
+  extern __shared__ float sv[];  // kSample floats
+  __shared__ unsigned int hist[2][kBins];
+  __shared__ unsigned long long scratch[1024];
+  __shared__ float sh_red[64];
+  __shared__ uint32_t sh_bucket[2];
+  __shared__ unsigned long long sh_k[2];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < kSample; i += kPrepThreads) sv[i] = __ldcg(sample + i);
   for (int i = threadIdx.x; i < 2 * 3 * kBins; i += kPrepThreads) ghist[i] = 0ull;
-  for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += kPrepThreads) pool_cnt[i] = 0u;  // incl. the ticket
+  for (int i = threadIdx.x; i < 2 * kMaxPools + 64; i += kPrepThreads) pool_cnt[i] = 0u;
   __syncthreads();
   // Window bounds = sample order statistics m/2 -+ 5.7 sigma, located by two levels of 2048 linear
   // bins (whole range, then the selected bin) and rounded OUTWARD by one fine bin: the bounds only
@@ -689,20 +691,21 @@ int launch_window_prepare(const float* a, int64_t lda, int64_t M, const float* b
   window_carve(ws, &win, &sample, &ghist, &pool_cnt, &cand);
   unsigned int cap = 0;
   window_workspace_bytes(M, N, &cap);
-  unsigned int* ticket = pool_cnt + 2 * kMaxPools + 2;
-  SIG_CUDA_OK(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
   static thread_local int configured_dev = -1;
   int dev = 0;
   SIG_CUDA_OK(cudaGetDevice(&dev));
   if (configured_dev != dev) {
-    SIG_CUDA_OK(cudaFuncSetAttribute(window_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SIG_CUDA_OK(cudaFuncSetAttribute(window_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(sizeof(float) * kSample)));
     configured_dev = dev;
   }
   const unsigned int npool = (unsigned int)std::min(num_sms(), kMaxPools);
-  window_prepare_kernel<<<kSample / kSamplesPerBlock, kPrepThreads, sizeof(float) * kSample, st>>>(
-      a, lda, M, b, ldb, N, D, sample, ticket, win, cap, npool, ghist, pool_cnt, state);
-  SIG_LAUNCH_OK("window_prepare_kernel");
+  static_assert(kSample % kSamplesPerBlock == 0, "whole blocks of samples");
+  window_sample_kernel<<<kSample / kSamplesPerBlock, kSampleThreads, 0, st>>>(a, lda, M, b, ldb, N, D, sample);
+  SIG_LAUNCH_OK("window_sample_kernel");
+  window_bounds_kernel<<<1, kPrepThreads, sizeof(float) * kSample, st>>>(sample, win, cap, npool, ghist, pool_cnt,
+                                                                         state);
+  SIG_LAUNCH_OK("window_bounds_kernel");
   *win_out = win;
   *cand_out = cand;
   return 0;

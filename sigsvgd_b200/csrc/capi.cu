@@ -666,9 +666,11 @@ static int phi_pipeline(const float* x, const float* score, int64_t B, int64_t N
   }
   // sig-space gradient, then K2 with the fused epilogue phi = (K.score - grad_k)/N
   // (one swarm, depth 3: the backward kernel forms the cotangent itself while staging)
-  const bool fuse_grad = B == 1 && sig_bwd_fuses_grad(d, depth);
+  // (batches of scenes: the same, each scene with its own record; scenes of a multiple of 8 particles)
+  const bool fuse_grad = sig_bwd_fuses_grad(d, depth) && (B == 1 || N % 8 == 0);
   SigGradSpec gs{feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, 0, state};
-  gs.coef_mode = use_tc ? (median_grad ? 1 : 2) : 0;
+  gs.coef_mode = (use_tc && B == 1) ? (median_grad ? 1 : 2) : 0;
+  gs.scene_rows = B > 1 ? N : 0;
   const SigGradSpec* spec = fuse_grad ? &gs : nullptr;
   if (!fuse_grad)
     SIG_PROPAGATE(launch_sig_grad(feat, ldf, feat, ldf, out_ks, C, out_rowsum, C, N, D, N, 0, state,

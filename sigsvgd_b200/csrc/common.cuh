@@ -91,7 +91,21 @@ struct SigGradSpec {
   const sigsvgd_bw_state* state;  // one record
   int coef_mode = 0;     // 0: state->coef / n_ties_all as set by median_coef; 1: derive them from the
                          // record's own sum_kd / n_ties (and store them); 2: same, gradient term off
+  // batches of independent scenes stacked along the rows (0 = one problem): scene b = row / scene_rows has
+  // its own record state[b], its tie indices count from the scene's first row, and its partners are
+  // the scene's own rows of sc_all.  coef_mode must be 0 then.
+  int64_t scene_rows = 0;
 };
+// the spec as the scene of global row `row` sees it
+__device__ __forceinline__ SigGradSpec scene_view(SigGradSpec gs, int64_t row) {
+  if (gs.scene_rows > 0 && gs.sc != nullptr) {
+    const int64_t scene = row / gs.scene_rows, r0 = scene * gs.scene_rows;
+    gs.state += scene;
+    gs.sc_all += r0 * gs.lds_all;
+    gs.row_offset = -r0;
+  }
+  return gs;
+}
 // Median-gradient coefficient for the fused cotangent: either the record's (coef_mode 0: set by
 // median_coef_kernel, e.g. from all-reduced sums on the sharded path) or derived here from the
 // record's own sums, coef = sum_kd / (h^2 median) -- one launch less

@@ -23,20 +23,21 @@ __global__ void __launch_bounds__(kThreads)
 absmax_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ mean, int64_t N,
               int64_t D, const float* __restrict__ score, int64_t lsc, int64_t P,
               unsigned int* __restrict__ mx) {
+  // a warp per row, lanes along the columns (coalesced, no index arithmetic per element)
   const int b = blockIdx.y;
-  const int64_t W = D + P;
-  const int64_t total = N * W;
+  const int lane = threadIdx.x & 31, wpb = kThreads / 32;
+  const float* __restrict__ mb = mean ? mean + (int64_t)b * D : nullptr;
   float ms = 0.f, mg = 0.f;
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * kThreads) {
-    const int64_t r = i / W, c = i - r * W;
-    const int64_t row = (int64_t)b * N + r;
-    if (c < D) {
-      float v = __ldg(s + row * lds + c);
-      if (mean) v -= __ldg(mean + (int64_t)b * D + c);
+  for (int64_t r = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5); r < N; r += (int64_t)gridDim.x * wpb) {
+    const float* __restrict__ sr = s + ((int64_t)b * N + r) * lds;
+    for (int64_t c = lane; c < D; c += 32) {
+      float v = __ldg(sr + c);
+      if (mb) v -= __ldg(mb + c);
       ms = fmaxf(ms, fabsf(v));
-    } else {
-      mg = fmaxf(mg, fabsf(__ldg(score + row * lsc + (c - D))));
+    }
+    if (score) {
+      const float* __restrict__ gr = score + ((int64_t)b * N + r) * lsc;
+      for (int64_t c = lane; c < P; c += 32) mg = fmaxf(mg, fabsf(__ldg(gr + c)));
     }
   }
 #pragma unroll
@@ -44,7 +45,7 @@ absmax_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict_
     ms = fmaxf(ms, __shfl_xor_sync(0xffffffffu, ms, o));
     mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
   }
-  if ((threadIdx.x & 31) == 0) {
+  if (lane == 0) {
     // NaN/inf inputs propagate through the GEMM anyway; the scale only needs finite maxima
     if (ms > 0.f && ms < INFINITY) atomicMax(mx + 2 * b, __float_as_uint(ms));
     if (mg > 0.f && mg < INFINITY) atomicMax(mx + 2 * b + 1, __float_as_uint(mg));
@@ -330,8 +331,10 @@ int launch_tc_scales(const float* s, int64_t lds, const float* mean, int64_t N, 
                 "tc_scales: bad shape N=%lld D=%lld P=%lld Cp=%lld", (long long)N, (long long)D,
                 (long long)P, (long long)Cp);
   SIG_CUDA_OK(cudaMemsetAsync(mx, 0, sizeof(unsigned int) * 2 * batch, st));
-  const int64_t want = ceil_div(N * (D + P), (int64_t)kThreads * 8);
-  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)num_sms() * 8));
+  // rows of a scene are dealt to gx blocks of kThreads/32 warps; enough blocks overall to fill the machine
+  const int64_t want = ceil_div(N, (int64_t)(kThreads / 32) * 2);
+  const int64_t cap = std::max<int64_t>(1, ceil_div((int64_t)num_sms() * 8, batch));
+  const int gx = (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
   absmax_kernel<<<dim3((unsigned)gx, (unsigned)batch), kThreads, 0, st>>>(s, lds, mean, N, D, score,
                                                                         lsc, P, mx);
   SIG_LAUNCH_OK("absmax_kernel");

@@ -201,7 +201,7 @@ template <int d>
 __global__ void __launch_bounds__(Sig4Cfg<d>::NT, 2)
 sig4_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig, const float* __restrict__ gsig,
                 int64_t N, int T, int basepoint, const float* __restrict__ add, int64_t ld_add, float alpha,
-                float beta, float* __restrict__ out, const SigGradSpec gs) {
+                float beta, float* __restrict__ out, const SigGradSpec gs_all) {
   using C = Sig4Cfg<d>;
   constexpr int DD = C::DD, D = C::D, CH = C::kChunk;
   extern __shared__ __align__(16) float smem[];
@@ -223,6 +223,7 @@ sig4_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig, cons
     for (int k = 0; k < d; ++k) S3[k] = __ldg(sn + C::O3 + ij * d + k);
     s2 = __ldg(sn + C::O2 + ij);
     s1 = __ldg(sn + i);
+    const SigGradSpec gs = scene_view(gs_all, n);
     if (gs.sc != nullptr) {
       // the cotangent formed while it is loaded (SigGradSpec): g = -(1/h^2)(sc*rowsum - K.Sc) [+ tie term]
       const float gam2 = 2.f * gs.state->gamma;  // -(1/h^2) = 2*gamma

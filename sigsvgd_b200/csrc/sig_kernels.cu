@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(kThreads)
 sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
                 const float* __restrict__ gsig, int64_t N, int T, int basepoint, int TC,
                 const float* __restrict__ add, int64_t ld_add, float alpha, float beta,
-                float* __restrict__ out, const SigGradSpec gs) {
+                float* __restrict__ out, const SigGradSpec gs_all) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = kThreads / G;
   constexpr int D = d + d * d + d * d * d;
   extern __shared__ __align__(16) float smem[];
@@ -552,6 +552,7 @@ sig3_bwd_kernel(const float* __restrict__ x, const float* __restrict__ sig,
   const int tid = threadIdx.x, grp = tid / G, lane = tid % G;
   const int il = lane < d ? lane : d - 1;
   const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const SigGradSpec gs = scene_view(gs_all, p0);  // (a CTA's particles lie in one scene)
   const int npart = (int)min((int64_t)PPC, N - p0);
   const bool active = grp < npart && lane < d;
   const int gq = grp < npart ? grp : 0;
@@ -776,7 +777,7 @@ __global__ void __launch_bounds__(kSegThreads)
 sig3_bwd_seg_kernel(const float* __restrict__ x, const float* __restrict__ sig,
                     const float* __restrict__ pref, const float* __restrict__ gsig, int64_t N, int T,
                     int basepoint, int seg_len, const float* __restrict__ add, int64_t ld_add,
-                    float alpha, float beta, float* __restrict__ out, const SigGradSpec gs) {
+                    float alpha, float beta, float* __restrict__ out, const SigGradSpec gs_all) {
   constexpr int G = group_size(d), DP = row_pad(d), PPC = 32 / G;
   constexpr int D = d + d * d + d * d * d;
   constexpr int L12 = d + d * d;  // levels 1-2: all the sweep needs of the state
@@ -785,6 +786,7 @@ sig3_bwd_seg_kernel(const float* __restrict__ x, const float* __restrict__ sig,
   const int tid = threadIdx.x, seg = tid >> 5, l32 = tid & 31, grp = l32 / G, lane = l32 % G;
   const int il = lane < d ? lane : d - 1;
   const int64_t p0 = (int64_t)blockIdx.x * PPC;
+  const SigGradSpec gs = scene_view(gs_all, p0);  // (a CTA's particles lie in one scene)
   const int npart = (int)min((int64_t)PPC, N - p0);
   const bool active = grp < npart && lane < d;
   const int gq = grp < npart ? grp : 0;
@@ -1298,6 +1300,8 @@ int launch_sig_bwd(const float* x, const float* sig, const float* gsig, int64_t 
     gs = *spec;
     SIG_CHECK_ARG(sig_bwd_fuses_grad(d, depth) && gs.sc && gs.sc_all && gs.ks && gs.rowsum && gs.state,
                   "signature_bwd: fused gradient needs depth 3 (d <= 8) or depth 4 (2 <= d <= 8) and a complete spec");
+    SIG_CHECK_ARG(gs.scene_rows == 0 || (gs.scene_rows % 8 == 0 && gs.coef_mode == 0 && N % gs.scene_rows == 0),
+                  "signature_bwd: scenes of a fused gradient need a multiple of 8 rows and coef_mode 0");
   }
   SIG_CHECK_ARG(N >= 0 && T >= 1 && d >= 1 && depth >= 1 && depth <= 8,
                 "signature_bwd: bad shape N=%lld T=%lld d=%lld depth=%d", (long long)N,

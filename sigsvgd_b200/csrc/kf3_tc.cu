@@ -173,12 +173,23 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     return k;
   };
   constexpr int kRowsPerUnit = FM * Cfg::kCtas;
+  // j-th item of this unit.  One problem: round-robin over all items (see above).  Batches of problems:
+  // a unit takes whole problems (every item of problem unit, unit + nunits, ...), so that the per-problem
+  // work of the converters -- bandwidth record, statistics flush -- happens once per problem, not per item
+  auto work_at = [&](int j) -> int {
+    if (p.batch == 1) {
+      const int64_t w = (int64_t)unit + (int64_t)j * nunits;
+      return w < num_work ? (int)w : -1;
+    }
+    const int64_t prob = (int64_t)unit + (int64_t)(j / work_per_problem) * nunits;
+    return prob < p.batch ? (int)(prob * work_per_problem + j % work_per_problem) : -1;
+  };
 
   if (warp == kWarpTma) {
     // ------------------------------------------------------------------ TMA producer (every CTA)
     if (lane == 0) {
       uint32_t it = 0;
-      for (int w = unit; w < num_work; w += nunits) {
+      for (int j = 0, w; (w = work_at(j)) >= 0; ++j) {
         const Work wk = decode(w);
         // columns of B this CTA stages: its half of the item, or (wide) its halves of the item's two parts
         const int n0 = min(wk.ncols, FN), n1 = wk.ncols - n0;
@@ -226,7 +237,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------------ MMA issuer (leader CTA)
     if (leader && lane == 0) {
       uint32_t it = 0, tcount = 0;
-      for (int w = unit; w < num_work; w += nunits, ++tcount) {
+      for (int j = 0, w; (w = work_at(j)) >= 0; ++j, ++tcount) {
         const Work wk = decode(w);
         const int n0 = min(wk.ncols, FN), n1 = wk.ncols - n0;
         const uint32_t idesc = ptx::make_idesc_f16(kRowsPerUnit, n0, false, true);
@@ -318,7 +329,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     };
     uint32_t it = 0;
     const uint32_t leader_full0 = kPair ? ptx::mapa(full_bar(0), 0) : full_bar(0);
-    for (int w = unit; w < num_work; w += nunits) {
+    for (int j = 0, w; (w = work_at(j)) >= 0; ++j) {
       const Work wk = decode(w);
       if (wk.b != cur_b) {  // CTA-uniform: every converter thread walks the same items
         if (p.stats && cur_b >= 0) flush_stats(cur_b);
@@ -413,7 +424,7 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                          (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
     float* xp = reinterpret_cast<float*>(smem + kStages * kStageBytes + kFBarBytes) + q * (32 * kFPitch);
     const uint32_t leader_tempty0 = kPair ? ptx::mapa(tempty_bar(0), 0) : tempty_bar(0);
-    for (int w = unit; w < num_work; w += nunits, ++tcount) {
+    for (int j = 0, w; (w = work_at(j)) >= 0; ++j, ++tcount) {
       const Work wk = decode(w);
       const int a = kWide ? 0 : (int)(tcount & 1);
       const uint32_t aph = kWide ? (tcount & 1u) : ((tcount >> 1) & 1u);
@@ -578,7 +589,8 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
     SIG_CUDA_OK(cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * C, batch * M, st));
   const int64_t items = batch * p.tiles_m * p.tiles_n * p.nsplit;
   SIG_CHECK_ARG(items < (1ll << 31), "tc_kf: too many work items");
-  const int units = (int)std::min<int64_t>(items, units_max);
+  // (batches: units take whole problems)
+  const int units = (int)std::min<int64_t>(batch > 1 ? batch : items, units_max);
   if (!pair) {
     if (pairs_max <= 0) {  // attributes were not set by max_pairs()
       SIG_CUDA_OK(cudaFuncSetAttribute(kf_fused_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,

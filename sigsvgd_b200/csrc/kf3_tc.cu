@@ -569,7 +569,9 @@ int tc_kf_fused(const float* a, int64_t lda, int64_t M, int64_t K, int mode, sig
   // (chains of 2048: 83, but twice the truncation error of the TMEM accumulation).
   const int units_max = pair ? pairs_max : num_sms();
   const int num_kb = (int)ceil_div(ceil_div(K, 16), 2);
-  const bool wide = pair && batch == 1 && C > FN &&
+  // Only for up to four 256-column tiles (C <= 1024: the update's 848 columns): with many column tiles
+  // the exposed epilogues cost more than the saved conversions (depth 4, C = 3249: 355 vs 296 us).
+  const bool wide = pair && batch == 1 && C > FN && C <= 4 * FN &&
                     ceil_div(M, 2 * FM) * ceil_div(C, 2 * FN) * ceil_div(num_kb, kFMaxChainKb) >= units_max;
   const int64_t max_cols = wide ? 2 * FN : FN;
   p.tiles_m = (int)ceil_div(M, pair ? 2 * FM : FM), p.tiles_n = (int)ceil_div(C, max_cols);

@@ -14,7 +14,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python bench.py --steps 2 --warmup 1 --skip-extras --no-cpu-baseline > $o/${tag}_ncu_launches.log 2>&1
 python tools/ncu_summary.py $o/${tag}_ncu_launches.csv > $o/${tag}_ncu_launches_summary.txt 2>&1
 timeout 120 python tools/run_phi.py 4096 3 > /dev/null 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -s 14 -c 7 -o $o/${tag}_full \
+timeout 900 ncu --set full --clock-control none --import-source on -s 16 -c 8 -o $o/${tag}_full \
     python tools/run_phi.py 4096 3 > $o/${tag}_ncu_full.log 2>&1
 timeout 300 python tools/depth4_check.py 4096,16384 4 > $o/${tag}_depth4.json 2> $o/${tag}_depth4.err
 timeout 300 python tools/bench_pieces.py 4096 > $o/${tag}_pieces.json 2> $o/${tag}_pieces.err

@@ -175,7 +175,11 @@ def test_world2_nccl(tc, N):
     _check(X, G, depth, np.concatenate([g[1] for g in got]), np.concatenate([g[2] for g in got]), recs)
     if tc:
         grecs = [g[4][1] for g in got]
-        assert grecs[0]["median"] == recs[0]["median"] and grecs[1]["h"] == recs[1]["h"]
+        # (two runs of the step: the column statistics are accumulated with floating-point atomics, so the
+        # centred features -- and with them the entry that is the median -- can differ in the last bits)
+        assert grecs[0]["median"] == grecs[1]["median"] and grecs[0]["h"] == grecs[1]["h"]
+        assert abs(grecs[0]["median"] - recs[0]["median"]) <= 1e-6 * recs[0]["median"]
+        assert abs(grecs[1]["h"] - recs[1]["h"]) <= 1e-6 * recs[1]["h"]
         skip = {t[0] for r in recs + grecs for t in r["ties"]}
         keep = np.array([i for i in range(N) if i not in skip])
         phi_e = np.concatenate([g[1] for g in got]).reshape(N, -1)[keep]

@@ -580,6 +580,40 @@ def run_ours(args):
                    "shapes": "35 policies x 30 x 2, 10 action samples, signature depth 3 (D = 14)",
                    "h2d_bytes_per_step": 16, "d2h_bytes_per_step": H * 2 * 4,
                    "rollout": "synthetic double integrator (ParticleModel / obstacle map absent on the GPU box)"}
+            # the rollout itself: the reference's loop over ParticleModel.step as torch
+            # statements vs the one-launch kernel pair, forward + gradient w.r.t. the actions, 350 x 30
+            try:
+                from sigsvgd_b200.rollout import particle_rollout
+
+                gen = torch.Generator().manual_seed(9)
+                acts = (10 * torch.randn(350, 30, 2, generator=gen)).to(dev).requires_grad_(True)
+                grid = torch.zeros(400, 400, dtype=torch.uint8, device=dev)
+                grid[150:250:20, :] = 1
+                s0 = torch.tensor([-1.8, -1.8, 0.0, 0.0], device=dev)
+                wgt = torch.randn(350, 31, 4, generator=gen).to(dev)
+
+                def fused():
+                    st_ = particle_rollout(s0, acts, 2.0, 0.015, float("inf"), 5.0, grid, 0.01, (200, 200), True)
+                    return torch.autograd.grad((st_ * wgt).sum(), acts)[0]
+
+                def looped():  # particle.py:155-172 per step, dust.py:293-300
+                    s_ = s0.expand(350, 1, -1).clone()
+                    for t in range(30):
+                        cur = s_[:, t]
+                        idx = (cur[:, :2] * 100.0 + 200).floor().long().clamp(0, 399)
+                        mask = grid[idx[:, 0], idx[:, 1]].float().unsqueeze(-1)
+                        nxt = cur + torch.cat((cur[:, 2:], acts[:, t] / 2.0), -1) * 0.015 * (1 - mask)
+                        nxt = torch.cat((nxt[:, :2], nxt[:, 2:].clamp(-5.0, 5.0)), -1)
+                        s_ = torch.cat([s_, nxt.unsqueeze(1)], dim=1)
+                    return torch.autograd.grad((s_ * wgt).sum(), acts)[0]
+
+                same = float((fused() - looped()).abs().max() / looped().abs().max())
+                out["rollout_350x30_fwd_bwd_ms"] = {
+                    "kernel_pair": timed(fused, steps, warmup, reduce_max=False),
+                    "torch_statements_per_step": timed(looped, steps, warmup, reduce_max=False),
+                    "max_rel_dev_of_the_gradients": same}
+            except Exception as e:
+                out["rollout_350x30_fwd_bwd_ms"] = {"error": f"{type(e).__name__}: {e}"[:200]}
             if rank == 0 and world == 1 and not args.no_cpu_baseline:
                 import oracle
 

@@ -334,6 +334,26 @@ int sigsvgd_sigpde_gram_bwd(const double* x, const double* y, int64_t A, int64_t
                             const double* gout, double* grad_x, void* ws, size_t ws_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Stein-MPC rollout of the particle model, SURVEY.md 8(f)-3.  Replaces the Python loop of DuSt._rollout
+ * (src/controllers/dust.py:293-300) over ParticleModel.step (src/models/particle.py:123-173; control_type
+ * "acceleration", deterministic) and the autograd graph torch records through it:
+ *   a = clamp(act / m, +-max_acc);  mask = can_crash ? grid[floor(x * inv_cell + off_x), floor(y * inv_cell +
+ *   off_y)] (indices clamped; ObstacleMap.get_collisions, src/utils/obstacle_map.py:68-97) : 0;
+ *   s' = s + ((vx, vy, ax, ay) * dt) * (1 - mask);  s'.v = clamp(s'.v, +-max_speed)
+ * init_state [4]; actions [R,H,2]; mass [R] or NULL (then mass_scalar); grid [gx,gy] bytes (0 / 1) or NULL;
+ * max_acc / max_speed may be +inf.  states [R,H+1,4] (bit-identical to the reference's fp32 CPU result: same
+ * operation order, no fused multiply-adds); flags [R,H] bytes (crash / active clamps) for the backward.
+ * sigsvgd_particle_rollout_bwd: grad_actions [R,H,2] for the cotangent grad_states [R,H+1,4] (the mask and
+ * the clamps are piecewise constant, as in torch's autograd).
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_particle_rollout(const float* init_state, const float* actions, const float* mass, float mass_scalar,
+                             int64_t R, int64_t H, float dt, float max_acc, float max_speed, const uint8_t* grid,
+                             int64_t gx, int64_t gy, float inv_cell, float off_x, float off_y, int can_crash,
+                             float* states, uint8_t* flags, void* stream);
+int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R, int64_t H, float dt,
+                                 const float* grad_states, const uint8_t* flags, float* grad_actions, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Fused optimiser step on the particles.  Replaces the update statements of
  * SVGD.step (src/inference/svgd.py:93-116): `optimizer.step()` of torch.optim.SGD / torch.optim.Adam
  * (default flags: no weight decay, no amsgrad, no nesterov, dampening 0) and the hand-written Adagrad

@@ -148,6 +148,11 @@ _SIGNATURES = {
     "sigsvgd_sigpde_gram_bwd": (
         c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_double, c_void_p,
                 c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "sigsvgd_particle_rollout": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int64, c_float, c_float, c_float, c_void_p, c_int64,
+                c_int64, c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_particle_rollout_bwd": (
+        c_int, [c_void_p, c_float, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_opt_step": (
         c_int, [c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_double, c_double,
                 c_float, c_float, c_float, c_int, c_void_p]),

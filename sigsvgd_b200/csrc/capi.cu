@@ -479,6 +479,20 @@ int sigsvgd_sigpde_gram_bwd(const double* x, const double* y, int64_t A, int64_t
                            (cudaStream_t)stream);
 }
 
+int sigsvgd_particle_rollout(const float* init_state, const float* actions, const float* mass, float mass_scalar,
+                             int64_t R, int64_t H, float dt, float max_acc, float max_speed, const uint8_t* grid,
+                             int64_t gx, int64_t gy, float inv_cell, float off_x, float off_y, int can_crash,
+                             float* states, uint8_t* flags, void* stream) {
+  return launch_particle_rollout(init_state, actions, mass, mass_scalar, R, H, dt, max_acc, max_speed, grid, gx, gy,
+                                 inv_cell, off_x, off_y, can_crash, states, flags, (cudaStream_t)stream);
+}
+
+int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R, int64_t H, float dt,
+                                 const float* grad_states, const uint8_t* flags, float* grad_actions, void* stream) {
+  return launch_particle_rollout_bwd(mass, mass_scalar, R, H, dt, grad_states, flags, grad_actions,
+                                     (cudaStream_t)stream);
+}
+
 int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
                      int kind, float lr, double beta1, double beta2, float eps, float c1, float c2, int first,
                      void* stream) {

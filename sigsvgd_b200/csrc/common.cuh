@@ -156,6 +156,15 @@ int launch_sigpde_bwd(const double* x, const double* y, int64_t A, int64_t B, in
                       int order, int kind, double h, const sigsvgd_bw_state* state, const double* gout,
                       double* grad_x, void* ws, size_t ws_bytes, cudaStream_t st);
 
+// Stein-MPC particle-model rollout (rollout.cu)
+int launch_particle_rollout(const float* init, const float* actions, const float* mass, float mass_scalar, int64_t R,
+                            int64_t H, float dt, float max_acc, float max_speed, const uint8_t* grid, int64_t gx,
+                            int64_t gy, float inv_cell, float off_x, float off_y, int can_crash, float* states,
+                            uint8_t* flags, cudaStream_t st);
+int launch_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R, int64_t H, float dt,
+                                const float* grad_states, const uint8_t* flags, float* grad_actions,
+                                cudaStream_t st);
+
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,
                        int64_t N, int64_t D, float* dist, int64_t ldd, int64_t batch,

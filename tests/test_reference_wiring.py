@@ -219,3 +219,28 @@ def test_unmodified_reference_signature_kernel_over_the_oracle_solver():
         assert rel_max(k_ref.numpy(), so.sigpde_gram(X64, X64, 2, so.RBF, h)) < 1e-6
     finally:
         tk.sigkernel = old
+
+
+def test_rollout_with_reads_the_unmodified_particle_model(monkeypatch):
+    """``rollout_with(model)`` over the reference's own ParticleModel + ObstacleMap objects, against the
+    unmodified ``DuSt._rollout`` (dust.py:250-309); the CUDA launch is replaced by the numpy checker."""
+    from oracle import make_golden_mpc
+    from oracle import rollout_oracle as ro
+    from sigsvgd_b200 import rollout as rmod
+
+    torch.manual_seed(0)
+    controller, simulator, _, state, prior, _ = make_golden_mpc.build_controller({"tau": [], "k_xx": [], "dk_dtau": []})
+    torch.autograd.set_detect_anomaly(False)
+
+    def checker(init_state, actions, mass=1.0, dt=0.05, max_accel=float("inf"), max_speed=float("inf"), grid=None,
+                cell_size=1.0, c_offset=(0, 0), can_crash=False):
+        m = mass.numpy() if isinstance(mass, torch.Tensor) else mass
+        s, _ = ro.particle_rollout_np(init_state.numpy(), actions.detach().numpy(), m, dt, max_accel, max_speed,
+                                      None if grid is None else grid.numpy(), cell_size, c_offset, can_crash)
+        return torch.as_tensor(s)
+
+    monkeypatch.setattr(rmod, "particle_rollout", checker)
+    base_actions = controller._sample_actions().detach()
+    ref_states, ref_actions, params = controller._rollout(state, base_actions, simulator, prior)
+    got = rmod.rollout_with(simulator)(state, base_actions.flatten(end_dim=-3), params)
+    assert torch.equal(got.reshape(ref_states.shape), ref_states)

@@ -487,14 +487,15 @@ def run_ours(args):
         """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
         opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
         10 action samples; src/controllers/dust.py:520-522, examples/particle_maze_config.yaml:8-20)
-        through the `SigKernel` branch of TrajectorySVGD (trajectory_svgd.py:55-69).  The reference's
-        ParticleModel / cost are not on the GPU box: the rollout is a double integrator (acceleration
-        control, dt = 0.015) with a quadratic cost to the target -- same tensor shapes and the same graph
-        from `actions` to the kernel; the kernel statements are the reference's."""
+        through the `SigKernel` branch of TrajectorySVGD (trajectory_svgd.py:55-69).  The rollout is the
+        particle model's (`sigsvgd_particle_rollout`, bit-identical to the reference model on its golden
+        vectors) with a block obstacle grid and a quadratic cost to the target; the kernel statements are the
+        reference's."""
         try:
             import warnings
 
             from sigsvgd_b200 import compat
+            from sigsvgd_b200.rollout import particle_rollout
 
             S, Pn, H, dt = 10, 35, 30, 0.015
             with warnings.catch_warnings():
@@ -508,6 +509,23 @@ def run_ours(args):
                 mask = torch.ones(Pn, H, 2, device=device)
                 mask[-5:] = 0.0
                 target = torch.tensor([1.8, 1.8], device=device)
+                grid = torch.zeros(400, 400, dtype=torch.uint8, device=device)  # 4 x 4 blocks, as sm_grid_4x4
+                for gi in range(4):
+                    for gj in range(4):
+                        grid[70 + 80 * gi:100 + 80 * gi, 70 + 80 * gj:100 + 80 * gj] = 1
+
+                def rollout(x0, acts):
+                    if device.type == "cuda":
+                        return particle_rollout(x0, acts, 2.0, dt, float("inf"), 5.0, grid, 0.01, (200, 200), True)
+                    s_ = x0.expand(acts.shape[0], 1, -1).clone()  # the CPU arm: the reference's statements per step
+                    for t in range(H):
+                        cur = s_[:, t]
+                        idx = (cur[:, :2] * 100.0 + 200).floor().long().clamp(0, 399)
+                        crash = grid[idx[:, 0], idx[:, 1]].float().unsqueeze(-1)
+                        nxt = cur + torch.cat((cur[:, 2:], acts[:, t] / 2.0), -1) * dt * (1 - crash)
+                        nxt = torch.cat((nxt[:, :2], nxt[:, 2:].clamp(-5.0, 5.0)), -1)
+                        s_ = torch.cat([s_, nxt.unsqueeze(1)], dim=1)
+                    return s_
 
                 def optimize(x0, opt_steps=2):
                     p = pol.clone()
@@ -515,8 +533,10 @@ def run_ours(args):
                     cost = None
                     for i in range(opt_steps):
                         actions = (p.detach()[None] + noise[i]).requires_grad_(True)
-                        vel = torch.cumsum(actions * dt, dim=-2) + x0[2:]
-                        pos = torch.cumsum(vel * dt, dim=-2) + x0[:2]
+                        # rollouts: DuSt._rollout over ParticleModel.step (mass 2, dt 0.015, speed clamp 5, crash
+                        # mask from an occupancy grid) as one launch, differentiable w.r.t. the actions
+                        states = rollout(x0, actions.flatten(end_dim=-3)).reshape(S, Pn, H + 1, 4)
+                        pos = states[..., 1:, :2]
                         cost = ((pos - target) ** 2).sum((-1, -2)) + 0.2 * (actions ** 2).sum((-1, -2))
                         score = torch.autograd.grad(-cost.sum(), actions, retain_graph=True)[0].mean(0).flatten(1)
                         tau = pos.mean(0)
@@ -579,7 +599,9 @@ def run_ours(args):
                    "ms_kernel_terms_only": ms_kernel, "opt_steps": 2,
                    "shapes": "35 policies x 30 x 2, 10 action samples, signature depth 3 (D = 14)",
                    "h2d_bytes_per_step": 16, "d2h_bytes_per_step": H * 2 * 4,
-                   "rollout": "synthetic double integrator (ParticleModel / obstacle map absent on the GPU box)"}
+                   "rollout": "sigsvgd_particle_rollout: the reference's ParticleModel.step loop (acceleration control, "
+                              "mass 2, dt 0.015, speed clamp 5, crash mask from a 4 x 4 block occupancy grid) as one launch; "
+                              "quadratic cost to the target"}
             # the rollout itself: the reference's loop over ParticleModel.step as torch
             # statements vs the one-launch kernel pair, forward + gradient w.r.t. the actions, 350 x 30
             try:

@@ -602,6 +602,18 @@ def run_ours(args):
                    "rollout": "sigsvgd_particle_rollout: the reference's ParticleModel.step loop (acceleration control, "
                               "mass 2, dt 0.015, speed clamp 5, crash mask from a 4 x 4 block occupancy grid) as one launch; "
                               "quadratic cost to the target"}
+            # the same step with the reference example's own kernel: the Goursat-PDE signature kernel at
+            # the yaml's dyadic order 3 (script_control_particle_maze.py:42-44)
+            try:
+                opt_pde = make(dev, compat.PdeSigKernel(compat.RBFKernel(sigma=32 ** 0.5), dyadic_order=3))
+
+                def e2e_pde():
+                    x0 = x0_host.to(dev, non_blocking=True)
+                    a_host.copy_(opt_pde(x0), non_blocking=True)
+
+                out["ms_per_mpc_step_e2e_pde_kernel_order3"] = timed(e2e_pde, steps, warmup, reduce_max=False)
+            except Exception as e:
+                out["ms_per_mpc_step_e2e_pde_kernel_order3"] = f"{type(e).__name__}: {e}"[:200]
             # the rollout itself: the reference's loop over ParticleModel.step as torch
             # statements vs the one-launch kernel pair, forward + gradient w.r.t. the actions, 350 x 30
             try:

@@ -35,6 +35,11 @@ constexpr int kPdeMaxWarps = 8;
 constexpr int kPdeSmemBudget = 200 * 1024;
 constexpr int kPdeBins = 2048;
 
+// doubles of the parked reverse solve of one pair: [strips of 32 fine rows][NN + 31 steps][32 lanes]
+__host__ __device__ inline size_t pde_r_doubles(int64_t MM, int64_t NN) {
+  return (size_t)((MM + 31) / 32) * (size_t)(NN + 31) * 32;
+}
+
 struct PdeArgs {
   const double* x;  // [A,M,D]
   const double* y;  // [B,N,D]
@@ -143,9 +148,12 @@ sigpde_fwd_kernel(PdeArgs p, int warps, double* __restrict__ k_out) {
 
 // grad_x[a, :, :] += sum_{b in this block's range} gout[a,b] d k(a,b) / d x^a  (grad_x zeroed by the launcher).
 // Grid (b-chunks, A); the block's warps take the b's of the chunk in turn.
-// scratch, per warp, in global memory (L2-resident): R [MM][NN] = the reverse solve's K at the nodes the
-// forward sweep pairs it with, then Wc [(M-1)(N-1)] = the per-coarse-cell sums (red.global.add.f64: one
-// warp owns them, no contention).  Shared memory per warp as in the forward kernel.
+// scratch, per warp, in global memory (L2-resident): R = the reverse solve's K at the nodes the forward
+// sweep pairs it with, then Wc [(M-1)(N-1)] = the per-coarse-cell sums (red.global.add.f64: one warp owns
+// them, no contention).  R is stored in the order the wavefront produces it -- [strip][step][lane], node
+// (r+1, c+1) of lane r % 32 at step c + r % 32 -- so that a warp's 32 stores of a step (and the mirrored
+// loads of the forward sweep) are one contiguous 256-byte run instead of 32 rows of a matrix.
+// Shared memory per warp as in the forward kernel.
 __global__ void __launch_bounds__(32 * kPdeMaxWarps)
 sigpde_bwd_kernel(PdeArgs p, int warps, int b_per_block, const double* __restrict__ gout,
                   double* __restrict__ scratch, double* __restrict__ grad_x) {
@@ -160,9 +168,17 @@ sigpde_bwd_kernel(PdeArgs p, int warps, int b_per_block, const double* __restric
   double* ys = gacc + M * D + (size_t)w * per_warp;
   double* g = ys + N * D;   // [M*N] increments
   double* top = g + M * N;  // [NN+1]
-  const size_t per_scratch = (size_t)MM * NN + (size_t)(M - 1) * (N - 1);
+  const size_t r_doubles = pde_r_doubles(MM, NN);
+  const size_t per_scratch = r_doubles + (size_t)(M - 1) * (N - 1);
   double* R = scratch + (((size_t)blockIdx.y * gridDim.x + blockIdx.x) * warps + w) * per_scratch;
-  double* Wc = R + (size_t)MM * NN;
+  double* Wc = R + r_doubles;
+  const size_t strip_pitch = (size_t)(NN + 31) * 32;
+  // Kf at node (rho, kappa) of the reverse solve (1 on its first row / column)
+  auto kf_at = [&](int rho, int kappa) -> double {
+    if (rho == 0 || kappa == 0) return 1.0;
+    const int r = rho - 1, c = kappa - 1;
+    return R[(size_t)(r >> 5) * strip_pitch + (size_t)(c + (r & 31)) * 32 + (r & 31)];
+  };
   for (int i = threadIdx.x; i < M * D; i += blockDim.x) {
     xs[i] = p.x[(size_t)a * M * D + i];
     gacc[i] = 0.0;
@@ -175,18 +191,16 @@ sigpde_bwd_kernel(PdeArgs p, int warps, int b_per_block, const double* __restric
     for (int i = lane; i < (M - 1) * (N - 1); i += 32) Wc[i] = 0.0;
     __syncwarp();
     build_increments(g, xs, ys, p, sc, lane);
-    // reverse solve: Kf[r+1][c+1] at the nodes with both indices <= MM-1 / NN-1; row 0 and column 0 are 1
-    for (int j = lane; j < NN; j += 32) R[j] = 1.0;
-    for (int i = lane; i < MM; i += 32) R[(size_t)i * NN] = 1.0;
+    // reverse solve: Kf[r+1][c+1], parked in wavefront order
     goursat_sweep(g, top, p, true, lane, [&](int r, int c, double, double val) {
-      if (r + 1 < MM && c + 1 < NN) R[(size_t)(r + 1) * NN + c + 1] = val;
+      R[(size_t)(r >> 5) * strip_pitch + (size_t)(c + (r & 31)) * 32 + (r & 31)] = val;
     });
     __syncwarp();
     // forward solve, pairing K at the lower corner of every fine cell with the reverse solve at the
     // mirrored node: GG[i,j] = K[i,j] * Krev[i+1,j+1] = K[i,j] * Kf[MM-1-i][NN-1-j]
     double run = 0.0;
     goursat_sweep(g, top, p, false, lane, [&](int r, int c, double lower, double) {
-      run = fma(lower, R[(size_t)(MM - 1 - r) * NN + (NN - 1 - c)], run);
+      run = fma(lower, kf_at(MM - 1 - r, NN - 1 - c), run);
       if ((((c + 1) >> o) != (c >> o)) || c == NN - 1) {  // last fine column of the coarse cell
         atomicAdd(&Wc[(r >> o) * (N - 1) + (c >> o)], run);
         run = 0.0;
@@ -362,7 +376,7 @@ static BwdPlan bwd_plan(int64_t A, int64_t B, int64_t M, int64_t N, int64_t D, i
   const int64_t want_blocks = 4 * (int64_t)num_sms();
   int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(ceil_div(B, pl.warps), ceil_div(want_blocks, A)));
   // the reverse solve of every resident pair is parked in global memory: keep that scratch under 4 GiB
-  const double per = 8.0 * ((double)((M - 1) << order) * (double)((N - 1) << order) + (double)(M - 1) * (N - 1));
+  const double per = 8.0 * ((double)pde_r_doubles((M - 1) << order, (N - 1) << order) + (double)(M - 1) * (N - 1));
   const double cap = 4.0 * 1024 * 1024 * 1024;
   while (chunks > 1 && per * A * chunks * pl.warps > cap) --chunks;
   while (pl.warps > 1 && per * A * chunks * pl.warps > cap) --pl.warps;
@@ -379,7 +393,7 @@ size_t sigpde_bwd_workspace_bytes(int64_t A, int64_t B, int64_t M, int64_t N, in
   if (A < 1 || B < 1 || M < 2 || N < 2 || D < 1 || order < 0 || order > 10) return 0;
   const BwdPlan pl = bwd_plan(A, B, M, N, D, order);
   if (pl.warps < 1) return 0;
-  const size_t per = (size_t)((M - 1) << order) * (size_t)((N - 1) << order) + (size_t)(M - 1) * (N - 1);
+  const size_t per = pde_r_doubles((M - 1) << order, (N - 1) << order) + (size_t)(M - 1) * (N - 1);
   return (size_t)A * pl.chunks * pl.warps * per * 8;
 }
 

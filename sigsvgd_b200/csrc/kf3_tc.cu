@@ -420,8 +420,12 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int q = warp & 3;
     uint32_t tcount = 0;
     const bool accumulate_out = p.nsplit > 1;
-    const bool vec_red = accumulate_out && (p.ldo & 3) == 0 && (p.N & 3) == 0 &&
-                         (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+    // 16-byte reductions (several chains per output) when the target allows; the single-CTA kernel (batches
+    // of small problems: one chain per output) also has 16-byte plain stores and fetches the column scales
+    // one chunk ahead -- measured: scenes 391 -> 250 us; the same two changes in the pair kernels cost the
+    // N = 4096 update 8 us (97 vs 89 us), so they are compiled out there
+    const bool vec_ok = (p.ldo & 3) == 0 && (p.N & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+    const bool vec_io = vec_ok && (accumulate_out || !kPair);
     float* xp = reinterpret_cast<float*>(smem + kStages * kStageBytes + kFBarBytes) + q * (32 * kFPitch);
     const uint32_t leader_tempty0 = kPair ? ptx::mapa(tempty_bar(0), 0) : tempty_bar(0);
     for (int j = 0, w; (w = work_at(j)) >= 0; ++j, ++tcount) {
@@ -433,6 +437,12 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const int64_t row0 = (int64_t)wk.tm * kRowsPerUnit + (int64_t)rank * FM + q * 32;  // within the problem
       float* const outb = p.out + (int64_t)wk.b * p.M * p.ldo;
       const float* const csb = p.colscale + (int64_t)wk.b * p.colscale_stride;
+      // column scales one chunk ahead (a global load per chunk on the drain's critical path otherwise)
+      auto load_scale = [&](int c) {
+        const int64_t col = (int64_t)wk.tn * p.tile_cols + c * 32 + lane;
+        return (c * 32 < wk.ncols && col < p.N) ? __ldg(csb + col) : 0.f;
+      };
+      float cvl_next = kPair ? 0.f : load_scale(0);
 #pragma unroll 1
       for (int c = 0; c < Cfg::kTileCols / 32; ++c) {
         const int64_t col0 = (int64_t)wk.tn * p.tile_cols + c * 32;
@@ -440,12 +450,18 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * FN + c * 32, v);
         const bool col_ok = col0 + lane < p.N;
-        const float cvl = col_ok ? __ldg(csb + col0 + lane) : 0.f;
+        float cvl;
+        if constexpr (kPair) {
+          cvl = col_ok ? __ldg(csb + col0 + lane) : 0.f;
+        } else {
+          cvl = cvl_next;
+          cvl_next = load_scale(c + 1);
+        }
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; ++e) xp[lane * kFPitch + e] = __uint_as_float(v[e]);
         __syncwarp();
-        if (vec_red) {
+        if (vec_io) {
           const int cg = (lane & 7) * 4;
           const float s0 = __shfl_sync(0xffffffffu, cvl, cg), s1 = __shfl_sync(0xffffffffu, cvl, cg + 1);
           const float s2 = __shfl_sync(0xffffffffu, cvl, cg + 2), s3 = __shfl_sync(0xffffffffu, cvl, cg + 3);
@@ -455,8 +471,9 @@ kf_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               const int r = rr + (lane >> 3);
               if (row0 + r < p.M) {
                 const float* src = xp + r * kFPitch + cg;
-                ptx::red_add_v4(outb + (row0 + r) * p.ldo + col0 + cg, src[0] * s0, src[1] * s1,
-                                src[2] * s2, src[3] * s3);
+                float* dst = outb + (row0 + r) * p.ldo + col0 + cg;
+                if (kPair || accumulate_out) ptx::red_add_v4(dst, src[0] * s0, src[1] * s1, src[2] * s2, src[3] * s3);
+                else *reinterpret_cast<float4*>(dst) = make_float4(src[0] * s0, src[1] * s1, src[2] * s2, src[3] * s3);
               }
             }
           }

@@ -483,6 +483,53 @@ def run_ours(args):
             torch.cuda.empty_cache()
             return {"error": f"{type(e).__name__}: {e}"[:300]}
 
+    def occupancy_leg(steps, warmup):
+        """the learned occupancy network of the robot-planning cost (3 -> 200 x 4 -> 1,
+        continuous_occupancy_map.py:10-35) queried WITH its input gradient at 256 particles x 200 spline steps x
+        60 body points (script_planning_robot.py:300-318 at BASELINE's Panda particle count) and the
+        self-collision network (7 -> 200 x 4 -> 1) at 256 x 200 configurations: one fused tcgen05 launch each,
+        against the same query as torch fp32 statements + autograd on the same GPU.  Random-initialised weights
+        (the trained ones are a download)."""
+        try:
+            from sigsvgd_b200 import occupancy
+
+            out = {}
+            for name, in_dim, P in (("occupancy_3d_256x200x60", 3, 256 * 200 * 60), ("self_collision_7d_256x200", 7, 256 * 200)):
+                torch.manual_seed(5)
+                layers = [torch.nn.Linear(in_dim, 200), torch.nn.ReLU()]
+                for _ in range(3):
+                    layers += [torch.nn.Linear(200, 200), torch.nn.ReLU()]
+                layers += [torch.nn.Linear(200, 1), torch.nn.Sigmoid()]
+                net = torch.nn.Sequential(*layers).to(dev)
+                with torch.no_grad():
+                    net[-2].weight.mul_(30.0)
+                f = occupancy.fuse(net)
+                x = torch.randn(P, in_dim, device=dev)
+
+                def torch_query():
+                    xr = x.detach().requires_grad_(True)
+                    y = net(xr)
+                    return y, torch.autograd.grad(y.sum(), xr)[0]
+
+                prob, grad = f.query_raw(x)
+                y_t, g_t = torch_query()
+                ms = timed(lambda: f.query_raw(x), steps, warmup, reduce_max=False)
+                ms_fwd = timed(lambda: f.query_raw(x, want_grad=False), steps, warmup, reduce_max=False)
+                ms_t = timed(torch_query, max(2, steps // 2), 2, reduce_max=False)
+                flops = 2.0 * P * (200 * in_dim + 3 * 200 * 200 + 200) * 2  # forward + input gradient
+                out[name] = {"points": P, "ms_fused_prob_and_grad": ms, "ms_fused_prob_only": ms_fwd,
+                             "ms_torch_fp32_forward_autograd": ms_t, "speedup_vs_torch": ms_t / ms,
+                             "useful_tflops": flops / ms / 1e9, "frac_of_bf16_peak": flops / ms / 1e9 / peak_tf,
+                             "max_abs_dev_prob_vs_torch_fp32": float((prob - y_t[:, 0]).abs().max()),
+                             "max_dev_grad_rel_to_max_grad": float((grad - g_t).abs().max() / g_t.abs().max()),
+                             "dtype": "fp16 operands, fp32 accumulate (torch arm: fp32)"}
+                del net, f, x, prob, grad, y_t, g_t
+            torch.cuda.empty_cache()
+            return out
+        except Exception as e:
+            torch.cuda.empty_cache()
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+
     def mpc_step(steps, warmup):
         """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
         opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
@@ -771,7 +818,7 @@ def run_ours(args):
         torch.cuda.empty_cache()
 
     # ---- extras: one swarm sharded over the ranks, batched scenes, the MPC step -----------------
-    sharded, scenes, mpc, deep, pde = [], None, None, None, None
+    sharded, scenes, mpc, deep, pde, occ = [], None, None, None, None, None
     if not args.skip_extras:
         if world > 1:
             sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
@@ -782,6 +829,7 @@ def run_ours(args):
             mpc = mpc_step(20, 5)
             deep = depth4_swarm(N, 10, 3)
             pde = sigpde_leg(5, 2)
+            occ = occupancy_leg(10, 3)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -817,6 +865,7 @@ def run_ours(args):
             "mpc_step": mpc,
             "depth4_swarm": deep,
             "sigpde": pde,
+            "occupancy_query": occ,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

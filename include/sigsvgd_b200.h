@@ -354,6 +354,27 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                  const float* grad_states, const uint8_t* flags, float* grad_actions, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Learned occupancy / self-collision networks of the robot-planning cost, SURVEY.md 8(f)-4.  Replaces the
+ * forward of ContinuousOccupancyMap (src/models/robot_learning/continuous_occupancy_map.py:10-35) and
+ * ContinuousSelfCollisionPredictor (continuous_self_collision_pred.py:11-36),
+ *   Linear(in, H) ReLU  [Linear(H, H) ReLU] x n_mid  Linear(H, 1) Sigmoid        (H = 200, n_mid = 3)
+ * as called by batch_cost_function (examples/script_planning_robot.py:300-318) on batch x timesteps x
+ * body-point positions, AND the input gradient torch's autograd forms for it (:107): one kernel, the H x H
+ * layers as tcgen05 GEMMs (fp16 operands, fp32 accumulation), activations never leave the SM.
+ * Limits: 1 <= in_dim <= 8, 1 <= hidden <= 208, 1 <= n_mid <= 4 (else SIGSVGD_ERR_INVALID / _UNSUPPORTED).
+ * sigsvgd_mlp_pack: weights in torch's nn.Linear layout -- w_first [H,in], b_first [H], w_mid [n_mid,H,H]
+ * (out, in), b_mid [n_mid,H], w_last [H], b_last [1] -> `packed` (sigsvgd_mlp_packed_bytes, 16-byte aligned);
+ * repeat after the weights change.
+ * sigsvgd_mlp_query: x [P,in] -> prob [P] and, unless grad == NULL, grad [P,in] = d prob_p / d x_p.
+ * ------------------------------------------------------------------------------------------- */
+size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid);
+int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
+                     const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,
+                     size_t packed_bytes, void* stream);
+int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P,
+                      float* prob, float* grad, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Fused optimiser step on the particles.  Replaces the update statements of
  * SVGD.step (src/inference/svgd.py:93-116): `optimizer.step()` of torch.optim.SGD / torch.optim.Adam
  * (default flags: no weight decay, no amsgrad, no nesterov, dampening 0) and the hand-written Adagrad

@@ -493,6 +493,20 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                      (cudaStream_t)stream);
 }
 
+size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid) { return mlp_packed_bytes(in_dim, hidden, n_mid); }
+
+int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
+                     const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,
+                     size_t packed_bytes, void* stream) {
+  return launch_mlp_pack(w_first, b_first, w_mid, b_mid, w_last, b_last, in_dim, hidden, n_mid, packed, packed_bytes,
+                         (cudaStream_t)stream);
+}
+
+int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P,
+                      float* prob, float* grad, void* stream) {
+  return launch_mlp_query(packed, in_dim, hidden, n_mid, x, P, prob, grad, (cudaStream_t)stream);
+}
+
 int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,
                      int kind, float lr, double beta1, double beta2, float eps, float c1, float c2, int first,
                      void* stream) {

@@ -1,0 +1,459 @@
+// Cost side of robot planning: the learned occupancy / self-collision networks
+//   Linear(in, H) ReLU  [Linear(H, H) ReLU] x n_mid  Linear(H, 1) Sigmoid
+// (reference: src/models/robot_learning/continuous_occupancy_map.py:10-35 and
+// continuous_self_collision_pred.py:11-36; H = 200, n_mid = 3, in = 3 or the robot's dof), queried at
+// batch x timesteps x body-points positions per cost evaluation (examples/script_planning_robot.py:300-318)
+// and differentiated with respect to the query points (the cost's autograd.grad, :107).
+//
+// One kernel does the whole query: probability AND d probability / d point.  A CTA owns 128 query points
+// (one TMEM lane each).  The first layer (K = in <= 8) and the last (N = 1) are SIMT; every H x H layer --
+// forward, and again transposed for the input gradient -- is one 128 x 208 x 208 tcgen05 GEMM:
+//   A = the activations (or the back-propagated row vector) of the 128 points, fp16, written by the
+//       epilogue threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
+//   B = the layer's fp16 weights (or their transpose), one TMA load of 4 boxes per layer, prefetched
+//       while the previous layer's epilogue runs;
+//   D = fp32 in tensor memory; the epilogue (bias, ReLU, ReLU mask bits, fp16 pack) reads it with
+//       tcgen05.ld.  Nothing but the points, the probabilities and the gradients touches HBM.
+// The backward pass propagates d logit / d h (O(weights) magnitudes, safe in fp16); the sigmoid's
+// p (1 - p) multiplies the final 1 x in row in fp32.
+// Arithmetic: fp16 operands, fp32 accumulation (the reference runs fp32 GEMMs): the tests state the
+// tolerance (about 1e-3 of the output scale).
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+#include "gemm_tc.cuh"
+#include "tc_ptx.cuh"
+
+namespace sigsvgd {
+
+int make_tmap_f16(CUtensorMap* tm, const __half* base, int64_t inner, int64_t outer, int64_t ld,
+                  uint32_t box_inner, uint32_t box_outer);  // tmap.cu
+
+namespace {
+
+constexpr int kHP = 208;             // padded hidden width (13 k16 steps; N of the MMA)
+constexpr int kMaxIn = 8;            // first-layer fan-in held in registers
+constexpr int kMaxMid = 4;           // H x H layers
+constexpr int kRows = 128;           // query points per CTA
+constexpr int kMlpThreads = 256;     // two threads per point: columns [0, 96) and [96, 208)
+constexpr int kSplitCol = 96;
+constexpr uint32_t kAChunkBytes = kRows * 128;  // 64 fp16 columns of 128 rows
+constexpr uint32_t kWChunkBytes = kHP * 128;    // 64 fp16 columns of 208 rows
+constexpr uint32_t kABytes = 4 * kAChunkBytes;
+constexpr uint32_t kWBytes = 4 * kWChunkBytes;
+constexpr int kK16Steps = kHP / 16;  // 13
+constexpr uint32_t kTmemCols = 256;
+
+// fp32 parameter block (floats): W1 [kHP][kMaxIn] | b1 [kHP] | bmid [n_mid][kHP] | wlast [kHP] | blast [4]
+__host__ __device__ constexpr int param_floats(int n_mid) { return kHP * (kMaxIn + 2 + n_mid) + 4; }
+constexpr int kMaskWords = 4;  // per half: 12 or 14 groups of 8 columns -> <= 128 bits
+constexpr uint32_t kMaskLayerBytes = 2 * kMaskWords * kRows * 4;
+
+struct MlpSmem {
+  uint32_t a, w, params, masks, zpart, gpart, bars, total;
+};
+__host__ __device__ inline MlpSmem mlp_smem(int n_mid) {
+  MlpSmem s;
+  s.a = 0;
+  s.w = kABytes;
+  s.params = s.w + kWBytes;
+  s.masks = s.params + (uint32_t)((param_floats(n_mid) * 4 + 15) & ~15);
+  s.zpart = s.masks + (uint32_t)n_mid * kMaskLayerBytes;
+  s.gpart = s.zpart + 2 * kRows * 4;
+  s.bars = s.gpart + 2 * kMaxIn * kRows * 4;
+  s.total = s.bars + 64 + 1024;  // + slack for the 1024-byte alignment of the operand tiles
+  return s;
+}
+
+struct MlpArgs {
+  const float* params;  // fp32 block of the packed weights
+  const float* x;       // [P, in]
+  float* prob;          // [P]
+  float* grad;          // [P, in] or nullptr
+  int64_t P;
+  int in_dim, hidden, n_mid, num_tiles;
+};
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32"
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+  const __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// byte offset of the 16-byte unit holding columns [8u', 8u'+8) of `row` in the K-major SWIZZLE_128B
+// operand tile (64-column chunks of kRows x 128 bytes)
+__device__ __forceinline__ uint32_t a_unit_offset(int row, int col) {
+  const int chunk = col >> 6, unit = (col & 63) >> 3;
+  return (uint32_t)chunk * kAChunkBytes + (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u +
+         (uint32_t)((unit ^ (row & 7)) << 4);
+}
+
+enum { kFwd = 0, kFwdLast = 1, kBwd = 2, kBwdLast = 3 };
+
+// One group of 8 accumulator columns [col, col + 8) of this thread's row.
+//   kFwd      h = relu(acc + bias)             -> A, mask bits
+//   kFwdLast  h = relu(acc + bias); z += h . wlast;  (d logit / d pre) = wlast where h > 0 -> A
+//   kBwd      v = acc where the layer's input was active (mask)  -> A
+//   kBwdLast  v = acc where h1 was active; gx[i] += v . W1[:, i]
+template <int kMode>
+__device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
+                                       const float* wlast, const float* w1, uint32_t& mask_byte, float& z,
+                                       float (&gx)[kMaxIn], bool write_a) {
+  float h[8];
+  if constexpr (kMode == kFwd || kMode == kFwdLast) {
+    const float4 b0 = *reinterpret_cast<const float4*>(bias + col);
+    const float4 b1 = *reinterpret_cast<const float4*>(bias + col + 4);
+    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    uint32_t m = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      h[k] = fminf(fmaxf(__uint_as_float(v[k]) + bb[k], 0.f), 65504.f);
+      m |= (h[k] > 0.f ? 1u : 0u) << k;
+    }
+    mask_byte = m;
+    if constexpr (kMode == kFwdLast) {
+      const float4 w0 = *reinterpret_cast<const float4*>(wlast + col);
+      const float4 w1v = *reinterpret_cast<const float4*>(wlast + col + 4);
+      const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1v.x, w1v.y, w1v.z, w1v.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        z = fmaf(h[k], ww[k], z);
+        h[k] = (m >> k) & 1u ? ww[k] : 0.f;
+      }
+    }
+  } else {
+    const uint32_t m = mask_byte;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) h[k] = (m >> k) & 1u ? __uint_as_float(v[k]) : 0.f;
+    if constexpr (kMode == kBwdLast) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float4 r0 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn);
+        const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
+        gx[0] = fmaf(h[k], r0.x, gx[0]), gx[1] = fmaf(h[k], r0.y, gx[1]);
+        gx[2] = fmaf(h[k], r0.z, gx[2]), gx[3] = fmaf(h[k], r0.w, gx[3]);
+        gx[4] = fmaf(h[k], r1.x, gx[4]), gx[5] = fmaf(h[k], r1.y, gx[5]);
+        gx[6] = fmaf(h[k], r1.z, gx[6]), gx[7] = fmaf(h[k], r1.w, gx[7]);
+      }
+    }
+  }
+  if (kMode != kBwdLast && write_a) {
+    uint4 o;
+    o.x = pack_h2(h[0], h[1]), o.y = pack_h2(h[2], h[3]), o.z = pack_h2(h[4], h[5]), o.w = pack_h2(h[6], h[7]);
+    *reinterpret_cast<uint4*>(a_tile + a_unit_offset(row, col)) = o;
+  }
+}
+
+// 32 (or 16) accumulator columns starting at `col`: one mask word (or half of one)
+template <int kMode, int kCols>
+__device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
+                                           const float* wlast, const float* w1, uint32_t& mask_word, float& z,
+                                           float (&gx)[kMaxIn], bool write_a) {
+  uint32_t out_word = 0;
+#pragma unroll
+  for (int g = 0; g < kCols / 8; ++g) {
+    uint32_t mb = (mask_word >> (8 * g)) & 0xffu;
+    group8<kMode>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a);
+    out_word |= mb << (8 * g);
+  }
+  if constexpr (kMode == kFwd || kMode == kFwdLast) mask_word = out_word;
+}
+
+// The epilogue of one GEMM for this thread: its row, columns [0, 96) (half 0) or [96, 208) (half 1).
+// mask_in / mask_out: [kMaskWords][kRows] words of this half (read in the backward modes, written in kFwd).
+template <int kMode>
+__device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, uint8_t* a_tile, const float* bias,
+                                         const float* wlast, const float* w1, uint32_t* mask, float& z,
+                                         float (&gx)[kMaxIn], bool write_a) {
+  const int col0 = half ? kSplitCol : 0;
+  constexpr bool kReads = kMode == kBwd || kMode == kBwdLast;
+  constexpr bool kWrites = kMode == kFwd;
+  uint32_t va[32], vb[32];
+  ptx::tmem_ld_32x32(tmem_row + col0, va);
+  ptx::tmem_ld_32x32(tmem_row + col0 + 32, vb);
+  uint32_t m0 = kReads ? mask[0 * kRows + row] : 0u, m1 = kReads ? mask[1 * kRows + row] : 0u;
+  ptx::tmem_ld_wait();
+  block_cols<kMode, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a);
+  block_cols<kMode, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a);
+  if (kWrites) mask[0 * kRows + row] = m0, mask[1 * kRows + row] = m1;
+  ptx::tmem_ld_32x32(tmem_row + col0 + 64, va);
+  uint32_t vc[16];
+  if (half) tmem_ld_32x16(tmem_row + col0 + 96, vc);  // columns 192 .. 207
+  uint32_t m2 = kReads ? mask[2 * kRows + row] : 0u, m3 = (kReads && half) ? mask[3 * kRows + row] : 0u;
+  ptx::tmem_ld_wait();
+  block_cols<kMode, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a);
+  if (kWrites) mask[2 * kRows + row] = m2;
+  if (half) {
+    block_cols<kMode, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a);
+    if (kWrites) mask[3 * kRows + row] = m3;
+  }
+}
+
+__global__ void __launch_bounds__(kMlpThreads, 1)
+mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (sbase - raw);
+  const MlpSmem L = mlp_smem(p.n_mid);
+  uint8_t* const a_tile = smem + L.a;
+  float* const prm = reinterpret_cast<float*>(smem + L.params);
+  const float* const w1 = prm;                               // [kHP][kMaxIn]
+  const float* const b1 = prm + kHP * kMaxIn;                // [kHP]
+  const float* const bmid = b1 + kHP;                        // [n_mid][kHP]
+  const float* const wlast = bmid + p.n_mid * kHP;           // [kHP]
+  const float* const blast = wlast + kHP;
+  uint32_t* const masks = reinterpret_cast<uint32_t*>(smem + L.masks);
+  float* const zpart = reinterpret_cast<float*>(smem + L.zpart);   // [2][kRows]
+  float* const gpart = reinterpret_cast<float*>(smem + L.gpart);   // [2][kMaxIn][kRows]
+  const uint32_t w_full = sbase + L.bars, mma_done = w_full + 8;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + L.bars + 16);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int half = tid / kRows, row = tid % kRows;
+  const bool want_grad = p.grad != nullptr;
+  const int S = want_grad ? 2 * p.n_mid : p.n_mid;  // GEMMs per tile
+
+  for (int i = tid; i < param_floats(p.n_mid); i += kMlpThreads) prm[i] = __ldg(p.params + i);
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tmW);
+    ptx::mbar_init(w_full, 1);
+    ptx::mbar_init(mma_done, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32((const void*)tmem_slot), kTmemCols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_row = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+
+  // weights of GEMM s of a tile: forward layers 0 .. n_mid-1, then the transposes n_mid-1 .. 0
+  auto load_w = [&](int s) {
+    const int l2 = s < p.n_mid ? s : p.n_mid + (2 * p.n_mid - 1 - s);
+    ptx::mbar_expect_tx(w_full, kWBytes);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) ptx::tma_load_2d(sbase + L.w + c * kWChunkBytes, &tmW, w_full, c * 64, l2 * kHP);
+  };
+  if (tid == 0 && (int)blockIdx.x < p.num_tiles) load_w(0);
+  uint32_t wphase = 0, mphase = 0;
+  constexpr uint32_t idesc = ptx::make_idesc_f16(kRows, kHP, false, false);
+
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+    const int64_t r = (int64_t)tile * kRows + row;
+    const bool row_ok = r < p.P;
+    // ---------------------------------------------------------------- first layer (SIMT)
+    float x[kMaxIn];
+#pragma unroll
+    for (int i = 0; i < kMaxIn; ++i) x[i] = (row_ok && i < p.in_dim) ? __ldg(p.x + r * p.in_dim + i) : 0.f;
+    {
+      const int col0 = half ? kSplitCol : 0, ngroups = half ? 14 : 12;
+      uint32_t word = 0;
+      for (int g = 0; g < ngroups; ++g) {
+        const int col = col0 + 8 * g;
+        float h[8];
+        uint32_t m = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 r0 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn);
+          const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
+          float acc = b1[col + k];
+          acc = fmaf(r0.x, x[0], acc), acc = fmaf(r0.y, x[1], acc), acc = fmaf(r0.z, x[2], acc);
+          acc = fmaf(r0.w, x[3], acc), acc = fmaf(r1.x, x[4], acc), acc = fmaf(r1.y, x[5], acc);
+          acc = fmaf(r1.z, x[6], acc), acc = fmaf(r1.w, x[7], acc);
+          h[k] = fminf(fmaxf(acc, 0.f), 65504.f);
+          m |= (h[k] > 0.f ? 1u : 0u) << k;
+        }
+        uint4 o;
+        o.x = pack_h2(h[0], h[1]), o.y = pack_h2(h[2], h[3]), o.z = pack_h2(h[4], h[5]), o.w = pack_h2(h[6], h[7]);
+        *reinterpret_cast<uint4*>(a_tile + a_unit_offset(row, col)) = o;
+        word |= m << (8 * (g & 3));
+        if ((g & 3) == 3 || g == ngroups - 1) {
+          masks[(half * kMaskWords + (g >> 2)) * kRows + row] = word;  // mask layer 0 = h1
+          word = 0;
+        }
+      }
+    }
+    float z = 0.f;
+    float gx[kMaxIn];
+#pragma unroll
+    for (int i = 0; i < kMaxIn; ++i) gx[i] = 0.f;
+
+    for (int s = 0; s < S; ++s) {
+      ptx::fence_proxy_async_smem();  // this thread's operand stores -> visible to the tensor core
+      ptx::tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        ptx::mbar_wait(w_full, wphase);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < kK16Steps; ++k) {
+          const uint32_t off = (uint32_t)(k >> 2), kk = (uint32_t)(k & 3);
+          const uint64_t ad = ptx::make_smem_desc(sbase + L.a + off * kAChunkBytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
+          const uint64_t bd = ptx::make_smem_desc(sbase + L.w + off * kWChunkBytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
+          ptx::umma_f16(tmem_base, ad, bd, idesc, k ? 1u : 0u);
+        }
+        ptx::umma_commit(mma_done);
+      }
+      wphase ^= 1u;
+      ptx::mbar_wait(mma_done, mphase);
+      mphase ^= 1u;
+      ptx::tc_fence_after();
+      if (tid == 0) {  // the weight tile is free: fetch the next GEMM's (of this tile or of the next one)
+        if (s + 1 < S) load_w(s + 1);
+        else if (tile + (int)gridDim.x < p.num_tiles) load_w(0);
+      }
+      if (s < p.n_mid - 1) {  // hidden layer s+2; its mask is layer s+1
+        epilogue<kFwd>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1,
+                       masks + ((s + 1) * 2 + half) * kMaskWords * kRows, z, gx, true);
+      } else if (s == p.n_mid - 1) {
+        epilogue<kFwdLast>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad);
+        zpart[half * kRows + row] = z;
+      } else {
+        const int l = 2 * p.n_mid - 1 - s;  // transposed layer l: the result is masked by h_{l+1} = mask layer l
+        uint32_t* const mk = masks + (l * 2 + half) * kMaskWords * kRows;
+        if (l > 0) epilogue<kBwd>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true);
+        else epilogue<kBwdLast>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false);
+      }
+    }
+    if (want_grad) {
+#pragma unroll
+      for (int i = 0; i < kMaxIn; ++i) gpart[(half * kMaxIn + i) * kRows + row] = gx[i];
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (half == 0 && row_ok) {
+      const float logit = zpart[row] + zpart[kRows + row] + blast[0];
+      const float pr = 1.f / (1.f + __expf(-logit));
+      p.prob[r] = pr;
+      if (want_grad) {
+        const float gz = pr * (1.f - pr);
+        for (int i = 0; i < p.in_dim; ++i)
+          p.grad[r * p.in_dim + i] = gz * (gpart[i * kRows + row] + gpart[(kMaxIn + i) * kRows + row]);
+      }
+    }
+    // (the next tile's first-layer stores touch the operand tile and mask layer 0 only: every reader of
+    //  those is behind the barrier above; zpart / gpart are rewritten several barriers later)
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// fp16 weight tiles [2 n_mid][kHP][kHP] (layer l, then the transposes) and the fp32 parameter block
+__global__ void mlp_pack_kernel(const float* __restrict__ w_first, const float* __restrict__ b_first,
+                                const float* __restrict__ w_mid, const float* __restrict__ b_mid,
+                                const float* __restrict__ w_last, const float* __restrict__ b_last, int in_dim, int H,
+                                int n_mid, __half* __restrict__ wh, float* __restrict__ prm) {
+  const int64_t n16 = (int64_t)2 * n_mid * kHP * kHP;
+  const int64_t n32 = param_floats(n_mid);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n16 + n32; i += (int64_t)gridDim.x * blockDim.x) {
+    if (i < n16) {
+      const int l2 = (int)(i / (kHP * kHP)), n = (int)(i / kHP) % kHP, k = (int)(i % kHP);
+      float v = 0.f;
+      if (n < H && k < H) v = l2 < n_mid ? w_mid[((int64_t)l2 * H + n) * H + k] : w_mid[((int64_t)(l2 - n_mid) * H + k) * H + n];
+      wh[i] = __float2half_rn(v);
+    } else {
+      const int j = (int)(i - n16);
+      float v = 0.f;
+      if (j < kHP * kMaxIn) {
+        const int u = j / kMaxIn, c = j % kMaxIn;
+        if (u < H && c < in_dim) v = w_first[u * in_dim + c];
+      } else if (j < kHP * (kMaxIn + 1)) {
+        const int u = j - kHP * kMaxIn;
+        if (u < H) v = b_first[u];
+      } else if (j < kHP * (kMaxIn + 1 + n_mid)) {
+        const int q = j - kHP * (kMaxIn + 1), l = q / kHP, u = q % kHP;
+        if (u < H) v = b_mid[l * H + u];
+      } else if (j < kHP * (kMaxIn + 2 + n_mid)) {
+        const int u = j - kHP * (kMaxIn + 1 + n_mid);
+        if (u < H) v = w_last[u];
+      } else if (j == kHP * (kMaxIn + 2 + n_mid)) {
+        v = b_last[0];
+      }
+      prm[j] = v;
+    }
+  }
+}
+
+int mlp_check(int in_dim, int hidden, int n_mid) {
+  SIG_CHECK_ARG(in_dim >= 1 && in_dim <= kMaxIn, "mlp: in_dim must be in [1, %d] (got %d)", kMaxIn, in_dim);
+  SIG_CHECK_ARG(hidden >= 1 && hidden <= kHP, "mlp: hidden width must be in [1, %d] (got %d)", kHP, hidden);
+  if (n_mid < 1 || n_mid > kMaxMid) {
+    set_error("mlp: %d hidden-to-hidden layers; this kernel takes 1 .. %d", n_mid, kMaxMid);
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  return 0;
+}
+
+}  // namespace
+
+size_t mlp_packed_bytes(int in_dim, int hidden, int n_mid) {
+  if (mlp_check(in_dim, hidden, n_mid) != 0) return 0;
+  return (size_t)2 * n_mid * kHP * kHP * sizeof(__half) + (size_t)param_floats(n_mid) * sizeof(float);
+}
+
+int launch_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
+                    const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,
+                    size_t packed_bytes, cudaStream_t st) {
+  SIG_PROPAGATE(mlp_check(in_dim, hidden, n_mid));
+  SIG_CHECK_ARG(w_first && b_first && w_mid && b_mid && w_last && b_last && packed, "mlp_pack: NULL pointer");
+  SIG_CHECK_ARG((reinterpret_cast<uintptr_t>(packed) & 15u) == 0, "mlp_pack: the packed buffer must be 16-byte aligned");
+  if (packed_bytes < mlp_packed_bytes(in_dim, hidden, n_mid)) {
+    set_error("mlp_pack: packed buffer of %zu bytes, %zu needed", packed_bytes, mlp_packed_bytes(in_dim, hidden, n_mid));
+    return SIGSVGD_ERR_WORKSPACE;
+  }
+  __half* wh = reinterpret_cast<__half*>(packed);
+  float* prm = reinterpret_cast<float*>(wh + (size_t)2 * n_mid * kHP * kHP);
+  mlp_pack_kernel<<<num_sms() * 2, 256, 0, st>>>(w_first, b_first, w_mid, b_mid, w_last, b_last, in_dim, hidden, n_mid,
+                                                 wh, prm);
+  SIG_LAUNCH_OK("mlp_pack_kernel");
+  return 0;
+}
+
+int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P, float* prob,
+                     float* grad, cudaStream_t st) {
+  SIG_PROPAGATE(mlp_check(in_dim, hidden, n_mid));
+  SIG_CHECK_ARG(P >= 0 && P < (1ll << 31) * kRows, "mlp_query: bad number of points");
+  if (P == 0) return 0;
+  SIG_CHECK_ARG(packed && x && prob, "mlp_query: NULL pointer");
+  if (!tc_available()) {
+    set_error("mlp_query: the driver does not export cuTensorMapEncodeTiled (no TMA): no fallback exists");
+    return SIGSVGD_ERR_UNSUPPORTED;
+  }
+  const __half* wh = reinterpret_cast<const __half*>(packed);
+  CUtensorMap tw;
+  SIG_PROPAGATE(make_tmap_f16(&tw, wh, kHP, (int64_t)2 * n_mid * kHP, kHP, 64, kHP));
+  MlpArgs a;
+  a.params = reinterpret_cast<const float*>(wh + (size_t)2 * n_mid * kHP * kHP);
+  a.x = x, a.prob = prob, a.grad = grad, a.P = P;
+  a.in_dim = in_dim, a.hidden = hidden, a.n_mid = n_mid;
+  a.num_tiles = (int)ceil_div(P, kRows);
+  const MlpSmem L = mlp_smem(n_mid);
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  SIG_CUDA_OK(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    SIG_CUDA_OK(cudaFuncSetAttribute(mlp_query_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)mlp_smem(kMaxMid).total));
+    configured_dev = dev;
+  }
+  const int grid = std::min(a.num_tiles, num_sms());
+  mlp_query_kernel<<<grid, kMlpThreads, L.total, st>>>(tw, a);
+  SIG_LAUNCH_OK("mlp_query_kernel");
+  return 0;
+}
+
+}  // namespace sigsvgd

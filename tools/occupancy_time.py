@@ -1,0 +1,59 @@
+"""Timing of the fused occupancy-network query against torch fp32 + autograd on the same GPU.
+Usage: python tools/occupancy_time.py [P] [in_dim]"""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from sigsvgd_b200 import occupancy  # noqa: E402
+
+
+def timed(fn, n=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / n
+
+
+def main():
+    P = int(sys.argv[1]) if len(sys.argv) > 1 else 256 * 200 * 60
+    in_dim = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    dev = torch.device("cuda:0")
+    torch.manual_seed(5)
+    layers = [torch.nn.Linear(in_dim, 200), torch.nn.ReLU()]
+    for _ in range(3):
+        layers += [torch.nn.Linear(200, 200), torch.nn.ReLU()]
+    layers += [torch.nn.Linear(200, 1), torch.nn.Sigmoid()]
+    net = torch.nn.Sequential(*layers).to(dev)
+    with torch.no_grad():
+        net[-2].weight.mul_(30.0)
+    f = occupancy.fuse(net)
+    x = torch.randn(P, in_dim, device=dev)
+
+    def torch_query():
+        xr = x.detach().requires_grad_(True)
+        y = net(xr)
+        return y, torch.autograd.grad(y.sum(), xr)[0]
+
+    prob, grad = f.query_raw(x)
+    y_t, g_t = torch_query()
+    ms = timed(lambda: f.query_raw(x))
+    ms_f = timed(lambda: f.query_raw(x, want_grad=False))
+    ms_t = timed(torch_query, 4, 2)
+    flops = 2.0 * P * (200 * in_dim + 3 * 200 * 200 + 200) * 2
+    print(json.dumps({"points": P, "in_dim": in_dim, "ms_fused": ms, "ms_fused_fwd_only": ms_f, "ms_torch_fp32": ms_t,
+                      "speedup": ms_t / ms, "useful_tflops": flops / ms / 1e9,
+                      "dev_prob": float((prob - y_t[:, 0]).abs().max()),
+                      "dev_grad_rel": float((grad - g_t).abs().max() / g_t.abs().max())}))
+
+
+if __name__ == "__main__":
+    main()

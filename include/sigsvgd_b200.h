@@ -360,7 +360,11 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
  *   Linear(in, H) ReLU  [Linear(H, H) ReLU] x n_mid  Linear(H, 1) Sigmoid        (H = 200, n_mid = 3)
  * as called by batch_cost_function (examples/script_planning_robot.py:300-318) on batch x timesteps x
  * body-point positions, AND the input gradient torch's autograd forms for it (:107): one kernel, the H x H
- * layers as tcgen05 GEMMs (fp16 operands, fp32 accumulation), activations never leave the SM.
+ * layers as tcgen05 GEMMs, activations never leave the SM.
+ * precise != 0: operands as fp16 hi + lo planes, 3 MMAs per product: the reference's fp32 GEMMs to fp32 accuracy
+ * (the ReLU patterns, hence the piecewise-constant Jacobians, agree with the reference's);  precise == 0: hi
+ * planes only, 1 MMA: probabilities to ~5e-4, and about 1 point in 20 has a pre-activation within fp16 rounding
+ * of zero and takes the neighbouring linear piece's gradient.
  * Limits: 1 <= in_dim <= 8, 1 <= hidden <= 208, 1 <= n_mid <= 4 (else SIGSVGD_ERR_INVALID / _UNSUPPORTED).
  * sigsvgd_mlp_pack: weights in torch's nn.Linear layout -- w_first [H,in], b_first [H], w_mid [n_mid,H,H]
  * (out, in), b_mid [n_mid,H], w_last [H], b_last [1] -> `packed` (sigsvgd_mlp_packed_bytes, 16-byte aligned);
@@ -368,10 +372,12 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
  * sigsvgd_mlp_query: x [P,in] -> prob [P] and, unless grad == NULL, grad [P,in] = d prob_p / d x_p.
  * ------------------------------------------------------------------------------------------- */
 size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid);
+/* development aid (environment SIGSVGD_MLP_PROFILE=1): cycles thread 0 of every CTA spent per phase, summed */
+int sigsvgd_mlp_profile_cycles(unsigned long long* out8, int reset);
 int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
                      const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,
                      size_t packed_bytes, void* stream);
-int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P,
+int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int precise, const float* x, int64_t P,
                       float* prob, float* grad, void* stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -493,6 +493,8 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                      (cudaStream_t)stream);
 }
 
+int sigsvgd_mlp_profile_cycles(unsigned long long* out8, int reset) { return mlp_profile_cycles(out8, reset); }
+
 size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid) { return mlp_packed_bytes(in_dim, hidden, n_mid); }
 
 int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
@@ -502,9 +504,9 @@ int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_
                          (cudaStream_t)stream);
 }
 
-int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P,
+int sigsvgd_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int precise, const float* x, int64_t P,
                       float* prob, float* grad, void* stream) {
-  return launch_mlp_query(packed, in_dim, hidden, n_mid, x, P, prob, grad, (cudaStream_t)stream);
+  return launch_mlp_query(packed, in_dim, hidden, n_mid, precise, x, P, prob, grad, (cudaStream_t)stream);
 }
 
 int sigsvgd_opt_step(float* x, const float* dir, float sign, float* m, float* v, float* grad_out, int64_t n,

@@ -167,11 +167,12 @@ int launch_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R,
 
 // occupancy / self-collision network query with its input gradient (mlp_tc.cu)
 size_t mlp_packed_bytes(int in_dim, int hidden, int n_mid);
+int mlp_profile_cycles(unsigned long long* out8, int reset);
 int launch_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
                     const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,
                     size_t packed_bytes, cudaStream_t st);
-int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P, float* prob,
-                     float* grad, cudaStream_t st);
+int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int precise, const float* x, int64_t P,
+                     float* prob, float* grad, cudaStream_t st);
 
 // SIMT GEMMs (gemm_simt.cu)
 int launch_sqdist_simt(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M,

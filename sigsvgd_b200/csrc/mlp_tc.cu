@@ -7,21 +7,28 @@
 //
 // One kernel does the whole query: probability AND d probability / d point.  A CTA owns 128 query points
 // (one TMEM lane each).  The first layer (K = in <= 8) and the last (N = 1) are SIMT; every H x H layer --
-// forward, and again transposed for the input gradient -- is one 128 x 208 x 208 tcgen05 GEMM:
-//   A = the activations (or the back-propagated row vector) of the 128 points, fp16, written by the
-//       epilogue threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
-//   B = the layer's fp16 weights (or their transpose), one TMA load of 4 boxes per layer, prefetched
-//       while the previous layer's epilogue runs;
+// forward, and again transposed for the input gradient -- is a 128 x 208 x 208 tcgen05 GEMM:
+//   A = the activations (or the back-propagated rows) of the 128 points, fp16, written by the epilogue
+//       threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
+//   B = the layer's fp16 weights (or their transpose), streamed by TMA through a ring of [112 | 96 rows x
+//       64 columns] stages that runs ahead across layers and tiles (the weights never depend on the data);
 //   D = fp32 in tensor memory; the epilogue (bias, ReLU, ReLU mask bits, fp16 pack) reads it with
 //       tcgen05.ld.  Nothing but the points, the probabilities and the gradients touches HBM.
-// The backward pass propagates d logit / d h (O(weights) magnitudes, safe in fp16); the sigmoid's
-// p (1 - p) multiplies the final 1 x in row in fp32.
-// Arithmetic: fp16 operands, fp32 accumulation (the reference runs fp32 GEMMs): the tests state the
-// tolerance (about 1e-3 of the output scale).
+// The backward pass propagates d logit / d h; the sigmoid's p (1 - p) multiplies the final 1 x in row.
+//
+// Arithmetic, two modes:
+//   precise  every fp32 operand is held as two fp16 planes, x = hi + lo, and a product is accumulated as
+//            hi.hi + lo.hi + hi.lo (3 MMAs, fp32 accumulator; the dropped lo.lo term is 2^-22 relative): the
+//            reference's fp32 GEMMs to fp32 accuracy, so that the ReLU patterns -- and with them the
+//            piecewise-constant Jacobian -- agree with the reference's except where a pre-activation lies
+//            within fp32 rounding of zero (where the reference itself is arbitrary);
+//   fast     hi planes only (1 MMA): probabilities to ~5e-4; about 1 point in 20 has some pre-activation
+//            within the fp16 rounding error of zero and takes the neighbouring linear piece's gradient.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "gemm_tc.cuh"
@@ -34,39 +41,50 @@ int make_tmap_f16(CUtensorMap* tm, const __half* base, int64_t inner, int64_t ou
 
 namespace {
 
-constexpr int kHP = 208;             // padded hidden width (13 k16 steps; N of the MMA)
+constexpr int kHP = 208;             // padded hidden width (13 k16 steps; N of the GEMM)
 constexpr int kMaxIn = 8;            // first-layer fan-in held in registers
 constexpr int kMaxMid = 4;           // H x H layers
 constexpr int kRows = 128;           // query points per CTA
 constexpr int kMlpThreads = 256;     // two threads per point: columns [0, 96) and [96, 208)
 constexpr int kSplitCol = 96;
 constexpr uint32_t kAChunkBytes = kRows * 128;  // 64 fp16 columns of 128 rows
-constexpr uint32_t kWChunkBytes = kHP * 128;    // 64 fp16 columns of 208 rows
-constexpr uint32_t kABytes = 4 * kAChunkBytes;
-constexpr uint32_t kWBytes = 4 * kWChunkBytes;
-constexpr int kK16Steps = kHP / 16;  // 13
+constexpr uint32_t kABytes = 4 * kAChunkBytes;  // one plane of the operand tile
+constexpr int kPart0Rows = 112, kPart1Rows = 96;  // the weight rows of a stage (N of one MMA; both % 16 == 0)
 constexpr uint32_t kTmemCols = 256;
+// A stage of the weight ring = [rows x 64 fp16 columns] of one plane, SWIZZLE_128B.  precise: the rows of a
+// layer in two parts (112 | 96), 16 stage loads per GEMM (4 column chunks x 2 parts x 2 planes), which leaves
+// room for the lo plane of the operand tile; fast: all 208 rows, 4 loads per GEMM (a whole layer in flight).
+template <bool kPrecise>
+struct MlpCfg {
+  static constexpr int kStages = kPrecise ? 3 : 4;
+  static constexpr int kParts = 1;
+  static constexpr int kJobs = kPrecise ? 8 : 4;
+  static constexpr uint32_t kStageBytes = kHP * 128;
+};
 
 // fp32 parameter block (floats): W1 [kHP][kMaxIn] | b1 [kHP] | bmid [n_mid][kHP] | wlast [kHP] | blast [4]
 __host__ __device__ constexpr int param_floats(int n_mid) { return kHP * (kMaxIn + 2 + n_mid) + 4; }
-constexpr int kMaskWords = 4;  // per half: 12 or 14 groups of 8 columns -> <= 128 bits
-constexpr uint32_t kMaskLayerBytes = 2 * kMaskWords * kRows * 4;
+constexpr int kMaskWords = 4;  // per thread and hidden layer: 12 or 14 groups of 8 columns -> <= 128 bits
 
 struct MlpSmem {
-  uint32_t a, w, params, masks, zpart, gpart, bars, total;
+  uint32_t a_hi, a_lo, ring, params, bars, total;
 };
-__host__ __device__ inline MlpSmem mlp_smem(int n_mid) {
+__host__ __device__ inline MlpSmem mlp_smem(int n_mid, bool precise) {
   MlpSmem s;
-  s.a = 0;
-  s.w = kABytes;
-  s.params = s.w + kWBytes;
-  s.masks = s.params + (uint32_t)((param_floats(n_mid) * 4 + 15) & ~15);
-  s.zpart = s.masks + (uint32_t)n_mid * kMaskLayerBytes;
-  s.gpart = s.zpart + 2 * kRows * 4;
-  s.bars = s.gpart + 2 * kMaxIn * kRows * 4;
-  s.total = s.bars + 64 + 1024;  // + slack for the 1024-byte alignment of the operand tiles
+  s.a_hi = 0;
+  s.a_lo = kABytes;  // (precise only)
+  s.ring = precise ? 2 * kABytes : kABytes;
+  s.params = s.ring + (precise ? MlpCfg<true>::kStages * MlpCfg<true>::kStageBytes
+                               : MlpCfg<false>::kStages * MlpCfg<false>::kStageBytes);
+  s.bars = s.params + (uint32_t)((param_floats(n_mid) * 4 + 15) & ~15);
+  s.total = s.bars + 256 + 1024;  // barriers; + slack for the 1024-byte alignment of the operand tiles
   return s;
 }
+
+// SIGSVGD_MLP_PROFILE=1: thread 0 of every CTA adds the cycles it spent per phase (first layer | barrier |
+// MMA issue incl. waits for full stages | wait for the MMAs | epilogue | output) -- read with
+// sigsvgd_mlp_profile_cycles (tools/occupancy_time.py)
+__device__ unsigned long long g_mlp_prof[8];
 
 struct MlpArgs {
   const float* params;  // fp32 block of the packed weights
@@ -74,7 +92,7 @@ struct MlpArgs {
   float* prob;          // [P]
   float* grad;          // [P, in] or nullptr
   int64_t P;
-  int in_dim, hidden, n_mid, num_tiles;
+  int in_dim, hidden, n_mid, num_tiles, profile;
 };
 
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
@@ -87,17 +105,30 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "memory");
 }
 
-__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-  const __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<const uint32_t*>(&h);
-}
-
 // byte offset of the 16-byte unit holding columns [8u', 8u'+8) of `row` in the K-major SWIZZLE_128B
 // operand tile (64-column chunks of kRows x 128 bytes)
 __device__ __forceinline__ uint32_t a_unit_offset(int row, int col) {
   const int chunk = col >> 6, unit = (col & 63) >> 3;
   return (uint32_t)chunk * kAChunkBytes + (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u +
          (uint32_t)((unit ^ (row & 7)) << 4);
+}
+
+// 8 operand values of one row -> the hi plane (and, kLo, the lo plane = the rounding remainder) of the tile
+template <bool kLo>
+__device__ __forceinline__ void store_operand8(const float (&h)[8], uint8_t* a_tile, uint32_t off) {
+  __half2 hh[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) hh[k] = __floats2half2_rn(h[2 * k], h[2 * k + 1]);
+  *reinterpret_cast<uint4*>(a_tile + off) = *reinterpret_cast<const uint4*>(hh);
+  if constexpr (kLo) {
+    __half2 ll[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __half22float2(hh[k]);
+      ll[k] = __floats2half2_rn(h[2 * k] - f.x, h[2 * k + 1] - f.y);
+    }
+    *reinterpret_cast<uint4*>(a_tile + kABytes + off) = *reinterpret_cast<const uint4*>(ll);
+  }
 }
 
 enum { kFwd = 0, kFwdLast = 1, kBwd = 2, kBwdLast = 3 };
@@ -107,7 +138,7 @@ enum { kFwd = 0, kFwdLast = 1, kBwd = 2, kBwdLast = 3 };
 //   kFwdLast  h = relu(acc + bias); z += h . wlast;  (d logit / d pre) = wlast where h > 0 -> A
 //   kBwd      v = acc where the layer's input was active (mask)  -> A
 //   kBwdLast  v = acc where h1 was active; gx[i] += v . W1[:, i]
-template <int kMode>
+template <int kMode, bool kLo>
 __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
                                        const float* wlast, const float* w1, uint32_t& mask_byte, float& z,
                                        float (&gx)[kMaxIn], bool write_a) {
@@ -149,15 +180,11 @@ __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint
       }
     }
   }
-  if (kMode != kBwdLast && write_a) {
-    uint4 o;
-    o.x = pack_h2(h[0], h[1]), o.y = pack_h2(h[2], h[3]), o.z = pack_h2(h[4], h[5]), o.w = pack_h2(h[6], h[7]);
-    *reinterpret_cast<uint4*>(a_tile + a_unit_offset(row, col)) = o;
-  }
+  if (kMode != kBwdLast && write_a) store_operand8<kLo>(h, a_tile, a_unit_offset(row, col));
 }
 
 // 32 (or 16) accumulator columns starting at `col`: one mask word (or half of one)
-template <int kMode, int kCols>
+template <int kMode, bool kLo, int kCols>
 __device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
                                            const float* wlast, const float* w1, uint32_t& mask_word, float& z,
                                            float (&gx)[kMaxIn], bool write_a) {
@@ -165,15 +192,15 @@ __device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, 
 #pragma unroll
   for (int g = 0; g < kCols / 8; ++g) {
     uint32_t mb = (mask_word >> (8 * g)) & 0xffu;
-    group8<kMode>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a);
+    group8<kMode, kLo>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a);
     out_word |= mb << (8 * g);
   }
   if constexpr (kMode == kFwd || kMode == kFwdLast) mask_word = out_word;
 }
 
 // The epilogue of one GEMM for this thread: its row, columns [0, 96) (half 0) or [96, 208) (half 1).
-// mask_in / mask_out: [kMaskWords][kRows] words of this half (read in the backward modes, written in kFwd).
-template <int kMode>
+// mask: this thread's kMaskWords words of the layer (read in the backward modes, written in kFwd).
+template <int kMode, bool kLo>
 __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, uint8_t* a_tile, const float* bias,
                                          const float* wlast, const float* w1, uint32_t* mask, float& z,
                                          float (&gx)[kMaxIn], bool write_a) {
@@ -183,43 +210,52 @@ __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, u
   uint32_t va[32], vb[32];
   ptx::tmem_ld_32x32(tmem_row + col0, va);
   ptx::tmem_ld_32x32(tmem_row + col0 + 32, vb);
-  uint32_t m0 = kReads ? mask[0 * kRows + row] : 0u, m1 = kReads ? mask[1 * kRows + row] : 0u;
+  uint32_t m0 = kReads ? mask[0] : 0u, m1 = kReads ? mask[1] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a);
-  block_cols<kMode, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a);
-  if (kWrites) mask[0 * kRows + row] = m0, mask[1 * kRows + row] = m1;
+  block_cols<kMode, kLo, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a);
+  block_cols<kMode, kLo, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a);
+  if (kWrites) mask[0] = m0, mask[1] = m1;
   ptx::tmem_ld_32x32(tmem_row + col0 + 64, va);
   uint32_t vc[16];
   if (half) tmem_ld_32x16(tmem_row + col0 + 96, vc);  // columns 192 .. 207
-  uint32_t m2 = kReads ? mask[2 * kRows + row] : 0u, m3 = (kReads && half) ? mask[3 * kRows + row] : 0u;
+  uint32_t m2 = kReads ? mask[2] : 0u, m3 = (kReads && half) ? mask[3] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a);
-  if (kWrites) mask[2 * kRows + row] = m2;
+  block_cols<kMode, kLo, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a);
+  if (kWrites) mask[2] = m2;
   if (half) {
-    block_cols<kMode, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a);
-    if (kWrites) mask[3 * kRows + row] = m3;
+    block_cols<kMode, kLo, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a);
+    if (kWrites) mask[3] = m3;
   }
 }
 
+template <bool kPrecise>
 __global__ void __launch_bounds__(kMlpThreads, 1)
-mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
+mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1, const MlpArgs p) {
+  using Cfg = MlpCfg<kPrecise>;
+  constexpr int NS = Cfg::kStages, J = Cfg::kJobs;
+  constexpr uint32_t kStageBytes = Cfg::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (sbase - raw);
-  const MlpSmem L = mlp_smem(p.n_mid);
-  uint8_t* const a_tile = smem + L.a;
+  const MlpSmem L = mlp_smem(p.n_mid, kPrecise);
+  uint8_t* const a_tile = smem + L.a_hi;
   float* const prm = reinterpret_cast<float*>(smem + L.params);
   const float* const w1 = prm;                               // [kHP][kMaxIn]
   const float* const b1 = prm + kHP * kMaxIn;                // [kHP]
   const float* const bmid = b1 + kHP;                        // [n_mid][kHP]
   const float* const wlast = bmid + p.n_mid * kHP;           // [kHP]
   const float* const blast = wlast + kHP;
-  uint32_t* const masks = reinterpret_cast<uint32_t*>(smem + L.masks);
-  float* const zpart = reinterpret_cast<float*>(smem + L.zpart);   // [2][kRows]
-  float* const gpart = reinterpret_cast<float*>(smem + L.gpart);   // [2][kMaxIn][kRows]
-  const uint32_t w_full = sbase + L.bars, mma_done = w_full + 8;
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + L.bars + 16);
+  // partial logits / gradients of the two threads of a row meet in the operand tile's space once the tile's
+  // last GEMM has read it
+  float* const zpart = reinterpret_cast<float*>(smem + L.a_hi);    // [2][kRows]
+  float* const gpart = zpart + 2 * kRows;                          // [2][kMaxIn][kRows]
+  uint32_t masks[kMaxMid][kMaskWords];  // ReLU patterns of this thread's columns of h1 .. h_{n_mid} (thread-local)
+  const uint32_t bar0 = sbase + L.bars;
+  auto full_bar = [&](int st) { return bar0 + 8u * st; };
+  auto empty_bar = [&](int st) { return bar0 + 8u * (NS + st); };
+  const uint32_t mma_done = bar0 + 8u * (2 * NS);
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + L.bars + 8 * (2 * NS + 1));
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int half = tid / kRows, row = tid % kRows;
@@ -228,8 +264,12 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
 
   for (int i = tid; i < param_floats(p.n_mid); i += kMlpThreads) prm[i] = __ldg(p.params + i);
   if (tid == 0) {
-    ptx::tma_prefetch_desc(&tmW);
-    ptx::mbar_init(w_full, 1);
+    ptx::tma_prefetch_desc(&tmW0);
+    ptx::tma_prefetch_desc(&tmW1);
+    for (int st = 0; st < NS; ++st) {
+      ptx::mbar_init(full_bar(st), 1);
+      ptx::mbar_init(empty_bar(st), 1);
+    }
     ptx::mbar_init(mma_done, 1);
     ptx::fence_mbar_init();
   }
@@ -240,16 +280,46 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_row = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 
-  // weights of GEMM s of a tile: forward layers 0 .. n_mid-1, then the transposes n_mid-1 .. 0
-  auto load_w = [&](int s) {
-    const int l2 = s < p.n_mid ? s : p.n_mid + (2 * p.n_mid - 1 - s);
-    ptx::mbar_expect_tx(w_full, kWBytes);
-#pragma unroll
-    for (int c = 0; c < 4; ++c) ptx::tma_load_2d(sbase + L.w + c * kWChunkBytes, &tmW, w_full, c * 64, l2 * kHP);
+  // ---- the weight stream (thread 0).  Stage load q of this CTA: GEMM (q / J) % S of its (q / (J S))-th tile,
+  // job q % J = (column chunk c, row part, plane).  GEMM s multiplies by layer s (s < n_mid) or by the
+  // transpose of layer 2 n_mid - 1 - s.
+  const int my_tiles = (int)blockIdx.x < p.num_tiles ? (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const uint32_t total_loads = (uint32_t)my_tiles * (uint32_t)S * (uint32_t)J;
+  auto job_of = [&](int j, int& c, int& part, int& plane) {
+    if constexpr (kPrecise) c = j >> 1, part = 0, plane = j & 1;
+    else c = j, part = 0, plane = 0;
   };
-  if (tid == 0 && (int)blockIdx.x < p.num_tiles) load_w(0);
-  uint32_t wphase = 0, mphase = 0;
-  constexpr uint32_t idesc = ptx::make_idesc_f16(kRows, kHP, false, false);
+  auto issue_load = [&](uint32_t q) {
+    const int s = (int)((q / J) % (uint32_t)S), j = (int)(q % J);
+    int c, part, plane;
+    job_of(j, c, part, plane);
+    const int l2 = s < p.n_mid ? s : p.n_mid + (2 * p.n_mid - 1 - s);
+    const int st = (int)(q % NS);
+    if (q >= (uint32_t)NS) ptx::mbar_wait(empty_bar(st), ((q / NS) - 1u) & 1u);  // the MMAs of load q - NS are done
+    const int row0 = (plane * 2 * p.n_mid + l2) * kHP + (part ? kPart0Rows : 0);
+    ptx::mbar_expect_tx(full_bar(st), Cfg::kParts == 1 ? kStageBytes : (uint32_t)(part ? kPart1Rows : kPart0Rows) * 128u);
+    ptx::tma_load_2d(sbase + L.ring + (uint32_t)st * kStageBytes, part ? &tmW1 : &tmW0, full_bar(st), c * 64, row0);
+  };
+  // Two single-thread roles during a GEMM, both epilogue threads otherwise: thread 0 issues the MMAs (it waits
+  // for full stages only), thread 32 refills the ring NS loads ahead (it waits for the MMAs that free a stage).
+  uint32_t head = 0;    // next stage load to issue (thread 32)
+  uint32_t gemm_q = 0;  // first stage load of the current GEMM (uniform)
+  if (tid == 32) {
+    while (head < total_loads && head < (uint32_t)NS) issue_load(head++);
+  }
+  uint32_t mphase = 0;
+  long long prof[6] = {0, 0, 0, 0, 0, 0}, t_prev = 0;
+  const bool profiling = p.profile && tid == 0;
+  auto lap = [&](int k) {
+    if (profiling) {
+      const long long t = clock64();
+      prof[k] += t - t_prev;
+      t_prev = t;
+    }
+  };
+  if (profiling) t_prev = clock64();
+  constexpr uint32_t idesc0 = ptx::make_idesc_f16(kRows, Cfg::kParts == 1 ? kHP : kPart0Rows, false, false);
+  constexpr uint32_t idesc1 = ptx::make_idesc_f16(kRows, kPart1Rows, false, false);
 
   for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
     const int64_t r = (int64_t)tile * kRows + row;
@@ -276,16 +346,15 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
           h[k] = fminf(fmaxf(acc, 0.f), 65504.f);
           m |= (h[k] > 0.f ? 1u : 0u) << k;
         }
-        uint4 o;
-        o.x = pack_h2(h[0], h[1]), o.y = pack_h2(h[2], h[3]), o.z = pack_h2(h[4], h[5]), o.w = pack_h2(h[6], h[7]);
-        *reinterpret_cast<uint4*>(a_tile + a_unit_offset(row, col)) = o;
+        store_operand8<kPrecise>(h, a_tile, a_unit_offset(row, col));
         word |= m << (8 * (g & 3));
         if ((g & 3) == 3 || g == ngroups - 1) {
-          masks[(half * kMaskWords + (g >> 2)) * kRows + row] = word;  // mask layer 0 = h1
+          masks[0][g >> 2] = word;  // mask layer 0 = h1
           word = 0;
         }
       }
     }
+    lap(0);
     float z = 0.f;
     float gx[kMaxIn];
 #pragma unroll
@@ -295,39 +364,64 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
       ptx::fence_proxy_async_smem();  // this thread's operand stores -> visible to the tensor core
       ptx::tc_fence_before();
       __syncthreads();
-      if (tid == 0) {
-        ptx::mbar_wait(w_full, wphase);
+      lap(1);
+      if (tid == 32) {
+        // (not the slot of this GEMM's last job: waiting for it would hold this thread -- and, at the
+        //  warp-collective tcgen05.ld, its warp -- past the end of the GEMM; it is refilled first thing in the
+        //  next one, three jobs before it is needed)
+        const uint32_t lim = min(total_loads, gemm_q + (uint32_t)(J + NS - 1));
+        while (head < lim) issue_load(head++);
+      } else if (tid == 0) {
         ptx::tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < kK16Steps; ++k) {
-          const uint32_t off = (uint32_t)(k >> 2), kk = (uint32_t)(k & 3);
-          const uint64_t ad = ptx::make_smem_desc(sbase + L.a + off * kAChunkBytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
-          const uint64_t bd = ptx::make_smem_desc(sbase + L.w + off * kWChunkBytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
-          ptx::umma_f16(tmem_base, ad, bd, idesc, k ? 1u : 0u);
+        for (int j = 0; j < J; ++j) {
+          const uint32_t q = gemm_q + (uint32_t)j;
+          int c, part, plane;
+          job_of(j, c, part, plane);
+          const int st = (int)(q % NS);
+          ptx::mbar_wait(full_bar(st), (q / NS) & 1u);
+          ptx::tc_fence_after();
+          const uint32_t bst = sbase + L.ring + (uint32_t)st * kStageBytes;
+          const uint32_t acol = sbase + L.a_hi + (uint32_t)c * kAChunkBytes;
+          const uint32_t dcol = tmem_base + (part ? (uint32_t)kPart0Rows : 0u);
+          const uint32_t idesc = part ? idesc1 : idesc0;
+          const int ksteps = c < 3 ? 4 : 1;  // columns 192 .. 207 only in the last chunk
+          for (int kk = 0; kk < ksteps; ++kk) {
+            const uint64_t bd = ptx::make_smem_desc(bst + kk * 32, 16, 1024, ptx::kLayoutSw128);
+            const uint64_t ah = ptx::make_smem_desc(acol + kk * 32, 16, 1024, ptx::kLayoutSw128);
+            if (plane == 0) {
+              ptx::umma_f16(dcol, ah, bd, idesc, (c | kk) ? 1u : 0u);  // hi . hi opens the accumulator
+              if constexpr (kPrecise) {
+                const uint64_t al = ptx::make_smem_desc(acol + kABytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
+                ptx::umma_f16(dcol, al, bd, idesc, 1u);  // lo . hi
+              }
+            } else {
+              ptx::umma_f16(dcol, ah, bd, idesc, 1u);  // hi . lo
+            }
+          }
+          ptx::umma_commit(empty_bar(st));
         }
         ptx::umma_commit(mma_done);
       }
-      wphase ^= 1u;
+      gemm_q += (uint32_t)J;
+      lap(2);
       ptx::mbar_wait(mma_done, mphase);
       mphase ^= 1u;
       ptx::tc_fence_after();
-      if (tid == 0) {  // the weight tile is free: fetch the next GEMM's (of this tile or of the next one)
-        if (s + 1 < S) load_w(s + 1);
-        else if (tile + (int)gridDim.x < p.num_tiles) load_w(0);
-      }
+      lap(3);
       if (s < p.n_mid - 1) {  // hidden layer s+2; its mask is layer s+1
-        epilogue<kFwd>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1,
-                       masks + ((s + 1) * 2 + half) * kMaskWords * kRows, z, gx, true);
+        epilogue<kFwd, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1,
+                                 masks[s + 1], z, gx, true);
       } else if (s == p.n_mid - 1) {
-        epilogue<kFwdLast>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad);
-        zpart[half * kRows + row] = z;
+        epilogue<kFwdLast, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad);
       } else {
         const int l = 2 * p.n_mid - 1 - s;  // transposed layer l: the result is masked by h_{l+1} = mask layer l
-        uint32_t* const mk = masks + (l * 2 + half) * kMaskWords * kRows;
-        if (l > 0) epilogue<kBwd>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true);
-        else epilogue<kBwdLast>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false);
+        uint32_t* const mk = masks[l];
+        if (l > 0) epilogue<kBwd, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true);
+        else epilogue<kBwdLast, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false);
       }
+      lap(4);
     }
+    zpart[half * kRows + row] = z;
     if (want_grad) {
 #pragma unroll
       for (int i = 0; i < kMaxIn; ++i) gpart[(half * kMaxIn + i) * kRows + row] = gx[i];
@@ -344,15 +438,19 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
           p.grad[r * p.in_dim + i] = gz * (gpart[i * kRows + row] + gpart[(kMaxIn + i) * kRows + row]);
       }
     }
-    // (the next tile's first-layer stores touch the operand tile and mask layer 0 only: every reader of
-    //  those is behind the barrier above; zpart / gpart are rewritten several barriers later)
+    __syncthreads();  // the next tile's first layer overwrites the operand tile (where zpart / gpart live)
+    lap(5);
+  }
+  if (profiling) {
+    for (int k = 0; k < 6; ++k) atomicAdd(&g_mlp_prof[k], (unsigned long long)prof[k]);
   }
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
-// fp16 weight tiles [2 n_mid][kHP][kHP] (layer l, then the transposes) and the fp32 parameter block
+// fp16 weight planes [hi | lo][2 n_mid][kHP][kHP] (layer l, then the transposes; lo = the rounding remainder
+// of hi) and the fp32 parameter block
 __global__ void mlp_pack_kernel(const float* __restrict__ w_first, const float* __restrict__ b_first,
                                 const float* __restrict__ w_mid, const float* __restrict__ b_mid,
                                 const float* __restrict__ w_last, const float* __restrict__ b_last, int in_dim, int H,
@@ -364,7 +462,9 @@ __global__ void mlp_pack_kernel(const float* __restrict__ w_first, const float* 
       const int l2 = (int)(i / (kHP * kHP)), n = (int)(i / kHP) % kHP, k = (int)(i % kHP);
       float v = 0.f;
       if (n < H && k < H) v = l2 < n_mid ? w_mid[((int64_t)l2 * H + n) * H + k] : w_mid[((int64_t)(l2 - n_mid) * H + k) * H + n];
-      wh[i] = __float2half_rn(v);
+      const __half hi = __float2half_rn(v);
+      wh[i] = hi;
+      wh[n16 + i] = __float2half_rn(v - __half2float(hi));
     } else {
       const int j = (int)(i - n16);
       float v = 0.f;
@@ -398,11 +498,38 @@ int mlp_check(int in_dim, int hidden, int n_mid) {
   return 0;
 }
 
+size_t plane_halfs(int n_mid) { return (size_t)2 * n_mid * kHP * kHP; }
+
+template <bool kPrecise>
+int launch_query(const CUtensorMap& t0, const CUtensorMap& t1, const MlpArgs& a, cudaStream_t st) {
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  SIG_CUDA_OK(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    SIG_CUDA_OK(cudaFuncSetAttribute(mlp_query_kernel<kPrecise>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)mlp_smem(kMaxMid, kPrecise).total));
+    configured_dev = dev;
+  }
+  const int grid = std::min(a.num_tiles, num_sms());
+  mlp_query_kernel<kPrecise><<<grid, kMlpThreads, mlp_smem(a.n_mid, kPrecise).total, st>>>(t0, t1, a);
+  SIG_LAUNCH_OK("mlp_query_kernel");
+  return 0;
+}
+
 }  // namespace
+
+int mlp_profile_cycles(unsigned long long* out8, int reset) {
+  SIG_CUDA_OK(cudaMemcpyFromSymbol(out8, g_mlp_prof, sizeof(g_mlp_prof)));
+  if (reset) {
+    unsigned long long zero[8] = {0};
+    SIG_CUDA_OK(cudaMemcpyToSymbol(g_mlp_prof, zero, sizeof(zero)));
+  }
+  return 0;
+}
 
 size_t mlp_packed_bytes(int in_dim, int hidden, int n_mid) {
   if (mlp_check(in_dim, hidden, n_mid) != 0) return 0;
-  return (size_t)2 * n_mid * kHP * kHP * sizeof(__half) + (size_t)param_floats(n_mid) * sizeof(float);
+  return 2 * plane_halfs(n_mid) * sizeof(__half) + (size_t)param_floats(n_mid) * sizeof(float);
 }
 
 int launch_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
@@ -416,15 +543,15 @@ int launch_mlp_pack(const float* w_first, const float* b_first, const float* w_m
     return SIGSVGD_ERR_WORKSPACE;
   }
   __half* wh = reinterpret_cast<__half*>(packed);
-  float* prm = reinterpret_cast<float*>(wh + (size_t)2 * n_mid * kHP * kHP);
+  float* prm = reinterpret_cast<float*>(wh + 2 * plane_halfs(n_mid));
   mlp_pack_kernel<<<num_sms() * 2, 256, 0, st>>>(w_first, b_first, w_mid, b_mid, w_last, b_last, in_dim, hidden, n_mid,
                                                  wh, prm);
   SIG_LAUNCH_OK("mlp_pack_kernel");
   return 0;
 }
 
-int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, const float* x, int64_t P, float* prob,
-                     float* grad, cudaStream_t st) {
+int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int precise, const float* x, int64_t P,
+                     float* prob, float* grad, cudaStream_t st) {
   SIG_PROPAGATE(mlp_check(in_dim, hidden, n_mid));
   SIG_CHECK_ARG(P >= 0 && P < (1ll << 31) * kRows, "mlp_query: bad number of points");
   if (P == 0) return 0;
@@ -434,26 +561,17 @@ int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, cons
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   const __half* wh = reinterpret_cast<const __half*>(packed);
-  CUtensorMap tw;
-  SIG_PROPAGATE(make_tmap_f16(&tw, wh, kHP, (int64_t)2 * n_mid * kHP, kHP, 64, kHP));
+  CUtensorMap t0, t1;  // the same planes; boxes of 112 and of 96 rows (precise) or of all 208 (fast)
+  SIG_PROPAGATE(make_tmap_f16(&t0, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kHP));
+  SIG_PROPAGATE(make_tmap_f16(&t1, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kPart1Rows));
   MlpArgs a;
-  a.params = reinterpret_cast<const float*>(wh + (size_t)2 * n_mid * kHP * kHP);
+  a.params = reinterpret_cast<const float*>(wh + 2 * plane_halfs(n_mid));
   a.x = x, a.prob = prob, a.grad = grad, a.P = P;
   a.in_dim = in_dim, a.hidden = hidden, a.n_mid = n_mid;
   a.num_tiles = (int)ceil_div(P, kRows);
-  const MlpSmem L = mlp_smem(n_mid);
-  static thread_local int configured_dev = -1;
-  int dev = 0;
-  SIG_CUDA_OK(cudaGetDevice(&dev));
-  if (configured_dev != dev) {
-    SIG_CUDA_OK(cudaFuncSetAttribute(mlp_query_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)mlp_smem(kMaxMid).total));
-    configured_dev = dev;
-  }
-  const int grid = std::min(a.num_tiles, num_sms());
-  mlp_query_kernel<<<grid, kMlpThreads, L.total, st>>>(tw, a);
-  SIG_LAUNCH_OK("mlp_query_kernel");
-  return 0;
+  static const bool profile = getenv("SIGSVGD_MLP_PROFILE") != nullptr;
+  a.profile = profile ? 1 : 0;
+  return precise ? launch_query<true>(t0, t1, a, st) : launch_query<false>(t0, t1, a, st);
 }
 
 }  // namespace sigsvgd

@@ -15,8 +15,11 @@ planner holds them fixed).  A maintainer's two lines::
     exp_datapack.occmap = sigsvgd_b200.occupancy.fuse(exp_datapack.occmap)
     exp_datapack.self_collision_pred = sigsvgd_b200.occupancy.fuse(exp_datapack.self_collision_pred)
 
-Arithmetic: fp16 operands with fp32 accumulation (the reference: fp32); tests/test_gpu_occupancy.py states
-the tolerance.  There is no CPU path."""
+Arithmetic: ``precise=True`` (default) holds every operand as fp16 hi + lo planes and spends 3 MMAs per product:
+the reference's fp32 GEMMs to fp32 accuracy, so that the ReLU patterns (and the piecewise-constant Jacobians)
+agree with the reference's.  ``precise=False`` uses the hi planes only (about 1.5x faster): probabilities to
+~5e-4, and roughly 1 point in 20 has a pre-activation within fp16 rounding of zero and takes the neighbouring
+linear piece's gradient.  tests/test_gpu_occupancy.py states both tolerances.  There is no CPU path."""
 from __future__ import annotations
 
 from typing import List, Tuple
@@ -57,11 +60,11 @@ class _Query(torch.autograd.Function):
 class FusedOccupancy:
     """Packed weights of one network plus the query call.  ``repack()`` after the weights change."""
 
-    def __init__(self, weights, biases, device=None):
+    def __init__(self, weights, biases, device=None, precise: bool = True):
         dev = torch.device(device) if device is not None else weights[0].device
         if dev.type != "cuda":
             raise RuntimeError("FusedOccupancy: CUDA only; sigsvgd_b200 has no CPU fallback")
-        self.device = dev
+        self.device, self.precise = dev, bool(precise)
         self._src = (list(weights), list(biases))
         self.repack()
 
@@ -88,8 +91,9 @@ class FusedOccupancy:
                      self.in_dim, self.hidden, self.n_mid, ops._p(self.packed), nbytes, ops._stream())
         return self
 
-    def query_raw(self, x2d: torch.Tensor, want_grad: bool = True):
+    def query_raw(self, x2d: torch.Tensor, want_grad: bool = True, precise=None):
         """x [P, in] float32 CUDA -> (prob [P], d prob / d x [P, in] or None)."""
+        precise = self.precise if precise is None else bool(precise)
         if not x2d.is_cuda:
             raise RuntimeError("FusedOccupancy: CUDA tensors only; sigsvgd_b200 has no CPU fallback")
         if x2d.dim() != 2 or x2d.shape[1] != self.in_dim:
@@ -99,7 +103,7 @@ class FusedOccupancy:
         with torch.cuda.device(x.device):
             prob = torch.empty(P, dtype=torch.float32, device=x.device)
             grad = torch.empty(P, self.in_dim, dtype=torch.float32, device=x.device) if want_grad else None
-            ops.call("sigsvgd_mlp_query", ops._p(self.packed), self.in_dim, self.hidden, self.n_mid, ops._p(x), P,
+            ops.call("sigsvgd_mlp_query", ops._p(self.packed), self.in_dim, self.hidden, self.n_mid, int(precise), ops._p(x), P,
                      ops._p(prob), ops._p(grad), ops._stream())
         return prob, grad
 
@@ -109,11 +113,11 @@ class FusedOccupancy:
         return out.reshape(*lead, 1).to(x.dtype)
 
 
-def fuse(module, device=None) -> FusedOccupancy:
+def fuse(module, device=None, precise: bool = True) -> FusedOccupancy:
     """Drop-in for ``module.__call__`` (a ``ContinuousOccupancyMap`` / ``ContinuousSelfCollisionPredictor`` or any
     module with the same ``layers`` stack)."""
     ws, bs = linear_stack(module)
-    return FusedOccupancy(ws, bs, device)
+    return FusedOccupancy(ws, bs, device, precise)
 
 
 __all__ = ["FusedOccupancy", "fuse", "linear_stack"]

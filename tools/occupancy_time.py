@@ -43,16 +43,33 @@ def main():
         y = net(xr)
         return y, torch.autograd.grad(y.sum(), xr)[0]
 
-    prob, grad = f.query_raw(x)
     y_t, g_t = torch_query()
-    ms = timed(lambda: f.query_raw(x))
-    ms_f = timed(lambda: f.query_raw(x, want_grad=False))
+    y_t, g_t = y_t.detach(), g_t.detach()
     ms_t = timed(torch_query, 4, 2)
     flops = 2.0 * P * (200 * in_dim + 3 * 200 * 200 + 200) * 2
-    print(json.dumps({"points": P, "in_dim": in_dim, "ms_fused": ms, "ms_fused_fwd_only": ms_f, "ms_torch_fp32": ms_t,
-                      "speedup": ms_t / ms, "useful_tflops": flops / ms / 1e9,
-                      "dev_prob": float((prob - y_t[:, 0]).abs().max()),
-                      "dev_grad_rel": float((grad - g_t).abs().max() / g_t.abs().max())}))
+    out = {"points": P, "in_dim": in_dim, "ms_torch_fp32": ms_t}
+    for name, precise in (("precise", True), ("fast", False)):
+        prob, grad = f.query_raw(x, precise=precise)
+        ms = timed(lambda: f.query_raw(x, precise=precise))
+        ms_f = timed(lambda: f.query_raw(x, want_grad=False, precise=precise))
+        dev = (grad - g_t).abs().amax(1) / g_t.abs().max()
+        out[name] = {"ms": ms, "ms_fwd_only": ms_f, "speedup_vs_torch": ms_t / ms, "useful_tflops": flops / ms / 1e9,
+                     "dev_prob": float((prob - y_t[:, 0]).abs().max()), "dev_grad_median": float(dev.median()),
+                     "frac_points_grad_dev_above_1e-3": float((dev > 1e-3).float().mean())}
+        if os.environ.get("SIGSVGD_MLP_PROFILE"):
+            import ctypes
+
+            from sigsvgd_b200 import _lib
+            buf = (ctypes.c_ulonglong * 8)()
+            _lib.load().sigsvgd_mlp_profile_cycles(buf, 1)
+            f.query_raw(x, precise=precise)
+            torch.cuda.synchronize()
+            _lib.load().sigsvgd_mlp_profile_cycles(buf, 1)
+            tot = float(sum(buf[:6])) or 1.0
+            names = ["first_layer", "barrier", "mma_issue", "mma_wait", "epilogue", "output"]
+            out[name]["thread0_cycle_share"] = {n: round(buf[i] / tot, 3) for i, n in enumerate(names)}
+            out[name]["thread0_cycles_per_tile"] = tot / (148 * ((P + 127) // 128 / 148))
+    print(json.dumps(out))
 
 
 if __name__ == "__main__":

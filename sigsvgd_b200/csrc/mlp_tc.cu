@@ -10,8 +10,10 @@
 // forward, and again transposed for the input gradient -- is a 128 x 208 x 208 tcgen05 GEMM:
 //   A = the activations (or the back-propagated rows) of the 128 points, fp16, written by the epilogue
 //       threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
-//   B = the layer's fp16 weights (or their transpose), streamed by TMA through a ring of [112 | 96 rows x
-//       64 columns] stages that runs ahead across layers and tiles (the weights never depend on the data);
+//   B = the layer's fp16 weights (or their transpose), streamed by TMA through a ring of [208 rows x 64
+//       columns] stages that runs ahead across layers and tiles (the weights never depend on the data).
+//       Weight delivery from L2 is what bounds the kernel, so CTAs run as clusters of two that walk the same
+//       weight sequence: each loads half of every stage and multicasts it to both;
 //   D = fp32 in tensor memory; the epilogue (bias, ReLU, ReLU mask bits, fp16 pack) reads it with
 //       tcgen05.ld.  Nothing but the points, the probabilities and the gradients touches HBM.
 // The backward pass propagates d logit / d h; the sigmoid's p (1 - p) multiplies the final 1 x in row.
@@ -49,15 +51,14 @@ constexpr int kMlpThreads = 256;     // two threads per point: columns [0, 96) a
 constexpr int kSplitCol = 96;
 constexpr uint32_t kAChunkBytes = kRows * 128;  // 64 fp16 columns of 128 rows
 constexpr uint32_t kABytes = 4 * kAChunkBytes;  // one plane of the operand tile
-constexpr int kPart0Rows = 112, kPart1Rows = 96;  // the weight rows of a stage (N of one MMA; both % 16 == 0)
+constexpr int kHalfRows = kHP / 2;   // rows of a stage that one CTA of the cluster loads (and multicasts)
 constexpr uint32_t kTmemCols = 256;
-// A stage of the weight ring = [rows x 64 fp16 columns] of one plane, SWIZZLE_128B.  precise: the rows of a
-// layer in two parts (112 | 96), 16 stage loads per GEMM (4 column chunks x 2 parts x 2 planes), which leaves
-// room for the lo plane of the operand tile; fast: all 208 rows, 4 loads per GEMM (a whole layer in flight).
+// A stage of the weight ring = [208 rows x 64 fp16 columns] of one plane, SWIZZLE_128B (large boxes: rings of
+// twice as many half-size stages were measured 1.5x slower).  precise: 8 stage loads per GEMM (4 column chunks
+// x 2 planes), 3 stages beside the two planes of the operand tile; fast: 4 loads per GEMM, 4 stages.
 template <bool kPrecise>
 struct MlpCfg {
   static constexpr int kStages = kPrecise ? 3 : 4;
-  static constexpr int kParts = 1;
   static constexpr int kJobs = kPrecise ? 8 : 4;
   static constexpr uint32_t kStageBytes = kHP * 128;
 };
@@ -94,6 +95,25 @@ struct MlpArgs {
   int64_t P;
   int in_dim, hidden, n_mid, num_tiles, profile;
 };
+
+// TMA load whose box lands at the same shared-memory offset in every CTA of `mask` (and counts its bytes on
+// the barrier at the same offset in each of them)
+__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
+                                                      uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;"
+      :
+      : "r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+// arrive on the barrier at this offset in every CTA of `mask` once this CTA's MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(mask)
+      : "memory");
+}
 
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
@@ -230,7 +250,7 @@ __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, u
 
 template <bool kPrecise>
 __global__ void __launch_bounds__(kMlpThreads, 1)
-mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1, const MlpArgs p) {
+mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
   using Cfg = MlpCfg<kPrecise>;
   constexpr int NS = Cfg::kStages, J = Cfg::kJobs;
   constexpr uint32_t kStageBytes = Cfg::kStageBytes;
@@ -264,41 +284,46 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
 
   for (int i = tid; i < param_floats(p.n_mid); i += kMlpThreads) prm[i] = __ldg(p.params + i);
   if (tid == 0) {
-    ptx::tma_prefetch_desc(&tmW0);
-    ptx::tma_prefetch_desc(&tmW1);
+    ptx::tma_prefetch_desc(&tmW);
     for (int st = 0; st < NS; ++st) {
       ptx::mbar_init(full_bar(st), 1);
-      ptx::mbar_init(empty_bar(st), 1);
+      ptx::mbar_init(empty_bar(st), 2);  // both CTAs of the cluster release a stage (their loads land in both)
     }
     ptx::mbar_init(mma_done, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(ptx::smem_u32((const void*)tmem_slot), kTmemCols);
   ptx::tc_fence_before();
-  __syncthreads();
+  ptx::cluster_sync();  // (also a CTA barrier) the peer's barriers exist before anything is multicast to them
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_row = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 
-  // ---- the weight stream (thread 0).  Stage load q of this CTA: GEMM (q / J) % S of its (q / (J S))-th tile,
-  // job q % J = (column chunk c, row part, plane).  GEMM s multiplies by layer s (s < n_mid) or by the
-  // transpose of layer 2 n_mid - 1 - s.
-  const int my_tiles = (int)blockIdx.x < p.num_tiles ? (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // ---- the weight stream.  Both CTAs of a cluster consume the same sequence of stage loads: load q belongs to
+  // GEMM (q / J) % S of the cluster's (q / (J S))-th pair of tiles, job q % J = (column chunk c, plane).  GEMM s
+  // multiplies by layer s (s < n_mid) or by the transpose of layer 2 n_mid - 1 - s.  A CTA whose tile lies
+  // beyond the last one still walks the sequence (on zero rows, storing nothing): its peer needs its half.
+  const uint32_t crank = ptx::cluster_ctarank();
+  const int cluster_id = (int)blockIdx.x >> 1, num_clusters = (int)gridDim.x >> 1;
+  const int num_pairs = (p.num_tiles + 1) / 2;
+  const int my_tiles = cluster_id < num_pairs ? (num_pairs - cluster_id + num_clusters - 1) / num_clusters : 0;
   const uint32_t total_loads = (uint32_t)my_tiles * (uint32_t)S * (uint32_t)J;
-  auto job_of = [&](int j, int& c, int& part, int& plane) {
-    if constexpr (kPrecise) c = j >> 1, part = 0, plane = j & 1;
-    else c = j, part = 0, plane = 0;
+  auto job_of = [&](int j, int& c, int& plane) {
+    if constexpr (kPrecise) c = j >> 1, plane = j & 1;
+    else c = j, plane = 0;
   };
   auto issue_load = [&](uint32_t q) {
     const int s = (int)((q / J) % (uint32_t)S), j = (int)(q % J);
-    int c, part, plane;
-    job_of(j, c, part, plane);
+    int c, plane;
+    job_of(j, c, plane);
     const int l2 = s < p.n_mid ? s : p.n_mid + (2 * p.n_mid - 1 - s);
     const int st = (int)(q % NS);
-    if (q >= (uint32_t)NS) ptx::mbar_wait(empty_bar(st), ((q / NS) - 1u) & 1u);  // the MMAs of load q - NS are done
-    const int row0 = (plane * 2 * p.n_mid + l2) * kHP + (part ? kPart0Rows : 0);
-    ptx::mbar_expect_tx(full_bar(st), Cfg::kParts == 1 ? kStageBytes : (uint32_t)(part ? kPart1Rows : kPart0Rows) * 128u);
-    ptx::tma_load_2d(sbase + L.ring + (uint32_t)st * kStageBytes, part ? &tmW1 : &tmW0, full_bar(st), c * 64, row0);
+    // the MMAs of load q - NS are done in BOTH CTAs (this CTA's half lands in both)
+    if (q >= (uint32_t)NS) ptx::mbar_wait(empty_bar(st), ((q / NS) - 1u) & 1u);
+    const int row0 = (plane * 2 * p.n_mid + l2) * kHP + (int)crank * kHalfRows;
+    ptx::mbar_expect_tx(full_bar(st), kStageBytes);  // this CTA's half and the peer's
+    tma_load_2d_multicast(sbase + L.ring + (uint32_t)st * kStageBytes + crank * (uint32_t)(kHalfRows * 128), &tmW,
+                          full_bar(st), c * 64, row0, (uint16_t)3);
   };
   // Two single-thread roles during a GEMM, both epilogue threads otherwise: thread 0 issues the MMAs (it waits
   // for full stages only), thread 32 refills the ring NS loads ahead (it waits for the MMAs that free a stage).
@@ -318,10 +343,10 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
     }
   };
   if (profiling) t_prev = clock64();
-  constexpr uint32_t idesc0 = ptx::make_idesc_f16(kRows, Cfg::kParts == 1 ? kHP : kPart0Rows, false, false);
-  constexpr uint32_t idesc1 = ptx::make_idesc_f16(kRows, kPart1Rows, false, false);
+  constexpr uint32_t idesc = ptx::make_idesc_f16(kRows, kHP, false, false);
 
-  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+  for (int it = 0; it < my_tiles; ++it) {
+    const int tile = (it * num_clusters + cluster_id) * 2 + (int)crank;
     const int64_t r = (int64_t)tile * kRows + row;
     const bool row_ok = r < p.P;
     // ---------------------------------------------------------------- first layer (SIMT)
@@ -375,15 +400,14 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         ptx::tc_fence_after();
         for (int j = 0; j < J; ++j) {
           const uint32_t q = gemm_q + (uint32_t)j;
-          int c, part, plane;
-          job_of(j, c, part, plane);
+          int c, plane;
+          job_of(j, c, plane);
           const int st = (int)(q % NS);
           ptx::mbar_wait(full_bar(st), (q / NS) & 1u);
           ptx::tc_fence_after();
           const uint32_t bst = sbase + L.ring + (uint32_t)st * kStageBytes;
           const uint32_t acol = sbase + L.a_hi + (uint32_t)c * kAChunkBytes;
-          const uint32_t dcol = tmem_base + (part ? (uint32_t)kPart0Rows : 0u);
-          const uint32_t idesc = part ? idesc1 : idesc0;
+          const uint32_t dcol = tmem_base;
           const int ksteps = c < 3 ? 4 : 1;  // columns 192 .. 207 only in the last chunk
           for (int kk = 0; kk < ksteps; ++kk) {
             const uint64_t bd = ptx::make_smem_desc(bst + kk * 32, 16, 1024, ptx::kLayoutSw128);
@@ -398,7 +422,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
               ptx::umma_f16(dcol, ah, bd, idesc, 1u);  // hi . lo
             }
           }
-          ptx::umma_commit(empty_bar(st));
+          umma_commit_multicast(empty_bar(st), (uint16_t)3);
         }
         ptx::umma_commit(mma_done);
       }
@@ -445,7 +469,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
     for (int k = 0; k < 6; ++k) atomicAdd(&g_mlp_prof[k], (unsigned long long)prof[k]);
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  ptx::cluster_sync();  // the peer's last commits arrive on this CTA's barriers: do not leave before them
   if (warp == 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -501,7 +525,7 @@ int mlp_check(int in_dim, int hidden, int n_mid) {
 size_t plane_halfs(int n_mid) { return (size_t)2 * n_mid * kHP * kHP; }
 
 template <bool kPrecise>
-int launch_query(const CUtensorMap& t0, const CUtensorMap& t1, const MlpArgs& a, cudaStream_t st) {
+int launch_query(const CUtensorMap& tw, const MlpArgs& a, cudaStream_t st) {
   static thread_local int configured_dev = -1;
   int dev = 0;
   SIG_CUDA_OK(cudaGetDevice(&dev));
@@ -510,8 +534,18 @@ int launch_query(const CUtensorMap& t0, const CUtensorMap& t1, const MlpArgs& a,
                                      (int)mlp_smem(kMaxMid, kPrecise).total));
     configured_dev = dev;
   }
-  const int grid = std::min(a.num_tiles, num_sms());
-  mlp_query_kernel<kPrecise><<<grid, kMlpThreads, mlp_smem(a.n_mid, kPrecise).total, st>>>(t0, t1, a);
+  // clusters of two CTAs (one per SM) that share every weight load
+  const int clusters = (int)std::min<int64_t>(ceil_div(a.num_tiles, 2), std::max(1, num_sms() / 2));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * (unsigned)clusters);
+  cfg.blockDim = dim3(kMlpThreads);
+  cfg.dynamicSmemBytes = mlp_smem(a.n_mid, kPrecise).total;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr, cfg.numAttrs = 1;
+  SIG_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_query_kernel<kPrecise>, tw, a));
   SIG_LAUNCH_OK("mlp_query_kernel");
   return 0;
 }
@@ -561,9 +595,8 @@ int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int 
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   const __half* wh = reinterpret_cast<const __half*>(packed);
-  CUtensorMap t0, t1;  // the same planes; boxes of 112 and of 96 rows (precise) or of all 208 (fast)
-  SIG_PROPAGATE(make_tmap_f16(&t0, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kHP));
-  SIG_PROPAGATE(make_tmap_f16(&t1, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kPart1Rows));
+  CUtensorMap tw;  // boxes of [104 rows x 64 columns]: half a stage
+  SIG_PROPAGATE(make_tmap_f16(&tw, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kHalfRows));
   MlpArgs a;
   a.params = reinterpret_cast<const float*>(wh + 2 * plane_halfs(n_mid));
   a.x = x, a.prob = prob, a.grad = grad, a.P = P;
@@ -571,7 +604,7 @@ int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int 
   a.num_tiles = (int)ceil_div(P, kRows);
   static const bool profile = getenv("SIGSVGD_MLP_PROFILE") != nullptr;
   a.profile = profile ? 1 : 0;
-  return precise ? launch_query<true>(t0, t1, a, st) : launch_query<false>(t0, t1, a, st);
+  return precise ? launch_query<true>(tw, a, st) : launch_query<false>(tw, a, st);
 }
 
 }  // namespace sigsvgd

@@ -511,18 +511,28 @@ def run_ours(args):
                     y = net(xr)
                     return y, torch.autograd.grad(y.sum(), xr)[0]
 
-                prob, grad = f.query_raw(x)
                 y_t, g_t = torch_query()
-                ms = timed(lambda: f.query_raw(x), steps, warmup, reduce_max=False)
-                ms_fwd = timed(lambda: f.query_raw(x, want_grad=False), steps, warmup, reduce_max=False)
+                y_t, g_t = y_t.detach(), g_t.detach()
                 ms_t = timed(torch_query, max(2, steps // 2), 2, reduce_max=False)
                 flops = 2.0 * P * (200 * in_dim + 3 * 200 * 200 + 200) * 2  # forward + input gradient
-                out[name] = {"points": P, "ms_fused_prob_and_grad": ms, "ms_fused_prob_only": ms_fwd,
-                             "ms_torch_fp32_forward_autograd": ms_t, "speedup_vs_torch": ms_t / ms,
-                             "useful_tflops": flops / ms / 1e9, "frac_of_bf16_peak": flops / ms / 1e9 / peak_tf,
-                             "max_abs_dev_prob_vs_torch_fp32": float((prob - y_t[:, 0]).abs().max()),
-                             "max_dev_grad_rel_to_max_grad": float((grad - g_t).abs().max() / g_t.abs().max()),
-                             "dtype": "fp16 operands, fp32 accumulate (torch arm: fp32)"}
+                out[name] = {"points": P, "ms_torch_fp32_forward_autograd": ms_t}
+                for mode, precise in (("precise", True), ("fast", False)):
+                    prob, grad = f.query_raw(x, precise=precise)
+                    ms = timed(lambda: f.query_raw(x, precise=precise), steps, warmup, reduce_max=False)
+                    ms_fwd = timed(lambda: f.query_raw(x, want_grad=False, precise=precise), steps, warmup, reduce_max=False)
+                    dev_g = (grad - g_t).abs().amax(1) / g_t.abs().max()
+                    mmas = 3 if precise else 1
+                    out[name][mode] = {
+                        "ms_prob_and_grad": ms, "ms_prob_only": ms_fwd, "speedup_vs_torch": ms_t / ms,
+                        "useful_tflops": flops / ms / 1e9,
+                        "tensor_tflops_issued": 2.0 * P * 6 * 208 * 208 * mmas / ms / 1e9,
+                        "frac_of_bf16_peak_issued": 2.0 * P * 6 * 208 * 208 * mmas / ms / 1e9 / peak_tf,
+                        "max_abs_dev_prob_vs_torch_fp32": float((prob - y_t[:, 0]).abs().max()),
+                        "median_dev_grad_rel_to_max_grad": float(dev_g.median()),
+                        "frac_points_grad_dev_above_1e-3": float((dev_g > 1e-3).float().mean()),
+                        "arithmetic": ("fp16 hi + lo planes, 3 MMAs per product, fp32 accumulate" if precise else
+                                       "fp16 operands, 1 MMA per product, fp32 accumulate")}
+                prob = grad = None
                 del net, f, x, prob, grad, y_t, g_t
             torch.cuda.empty_cache()
             return out

@@ -11,9 +11,7 @@
 //   A = the activations (or the back-propagated rows) of the 128 points, fp16, written by the epilogue
 //       threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
 //   B = the layer's fp16 weights (or their transpose), streamed by TMA through a ring of [208 rows x 64
-//       columns] stages that runs ahead across layers and tiles (the weights never depend on the data).
-//       Weight delivery from L2 is what bounds the kernel, so CTAs run as clusters of two that walk the same
-//       weight sequence: each loads half of every stage and multicasts it to both;
+//       columns] stages that runs ahead across layers and tiles (the weights never depend on the data);
 //   D = fp32 in tensor memory; the epilogue (bias, ReLU, ReLU mask bits, fp16 pack) reads it with
 //       tcgen05.ld.  Nothing but the points, the probabilities and the gradients touches HBM.
 // The backward pass propagates d logit / d h; the sigmoid's p (1 - p) multiplies the final 1 x in row.
@@ -26,6 +24,16 @@
 //            within fp32 rounding of zero (where the reference itself is arbitrary);
 //   fast     hi planes only (1 MMA): probabilities to ~5e-4; about 1 point in 20 has some pre-activation
 //            within the fp16 rounding error of zero and takes the neighbouring linear piece's gradient.
+//
+// Measured (B200, 3.07 M points, 3 -> 200 x 4 -> 1, probabilities and gradients): precise 6.2 ms, fast 3.2 ms,
+// torch fp32 statements + autograd 56 ms.  Thread 0's cycles (SIGSVGD_MLP_PROFILE): the GEMM phase is 63 %
+// (precise) / 37 % (fast) of a tile and runs ~185 cycles per 128 x 208 x 16 MMA (nominal 106, cuBLAS-rate
+// ~150): it is the tensor pipe, not the weight stream -- clusters of two CTAs multicasting each other half of
+// every stage, and CTA pairs (cta_group::2, each CTA staging half the weight rows) both ran and both changed
+// nothing (tools/experiments/mlp_cluster_multicast.cu.txt, mlp_pair_cta_group2.cu.txt), whereas rings of twice
+// as many half-size stages were 1.5x slower (TMA request count).  What is left is the serial epilogue (25-40 %)
+// and first layer (10-18 %): overlapping them with the next tile's GEMMs needs a second operand tile, which
+// fits beside the ring in fast mode only.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -51,11 +59,10 @@ constexpr int kMlpThreads = 256;     // two threads per point: columns [0, 96) a
 constexpr int kSplitCol = 96;
 constexpr uint32_t kAChunkBytes = kRows * 128;  // 64 fp16 columns of 128 rows
 constexpr uint32_t kABytes = 4 * kAChunkBytes;  // one plane of the operand tile
-constexpr int kHalfRows = kHP / 2;   // rows of a stage that one CTA of the cluster loads (and multicasts)
 constexpr uint32_t kTmemCols = 256;
-// A stage of the weight ring = [208 rows x 64 fp16 columns] of one plane, SWIZZLE_128B (large boxes: rings of
-// twice as many half-size stages were measured 1.5x slower).  precise: 8 stage loads per GEMM (4 column chunks
-// x 2 planes), 3 stages beside the two planes of the operand tile; fast: 4 loads per GEMM, 4 stages.
+// A stage of the weight ring = [208 rows x 64 fp16 columns] of one plane, SWIZZLE_128B.  precise: 8 stage
+// loads per GEMM (4 column chunks x 2 planes), 3 stages beside the two planes of the operand tile; fast: 4
+// loads per GEMM, 4 stages (a whole layer in flight).
 template <bool kPrecise>
 struct MlpCfg {
   static constexpr int kStages = kPrecise ? 3 : 4;
@@ -95,25 +102,6 @@ struct MlpArgs {
   int64_t P;
   int in_dim, hidden, n_mid, num_tiles, profile;
 };
-
-// TMA load whose box lands at the same shared-memory offset in every CTA of `mask` (and counts its bytes on
-// the barrier at the same offset in each of them)
-__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
-                                                      uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      :
-      : "r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
-      : "memory");
-}
-// arrive on the barrier at this offset in every CTA of `mask` once this CTA's MMAs issued so far have retired
-__device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-      "h"(mask)
-      : "memory");
-}
 
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
@@ -161,7 +149,7 @@ enum { kFwd = 0, kFwdLast = 1, kBwd = 2, kBwdLast = 3 };
 template <int kMode, bool kLo>
 __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
                                        const float* wlast, const float* w1, uint32_t& mask_byte, float& z,
-                                       float (&gx)[kMaxIn], bool write_a) {
+                                       float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   float h[8];
   if constexpr (kMode == kFwd || kMode == kFwdLast) {
     const float4 b0 = *reinterpret_cast<const float4*>(bias + col);
@@ -192,11 +180,13 @@ __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float4 r0 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn);
-        const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
         gx[0] = fmaf(h[k], r0.x, gx[0]), gx[1] = fmaf(h[k], r0.y, gx[1]);
         gx[2] = fmaf(h[k], r0.z, gx[2]), gx[3] = fmaf(h[k], r0.w, gx[3]);
-        gx[4] = fmaf(h[k], r1.x, gx[4]), gx[5] = fmaf(h[k], r1.y, gx[5]);
-        gx[6] = fmaf(h[k], r1.z, gx[6]), gx[7] = fmaf(h[k], r1.w, gx[7]);
+        if (wide_in) {  // (uniform) more than four inputs
+          const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
+          gx[4] = fmaf(h[k], r1.x, gx[4]), gx[5] = fmaf(h[k], r1.y, gx[5]);
+          gx[6] = fmaf(h[k], r1.z, gx[6]), gx[7] = fmaf(h[k], r1.w, gx[7]);
+        }
       }
     }
   }
@@ -207,12 +197,12 @@ __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint
 template <int kMode, bool kLo, int kCols>
 __device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
                                            const float* wlast, const float* w1, uint32_t& mask_word, float& z,
-                                           float (&gx)[kMaxIn], bool write_a) {
+                                           float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   uint32_t out_word = 0;
 #pragma unroll
   for (int g = 0; g < kCols / 8; ++g) {
     uint32_t mb = (mask_word >> (8 * g)) & 0xffu;
-    group8<kMode, kLo>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a);
+    group8<kMode, kLo>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a, wide_in);
     out_word |= mb << (8 * g);
   }
   if constexpr (kMode == kFwd || kMode == kFwdLast) mask_word = out_word;
@@ -223,7 +213,7 @@ __device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, 
 template <int kMode, bool kLo>
 __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, uint8_t* a_tile, const float* bias,
                                          const float* wlast, const float* w1, uint32_t* mask, float& z,
-                                         float (&gx)[kMaxIn], bool write_a) {
+                                         float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   const int col0 = half ? kSplitCol : 0;
   constexpr bool kReads = kMode == kBwd || kMode == kBwdLast;
   constexpr bool kWrites = kMode == kFwd;
@@ -232,18 +222,18 @@ __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, u
   ptx::tmem_ld_32x32(tmem_row + col0 + 32, vb);
   uint32_t m0 = kReads ? mask[0] : 0u, m1 = kReads ? mask[1] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, kLo, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a);
-  block_cols<kMode, kLo, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a);
+  block_cols<kMode, kLo, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a, wide_in);
+  block_cols<kMode, kLo, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a, wide_in);
   if (kWrites) mask[0] = m0, mask[1] = m1;
   ptx::tmem_ld_32x32(tmem_row + col0 + 64, va);
   uint32_t vc[16];
   if (half) tmem_ld_32x16(tmem_row + col0 + 96, vc);  // columns 192 .. 207
   uint32_t m2 = kReads ? mask[2] : 0u, m3 = (kReads && half) ? mask[3] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, kLo, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a);
+  block_cols<kMode, kLo, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a, wide_in);
   if (kWrites) mask[2] = m2;
   if (half) {
-    block_cols<kMode, kLo, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a);
+    block_cols<kMode, kLo, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a, wide_in);
     if (kWrites) mask[3] = m3;
   }
 }
@@ -280,6 +270,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
   const int tid = threadIdx.x, warp = tid >> 5;
   const int half = tid / kRows, row = tid % kRows;
   const bool want_grad = p.grad != nullptr;
+  const bool wide_in = p.in_dim > 4;
   const int S = want_grad ? 2 * p.n_mid : p.n_mid;  // GEMMs per tile
 
   for (int i = tid; i < param_floats(p.n_mid); i += kMlpThreads) prm[i] = __ldg(p.params + i);
@@ -287,26 +278,22 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
     ptx::tma_prefetch_desc(&tmW);
     for (int st = 0; st < NS; ++st) {
       ptx::mbar_init(full_bar(st), 1);
-      ptx::mbar_init(empty_bar(st), 2);  // both CTAs of the cluster release a stage (their loads land in both)
+      ptx::mbar_init(empty_bar(st), 1);
     }
     ptx::mbar_init(mma_done, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(ptx::smem_u32((const void*)tmem_slot), kTmemCols);
   ptx::tc_fence_before();
-  ptx::cluster_sync();  // (also a CTA barrier) the peer's barriers exist before anything is multicast to them
+  __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_row = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 
-  // ---- the weight stream.  Both CTAs of a cluster consume the same sequence of stage loads: load q belongs to
-  // GEMM (q / J) % S of the cluster's (q / (J S))-th pair of tiles, job q % J = (column chunk c, plane).  GEMM s
-  // multiplies by layer s (s < n_mid) or by the transpose of layer 2 n_mid - 1 - s.  A CTA whose tile lies
-  // beyond the last one still walks the sequence (on zero rows, storing nothing): its peer needs its half.
-  const uint32_t crank = ptx::cluster_ctarank();
-  const int cluster_id = (int)blockIdx.x >> 1, num_clusters = (int)gridDim.x >> 1;
-  const int num_pairs = (p.num_tiles + 1) / 2;
-  const int my_tiles = cluster_id < num_pairs ? (num_pairs - cluster_id + num_clusters - 1) / num_clusters : 0;
+  // ---- the weight stream.  Stage load q of this CTA: GEMM (q / J) % S of its (q / (J S))-th tile,
+  // job q % J = (column chunk c, plane).  GEMM s multiplies by layer s (s < n_mid) or by the
+  // transpose of layer 2 n_mid - 1 - s.
+  const int my_tiles = (int)blockIdx.x < p.num_tiles ? (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const uint32_t total_loads = (uint32_t)my_tiles * (uint32_t)S * (uint32_t)J;
   auto job_of = [&](int j, int& c, int& plane) {
     if constexpr (kPrecise) c = j >> 1, plane = j & 1;
@@ -318,12 +305,10 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
     job_of(j, c, plane);
     const int l2 = s < p.n_mid ? s : p.n_mid + (2 * p.n_mid - 1 - s);
     const int st = (int)(q % NS);
-    // the MMAs of load q - NS are done in BOTH CTAs (this CTA's half lands in both)
-    if (q >= (uint32_t)NS) ptx::mbar_wait(empty_bar(st), ((q / NS) - 1u) & 1u);
-    const int row0 = (plane * 2 * p.n_mid + l2) * kHP + (int)crank * kHalfRows;
-    ptx::mbar_expect_tx(full_bar(st), kStageBytes);  // this CTA's half and the peer's
-    tma_load_2d_multicast(sbase + L.ring + (uint32_t)st * kStageBytes + crank * (uint32_t)(kHalfRows * 128), &tmW,
-                          full_bar(st), c * 64, row0, (uint16_t)3);
+    if (q >= (uint32_t)NS) ptx::mbar_wait(empty_bar(st), ((q / NS) - 1u) & 1u);  // the MMAs of load q - NS are done
+    const int row0 = (plane * 2 * p.n_mid + l2) * kHP;
+    ptx::mbar_expect_tx(full_bar(st), kStageBytes);
+    ptx::tma_load_2d(sbase + L.ring + (uint32_t)st * kStageBytes, &tmW, full_bar(st), c * 64, row0);
   };
   // Two single-thread roles during a GEMM, both epilogue threads otherwise: thread 0 issues the MMAs (it waits
   // for full stages only), thread 32 refills the ring NS loads ahead (it waits for the MMAs that free a stage).
@@ -333,7 +318,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
     while (head < total_loads && head < (uint32_t)NS) issue_load(head++);
   }
   uint32_t mphase = 0;
-  long long prof[6] = {0, 0, 0, 0, 0, 0}, t_prev = 0;
+  long long prof[7] = {0, 0, 0, 0, 0, 0, 0}, t_prev = 0;
   const bool profiling = p.profile && tid == 0;
   auto lap = [&](int k) {
     if (profiling) {
@@ -345,8 +330,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
   if (profiling) t_prev = clock64();
   constexpr uint32_t idesc = ptx::make_idesc_f16(kRows, kHP, false, false);
 
-  for (int it = 0; it < my_tiles; ++it) {
-    const int tile = (it * num_clusters + cluster_id) * 2 + (int)crank;
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
     const int64_t r = (int64_t)tile * kRows + row;
     const bool row_ok = r < p.P;
     // ---------------------------------------------------------------- first layer (SIMT)
@@ -363,11 +347,14 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float4 r0 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn);
-          const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
           float acc = b1[col + k];
           acc = fmaf(r0.x, x[0], acc), acc = fmaf(r0.y, x[1], acc), acc = fmaf(r0.z, x[2], acc);
-          acc = fmaf(r0.w, x[3], acc), acc = fmaf(r1.x, x[4], acc), acc = fmaf(r1.y, x[5], acc);
-          acc = fmaf(r1.z, x[6], acc), acc = fmaf(r1.w, x[7], acc);
+          acc = fmaf(r0.w, x[3], acc);
+          if (wide_in) {  // (uniform) more than four inputs
+            const float4 r1 = *reinterpret_cast<const float4*>(w1 + (col + k) * kMaxIn + 4);
+            acc = fmaf(r1.x, x[4], acc), acc = fmaf(r1.y, x[5], acc);
+            acc = fmaf(r1.z, x[6], acc), acc = fmaf(r1.w, x[7], acc);
+          }
           h[k] = fminf(fmaxf(acc, 0.f), 65504.f);
           m |= (h[k] > 0.f ? 1u : 0u) << k;
         }
@@ -403,8 +390,10 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
           int c, plane;
           job_of(j, c, plane);
           const int st = (int)(q % NS);
+          const long long tw0 = profiling ? clock64() : 0;
           ptx::mbar_wait(full_bar(st), (q / NS) & 1u);
           ptx::tc_fence_after();
+          if (profiling) prof[6] += clock64() - tw0;  // (part of phase 2) waiting for the weights
           const uint32_t bst = sbase + L.ring + (uint32_t)st * kStageBytes;
           const uint32_t acol = sbase + L.a_hi + (uint32_t)c * kAChunkBytes;
           const uint32_t dcol = tmem_base;
@@ -422,7 +411,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
               ptx::umma_f16(dcol, ah, bd, idesc, 1u);  // hi . lo
             }
           }
-          umma_commit_multicast(empty_bar(st), (uint16_t)3);
+          ptx::umma_commit(empty_bar(st));
         }
         ptx::umma_commit(mma_done);
       }
@@ -434,14 +423,14 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
       lap(3);
       if (s < p.n_mid - 1) {  // hidden layer s+2; its mask is layer s+1
         epilogue<kFwd, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1,
-                                 masks[s + 1], z, gx, true);
+                                 masks[s + 1], z, gx, true, wide_in);
       } else if (s == p.n_mid - 1) {
-        epilogue<kFwdLast, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad);
+        epilogue<kFwdLast, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad, wide_in);
       } else {
         const int l = 2 * p.n_mid - 1 - s;  // transposed layer l: the result is masked by h_{l+1} = mask layer l
         uint32_t* const mk = masks[l];
-        if (l > 0) epilogue<kBwd, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true);
-        else epilogue<kBwdLast, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false);
+        if (l > 0) epilogue<kBwd, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true, wide_in);
+        else epilogue<kBwdLast, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false, wide_in);
       }
       lap(4);
     }
@@ -466,10 +455,10 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
     lap(5);
   }
   if (profiling) {
-    for (int k = 0; k < 6; ++k) atomicAdd(&g_mlp_prof[k], (unsigned long long)prof[k]);
+    for (int k = 0; k < 7; ++k) atomicAdd(&g_mlp_prof[k], (unsigned long long)prof[k]);
   }
   ptx::tc_fence_before();
-  ptx::cluster_sync();  // the peer's last commits arrive on this CTA's barriers: do not leave before them
+  __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -534,18 +523,8 @@ int launch_query(const CUtensorMap& tw, const MlpArgs& a, cudaStream_t st) {
                                      (int)mlp_smem(kMaxMid, kPrecise).total));
     configured_dev = dev;
   }
-  // clusters of two CTAs (one per SM) that share every weight load
-  const int clusters = (int)std::min<int64_t>(ceil_div(a.num_tiles, 2), std::max(1, num_sms() / 2));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * (unsigned)clusters);
-  cfg.blockDim = dim3(kMlpThreads);
-  cfg.dynamicSmemBytes = mlp_smem(a.n_mid, kPrecise).total;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr, cfg.numAttrs = 1;
-  SIG_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_query_kernel<kPrecise>, tw, a));
+  const int grid = std::min(a.num_tiles, num_sms());
+  mlp_query_kernel<kPrecise><<<grid, kMlpThreads, mlp_smem(a.n_mid, kPrecise).total, st>>>(tw, a);
   SIG_LAUNCH_OK("mlp_query_kernel");
   return 0;
 }
@@ -595,8 +574,8 @@ int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int 
     return SIGSVGD_ERR_UNSUPPORTED;
   }
   const __half* wh = reinterpret_cast<const __half*>(packed);
-  CUtensorMap tw;  // boxes of [104 rows x 64 columns]: half a stage
-  SIG_PROPAGATE(make_tmap_f16(&tw, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kHalfRows));
+  CUtensorMap tw;  // boxes of [208 rows x 64 columns]: one stage
+  SIG_PROPAGATE(make_tmap_f16(&tw, wh, kHP, (int64_t)4 * n_mid * kHP, kHP, 64, kHP));
   MlpArgs a;
   a.params = reinterpret_cast<const float*>(wh + 2 * plane_halfs(n_mid));
   a.x = x, a.prob = prob, a.grad = grad, a.P = P;

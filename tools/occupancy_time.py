@@ -68,6 +68,7 @@ def main():
             tot = float(sum(buf[:6])) or 1.0
             names = ["first_layer", "barrier", "mma_issue", "mma_wait", "epilogue", "output"]
             out[name]["thread0_cycle_share"] = {n: round(buf[i] / tot, 3) for i, n in enumerate(names)}
+            out[name]["share_waiting_for_weights"] = round(buf[6] / tot, 3)
             out[name]["thread0_cycles_per_tile"] = tot / (148 * ((P + 127) // 128 / 148))
     print(json.dumps(out))
 

@@ -372,7 +372,9 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
  * sigsvgd_mlp_query: x [P,in] -> prob [P] and, unless grad == NULL, grad [P,in] = d prob_p / d x_p.
  * ------------------------------------------------------------------------------------------- */
 size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid);
-/* development aid (environment SIGSVGD_MLP_PROFILE=1): cycles thread 0 of every CTA spent per phase, summed */
+/* development aid, off by default and without effect on any result: after sigsvgd_mlp_profile_enable(1) thread 0 of
+ * every CTA of sigsvgd_mlp_query adds the cycles it spent per phase to eight counters, read (and reset) here */
+int sigsvgd_mlp_profile_enable(int on);
 int sigsvgd_mlp_profile_cycles(unsigned long long* out8, int reset);
 int sigsvgd_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
                      const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,

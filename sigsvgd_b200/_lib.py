@@ -154,6 +154,7 @@ _SIGNATURES = {
     "sigsvgd_particle_rollout_bwd": (
         c_int, [c_void_p, c_float, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_mlp_packed_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "sigsvgd_mlp_profile_enable": (c_int, [c_int]),
     "sigsvgd_mlp_profile_cycles": (c_int, [c_void_p, c_int]),
     "sigsvgd_mlp_pack": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_size_t,

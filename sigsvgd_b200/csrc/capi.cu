@@ -493,6 +493,8 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                      (cudaStream_t)stream);
 }
 
+int sigsvgd_mlp_profile_enable(int on) { return mlp_profile_enable(on); }
+
 int sigsvgd_mlp_profile_cycles(unsigned long long* out8, int reset) { return mlp_profile_cycles(out8, reset); }
 
 size_t sigsvgd_mlp_packed_bytes(int in_dim, int hidden, int n_mid) { return mlp_packed_bytes(in_dim, hidden, n_mid); }

@@ -167,6 +167,7 @@ int launch_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R,
 
 // occupancy / self-collision network query with its input gradient (mlp_tc.cu)
 size_t mlp_packed_bytes(int in_dim, int hidden, int n_mid);
+int mlp_profile_enable(int on);
 int mlp_profile_cycles(unsigned long long* out8, int reset);
 int launch_mlp_pack(const float* w_first, const float* b_first, const float* w_mid, const float* b_mid,
                     const float* w_last, const float* b_last, int in_dim, int hidden, int n_mid, void* packed,

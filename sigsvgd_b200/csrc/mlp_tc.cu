@@ -26,7 +26,7 @@
 //            within the fp16 rounding error of zero and takes the neighbouring linear piece's gradient.
 //
 // Measured (B200, 3.07 M points, 3 -> 200 x 4 -> 1, probabilities and gradients): precise 6.2 ms, fast 3.2 ms,
-// torch fp32 statements + autograd 56 ms.  Thread 0's cycles (SIGSVGD_MLP_PROFILE): the GEMM phase is 63 %
+// torch fp32 statements + autograd 56 ms.  Thread 0's cycles (sigsvgd_mlp_profile_enable): the GEMM phase is 63 %
 // (precise) / 37 % (fast) of a tile and runs ~185 cycles per 128 x 208 x 16 MMA (nominal 106, cuBLAS-rate
 // ~150): it is the tensor pipe, not the weight stream -- clusters of two CTAs multicasting each other half of
 // every stage, and CTA pairs (cta_group::2, each CTA staging half the weight rows) both ran and both changed
@@ -38,7 +38,7 @@
 #include <cuda_fp16.h>
 
 #include <algorithm>
-#include <cstdlib>
+#include <atomic>
 
 #include "common.cuh"
 #include "gemm_tc.cuh"
@@ -89,10 +89,12 @@ __host__ __device__ inline MlpSmem mlp_smem(int n_mid, bool precise) {
   return s;
 }
 
-// SIGSVGD_MLP_PROFILE=1: thread 0 of every CTA adds the cycles it spent per phase (first layer | barrier |
-// MMA issue incl. waits for full stages | wait for the MMAs | epilogue | output) -- read with
-// sigsvgd_mlp_profile_cycles (tools/occupancy_time.py)
+// Development aid, off unless sigsvgd_mlp_profile_enable(1) was called: thread 0 of every CTA adds the cycles
+// it spent per phase (first layer | barrier | MMA issue incl. waits for full stages | wait for the MMAs |
+// epilogue | output | of the third: waiting for weights) -- read with sigsvgd_mlp_profile_cycles
+// (tools/occupancy_time.py --profile).  It changes no result.
 __device__ unsigned long long g_mlp_prof[8];
+std::atomic<int> g_profile_enabled{0};
 
 struct MlpArgs {
   const float* params;  // fp32 block of the packed weights
@@ -531,6 +533,11 @@ int launch_query(const CUtensorMap& tw, const MlpArgs& a, cudaStream_t st) {
 
 }  // namespace
 
+int mlp_profile_enable(int on) {
+  g_profile_enabled.store(on ? 1 : 0, std::memory_order_relaxed);
+  return 0;
+}
+
 int mlp_profile_cycles(unsigned long long* out8, int reset) {
   SIG_CUDA_OK(cudaMemcpyFromSymbol(out8, g_mlp_prof, sizeof(g_mlp_prof)));
   if (reset) {
@@ -581,8 +588,7 @@ int launch_mlp_query(const void* packed, int in_dim, int hidden, int n_mid, int 
   a.x = x, a.prob = prob, a.grad = grad, a.P = P;
   a.in_dim = in_dim, a.hidden = hidden, a.n_mid = n_mid;
   a.num_tiles = (int)ceil_div(P, kRows);
-  static const bool profile = getenv("SIGSVGD_MLP_PROFILE") != nullptr;
-  a.profile = profile ? 1 : 0;
+  a.profile = g_profile_enabled.load(std::memory_order_relaxed);
   return precise ? launch_query<true>(tw, a, st) : launch_query<false>(tw, a, st);
 }
 

@@ -1,5 +1,5 @@
 """Timing of the fused occupancy-network query against torch fp32 + autograd on the same GPU.
-Usage: python tools/occupancy_time.py [P] [in_dim]"""
+Usage: python tools/occupancy_time.py [P] [in_dim] [--profile]"""
 import json
 import os
 import sys
@@ -24,8 +24,9 @@ def timed(fn, n=10, warm=3):
 
 
 def main():
-    P = int(sys.argv[1]) if len(sys.argv) > 1 else 256 * 200 * 60
-    in_dim = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    P = int(args[0]) if len(args) > 0 else 256 * 200 * 60
+    in_dim = int(args[1]) if len(args) > 1 else 3
     dev = torch.device("cuda:0")
     torch.manual_seed(5)
     layers = [torch.nn.Linear(in_dim, 200), torch.nn.ReLU()]
@@ -56,15 +57,17 @@ def main():
         out[name] = {"ms": ms, "ms_fwd_only": ms_f, "speedup_vs_torch": ms_t / ms, "useful_tflops": flops / ms / 1e9,
                      "dev_prob": float((prob - y_t[:, 0]).abs().max()), "dev_grad_median": float(dev.median()),
                      "frac_points_grad_dev_above_1e-3": float((dev > 1e-3).float().mean())}
-        if os.environ.get("SIGSVGD_MLP_PROFILE"):
+        if "--profile" in sys.argv:
             import ctypes
 
             from sigsvgd_b200 import _lib
             buf = (ctypes.c_ulonglong * 8)()
+            _lib.load().sigsvgd_mlp_profile_enable(1)
             _lib.load().sigsvgd_mlp_profile_cycles(buf, 1)
             f.query_raw(x, precise=precise)
             torch.cuda.synchronize()
             _lib.load().sigsvgd_mlp_profile_cycles(buf, 1)
+            _lib.load().sigsvgd_mlp_profile_enable(0)
             tot = float(sum(buf[:6])) or 1.0
             names = ["first_layer", "barrier", "mma_issue", "mma_wait", "epilogue", "output"]
             out[name]["thread0_cycle_share"] = {n: round(buf[i] / tot, 3) for i, n in enumerate(names)}

@@ -8,8 +8,9 @@
 // One kernel does the whole query: probability AND d probability / d point.  A CTA owns 128 query points
 // (one TMEM lane each).  The first layer (K = in <= 8) and the last (N = 1) are SIMT; every H x H layer --
 // forward, and again transposed for the input gradient -- is a 128 x 208 x 208 tcgen05 GEMM:
-//   A = the activations (or the back-propagated rows) of the 128 points, fp16, written by the epilogue
-//       threads straight into the K-major SWIZZLE_128B operand layout in shared memory;
+//   A = the activations (or the back-propagated rows) of the 128 points as packed fp16 pairs IN TENSOR MEMORY
+//       (row = lane, K = 208 -> 104 columns per plane), written by the epilogue threads with tcgen05.st: the
+//       MMA takes its A operand from there (the .ts form), shared memory feeds B only;
 //   B = the layer's fp16 weights (or their transpose), streamed by TMA through a ring of [208 rows x 64
 //       columns] stages that runs ahead across layers and tiles (the weights never depend on the data);
 //   D = fp32 in tensor memory; the epilogue (bias, ReLU, ReLU mask bits, fp16 pack) reads it with
@@ -25,15 +26,21 @@
 //   fast     hi planes only (1 MMA): probabilities to ~5e-4; about 1 point in 20 has some pre-activation
 //            within the fp16 rounding error of zero and takes the neighbouring linear piece's gradient.
 //
-// Measured (B200, 3.07 M points, 3 -> 200 x 4 -> 1, probabilities and gradients): precise 6.2 ms, fast 3.2 ms,
-// torch fp32 statements + autograd 56 ms.  Thread 0's cycles (sigsvgd_mlp_profile_enable): the GEMM phase is 63 %
-// (precise) / 37 % (fast) of a tile and runs ~185 cycles per 128 x 208 x 16 MMA (nominal 106, cuBLAS-rate
-// ~150): it is the tensor pipe, not the weight stream -- clusters of two CTAs multicasting each other half of
-// every stage, and CTA pairs (cta_group::2, each CTA staging half the weight rows) both ran and both changed
-// nothing (tools/experiments/mlp_cluster_multicast.cu.txt, mlp_pair_cta_group2.cu.txt), whereas rings of twice
-// as many half-size stages were 1.5x slower (TMA request count).  What is left is the serial epilogue (25-40 %)
-// and first layer (10-18 %): overlapping them with the next tile's GEMMs needs a second operand tile, which
-// fits beside the ring in fast mode only.
+// Measured (B200, 3.07 M points, 3 -> 200 x 4 -> 1, probabilities and gradients): precise 5.3 ms, fast 2.85 ms,
+// torch fp32 statements + autograd 56 ms.  What was tried on the way (thread 0's cycle counters,
+// sigsvgd_mlp_profile_enable, say where a tile's time goes):
+//  * the GEMM phase is ~60 % of a tile; only 4-7 % of the tile is spent waiting for weight stages.  Cutting the
+//    weight traffic changed nothing: clusters of two CTAs multicasting each other half of every stage, and
+//    CTA pairs (cta_group::2, each CTA staging half the weight rows) both ran green at the same speed
+//    (tools/experiments/mlp_cluster_multicast.cu.txt, mlp_pair_cta_group2.cu.txt); rings of twice as many
+//    half-size stages were 1.5x slower (TMA request count);
+//  * the MMA issue path mattered: issued by `if (tid == 0)`, every operand went through a register-to-uniform
+//    broadcast loop per MMA (R2UR / ELECT / BRA.U.ANY in the SASS); with the whole warp walking the jobs and
+//    one elected lane issuing, the operands live in uniform registers and the MMAs of a stage issue back to
+//    back (precise 6.9 -> 5.3 ms with A in tensor memory; A in shared memory had measured 6.0 ms);
+//  * an MMA still takes ~165 cycles (floor 128 x 208 / 256 = 104); the serial epilogue (25 %) and first layer
+//    (10 %) are the rest.  A second tile in flight would hide them, but two tiles' accumulators and operands
+//    (2 x 312 columns) do not fit the 512 columns of tensor memory.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -57,15 +64,16 @@ constexpr int kMaxMid = 4;           // H x H layers
 constexpr int kRows = 128;           // query points per CTA
 constexpr int kMlpThreads = 256;     // two threads per point: columns [0, 96) and [96, 208)
 constexpr int kSplitCol = 96;
-constexpr uint32_t kAChunkBytes = kRows * 128;  // 64 fp16 columns of 128 rows
-constexpr uint32_t kABytes = 4 * kAChunkBytes;  // one plane of the operand tile
-constexpr uint32_t kTmemCols = 256;
+constexpr uint32_t kTmemCols = 512;
+// tensor-memory columns: the accumulator [0, 208), the operand A as packed fp16 pairs (K = 208 -> 104 columns):
+// hi plane at 256, lo plane (precise) at 384
+constexpr uint32_t kTmemAHi = 256, kTmemALo = 384;
 // A stage of the weight ring = [208 rows x 64 fp16 columns] of one plane, SWIZZLE_128B.  precise: 8 stage
 // loads per GEMM (4 column chunks x 2 planes), 3 stages beside the two planes of the operand tile; fast: 4
 // loads per GEMM, 4 stages (a whole layer in flight).
 template <bool kPrecise>
 struct MlpCfg {
-  static constexpr int kStages = kPrecise ? 3 : 4;
+  static constexpr int kStages = 6;
   static constexpr int kJobs = kPrecise ? 8 : 4;
   static constexpr uint32_t kStageBytes = kHP * 128;
 };
@@ -75,16 +83,15 @@ __host__ __device__ constexpr int param_floats(int n_mid) { return kHP * (kMaxIn
 constexpr int kMaskWords = 4;  // per thread and hidden layer: 12 or 14 groups of 8 columns -> <= 128 bits
 
 struct MlpSmem {
-  uint32_t a_hi, a_lo, ring, params, bars, total;
+  uint32_t ring, params, parts, bars, total;
 };
 __host__ __device__ inline MlpSmem mlp_smem(int n_mid, bool precise) {
   MlpSmem s;
-  s.a_hi = 0;
-  s.a_lo = kABytes;  // (precise only)
-  s.ring = precise ? 2 * kABytes : kABytes;
+  s.ring = 0;
   s.params = s.ring + (precise ? MlpCfg<true>::kStages * MlpCfg<true>::kStageBytes
                                : MlpCfg<false>::kStages * MlpCfg<false>::kStageBytes);
-  s.bars = s.params + (uint32_t)((param_floats(n_mid) * 4 + 15) & ~15);
+  s.parts = s.params + (uint32_t)((param_floats(n_mid) * 4 + 15) & ~15);
+  s.bars = s.parts + (2 + 2 * kMaxIn) * kRows * 4;
   s.total = s.bars + 256 + 1024;  // barriers; + slack for the 1024-byte alignment of the operand tiles
   return s;
 }
@@ -115,29 +122,47 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "memory");
 }
 
-// byte offset of the 16-byte unit holding columns [8u', 8u'+8) of `row` in the K-major SWIZZLE_128B
-// operand tile (64-column chunks of kRows x 128 bytes)
-__device__ __forceinline__ uint32_t a_unit_offset(int row, int col) {
-  const int chunk = col >> 6, unit = (col & 63) >> 3;
-  return (uint32_t)chunk * kAChunkBytes + (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u +
-         (uint32_t)((unit ^ (row & 7)) << 4);
+// 4 words (8 packed fp16) to this thread's lane of tensor memory, columns [taddr, taddr + 4)
+__device__ __forceinline__ void tmem_st_32x4(uint32_t taddr, const uint32_t (&w)[4]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(w[0]), "r"(w[1]),
+               "r"(w[2]), "r"(w[3])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// D[tmem] (+)= A[tmem] . B[smem]: the A operand read from tensor memory (row = lane, two fp16 per column)
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}\n"
+      :
+      : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
 
-// 8 operand values of one row -> the hi plane (and, kLo, the lo plane = the rounding remainder) of the tile
+// 8 operand values of this thread's row, columns [col, col + 8) -> the hi plane (and, kLo, the lo plane = the
+// rounding remainder) of the operand in tensor memory.  Warp-collective (every lane stores to its own lane).
 template <bool kLo>
-__device__ __forceinline__ void store_operand8(const float (&h)[8], uint8_t* a_tile, uint32_t off) {
+__device__ __forceinline__ void store_operand8(const float (&h)[8], uint32_t tmem_row, int col) {
   __half2 hh[4];
+  uint32_t w[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) hh[k] = __floats2half2_rn(h[2 * k], h[2 * k + 1]);
-  *reinterpret_cast<uint4*>(a_tile + off) = *reinterpret_cast<const uint4*>(hh);
+  for (int k = 0; k < 4; ++k) {
+    hh[k] = __floats2half2_rn(h[2 * k], h[2 * k + 1]);
+    w[k] = *reinterpret_cast<const uint32_t*>(&hh[k]);
+  }
+  tmem_st_32x4(tmem_row + kTmemAHi + (uint32_t)(col >> 1), w);
   if constexpr (kLo) {
-    __half2 ll[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 f = __half22float2(hh[k]);
-      ll[k] = __floats2half2_rn(h[2 * k] - f.x, h[2 * k + 1] - f.y);
+      const __half2 l = __floats2half2_rn(h[2 * k] - f.x, h[2 * k + 1] - f.y);
+      w[k] = *reinterpret_cast<const uint32_t*>(&l);
     }
-    *reinterpret_cast<uint4*>(a_tile + kABytes + off) = *reinterpret_cast<const uint4*>(ll);
+    tmem_st_32x4(tmem_row + kTmemALo + (uint32_t)(col >> 1), w);
   }
 }
 
@@ -149,7 +174,7 @@ enum { kFwd = 0, kFwdLast = 1, kBwd = 2, kBwdLast = 3 };
 //   kBwd      v = acc where the layer's input was active (mask)  -> A
 //   kBwdLast  v = acc where h1 was active; gx[i] += v . W1[:, i]
 template <int kMode, bool kLo>
-__device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
+__device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint32_t a_tmem, const float* bias,
                                        const float* wlast, const float* w1, uint32_t& mask_byte, float& z,
                                        float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   float h[8];
@@ -192,19 +217,19 @@ __device__ __forceinline__ void group8(const uint32_t* v, int col, int row, uint
       }
     }
   }
-  if (kMode != kBwdLast && write_a) store_operand8<kLo>(h, a_tile, a_unit_offset(row, col));
+  if (kMode != kBwdLast && write_a) store_operand8<kLo>(h, a_tmem, col);
 }
 
 // 32 (or 16) accumulator columns starting at `col`: one mask word (or half of one)
 template <int kMode, bool kLo, int kCols>
-__device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, uint8_t* a_tile, const float* bias,
+__device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, uint32_t a_tmem, const float* bias,
                                            const float* wlast, const float* w1, uint32_t& mask_word, float& z,
                                            float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   uint32_t out_word = 0;
 #pragma unroll
   for (int g = 0; g < kCols / 8; ++g) {
     uint32_t mb = (mask_word >> (8 * g)) & 0xffu;
-    group8<kMode, kLo>(v + 8 * g, col + 8 * g, row, a_tile, bias, wlast, w1, mb, z, gx, write_a, wide_in);
+    group8<kMode, kLo>(v + 8 * g, col + 8 * g, row, a_tmem, bias, wlast, w1, mb, z, gx, write_a, wide_in);
     out_word |= mb << (8 * g);
   }
   if constexpr (kMode == kFwd || kMode == kFwdLast) mask_word = out_word;
@@ -213,7 +238,7 @@ __device__ __forceinline__ void block_cols(const uint32_t* v, int col, int row, 
 // The epilogue of one GEMM for this thread: its row, columns [0, 96) (half 0) or [96, 208) (half 1).
 // mask: this thread's kMaskWords words of the layer (read in the backward modes, written in kFwd).
 template <int kMode, bool kLo>
-__device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, uint8_t* a_tile, const float* bias,
+__device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, uint32_t a_tmem, const float* bias,
                                          const float* wlast, const float* w1, uint32_t* mask, float& z,
                                          float (&gx)[kMaxIn], bool write_a, bool wide_in) {
   const int col0 = half ? kSplitCol : 0;
@@ -224,18 +249,18 @@ __device__ __forceinline__ void epilogue(uint32_t tmem_row, int half, int row, u
   ptx::tmem_ld_32x32(tmem_row + col0 + 32, vb);
   uint32_t m0 = kReads ? mask[0] : 0u, m1 = kReads ? mask[1] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, kLo, 32>(va, col0, row, a_tile, bias, wlast, w1, m0, z, gx, write_a, wide_in);
-  block_cols<kMode, kLo, 32>(vb, col0 + 32, row, a_tile, bias, wlast, w1, m1, z, gx, write_a, wide_in);
+  block_cols<kMode, kLo, 32>(va, col0, row, a_tmem, bias, wlast, w1, m0, z, gx, write_a, wide_in);
+  block_cols<kMode, kLo, 32>(vb, col0 + 32, row, a_tmem, bias, wlast, w1, m1, z, gx, write_a, wide_in);
   if (kWrites) mask[0] = m0, mask[1] = m1;
   ptx::tmem_ld_32x32(tmem_row + col0 + 64, va);
   uint32_t vc[16];
   if (half) tmem_ld_32x16(tmem_row + col0 + 96, vc);  // columns 192 .. 207
   uint32_t m2 = kReads ? mask[2] : 0u, m3 = (kReads && half) ? mask[3] : 0u;
   ptx::tmem_ld_wait();
-  block_cols<kMode, kLo, 32>(va, col0 + 64, row, a_tile, bias, wlast, w1, m2, z, gx, write_a, wide_in);
+  block_cols<kMode, kLo, 32>(va, col0 + 64, row, a_tmem, bias, wlast, w1, m2, z, gx, write_a, wide_in);
   if (kWrites) mask[2] = m2;
   if (half) {
-    block_cols<kMode, kLo, 16>(vc, col0 + 96, row, a_tile, bias, wlast, w1, m3, z, gx, write_a, wide_in);
+    block_cols<kMode, kLo, 16>(vc, col0 + 96, row, a_tmem, bias, wlast, w1, m3, z, gx, write_a, wide_in);
     if (kWrites) mask[3] = m3;
   }
 }
@@ -251,16 +276,14 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
   const uint32_t sbase = (raw + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (sbase - raw);
   const MlpSmem L = mlp_smem(p.n_mid, kPrecise);
-  uint8_t* const a_tile = smem + L.a_hi;
   float* const prm = reinterpret_cast<float*>(smem + L.params);
   const float* const w1 = prm;                               // [kHP][kMaxIn]
   const float* const b1 = prm + kHP * kMaxIn;                // [kHP]
   const float* const bmid = b1 + kHP;                        // [n_mid][kHP]
   const float* const wlast = bmid + p.n_mid * kHP;           // [kHP]
   const float* const blast = wlast + kHP;
-  // partial logits / gradients of the two threads of a row meet in the operand tile's space once the tile's
-  // last GEMM has read it
-  float* const zpart = reinterpret_cast<float*>(smem + L.a_hi);    // [2][kRows]
+  // partial logits / gradients of the two threads of a row meet here
+  float* const zpart = reinterpret_cast<float*>(smem + L.parts);   // [2][kRows]
   float* const gpart = zpart + 2 * kRows;                          // [2][kMaxIn][kRows]
   uint32_t masks[kMaxMid][kMaskWords];  // ReLU patterns of this thread's columns of h1 .. h_{n_mid} (thread-local)
   const uint32_t bar0 = sbase + L.bars;
@@ -360,7 +383,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
           h[k] = fminf(fmaxf(acc, 0.f), 65504.f);
           m |= (h[k] > 0.f ? 1u : 0u) << k;
         }
-        store_operand8<kPrecise>(h, a_tile, a_unit_offset(row, col));
+        store_operand8<kPrecise>(h, tmem_row, col);
         word |= m << (8 * (g & 3));
         if ((g & 3) == 3 || g == ngroups - 1) {
           masks[0][g >> 2] = word;  // mask layer 0 = h1
@@ -375,7 +398,7 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
     for (int i = 0; i < kMaxIn; ++i) gx[i] = 0.f;
 
     for (int s = 0; s < S; ++s) {
-      ptx::fence_proxy_async_smem();  // this thread's operand stores -> visible to the tensor core
+      tmem_st_wait();  // this thread's operand stores have landed in tensor memory
       ptx::tc_fence_before();
       __syncthreads();
       lap(1);
@@ -385,37 +408,45 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
         //  next one, three jobs before it is needed)
         const uint32_t lim = min(total_loads, gemm_q + (uint32_t)(J + NS - 1));
         while (head < lim) issue_load(head++);
-      } else if (tid == 0) {
+      } else if (warp == 0) {
+        // The whole warp walks the jobs (so that every operand of the MMAs is a warp-uniform value, which the
+        // compiler keeps in uniform registers: computed by thread 0 alone they went through per-MMA
+        // register-to-uniform broadcasts, and the issue path, not the tensor pipe, set the pace); one elected
+        // lane issues.
         ptx::tc_fence_after();
+        const uint32_t ring_u = __shfl_sync(0xffffffffu, sbase + L.ring, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
         for (int j = 0; j < J; ++j) {
           const uint32_t q = gemm_q + (uint32_t)j;
           int c, plane;
           job_of(j, c, plane);
-          const int st = (int)(q % NS);
+          const uint32_t st = q % (uint32_t)NS;
           const long long tw0 = profiling ? clock64() : 0;
-          ptx::mbar_wait(full_bar(st), (q / NS) & 1u);
+          ptx::mbar_wait(full_bar((int)st), (q / NS) & 1u);
           ptx::tc_fence_after();
           if (profiling) prof[6] += clock64() - tw0;  // (part of phase 2) waiting for the weights
-          const uint32_t bst = sbase + L.ring + (uint32_t)st * kStageBytes;
-          const uint32_t acol = sbase + L.a_hi + (uint32_t)c * kAChunkBytes;
-          const uint32_t dcol = tmem_base;
+          const uint32_t bst = ring_u + st * kStageBytes;
+          const uint32_t acol = tmem_u + kTmemAHi + (uint32_t)c * 32u;  // 64 fp16 = 32 columns per chunk
           const int ksteps = c < 3 ? 4 : 1;  // columns 192 .. 207 only in the last chunk
-          for (int kk = 0; kk < ksteps; ++kk) {
-            const uint64_t bd = ptx::make_smem_desc(bst + kk * 32, 16, 1024, ptx::kLayoutSw128);
-            const uint64_t ah = ptx::make_smem_desc(acol + kk * 32, 16, 1024, ptx::kLayoutSw128);
-            if (plane == 0) {
-              ptx::umma_f16(dcol, ah, bd, idesc, (c | kk) ? 1u : 0u);  // hi . hi opens the accumulator
-              if constexpr (kPrecise) {
-                const uint64_t al = ptx::make_smem_desc(acol + kABytes + kk * 32, 16, 1024, ptx::kLayoutSw128);
-                ptx::umma_f16(dcol, al, bd, idesc, 1u);  // lo . hi
+          if (ptx::elect_one()) {
+            for (int kk = 0; kk < ksteps; ++kk) {
+              const uint64_t bd = ptx::make_smem_desc(bst + kk * 32, 16, 1024, ptx::kLayoutSw128);
+              const uint32_t ah = acol + (uint32_t)kk * 8u;  // 16 fp16 = 8 columns per K step
+              if (plane == 0) {
+                umma_f16_ts(tmem_u, ah, bd, idesc, (c | kk) ? 1u : 0u);  // hi . hi opens the accumulator
+                if constexpr (kPrecise) {
+                  umma_f16_ts(tmem_u, ah + (kTmemALo - kTmemAHi), bd, idesc, 1u);  // lo . hi
+                }
+              } else {
+                umma_f16_ts(tmem_u, ah, bd, idesc, 1u);  // hi . lo
               }
-            } else {
-              ptx::umma_f16(dcol, ah, bd, idesc, 1u);  // hi . lo
             }
+            ptx::umma_commit(empty_bar((int)st));
           }
-          ptx::umma_commit(empty_bar(st));
+          __syncwarp();
         }
-        ptx::umma_commit(mma_done);
+        if (ptx::elect_one()) ptx::umma_commit(mma_done);
+        __syncwarp();
       }
       gemm_q += (uint32_t)J;
       lap(2);
@@ -424,15 +455,15 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
       ptx::tc_fence_after();
       lap(3);
       if (s < p.n_mid - 1) {  // hidden layer s+2; its mask is layer s+1
-        epilogue<kFwd, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1,
+        epilogue<kFwd, kPrecise>(tmem_row, half, row, tmem_row, bmid + s * kHP, wlast, w1,
                                  masks[s + 1], z, gx, true, wide_in);
       } else if (s == p.n_mid - 1) {
-        epilogue<kFwdLast, kPrecise>(tmem_row, half, row, a_tile, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad, wide_in);
+        epilogue<kFwdLast, kPrecise>(tmem_row, half, row, tmem_row, bmid + s * kHP, wlast, w1, nullptr, z, gx, want_grad, wide_in);
       } else {
         const int l = 2 * p.n_mid - 1 - s;  // transposed layer l: the result is masked by h_{l+1} = mask layer l
         uint32_t* const mk = masks[l];
-        if (l > 0) epilogue<kBwd, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, true, wide_in);
-        else epilogue<kBwdLast, kPrecise>(tmem_row, half, row, a_tile, nullptr, wlast, w1, mk, z, gx, false, wide_in);
+        if (l > 0) epilogue<kBwd, kPrecise>(tmem_row, half, row, tmem_row, nullptr, wlast, w1, mk, z, gx, true, wide_in);
+        else epilogue<kBwdLast, kPrecise>(tmem_row, half, row, tmem_row, nullptr, wlast, w1, mk, z, gx, false, wide_in);
       }
       lap(4);
     }
@@ -453,7 +484,6 @@ mlp_query_kernel(const __grid_constant__ CUtensorMap tmW, const MlpArgs p) {
           p.grad[r * p.in_dim + i] = gz * (gpart[i * kRows + row] + gpart[(kMaxIn + i) * kRows + row]);
       }
     }
-    __syncthreads();  // the next tile's first layer overwrites the operand tile (where zpart / gpart live)
     lap(5);
   }
   if (profiling) {

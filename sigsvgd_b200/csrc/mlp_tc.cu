@@ -38,8 +38,9 @@
 //    broadcast loop per MMA (R2UR / ELECT / BRA.U.ANY in the SASS); with the whole warp walking the jobs and
 //    one elected lane issuing, the operands live in uniform registers and the MMAs of a stage issue back to
 //    back (precise 6.9 -> 5.3 ms with A in tensor memory; A in shared memory had measured 6.0 ms);
-//  * an MMA still takes ~165 cycles (floor 128 x 208 / 256 = 104); the serial epilogue (25 %) and first layer
-//    (10 %) are the rest.  A second tile in flight would hide them, but two tiles' accumulators and operands
+//  * an MMA still takes ~165 cycles (floor 128 x 208 / 256 = 104) and that is its throughput, not a latency:
+//    splitting the 208 columns into two accumulators (112 + 96) issued alternately was 3 % slower; the serial
+//    epilogue (25 %) and first layer (10 %) are the rest.  A second tile in flight would hide them, but two tiles' accumulators and operands
 //    (2 x 312 columns) do not fit the 512 columns of tensor memory.
 #include <cuda.h>
 #include <cuda_fp16.h>

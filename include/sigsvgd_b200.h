@@ -354,6 +354,21 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                  const float* grad_states, const uint8_t* flags, float* grad_actions, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Forward kinematics of a serial chain, SURVEY.md 8(f)-4.  Replaces Robot.qs_to_joints_xs
+ * (src/models/robot/robot_simulator.py:138-170: differentiable_robot_model's
+ * compute_forward_kinematics_all_links, positions only) and autograd through it.
+ * The chain is described in HOST memory, URDF semantics per joint j (parent -> child):
+ *   T_child = T_parent . [rot_j | xyz_j] . Rot(axis_j, q[dof_j])       (dof_j = -1: fixed joint)
+ * xyz [J,3]; rot [J,9] (R_rpy of the joint origin, row-major); axis [J,3] (unit); dof [J]; J, n_dof <= 16.
+ * q [B,n_dof] -> xs [J,B,3]: the position of every child-link frame (the caller picks its target links).
+ * sigsvgd_chain_fk_bwd: gq [B,n_dof] = d (sum gxs . xs) / d q, geometric Jacobian, nothing saved by the forward.
+ * ------------------------------------------------------------------------------------------- */
+int sigsvgd_chain_fk(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                     const float* q, int64_t B, float* xs, void* stream);
+int sigsvgd_chain_fk_bwd(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                         const float* q, int64_t B, const float* gxs, float* gq, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Learned occupancy / self-collision networks of the robot-planning cost, SURVEY.md 8(f)-4.  Replaces the
  * forward of ContinuousOccupancyMap (src/models/robot_learning/continuous_occupancy_map.py:10-35) and
  * ContinuousSelfCollisionPredictor (continuous_self_collision_pred.py:11-36),

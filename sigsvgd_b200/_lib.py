@@ -153,6 +153,10 @@ _SIGNATURES = {
                 c_int64, c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_particle_rollout_bwd": (
         c_int, [c_void_p, c_float, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "sigsvgd_chain_fk": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
+    "sigsvgd_chain_fk_bwd": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
     "sigsvgd_mlp_packed_bytes": (c_size_t, [c_int, c_int, c_int]),
     "sigsvgd_mlp_profile_enable": (c_int, [c_int]),
     "sigsvgd_mlp_profile_cycles": (c_int, [c_void_p, c_int]),

@@ -493,6 +493,16 @@ int sigsvgd_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R
                                      (cudaStream_t)stream);
 }
 
+int sigsvgd_chain_fk(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                     const float* q, int64_t B, float* xs, void* stream) {
+  return launch_chain_fk(xyz, rot, axis, dof, J, n_dof, q, B, xs, (cudaStream_t)stream);
+}
+
+int sigsvgd_chain_fk_bwd(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                         const float* q, int64_t B, const float* gxs, float* gq, void* stream) {
+  return launch_chain_fk_bwd(xyz, rot, axis, dof, J, n_dof, q, B, gxs, gq, (cudaStream_t)stream);
+}
+
 int sigsvgd_mlp_profile_enable(int on) { return mlp_profile_enable(on); }
 
 int sigsvgd_mlp_profile_cycles(unsigned long long* out8, int reset) { return mlp_profile_cycles(out8, reset); }

@@ -165,6 +165,12 @@ int launch_particle_rollout_bwd(const float* mass, float mass_scalar, int64_t R,
                                 const float* grad_states, const uint8_t* flags, float* grad_actions,
                                 cudaStream_t st);
 
+// serial-chain forward kinematics (fk.cu)
+int launch_chain_fk(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                    const float* q, int64_t B, float* xs, cudaStream_t st);
+int launch_chain_fk_bwd(const float* xyz, const float* rot, const float* axis, const int* dof, int J, int n_dof,
+                        const float* q, int64_t B, const float* gxs, float* gq, cudaStream_t st);
+
 // occupancy / self-collision network query with its input gradient (mlp_tc.cu)
 size_t mlp_packed_bytes(int in_dim, int hidden, int n_mid);
 int mlp_profile_enable(int on);

@@ -540,6 +540,26 @@ def run_ours(args):
             torch.cuda.empty_cache()
             return {"error": f"{type(e).__name__}: {e}"[:300]}
 
+    def robot_cost_leg():
+        """SURVEY.md 8(f)-4 assembled: the reference's robot-planning cost and its gradient w.r.t. the knots
+        (examples/script_planning_robot.py:248-356, :107) at BASELINE's 256 Panda particles, 3 knots, 200 spline
+        steps -- as torch statements, and with this package's drop-ins for the forward kinematics and the two
+        networks (tools/robot_cost_time.py holds both arms)."""
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import robot_cost_time
+
+            out = {}
+            for mode, precise in (("precise", True), ("fast", False)):
+                r = robot_cost_time.run(dev, 256, 200, precise=precise)
+                r["speedup_vs_torch"] = r["ms_torch_statements"] / r["ms_fused_drop_ins"]
+                out[mode] = r
+            torch.cuda.empty_cache()
+            return out
+        except Exception as e:
+            torch.cuda.empty_cache()
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+
     def mpc_step(steps, warmup):
         """"ms/MPC step" half of the metric (BASELINE.json configs[2]): one `stein_sampler.optimize(...,
         opt_steps=2)` of the particle-maze controller at its shapes (35 policies x 30 steps x 2 controls,
@@ -828,7 +848,7 @@ def run_ours(args):
         torch.cuda.empty_cache()
 
     # ---- extras: one swarm sharded over the ranks, batched scenes, the MPC step -----------------
-    sharded, scenes, mpc, deep, pde, occ = [], None, None, None, None, None
+    sharded, scenes, mpc, deep, pde, occ, rcost = [], None, None, None, None, None, None
     if not args.skip_extras:
         if world > 1:
             sharded.append(sharded_swarm(N, min(args.steps, 20), 3))
@@ -840,6 +860,7 @@ def run_ours(args):
             deep = depth4_swarm(N, 10, 3)
             pde = sigpde_leg(5, 2)
             occ = occupancy_leg(10, 3)
+            rcost = robot_cost_leg()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -876,6 +897,7 @@ def run_ours(args):
             "depth4_swarm": deep,
             "sigpde": pde,
             "occupancy_query": occ,
+            "robot_cost": rcost,
             "roofline": roof,
             "cpu_baseline": cpu,
         }

@@ -554,6 +554,8 @@ def run_ours(args):
                 r = robot_cost_time.run(dev, 256, 200, precise=precise)
                 r["speedup_vs_torch"] = r["ms_torch_statements"] / r["ms_fused_drop_ins"]
                 out[mode] = r
+            if world == 1:
+                out["cpu_sample"] = robot_cost_time.run_cpu_sample()
             torch.cuda.empty_cache()
             return out
         except Exception as e:

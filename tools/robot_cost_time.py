@@ -132,6 +132,35 @@ def run(dev, particles=256, timesteps=200, knots=3, precise=True):
             "median_dev_grad_rel_to_max_grad": float((gf - gt).abs().median() / gt.abs().max())}
 
 
+def run_cpu_sample(particles=32, timesteps=200, knots=3, repeats=2):
+    """The torch arm on the host cores (the reference's own CPU path for the cost) on a bounded sample of the
+    workload: ``particles`` of the 256, same spline steps and body points."""
+    import time
+
+    dev = torch.device("cpu")
+    g = np.load(os.path.join(ROOT, "tests", "golden", "panda_chain.npz"))
+    lo = torch.tensor(g["limits_lo"], dtype=torch.float32)
+    hi = torch.tensor(g["limits_hi"], dtype=torch.float32)
+    occ, col = _net(3, 5, dev), _net(7, 6, dev)
+    gen = torch.Generator().manual_seed(0)
+    x = (lo + torch.rand(particles, knots, 7, generator=gen) * (hi - lo)) * 0.5
+    start, target = (0.3 * lo)[None, None, :], (0.3 * hi)[None, None, :]
+    cost = cost_fn(_torch_fk(g, dev), occ, col, timesteps)
+
+    def f():
+        xx = x.detach().requires_grad_(True)
+        c = cost(xx, start, target)
+        return torch.autograd.grad(-c.sum(), xx)[0]
+
+    f()
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        f()
+    ms = (time.perf_counter() - t0) / repeats * 1e3
+    return {"particles": particles, "ms": ms, "ms_scaled_to_256_particles": ms * 256 / particles,
+            "cores": torch.get_num_threads(), "kind": "the reference's torch statements on the host cores"}
+
+
 if __name__ == "__main__":
     P = int(sys.argv[1]) if len(sys.argv) > 1 else 256
     T = int(sys.argv[2]) if len(sys.argv) > 2 else 200
@@ -139,3 +168,4 @@ if __name__ == "__main__":
         out = run(torch.device("cuda:0"), P, T, precise=precise)
         out["speedup"] = out["ms_torch_statements"] / out["ms_fused_drop_ins"]
         print(json.dumps(out))
+    print(json.dumps({"cpu_sample": run_cpu_sample()}))
